@@ -1,0 +1,346 @@
+/*
+ * cstone_b200.h — C ABI of libcstone_b200.so
+ *
+ * B200 (sm_100a) implementation of the cornerstone-octree domain hot path:
+ * SFC keys -> key sort + gather -> cornerstone leaf array count/rebalance ->
+ * internal-tree linking -> halo discovery -> radius neighbour search.
+ *
+ * Every entry point below replaces one `extern template` GPU function of the
+ * reference library `cstone_gpu` (the only FFI-like boundary the reference
+ * has).  The reference declaration each one stands in for is
+ * cited as  [ref: path:line]  relative to the reference's include/cstone/.
+ *
+ * Conventions
+ *  - plain C: raw DEVICE pointers and sizes, no C++ / torch types.
+ *  - key type suffix  _k32 (uint32_t) / _k64 (uint64_t); coordinate type
+ *    suffix _f32 / _f64.  `sfc_kind` selects the curve at run time
+ *    (CSTONE_SFC_MORTON / CSTONE_SFC_HILBERT) where the reference selects it
+ *    through the MortonKey<> / HilbertKey<> strong types.
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *  - return value: 0 on success, a positive cudaError_t, or a negative
+ *    CSTONE_E_* logic error.  Nothing is printed and the process is never
+ *    terminated by the library (the reference wrapper in INTEGRATION.md maps
+ *    non-zero to the reference behaviour: print + exit, or std::runtime_error).
+ *  - the callee never allocates caller-visible memory; scratch space is
+ *    caller-provided and sized by the *_temp_bytes functions.
+ *  - functions that return a scalar result through a HOST pointer
+ *    synchronise `stream` before returning (same as the reference, which
+ *    returns those values by value).
+ *  - there is no CPU fallback: without a CUDA device every call returns the
+ *    CUDA error.
+ */
+#ifndef CSTONE_B200_H
+#define CSTONE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CSTONE_B200_ABI_VERSION 1
+
+#define CSTONE_SFC_MORTON 0
+#define CSTONE_SFC_HILBERT 1
+
+/* boundary types, same values as cstone::BoundaryType [ref: sfc/box.hpp:89-94] */
+#define CSTONE_BOUNDARY_OPEN 0
+#define CSTONE_BOUNDARY_PERIODIC 1
+#define CSTONE_BOUNDARY_FIXED 2
+
+/* logic errors (negative so that they can not collide with cudaError_t) */
+#define CSTONE_E_INVALID_ARGUMENT (-1)
+#define CSTONE_E_TEMP_TOO_SMALL (-2) /* [ref: primitives/primitives_gpu.cu:353] throws runtime_error */
+#define CSTONE_E_TOO_LARGE (-3)
+#define CSTONE_E_STACK_OVERFLOW (-4) /* traversal stack exhausted [ref: traversal/traversal.hpp:102] */
+#define CSTONE_E_CAPACITY (-5)
+
+/* Memory layout identical to cstone::Box<T> [ref: sfc/box.hpp:111-191]:
+ * limits[6] = xmin,xmax,ymin,ymax,zmin,zmax; lengths; inverse lengths (computed
+ * ONCE on the host as T(1)/(max-min), never recomputed on the device);
+ * boundaries[3].  A `const cstone::Box<T>&` may be reinterpret_cast to it. */
+typedef struct cstone_box_f32
+{
+    float limits[6];
+    float lengths[3];
+    float inv_lengths[3];
+    char boundaries[3];
+} cstone_box_f32;
+
+typedef struct cstone_box_f64
+{
+    double limits[6];
+    double lengths[3];
+    double inv_lengths[3];
+    char boundaries[3];
+} cstone_box_f64;
+
+int cstone_b200_abi_version(void);
+/* human readable text for a status returned by any function below */
+const char* cstone_b200_status_string(int status);
+/* number of kernels launched by this library in the calling process so far */
+uint64_t cstone_b200_launch_count(void);
+
+/* ------------------------------------------------------------------------
+ * a1/a2  SFC keys
+ * [ref: sfc/sfc_gpu.h:38-39  computeSfcKeysGpu<KeyType,T>(x,y,z,keys,n,box)]
+ * keys[i] = sfc3D(x[i],y[i],z[i],box) unless keys[i] == removeKey (1<<3*maxLevel)
+ * ---------------------------------------------------------------------- */
+int cstone_b200_compute_sfc_keys_k32_f32(int sfc_kind, const float* x, const float* y, const float* z,
+                                         uint32_t* keys, size_t n, const cstone_box_f32* box, void* stream);
+int cstone_b200_compute_sfc_keys_k32_f64(int sfc_kind, const double* x, const double* y, const double* z,
+                                         uint32_t* keys, size_t n, const cstone_box_f64* box, void* stream);
+int cstone_b200_compute_sfc_keys_k64_f32(int sfc_kind, const float* x, const float* y, const float* z,
+                                         uint64_t* keys, size_t n, const cstone_box_f32* box, void* stream);
+int cstone_b200_compute_sfc_keys_k64_f64(int sfc_kind, const double* x, const double* y, const double* z,
+                                         uint64_t* keys, size_t n, const cstone_box_f64* box, void* stream);
+
+/* integer-coordinate encode / decode of n points (used by the known-answer
+ * tests; [ref: sfc/morton.hpp:111-168, sfc/hilbert.hpp:58-109,145-188]) */
+int cstone_b200_encode_sfc_k32(int sfc_kind, const uint32_t* ix, const uint32_t* iy, const uint32_t* iz,
+                               uint32_t* keys, size_t n, void* stream);
+int cstone_b200_encode_sfc_k64(int sfc_kind, const uint32_t* ix, const uint32_t* iy, const uint32_t* iz,
+                               uint64_t* keys, size_t n, void* stream);
+int cstone_b200_decode_sfc_k32(int sfc_kind, const uint32_t* keys, uint32_t* ix, uint32_t* iy, uint32_t* iz,
+                               size_t n, void* stream);
+int cstone_b200_decode_sfc_k64(int sfc_kind, const uint64_t* keys, uint32_t* ix, uint32_t* iy, uint32_t* iz,
+                               size_t n, void* stream);
+
+/* ------------------------------------------------------------------------
+ * a3  coordinate extrema   [ref: primitives/primitives_gpu.h:58-62 MinMaxGpu<T>]
+ * One fused pass over x,y,z (any of which may be NULL); out_minmax is a HOST
+ * array {xmin,xmax,ymin,ymax,zmin,zmax}; synchronises the stream.
+ * `temp` = device scratch of cstone_b200_minmax_temp_bytes() bytes.
+ * ---------------------------------------------------------------------- */
+uint64_t cstone_b200_minmax_temp_bytes(void);
+int cstone_b200_minmax3_f32(const float* x, const float* y, const float* z, size_t n, float* out_minmax,
+                            void* temp, void* stream);
+int cstone_b200_minmax3_f64(const double* x, const double* y, const double* z, size_t n, double* out_minmax,
+                            void* temp, void* stream);
+
+/* ------------------------------------------------------------------------
+ * a4  stable key sort carrying a 32-bit permutation (hand-written onesweep
+ * LSD radix sort, 8-bit digits, full key width).
+ * [ref: primitives/primitives_gpu.h:104-110 sortByKeyTempStorage / sortByKeyGpu,
+ *       primitives/gather.cuh:80-108 GpuSfcSorter]
+ *  keys[n], values[n]   in/out (sorted result always lands here)
+ *  key_buf[n], value_buf[n]  caller-provided alternate buffers
+ *  temp / temp_bytes    >= cstone_b200_sort_by_key_temp_bytes_*(n)
+ *  values_are_iota != 0: `values` is treated as 0,1,2,... on input without being
+ *  read (fuses sequenceGpu [ref: primitives/primitives_gpu.h:87] into pass 0).
+ * n must be < 2^30 per call (CSTONE_E_TOO_LARGE otherwise).
+ * ---------------------------------------------------------------------- */
+uint64_t cstone_b200_sort_by_key_temp_bytes_k32(uint64_t n);
+uint64_t cstone_b200_sort_by_key_temp_bytes_k64(uint64_t n);
+int cstone_b200_sort_by_key_k32(uint32_t* keys, uint32_t* values, uint32_t* key_buf, uint32_t* value_buf, size_t n,
+                                void* temp, uint64_t temp_bytes, int values_are_iota, void* stream);
+int cstone_b200_sort_by_key_k64(uint64_t* keys, uint32_t* values, uint64_t* key_buf, uint32_t* value_buf, size_t n,
+                                void* temp, uint64_t temp_bytes, int values_are_iota, void* stream);
+/* [ref: primitives/primitives_gpu.h:86-87 sequenceGpu] out[i] = init + i */
+int cstone_b200_sequence_u32(uint32_t* out, size_t n, uint32_t init, void* stream);
+
+/* ------------------------------------------------------------------------
+ * a5  gather / scatter through a LocalIndex map
+ * [ref: primitives/primitives_gpu.h:48-56 gatherGpu / scatterGpu]
+ *  dst[i] = src[map[i]]  (gather),  dst[map[i]] = src[i]  (scatter)
+ * elem_bytes in {4,8,12,16,24,32}.  gather_multi moves `num_arrays` arrays with ONE
+ * read of the map (src/dst/elem_bytes are HOST arrays of length num_arrays <= 16).
+ * ---------------------------------------------------------------------- */
+int cstone_b200_gather(const uint32_t* map, size_t n, const void* src, void* dst, int elem_bytes, void* stream);
+int cstone_b200_scatter(const uint32_t* map, size_t n, const void* src, void* dst, int elem_bytes, void* stream);
+int cstone_b200_gather_multi(const uint32_t* map, size_t n, int num_arrays, const void* const* src, void* const* dst,
+                             const int* elem_bytes, void* stream);
+
+/* ------------------------------------------------------------------------
+ * scans  [ref: primitives/primitives_gpu.h:112-122 exclusiveScanGpu / inclusiveScanGpu]
+ * single-pass decoupled look-back scan of n u32 values, out may alias in.
+ * temp >= cstone_b200_scan_temp_bytes(n).
+ * ---------------------------------------------------------------------- */
+uint64_t cstone_b200_scan_temp_bytes(uint64_t n);
+int cstone_b200_exclusive_scan_u32(const uint32_t* in, uint32_t* out, size_t n, uint32_t init, void* temp,
+                                   void* stream);
+int cstone_b200_inclusive_scan_u32(const uint32_t* in, uint32_t* out, size_t n, void* temp, void* stream);
+
+/* ------------------------------------------------------------------------
+ * a6  leaf particle counts
+ * [ref: tree/csarray_gpu.h:55-62 computeNodeCountsGpu<KeyType>]
+ * counts[i] = min(#keys in [tree[i], tree[i+1]), max_count).  The result does not
+ * depend on use_counts_as_guess (the guess only steers the reference's search).
+ * ---------------------------------------------------------------------- */
+int cstone_b200_compute_node_counts_k32(const uint32_t* tree, uint32_t* counts, int32_t num_nodes,
+                                        const uint32_t* first_key, const uint32_t* last_key, uint32_t max_count,
+                                        int use_counts_as_guess, void* stream);
+int cstone_b200_compute_node_counts_k64(const uint64_t* tree, uint32_t* counts, int32_t num_nodes,
+                                        const uint64_t* first_key, const uint64_t* last_key, uint32_t max_count,
+                                        int use_counts_as_guess, void* stream);
+
+/* ------------------------------------------------------------------------
+ * a7  rebalance decision + exclusive scan of the node ops
+ * [ref: tree/csarray_gpu.h:75-77 computeNodeOpsGpu<KeyType>]
+ * node_ops has num_nodes+1 entries and holds the exclusive scan on return;
+ * *new_num_nodes (HOST) = node_ops[num_nodes]; *converged (HOST, may be NULL)
+ * = 1 iff every op was 1.  temp >= cstone_b200_scan_temp_bytes(num_nodes+1).
+ * ---------------------------------------------------------------------- */
+int cstone_b200_compute_node_ops_k32(const uint32_t* tree, int32_t num_nodes, const uint32_t* counts,
+                                     uint32_t bucket_size, int32_t* node_ops, int32_t* new_num_nodes,
+                                     int32_t* converged, void* temp, void* stream);
+int cstone_b200_compute_node_ops_k64(const uint64_t* tree, int32_t num_nodes, const uint32_t* counts,
+                                     uint32_t bucket_size, int32_t* node_ops, int32_t* new_num_nodes,
+                                     int32_t* converged, void* temp, void* stream);
+/* the un-scanned per-leaf decision only (0 merge / 1 keep / 8,64,512,4096 split)
+ * [ref: tree/csarray.hpp:286-348 calculateNodeOp / rebalanceDecision] */
+int cstone_b200_rebalance_decision_k32(const uint32_t* tree, int32_t num_nodes, const uint32_t* counts,
+                                       uint32_t bucket_size, int32_t* node_ops, void* stream);
+int cstone_b200_rebalance_decision_k64(const uint64_t* tree, int32_t num_nodes, const uint32_t* counts,
+                                       uint32_t bucket_size, int32_t* node_ops, void* stream);
+
+/* ------------------------------------------------------------------------
+ * a8  emit the rebalanced leaf array
+ * [ref: tree/csarray_gpu.h:79-84 rebalanceTreeGpu<KeyType>]
+ * new_tree has new_num_nodes+1 entries; node_ops is the scanned array.
+ * ---------------------------------------------------------------------- */
+int cstone_b200_rebalance_tree_k32(const uint32_t* tree, int32_t num_nodes, int32_t new_num_nodes,
+                                   const int32_t* node_ops, uint32_t* new_tree, void* stream);
+int cstone_b200_rebalance_tree_k64(const uint64_t* tree, int32_t num_nodes, int32_t new_num_nodes,
+                                   const int32_t* node_ops, uint64_t* new_tree, void* stream);
+
+/* ------------------------------------------------------------------------
+ * a9  one update step / full build of the cornerstone leaf array
+ * [ref: tree/update_gpu.cuh:58-82 updateOctreeGpu; tree/csarray.hpp:429-465
+ *       updateOctree / computeOctree]
+ * tree / counts are ping-pong device buffers of `capacity` (+1 for trees) entries:
+ *   tree_a[capacity+1] in/out, tree_b[capacity+1] scratch, counts[capacity] in/out,
+ *   node_ops[capacity+1] scratch, temp >= cstone_b200_scan_temp_bytes(capacity+1).
+ * update_octree: *num_nodes (HOST, in/out); *converged (HOST out).  The updated
+ *   tree is left in tree_a.  Returns CSTONE_E_CAPACITY if the new tree does not fit
+ *   (*num_nodes then holds the required node count, tree_a/counts are unchanged).
+ * compute_octree: starts from the root {0, 2^(3*maxLevel)} and iterates
+ *   update_octree until converged; *num_nodes / *num_iterations are HOST outputs.
+ * ---------------------------------------------------------------------- */
+int cstone_b200_update_octree_k32(const uint32_t* first_key, const uint32_t* last_key, uint32_t bucket_size,
+                                  uint32_t max_count, uint32_t* tree_a, uint32_t* tree_b, uint32_t* counts,
+                                  int32_t* node_ops, int32_t capacity, int32_t* num_nodes, int32_t* converged,
+                                  void* temp, void* stream);
+int cstone_b200_update_octree_k64(const uint64_t* first_key, const uint64_t* last_key, uint32_t bucket_size,
+                                  uint32_t max_count, uint64_t* tree_a, uint64_t* tree_b, uint32_t* counts,
+                                  int32_t* node_ops, int32_t capacity, int32_t* num_nodes, int32_t* converged,
+                                  void* temp, void* stream);
+int cstone_b200_compute_octree_k32(const uint32_t* first_key, const uint32_t* last_key, uint32_t bucket_size,
+                                   uint32_t max_count, uint32_t* tree_a, uint32_t* tree_b, uint32_t* counts,
+                                   int32_t* node_ops, int32_t capacity, int32_t* num_nodes, int32_t* num_iterations,
+                                   void* temp, void* stream);
+int cstone_b200_compute_octree_k64(const uint64_t* first_key, const uint64_t* last_key, uint32_t bucket_size,
+                                   uint32_t max_count, uint64_t* tree_a, uint64_t* tree_b, uint32_t* counts,
+                                   int32_t* node_ops, int32_t capacity, int32_t* num_nodes, int32_t* num_iterations,
+                                   void* temp, void* stream);
+
+/* ------------------------------------------------------------------------
+ * a10  internal-tree linking
+ * [ref: tree/octree_gpu.h:49-50 buildOctreeGpu<KeyType>(cstoneTree, OctreeView d);
+ *       OctreeView tree/octree.hpp:279-293; sizes OctreeData::resize :327-342]
+ * With L = num_leaf_nodes, I = (L-1)/7, M = L+I the caller provides
+ *   prefixes[M], child_offsets[M(+1)], parents[max(1,(M-1)/8)],
+ *   level_range[max_tree_level+2] (12 for k32, 23 for k64), internal_to_leaf[M],
+ *   leaf_to_internal[M];  temp >= cstone_b200_build_octree_temp_bytes_*(L).
+ * ---------------------------------------------------------------------- */
+uint64_t cstone_b200_build_octree_temp_bytes_k32(int32_t num_leaf_nodes);
+uint64_t cstone_b200_build_octree_temp_bytes_k64(int32_t num_leaf_nodes);
+int cstone_b200_build_octree_k32(const uint32_t* leaves, int32_t num_leaf_nodes, uint32_t* prefixes,
+                                 int32_t* child_offsets, int32_t* parents, int32_t* level_range,
+                                 int32_t* internal_to_leaf, int32_t* leaf_to_internal, void* temp,
+                                 uint64_t temp_bytes, void* stream);
+int cstone_b200_build_octree_k64(const uint64_t* leaves, int32_t num_leaf_nodes, uint64_t* prefixes,
+                                 int32_t* child_offsets, int32_t* parents, int32_t* level_range,
+                                 int32_t* internal_to_leaf, int32_t* leaf_to_internal, void* temp,
+                                 uint64_t temp_bytes, void* stream);
+/* [ref: tree/octree_gpu.h:52-53 upsweepSumGpu] saturating child sum, level_range is a HOST pointer */
+int cstone_b200_upsweep_sum(int32_t num_levels, const int32_t* level_range_host, const int32_t* child_offsets,
+                            uint32_t* counts, void* stream);
+
+/* ------------------------------------------------------------------------
+ * a11  geometric node centres and half sizes
+ * [ref: focus/source_center_gpu.h computeGeoCentersGpu<KeyType,T>(prefixes,numNodes,centers,sizes,box);
+ *       sfc/box.hpp:334-351 centerAndSize]   centers/sizes are Vec3<T>[num_nodes] (AoS, 3 T each)
+ * ---------------------------------------------------------------------- */
+int cstone_b200_compute_geo_centers_k32_f32(int sfc_kind, const uint32_t* prefixes, int32_t num_nodes, float* centers,
+                                            float* sizes, const cstone_box_f32* box, void* stream);
+int cstone_b200_compute_geo_centers_k32_f64(int sfc_kind, const uint32_t* prefixes, int32_t num_nodes,
+                                            double* centers, double* sizes, const cstone_box_f64* box, void* stream);
+int cstone_b200_compute_geo_centers_k64_f32(int sfc_kind, const uint64_t* prefixes, int32_t num_nodes, float* centers,
+                                            float* sizes, const cstone_box_f32* box, void* stream);
+int cstone_b200_compute_geo_centers_k64_f64(int sfc_kind, const uint64_t* prefixes, int32_t num_nodes,
+                                            double* centers, double* sizes, const cstone_box_f64* box, void* stream);
+
+/* ------------------------------------------------------------------------
+ * a12  halo search radius per leaf
+ * [ref: primitives/primitives_gpu.h:84-85 segmentMax + scaleGpu as used by
+ *       halos/halos.hpp:148-160 Halos::discover]
+ * radii[i] = float(max(0, max h[segments[i] .. segments[i+1]))) * scale  for
+ * i in [0,num_segments); `segments` has num_segments+1 entries.
+ * ---------------------------------------------------------------------- */
+int cstone_b200_halo_radii_f32(const float* h, const uint32_t* segments, size_t num_segments, float scale,
+                               float* radii, void* stream);
+int cstone_b200_halo_radii_f64(const double* h, const uint32_t* segments, size_t num_segments, float scale,
+                               float* radii, void* stream);
+
+/* ------------------------------------------------------------------------
+ * a13  halo discovery by 3D box collision
+ * [ref: traversal/collisions_gpu.h:58-67 findHalosGpu<KeyType,RadiusType,T>]
+ * flags[num_leaf_nodes] must be zeroed by the caller; flags of colliding leaves
+ * outside [first_node,last_node) are set to 1.  The reference hard-wires the
+ * Hilbert curve here (SfcKind); sfc_kind = CSTONE_SFC_MORTON is an extension.
+ * ---------------------------------------------------------------------- */
+int cstone_b200_find_halos_k32_f32(int sfc_kind, const uint32_t* prefixes, const int32_t* child_offsets,
+                                   const int32_t* internal_to_leaf, const uint32_t* leaves, const float* radii,
+                                   const cstone_box_f32* box, int32_t first_node, int32_t last_node, int32_t* flags,
+                                   void* stream);
+int cstone_b200_find_halos_k32_f64(int sfc_kind, const uint32_t* prefixes, const int32_t* child_offsets,
+                                   const int32_t* internal_to_leaf, const uint32_t* leaves, const float* radii,
+                                   const cstone_box_f64* box, int32_t first_node, int32_t last_node, int32_t* flags,
+                                   void* stream);
+int cstone_b200_find_halos_k64_f32(int sfc_kind, const uint64_t* prefixes, const int32_t* child_offsets,
+                                   const int32_t* internal_to_leaf, const uint64_t* leaves, const float* radii,
+                                   const cstone_box_f32* box, int32_t first_node, int32_t last_node, int32_t* flags,
+                                   void* stream);
+int cstone_b200_find_halos_k64_f64(int sfc_kind, const uint64_t* prefixes, const int32_t* child_offsets,
+                                   const int32_t* internal_to_leaf, const uint64_t* leaves, const float* radii,
+                                   const cstone_box_f64* box, int32_t first_node, int32_t last_node, int32_t* flags,
+                                   void* stream);
+
+/* ------------------------------------------------------------------------
+ * a14  particle offsets of the present (assigned or halo) leaves
+ * [ref: domain/layout.hpp:150-164 computeNodeLayout]
+ * layout[i] = exclusive scan of ((first<=i<last) || flags[i]) ? counts[i] : 0,
+ * layout has num_leaf_nodes+1 entries.  temp >= cstone_b200_scan_temp_bytes(num_leaf_nodes+1)
+ * ---------------------------------------------------------------------- */
+int cstone_b200_compute_node_layout(const uint32_t* counts, const int32_t* flags, int32_t first_assigned,
+                                    int32_t last_assigned, int32_t num_leaf_nodes, uint32_t* layout, void* temp,
+                                    void* stream);
+
+/* ------------------------------------------------------------------------
+ * a15  radius neighbour search, CPU semantics and output layout
+ * [ref: findneighbors.hpp:167-178 findNeighbors(x,y,z,h,firstId,lastId,box,OctreeNsView,ngmax,
+ *       neighbors,neighborsCount); OctreeNsView tree/octree.hpp:296-317]
+ * (the reference library has no host entry point for its GPU traversal,
+ *  traversal/find_neighbors.cuh:435-446 is a device function; this one mirrors
+ *  the CPU driver.)  neighbors[(i-first_id)*ngmax + k] in the reference's
+ * depth-first visiting order, j != i, strict d2 < 4 h_i^2; neighbors_count holds
+ * the full count even when it exceeds ngmax.  centers/sizes: Vec3<T>[numNodes].
+ * ---------------------------------------------------------------------- */
+int cstone_b200_find_neighbors_f32(const float* x, const float* y, const float* z, const float* h, uint32_t first_id,
+                                   uint32_t last_id, const cstone_box_f32* box, const int32_t* child_offsets,
+                                   const int32_t* internal_to_leaf, const uint32_t* layout, const float* centers,
+                                   const float* sizes, float search_ext_factor, uint32_t ngmax, uint32_t* neighbors,
+                                   uint32_t* neighbors_count, void* stream);
+int cstone_b200_find_neighbors_f64(const double* x, const double* y, const double* z, const double* h,
+                                   uint32_t first_id, uint32_t last_id, const cstone_box_f64* box,
+                                   const int32_t* child_offsets, const int32_t* internal_to_leaf,
+                                   const uint32_t* layout, const double* centers, const double* sizes,
+                                   float search_ext_factor, uint32_t ngmax, uint32_t* neighbors,
+                                   uint32_t* neighbors_count, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CSTONE_B200_H */
