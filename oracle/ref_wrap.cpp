@@ -1,0 +1,300 @@
+/*
+ * ref_wrap.cpp — TEST INFRASTRUCTURE ONLY.
+ *
+ * Thin extern "C" wrappers around the UNMODIFIED reference CPU headers
+ * (/root/reference/include/cstone/...).  No reference source is copied: this file only
+ * #includes the headers where they lie and forwards calls.  Built by oracle/Makefile
+ * into oracle/_ref/liboracle_ref.so (git-ignored) with
+ *   g++ -std=c++20 -O3 -fopenmp -ffp-contract=off -I/root/reference/include
+ * It is the strongest checker we have: the reference's own code for every function of
+ * the hot path, used to pin the port (oracle/cstone_oracle.cpp) and the CUDA kernels.
+ */
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <utility>
+#include <vector>
+#include <omp.h>
+
+#include "cstone/sfc/sfc.hpp"
+#include "cstone/primitives/gather.hpp"
+#include "cstone/tree/csarray.hpp"
+#include "cstone/tree/octree.hpp"
+#include "cstone/focus/source_center.hpp"
+#include "cstone/traversal/collisions.hpp"
+#include "cstone/domain/layout.hpp"
+#include "cstone/findneighbors.hpp"
+
+#define ORACLE_PREFIX cstone_ref_
+#include "oracle_api.h"
+
+using namespace cstone;
+
+static_assert(sizeof(Box<float>) == sizeof(cstone_box_f32), "Box<float> layout");
+static_assert(sizeof(Box<double>) == sizeof(cstone_box_f64), "Box<double> layout");
+
+template<class T, class CB>
+static const Box<T>& asBox(const CB* b)
+{
+    return *reinterpret_cast<const Box<T>*>(b);
+}
+
+[[noreturn]] static void unsupported(const char* what)
+{
+    std::fprintf(stderr, "cstone_ref: %s is hard-wired to the Hilbert curve in the reference\n", what);
+    std::abort();
+}
+
+template<class K, class T, class CB>
+static void sfcKeys(int kind, const T* x, const T* y, const T* z, K* keys, size_t n, const CB* box)
+{
+    if (kind == CSTONE_SFC_MORTON)
+        computeSfcKeys(x, y, z, reinterpret_cast<MortonKey<K>*>(keys), n, asBox<T>(box));
+    else
+        computeSfcKeys(x, y, z, reinterpret_cast<HilbertKey<K>*>(keys), n, asBox<T>(box));
+}
+
+template<class K>
+static K encode(int kind, unsigned ix, unsigned iy, unsigned iz)
+{
+    return kind == CSTONE_SFC_MORTON ? iMorton<K>(ix, iy, iz) : iHilbert<K>(ix, iy, iz);
+}
+
+template<class K>
+static void decode(int kind, K key, unsigned* xyz)
+{
+    auto t = (kind == CSTONE_SFC_MORTON) ? decodeMorton<K>(key) : decodeHilbert<K>(key);
+    xyz[0] = util::get<0>(t);
+    xyz[1] = util::get<1>(t);
+    xyz[2] = util::get<2>(t);
+}
+
+template<class K>
+static void ibox(int kind, K key, unsigned level, int* out)
+{
+    IBox b = (kind == CSTONE_SFC_MORTON) ? mortonIBox<K>(key, level) : hilbertIBox<K>(key, level);
+    out[0] = b.xmin(), out[1] = b.xmax(), out[2] = b.ymin(), out[3] = b.ymax(), out[4] = b.zmin(), out[5] = b.zmax();
+}
+
+template<class K>
+static int32_t rebalanceTreeW(const K* tree, int32_t numNodes, int32_t* nodeOps, K* newTree, int32_t capacity)
+{
+    gsl::span<const K> treeSpan(tree, numNodes + 1);
+    std::vector<K> out;
+    rebalanceTree(treeSpan, out, nodeOps);
+    int32_t newNumNodes = int32_t(out.size()) - 1;
+    if (newNumNodes > capacity) return -newNumNodes;
+    std::copy(out.begin(), out.end(), newTree);
+    return newNumNodes;
+}
+
+template<class K>
+static int updateOctreeW(const K* first, const K* last, unsigned bucket, unsigned maxCount, K* tree, unsigned* counts,
+                         int32_t capacity, int32_t* numNodes)
+{
+    std::vector<K> t(tree, tree + *numNodes + 1);
+    std::vector<unsigned> c(counts, counts + *numNodes);
+    bool converged = updateOctree(first, last, bucket, t, c, maxCount);
+    int32_t newN   = int32_t(nNodes(t));
+    if (newN > capacity)
+    {
+        *numNodes = newN;
+        return -1;
+    }
+    std::copy(t.begin(), t.end(), tree);
+    std::copy(c.begin(), c.end(), counts);
+    *numNodes = newN;
+    return converged ? 1 : 0;
+}
+
+template<class K>
+static int32_t computeOctreeW(const K* first, const K* last, unsigned bucket, unsigned maxCount, K* tree,
+                              unsigned* counts, int32_t capacity)
+{
+    auto [t, c]  = computeOctree(first, last, bucket, maxCount);
+    int32_t newN = int32_t(nNodes(t));
+    if (newN > capacity) return -newN;
+    std::copy(t.begin(), t.end(), tree);
+    std::copy(c.begin(), c.end(), counts);
+    return newN;
+}
+
+template<class K>
+static void buildOctreeW(const K* leaves, int32_t L, K* prefixes, int32_t* childOffsets, int32_t* parents,
+                         int32_t* levelRange, int32_t* internalToLeaf, int32_t* leafToInternal)
+{
+    buildOctreeCpu(leaves, L, (L - 1) / 7, prefixes, childOffsets, parents, levelRange, internalToLeaf, leafToInternal);
+}
+
+template<class K, class T, class CB>
+static void geoCentersW(int kind, const K* prefixes, int32_t n, T* centers, T* sizes, const CB* box)
+{
+    if (kind != CSTONE_SFC_HILBERT) unsupported("nodeFpCenters");
+    nodeFpCenters<K>(gsl::span<const K>(prefixes, n), reinterpret_cast<Vec3<T>*>(centers),
+                     reinterpret_cast<Vec3<T>*>(sizes), asBox<T>(box));
+}
+
+//! halo radius as computed by Halos::discover, CPU branch (halos/halos.hpp:171-183), for arbitrary segments
+template<class Th>
+static void haloRadiiW(const Th* h, const uint32_t* seg, size_t numSegments, float scale, float* radii)
+{
+#pragma omp parallel for schedule(static)
+    for (size_t i = 0; i < numSegments; ++i)
+    {
+        radii[i] = 0.0f;
+        // reference GPU branch (segmentMax + scaleGpu): float(max) * scale; CPU branch: max * 2 * ext narrowed to float.
+        // Both agree for scale = 2 (power of two); we follow the GPU order of operations.
+        if (seg[i + 1] > seg[i]) { radii[i] = float(*std::max_element(h + seg[i], h + seg[i + 1])) * scale; }
+    }
+}
+
+template<class K, class T, class CB>
+static void findHalosW(int kind, const K* prefixes, const int32_t* childOffsets, const int32_t* internalToLeaf,
+                       const K* leaves, const float* radii, const CB* box, int32_t first, int32_t last, int32_t* flags)
+{
+    if (kind != CSTONE_SFC_HILBERT) unsupported("findHalos");
+    findHalos(prefixes, childOffsets, internalToLeaf, leaves, radii, asBox<T>(box), first, last, flags);
+}
+
+template<class T, class CB>
+static void findNeighborsW(const T* x, const T* y, const T* z, const T* h, uint32_t firstId, uint32_t lastId,
+                           const CB* box, const int32_t* childOffsets, const int32_t* internalToLeaf,
+                           const uint32_t* layout, const T* centers, const T* sizes, float ext, uint32_t ngmax,
+                           uint32_t* neighbors, uint32_t* neighborsCount)
+{
+    OctreeNsView<T, uint64_t> view{0,
+                                   nullptr,
+                                   childOffsets,
+                                   internalToLeaf,
+                                   nullptr,
+                                   nullptr,
+                                   layout,
+                                   reinterpret_cast<const Vec3<T>*>(centers),
+                                   reinterpret_cast<const Vec3<T>*>(sizes),
+                                   ext};
+    findNeighbors(x, y, z, h, firstId, lastId, asBox<T>(box), view, ngmax, neighbors, neighborsCount);
+}
+
+extern "C" {
+
+int cstone_ref_num_threads(void) { return omp_get_max_threads(); }
+void cstone_ref_set_num_threads(int n) { omp_set_num_threads(n); }
+
+uint32_t cstone_ref_encode_k32(int kind, unsigned ix, unsigned iy, unsigned iz) { return encode<uint32_t>(kind, ix, iy, iz); }
+uint64_t cstone_ref_encode_k64(int kind, unsigned ix, unsigned iy, unsigned iz) { return encode<uint64_t>(kind, ix, iy, iz); }
+void cstone_ref_decode_k32(int kind, uint32_t key, unsigned* xyz) { decode<uint32_t>(kind, key, xyz); }
+void cstone_ref_decode_k64(int kind, uint64_t key, unsigned* xyz) { decode<uint64_t>(kind, key, xyz); }
+
+void cstone_ref_compute_sfc_keys_k32_f32(int kind, const float* x, const float* y, const float* z, uint32_t* keys,
+                                         size_t n, const cstone_box_f32* box) { sfcKeys(kind, x, y, z, keys, n, box); }
+void cstone_ref_compute_sfc_keys_k32_f64(int kind, const double* x, const double* y, const double* z, uint32_t* keys,
+                                         size_t n, const cstone_box_f64* box) { sfcKeys(kind, x, y, z, keys, n, box); }
+void cstone_ref_compute_sfc_keys_k64_f32(int kind, const float* x, const float* y, const float* z, uint64_t* keys,
+                                         size_t n, const cstone_box_f32* box) { sfcKeys(kind, x, y, z, keys, n, box); }
+void cstone_ref_compute_sfc_keys_k64_f64(int kind, const double* x, const double* y, const double* z, uint64_t* keys,
+                                         size_t n, const cstone_box_f64* box) { sfcKeys(kind, x, y, z, keys, n, box); }
+void cstone_ref_sfc_ibox_k32(int kind, uint32_t key, unsigned level, int* b) { ibox<uint32_t>(kind, key, level, b); }
+void cstone_ref_sfc_ibox_k64(int kind, uint64_t key, unsigned level, int* b) { ibox<uint64_t>(kind, key, level, b); }
+
+void cstone_ref_sort_by_key_k32(uint32_t* keys, uint32_t* values, size_t n) { sort_by_key(keys, keys + n, values); }
+void cstone_ref_sort_by_key_k64(uint64_t* keys, uint32_t* values, size_t n) { sort_by_key(keys, keys + n, values); }
+
+void cstone_ref_gather(const uint32_t* map, size_t n, const void* src, void* dst, int elemBytes)
+{
+    gsl::span<const uint32_t> m(map, n);
+    switch (elemBytes)
+    {
+        case 4: gather<uint32_t>(m, (const uint32_t*)src, (uint32_t*)dst); break;
+        case 8: gather<uint32_t>(m, (const uint64_t*)src, (uint64_t*)dst); break;
+        case 12: gather<uint32_t>(m, (const util::array<uint32_t, 3>*)src, (util::array<uint32_t, 3>*)dst); break;
+        case 16: gather<uint32_t>(m, (const util::array<uint64_t, 2>*)src, (util::array<uint64_t, 2>*)dst); break;
+        case 24: gather<uint32_t>(m, (const util::array<uint64_t, 3>*)src, (util::array<uint64_t, 3>*)dst); break;
+        case 32: gather<uint32_t>(m, (const util::array<uint64_t, 4>*)src, (util::array<uint64_t, 4>*)dst); break;
+        default: std::abort();
+    }
+}
+
+void cstone_ref_compute_node_counts_k32(const uint32_t* tree, uint32_t* counts, int32_t n, const uint32_t* f,
+                                        const uint32_t* l, uint32_t maxCount, int guess)
+{
+    computeNodeCounts(tree, counts, n, f, l, maxCount, guess != 0);
+}
+void cstone_ref_compute_node_counts_k64(const uint64_t* tree, uint32_t* counts, int32_t n, const uint64_t* f,
+                                        const uint64_t* l, uint32_t maxCount, int guess)
+{
+    computeNodeCounts(tree, counts, n, f, l, maxCount, guess != 0);
+}
+int cstone_ref_rebalance_decision_k32(const uint32_t* tree, const uint32_t* counts, int32_t n, uint32_t bucket,
+                                      int32_t* ops) { return rebalanceDecision(tree, counts, n, bucket, ops); }
+int cstone_ref_rebalance_decision_k64(const uint64_t* tree, const uint32_t* counts, int32_t n, uint32_t bucket,
+                                      int32_t* ops) { return rebalanceDecision(tree, counts, n, bucket, ops); }
+int32_t cstone_ref_rebalance_tree_k32(const uint32_t* tree, int32_t n, int32_t* ops, uint32_t* newTree, int32_t cap)
+{ return rebalanceTreeW(tree, n, ops, newTree, cap); }
+int32_t cstone_ref_rebalance_tree_k64(const uint64_t* tree, int32_t n, int32_t* ops, uint64_t* newTree, int32_t cap)
+{ return rebalanceTreeW(tree, n, ops, newTree, cap); }
+int cstone_ref_update_octree_k32(const uint32_t* f, const uint32_t* l, uint32_t bucket, uint32_t maxCount,
+                                 uint32_t* tree, uint32_t* counts, int32_t cap, int32_t* n)
+{ return updateOctreeW(f, l, bucket, maxCount, tree, counts, cap, n); }
+int cstone_ref_update_octree_k64(const uint64_t* f, const uint64_t* l, uint32_t bucket, uint32_t maxCount,
+                                 uint64_t* tree, uint32_t* counts, int32_t cap, int32_t* n)
+{ return updateOctreeW(f, l, bucket, maxCount, tree, counts, cap, n); }
+int32_t cstone_ref_compute_octree_k32(const uint32_t* f, const uint32_t* l, uint32_t bucket, uint32_t maxCount,
+                                      uint32_t* tree, uint32_t* counts, int32_t cap)
+{ return computeOctreeW(f, l, bucket, maxCount, tree, counts, cap); }
+int32_t cstone_ref_compute_octree_k64(const uint64_t* f, const uint64_t* l, uint32_t bucket, uint32_t maxCount,
+                                      uint64_t* tree, uint32_t* counts, int32_t cap)
+{ return computeOctreeW(f, l, bucket, maxCount, tree, counts, cap); }
+
+void cstone_ref_build_octree_k32(const uint32_t* leaves, int32_t L, uint32_t* p, int32_t* co, int32_t* pa, int32_t* lr,
+                                 int32_t* i2l, int32_t* l2i) { buildOctreeW(leaves, L, p, co, pa, lr, i2l, l2i); }
+void cstone_ref_build_octree_k64(const uint64_t* leaves, int32_t L, uint64_t* p, int32_t* co, int32_t* pa, int32_t* lr,
+                                 int32_t* i2l, int32_t* l2i) { buildOctreeW(leaves, L, p, co, pa, lr, i2l, l2i); }
+void cstone_ref_upsweep_sum(int32_t numLevels, const int32_t* levelRange, const int32_t* childOffsets, uint32_t* counts)
+{
+    // as used by FocusedOctree::updateCounts: upsweep(levelRange, childOffsets, counts, NodeCount<unsigned>{})
+    upsweep(gsl::span<const int32_t>(levelRange, numLevels + 1), gsl::span<const int32_t>(childOffsets, size_t(levelRange[numLevels])),
+            counts, NodeCount<unsigned>{});
+}
+
+void cstone_ref_geo_centers_k32_f32(int kind, const uint32_t* p, int32_t n, float* c, float* s, const cstone_box_f32* b)
+{ geoCentersW(kind, p, n, c, s, b); }
+void cstone_ref_geo_centers_k32_f64(int kind, const uint32_t* p, int32_t n, double* c, double* s, const cstone_box_f64* b)
+{ geoCentersW(kind, p, n, c, s, b); }
+void cstone_ref_geo_centers_k64_f32(int kind, const uint64_t* p, int32_t n, float* c, float* s, const cstone_box_f32* b)
+{ geoCentersW(kind, p, n, c, s, b); }
+void cstone_ref_geo_centers_k64_f64(int kind, const uint64_t* p, int32_t n, double* c, double* s, const cstone_box_f64* b)
+{ geoCentersW(kind, p, n, c, s, b); }
+
+void cstone_ref_halo_radii_f32(const float* h, const uint32_t* seg, size_t n, float scale, float* r) { haloRadiiW(h, seg, n, scale, r); }
+void cstone_ref_halo_radii_f64(const double* h, const uint32_t* seg, size_t n, float scale, float* r) { haloRadiiW(h, seg, n, scale, r); }
+
+void cstone_ref_find_halos_k32_f32(int kind, const uint32_t* p, const int32_t* co, const int32_t* i2l, const uint32_t* lv,
+                                   const float* r, const cstone_box_f32* b, int32_t f, int32_t l, int32_t* flags)
+{ findHalosW<uint32_t, float>(kind, p, co, i2l, lv, r, b, f, l, flags); }
+void cstone_ref_find_halos_k32_f64(int kind, const uint32_t* p, const int32_t* co, const int32_t* i2l, const uint32_t* lv,
+                                   const float* r, const cstone_box_f64* b, int32_t f, int32_t l, int32_t* flags)
+{ findHalosW<uint32_t, double>(kind, p, co, i2l, lv, r, b, f, l, flags); }
+void cstone_ref_find_halos_k64_f32(int kind, const uint64_t* p, const int32_t* co, const int32_t* i2l, const uint64_t* lv,
+                                   const float* r, const cstone_box_f32* b, int32_t f, int32_t l, int32_t* flags)
+{ findHalosW<uint64_t, float>(kind, p, co, i2l, lv, r, b, f, l, flags); }
+void cstone_ref_find_halos_k64_f64(int kind, const uint64_t* p, const int32_t* co, const int32_t* i2l, const uint64_t* lv,
+                                   const float* r, const cstone_box_f64* b, int32_t f, int32_t l, int32_t* flags)
+{ findHalosW<uint64_t, double>(kind, p, co, i2l, lv, r, b, f, l, flags); }
+
+void cstone_ref_compute_node_layout(const uint32_t* counts, const int32_t* flags, int32_t first, int32_t last,
+                                    int32_t L, uint32_t* layout)
+{
+    computeNodeLayout(gsl::span<const unsigned>(counts, L), gsl::span<const int>(flags, L), first, last,
+                      gsl::span<LocalIndex>(layout, L + 1));
+}
+
+void cstone_ref_find_neighbors_f32(const float* x, const float* y, const float* z, const float* h, uint32_t f, uint32_t l,
+                                   const cstone_box_f32* box, const int32_t* co, const int32_t* i2l, const uint32_t* layout,
+                                   const float* c, const float* s, float ext, uint32_t ngmax, uint32_t* nb, uint32_t* nc)
+{ findNeighborsW(x, y, z, h, f, l, box, co, i2l, layout, c, s, ext, ngmax, nb, nc); }
+void cstone_ref_find_neighbors_f64(const double* x, const double* y, const double* z, const double* h, uint32_t f, uint32_t l,
+                                   const cstone_box_f64* box, const int32_t* co, const int32_t* i2l, const uint32_t* layout,
+                                   const double* c, const double* s, float ext, uint32_t ngmax, uint32_t* nb, uint32_t* nc)
+{ findNeighborsW(x, y, z, h, f, l, box, co, i2l, layout, c, s, ext, ngmax, nb, nc); }
+
+} // extern "C"
