@@ -1,0 +1,268 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes/numpy access to the CPU checkers (oracle_api.h).
+
+`load("port")`  -> oracle/liboracle_port.so        (our CPU restatement, prefix cstone_oracle_)
+`load("ref")`   -> oracle/_ref/liboracle_ref.so    (reference headers compiled here, prefix cstone_ref_)
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this
+module.  The product package (cornerstone_octree_b200) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_PATHS = {"port": os.path.join(_HERE, "liboracle_port.so"), "ref": os.path.join(_HERE, "_ref", "liboracle_ref.so")}
+_PREFIX = {"port": "cstone_oracle_", "ref": "cstone_ref_"}
+
+MORTON, HILBERT = 0, 1
+OPEN, PERIODIC, FIXED = 0, 1, 2
+
+
+class BoxF32(C.Structure):
+    _fields_ = [("limits", C.c_float * 6), ("lengths", C.c_float * 3), ("inv_lengths", C.c_float * 3),
+                ("boundaries", C.c_ubyte * 3)]
+
+
+class BoxF64(C.Structure):
+    _fields_ = [("limits", C.c_double * 6), ("lengths", C.c_double * 3), ("inv_lengths", C.c_double * 3),
+                ("boundaries", C.c_ubyte * 3)]
+
+
+def make_box(limits, boundaries=(OPEN, OPEN, OPEN), dtype=np.float64):
+    """Same arithmetic as cstone::Box<T> ctor [ref: sfc/box.hpp:128-137]: lengths = max-min and
+    inverse lengths = T(1)/(max-min), both evaluated in T."""
+    dtype = np.dtype(dtype)
+    lim = np.asarray(limits, dtype=dtype)
+    if lim.size == 2:
+        lim = np.array([lim[0], lim[1]] * 3, dtype=dtype)
+    box = BoxF32() if dtype == np.float32 else BoxF64()
+    one = dtype.type(1)
+    for i in range(6):
+        box.limits[i] = lim[i]
+    for d in range(3):
+        length = dtype.type(lim[2 * d + 1] - lim[2 * d])
+        box.lengths[d] = length
+        box.inv_lengths[d] = dtype.type(one / length)
+    for d in range(3):
+        box.boundaries[d] = int(boundaries[d])
+    return box
+
+
+def available(which):
+    return os.path.exists(_PATHS[which])
+
+
+def build(which="port"):
+    subprocess.check_call(["make", "-C", _HERE, which], stdout=subprocess.DEVNULL)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _ks(dtype):
+    return {np.dtype(np.uint32): "k32", np.dtype(np.uint64): "k64"}[np.dtype(dtype)]
+
+
+def _ts(dtype):
+    return {np.dtype(np.float32): "f32", np.dtype(np.float64): "f64"}[np.dtype(dtype)]
+
+
+def max_level(dtype):
+    return 10 if np.dtype(dtype) == np.uint32 else 21
+
+
+class Oracle:
+    """numpy front-end; every method allocates and returns its outputs."""
+
+    def __init__(self, which):
+        if not available(which):
+            raise FileNotFoundError(_PATHS[which])
+        self.which = which
+        self.lib = C.CDLL(_PATHS[which])
+        self.p = _PREFIX[which]
+
+    def _f(self, name, restype=None):
+        f = getattr(self.lib, self.p + name)
+        f.restype = restype
+        return f
+
+    # ---- misc
+    def num_threads(self):
+        return self._f("num_threads", C.c_int)()
+
+    def set_num_threads(self, n):
+        self._f("set_num_threads")(C.c_int(n))
+
+    # ---- SFC
+    def encode(self, kind, ix, iy, iz, kdtype=np.uint64):
+        f = self._f("encode_" + _ks(kdtype), C.c_uint32 if np.dtype(kdtype) == np.uint32 else C.c_uint64)
+        return f(C.c_int(kind), C.c_uint(ix), C.c_uint(iy), C.c_uint(iz))
+
+    def decode(self, kind, key, kdtype=np.uint64):
+        xyz = (C.c_uint * 3)()
+        kt = C.c_uint32 if np.dtype(kdtype) == np.uint32 else C.c_uint64
+        self._f("decode_" + _ks(kdtype))(C.c_int(kind), kt(int(key)), xyz)
+        return tuple(xyz)
+
+    def sfc_ibox(self, kind, key, level, kdtype=np.uint64):
+        out = (C.c_int * 6)()
+        kt = C.c_uint32 if np.dtype(kdtype) == np.uint32 else C.c_uint64
+        self._f("sfc_ibox_" + _ks(kdtype))(C.c_int(kind), kt(int(key)), C.c_uint(level), out)
+        return tuple(out)
+
+    def compute_sfc_keys(self, kind, x, y, z, box, kdtype=np.uint64, keys=None):
+        n = x.size
+        if keys is None:
+            keys = np.zeros(n, dtype=kdtype)
+        self._f("compute_sfc_keys_%s_%s" % (_ks(keys.dtype), _ts(x.dtype)))(
+            C.c_int(kind), _ptr(x), _ptr(y), _ptr(z), _ptr(keys), C.c_size_t(n), C.byref(box))
+        return keys
+
+    # ---- sort / gather
+    def sort_by_key(self, keys, values=None):
+        keys = keys.copy()
+        values = np.arange(keys.size, dtype=np.uint32) if values is None else values.copy()
+        self._f("sort_by_key_" + _ks(keys.dtype))(_ptr(keys), _ptr(values), C.c_size_t(keys.size))
+        return keys, values
+
+    def gather(self, order, src):
+        src = np.ascontiguousarray(src)
+        dst = np.empty((order.size,) + src.shape[1:], dtype=src.dtype)
+        elem = src.dtype.itemsize * int(np.prod(src.shape[1:], dtype=np.int64))
+        self._f("gather")(_ptr(order), C.c_size_t(order.size), _ptr(src), _ptr(dst), C.c_int(elem))
+        return dst
+
+    # ---- leaf array
+    def compute_node_counts(self, tree, keys, max_count=0xFFFFFFFF, guess=False, counts=None):
+        n = tree.size - 1
+        if counts is None:
+            counts = np.zeros(n, dtype=np.uint32)
+        first = keys.ctypes.data
+        last = first + keys.size * keys.itemsize
+        self._f("compute_node_counts_" + _ks(tree.dtype))(
+            _ptr(tree), _ptr(counts), C.c_int32(n), C.c_void_p(first), C.c_void_p(last), C.c_uint32(max_count),
+            C.c_int(int(guess)))
+        return counts
+
+    def rebalance_decision(self, tree, counts, bucket):
+        n = tree.size - 1
+        ops = np.zeros(n + 1, dtype=np.int32)
+        conv = self._f("rebalance_decision_" + _ks(tree.dtype), C.c_int)(
+            _ptr(tree), _ptr(counts), C.c_int32(n), C.c_uint32(bucket), _ptr(ops))
+        return ops, bool(conv)
+
+    def rebalance_tree(self, tree, ops):
+        """ops: n+1 un-scanned entries. returns (new_tree, scanned ops)."""
+        n = tree.size - 1
+        ops = ops.astype(np.int32).copy()
+        cap = int(ops[:n].sum())
+        new_tree = np.zeros(cap + 1, dtype=tree.dtype)
+        m = self._f("rebalance_tree_" + _ks(tree.dtype), C.c_int32)(
+            _ptr(tree), C.c_int32(n), _ptr(ops), _ptr(new_tree), C.c_int32(cap))
+        assert m == cap
+        return new_tree, ops
+
+    def update_octree(self, keys, bucket, tree, counts, max_count=0xFFFFFFFF):
+        n = tree.size - 1
+        cap = max(8 * n + 64, 4096 * 8) if n < 64 else 8 * n + 64
+        while True:
+            t = np.zeros(cap + 1, dtype=tree.dtype)
+            c = np.zeros(cap, dtype=np.uint32)
+            t[:n + 1] = tree
+            c[:n] = counts
+            nn = C.c_int32(n)
+            first = keys.ctypes.data
+            last = first + keys.size * keys.itemsize
+            conv = self._f("update_octree_" + _ks(tree.dtype), C.c_int)(
+                C.c_void_p(first), C.c_void_p(last), C.c_uint32(bucket), C.c_uint32(max_count), _ptr(t), _ptr(c),
+                C.c_int32(cap), C.byref(nn))
+            if conv >= 0:
+                return t[:nn.value + 1].copy(), c[:nn.value].copy(), bool(conv)
+            cap = nn.value
+
+    def compute_octree(self, keys, bucket, max_count=0xFFFFFFFF):
+        cap = max(1024, 16 * (keys.size // max(bucket, 1) + 1))
+        first = keys.ctypes.data
+        last = first + keys.size * keys.itemsize
+        while True:
+            t = np.zeros(cap + 1, dtype=keys.dtype)
+            c = np.zeros(cap, dtype=np.uint32)
+            n = self._f("compute_octree_" + _ks(keys.dtype), C.c_int32)(
+                C.c_void_p(first), C.c_void_p(last), C.c_uint32(bucket), C.c_uint32(max_count), _ptr(t), _ptr(c),
+                C.c_int32(cap))
+            if n >= 0:
+                return t[:n + 1].copy(), c[:n].copy()
+            cap = -n
+
+    # ---- internal tree
+    def build_octree(self, leaves):
+        L = leaves.size - 1
+        I = (L - 1) // 7
+        M = L + I
+        out = dict(
+            prefixes=np.zeros(M, dtype=leaves.dtype), child_offsets=np.zeros(M + 1, dtype=np.int32),
+            parents=np.zeros(max(1, (M - 1) // 8), dtype=np.int32),
+            level_range=np.zeros(max_level(leaves.dtype) + 2, dtype=np.int32),
+            internal_to_leaf=np.zeros(M, dtype=np.int32), leaf_to_internal=np.zeros(M, dtype=np.int32))
+        self._f("build_octree_" + _ks(leaves.dtype))(
+            _ptr(leaves), C.c_int32(L), _ptr(out["prefixes"]), _ptr(out["child_offsets"]), _ptr(out["parents"]),
+            _ptr(out["level_range"]), _ptr(out["internal_to_leaf"]), _ptr(out["leaf_to_internal"]))
+        out["num_leaf_nodes"], out["num_internal_nodes"], out["num_nodes"] = L, I, M
+        return out
+
+    def upsweep_sum(self, level_range, child_offsets, counts):
+        counts = counts.copy()
+        self._f("upsweep_sum")(C.c_int32(level_range.size - 1), _ptr(level_range), _ptr(child_offsets), _ptr(counts))
+        return counts
+
+    def geo_centers(self, kind, prefixes, box, fdtype=np.float64):
+        n = prefixes.size
+        centers = np.zeros((n, 3), dtype=fdtype)
+        sizes = np.zeros((n, 3), dtype=fdtype)
+        self._f("geo_centers_%s_%s" % (_ks(prefixes.dtype), _ts(fdtype)))(
+            C.c_int(kind), _ptr(prefixes), C.c_int32(n), _ptr(centers), _ptr(sizes), C.byref(box))
+        return centers, sizes
+
+    # ---- halos
+    def halo_radii(self, h, segments, scale=2.0):
+        n = segments.size - 1
+        radii = np.zeros(n, dtype=np.float32)
+        self._f("halo_radii_" + _ts(h.dtype))(_ptr(h), _ptr(segments), C.c_size_t(n), C.c_float(scale), _ptr(radii))
+        return radii
+
+    def find_halos(self, kind, octree, leaves, radii, box, first, last, fdtype=np.float64):
+        flags = np.zeros(leaves.size - 1, dtype=np.int32)
+        self._f("find_halos_%s_%s" % (_ks(leaves.dtype), _ts(fdtype)))(
+            C.c_int(kind), _ptr(octree["prefixes"]), _ptr(octree["child_offsets"]), _ptr(octree["internal_to_leaf"]),
+            _ptr(leaves), _ptr(radii), C.byref(box), C.c_int32(first), C.c_int32(last), _ptr(flags))
+        return flags
+
+    def compute_node_layout(self, counts, flags, first, last):
+        L = counts.size
+        layout = np.zeros(L + 1, dtype=np.uint32)
+        self._f("compute_node_layout")(_ptr(counts), _ptr(flags), C.c_int32(first), C.c_int32(last), C.c_int32(L),
+                                       _ptr(layout))
+        return layout
+
+    # ---- neighbours
+    def find_neighbors(self, x, y, z, h, first, last, box, octree, layout, centers, sizes, ngmax, ext=1.0):
+        nw = last - first
+        nb = np.zeros(nw * ngmax, dtype=np.uint32)
+        nc = np.zeros(nw, dtype=np.uint32)
+        self._f("find_neighbors_" + _ts(x.dtype))(
+            _ptr(x), _ptr(y), _ptr(z), _ptr(h), C.c_uint32(first), C.c_uint32(last), C.byref(box),
+            _ptr(octree["child_offsets"]), _ptr(octree["internal_to_leaf"]), _ptr(layout), _ptr(centers), _ptr(sizes),
+            C.c_float(ext), C.c_uint32(ngmax), _ptr(nb), _ptr(nc))
+        return nb.reshape(nw, ngmax), nc
+
+
+_cache = {}
+
+
+def load(which="port"):
+    if which not in _cache:
+        _cache[which] = Oracle(which)
+    return _cache[which]
