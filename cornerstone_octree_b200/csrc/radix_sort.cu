@@ -1,0 +1,386 @@
+/*
+ * radix_sort.cu — a4: stable LSD radix sort of (key, u32 value) pairs, hand-written "onesweep".
+ *
+ * Replaces sortByKeyGpu / sortByKeyTempStorage / sequenceGpu [ref: primitives/primitives_gpu.h:86-110,
+ * primitives/primitives_gpu.cu:285-392 (cub::DeviceRadixSort::SortPairs, thrust::sort_by_key)] as used by
+ * GpuSfcSorter [ref: primitives/gather.cuh:80-108] and buildOctreeGpu [ref: tree/octree_gpu.cu:161].
+ * Result = the unique stable ascending order (same as the CPU std::stable_sort path, primitives/gather.hpp:58-90).
+ *
+ * Algorithm (8-bit digits, full key width: 4 passes for 32-bit, 8 for 64-bit keys)
+ *   1. one histogram kernel over the keys fills the digit counts of ALL passes,
+ *   2. a tiny kernel turns them into exclusive bin offsets,
+ *   3. per pass ONE kernel ("onesweep"): every block takes a tile (atomic ticket), ranks its keys by digit with
+ *      warp-level match_any/popc (stable), publishes the per-digit tile counts and resolves the counts of all
+ *      earlier tiles by decoupled look-back (one status word per tile and digit), reorders the tile through
+ *      shared memory and writes keys and values in digit-contiguous runs.
+ *   Per pass each key and value is read once and written once: 2*(sizeof(K)+4) bytes per element.
+ *   With values_are_iota the first pass synthesises the value from the element index (no value read).
+ */
+#include "common.cuh"
+
+namespace csb
+{
+
+constexpr int kRadixBits    = 8;
+constexpr int kRadix        = 1 << kRadixBits;
+constexpr int kSortThreads  = 256; // == kRadix: thread d owns digit d in the look-back
+constexpr int kSortWarps    = kSortThreads / 32;
+constexpr int kSortItems    = 16;
+constexpr int kSortTile     = kSortThreads * kSortItems;
+constexpr uint32_t kStFlagShift     = 30;
+constexpr uint32_t kStValueMask     = (1u << kStFlagShift) - 1u;
+constexpr uint32_t kStAggregate     = 1u << kStFlagShift;
+constexpr uint32_t kStInclusive     = 2u << kStFlagShift;
+
+template<class K>
+__host__ __device__ constexpr int numPasses()
+{
+    return (KeyTraits<K>::keyBits + 1 + kRadixBits - 1) / kRadixBits; // +1: keys may carry the bit above keyBits
+}
+// 32-bit: 31 bits -> 4 passes; 64-bit: 64 bits -> 8 passes (removeKey = 2^63 and placeholder-bit keys use bit 63)
+
+struct SortTemp
+{
+    uint32_t* hist;    // [passes][256] counts, then exclusive offsets
+    uint32_t* tickets; // [passes] (stride 32 words)
+    uint32_t* status;  // [passes][numTiles][256]
+    size_t bytes;
+};
+
+inline size_t sortNumTiles(size_t n) { return (n + kSortTile - 1) / kSortTile; }
+
+template<class K>
+uint64_t sortTempBytes(uint64_t n)
+{
+    uint64_t P = numPasses<K>();
+    return P * kRadix * 4 + P * 32 * 4 + P * sortNumTiles(n) * kRadix * 4 + 256;
+}
+
+template<class K>
+SortTemp carveSortTemp(void* temp, size_t n)
+{
+    constexpr int P = numPasses<K>();
+    SortTemp t;
+    t.hist    = reinterpret_cast<uint32_t*>(temp);
+    t.tickets = t.hist + P * kRadix;
+    t.status  = t.tickets + P * 32;
+    t.bytes   = size_t(P) * kRadix * 4 + size_t(P) * 32 * 4 + size_t(P) * sortNumTiles(n) * kRadix * 4;
+    return t;
+}
+
+__device__ inline uint32_t ldRelaxed(const uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ inline void stRelaxed(uint32_t* p, uint32_t v)
+{
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------
+// 1. digit histograms of all passes in one sweep over the keys
+// ------------------------------------------------------------------------------------------------
+template<class K>
+__global__ void __launch_bounds__(512) histogramKernel(const K* __restrict__ keys, size_t n, uint32_t* __restrict__ hist)
+{
+    constexpr int P = numPasses<K>();
+    __shared__ uint32_t sHist[P * kRadix];
+    for (int i = threadIdx.x; i < P * kRadix; i += blockDim.x)
+        sHist[i] = 0;
+    __syncthreads();
+
+    size_t stride = size_t(gridDim.x) * blockDim.x;
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        K key = keys[i];
+#pragma unroll
+        for (int p = 0; p < P; ++p)
+            atomicAdd(&sHist[p * kRadix + (unsigned(key >> (p * kRadixBits)) & (kRadix - 1))], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < P * kRadix; i += blockDim.x)
+    {
+        uint32_t c = sHist[i];
+        if (c) atomicAdd(&hist[i], c);
+    }
+}
+
+// 2. exclusive scan of each pass's 256 bins (one block of 256 threads per pass)
+__global__ void __launch_bounds__(kRadix) binOffsetsKernel(uint32_t* __restrict__ hist)
+{
+    __shared__ uint32_t sWarp[kRadix / 32];
+    uint32_t* h   = hist + blockIdx.x * kRadix;
+    uint32_t c    = h[threadIdx.x];
+    uint32_t incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+        uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (int(laneId()) >= o) incl += t;
+    }
+    if (laneId() == 31) sWarp[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    uint32_t off = 0;
+    for (int w = 0; w < int(threadIdx.x >> 5); ++w)
+        off += sWarp[w];
+    h[threadIdx.x] = off + incl - c;
+}
+
+// ------------------------------------------------------------------------------------------------
+// 3. one onesweep pass
+// ------------------------------------------------------------------------------------------------
+template<class K>
+struct SortSmem
+{
+    K keys[kSortTile];
+    uint32_t vals[kSortTile];
+    uint32_t warpHist[kSortWarps][kRadix];
+    uint32_t digitStart[kRadix]; // exclusive scan of the tile's digit counts
+    uint32_t globalBase[kRadix]; // global position of local slot 0 of each digit, minus digitStart
+    uint32_t warpSums[kSortWarps];
+    uint32_t tile;
+};
+
+template<class K, bool Iota>
+__global__ void __launch_bounds__(kSortThreads) onesweepKernel(const K* __restrict__ keysIn,
+                                                                const uint32_t* __restrict__ valsIn,
+                                                                K* __restrict__ keysOut,
+                                                                uint32_t* __restrict__ valsOut,
+                                                                uint32_t n,
+                                                                int shift,
+                                                                const uint32_t* __restrict__ binOffsets,
+                                                                uint32_t* __restrict__ ticket,
+                                                                uint32_t* __restrict__ status)
+{
+    extern __shared__ __align__(16) unsigned char smemRaw[];
+    SortSmem<K>& sm = *reinterpret_cast<SortSmem<K>*>(smemRaw);
+
+    const unsigned tid  = threadIdx.x;
+    const unsigned lane = tid & 31u;
+    const unsigned warp = tid >> 5;
+
+    if (tid == 0) sm.tile = atomicAdd(ticket, 1u);
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w)
+        sm.warpHist[w][tid] = 0;
+    __syncthreads();
+    const uint32_t tile     = sm.tile;
+    const uint32_t tileBase = tile * uint32_t(kSortTile);
+    const uint32_t warpBase = tileBase + warp * (32u * kSortItems);
+
+    // ---- load (warp-striped: item i of lane l is element warpBase + 32 i + l); order = (warp, i, lane)
+    K key[kSortItems];
+    uint32_t val[kSortItems];
+#pragma unroll
+    for (int i = 0; i < kSortItems; ++i)
+    {
+        uint32_t idx = warpBase + 32u * i + lane;
+        key[i]       = (idx < n) ? keysIn[idx] : K(~K(0)); // padding sorts behind everything, never written
+    }
+#pragma unroll
+    for (int i = 0; i < kSortItems; ++i)
+    {
+        uint32_t idx = warpBase + 32u * i + lane;
+        if (Iota) val[i] = idx;
+        else val[i] = (idx < n) ? valsIn[idx] : 0u;
+    }
+
+    // ---- stable ranking inside the warp
+    uint16_t rank[kSortItems];
+    uint32_t* myHist        = sm.warpHist[warp];
+    const unsigned lanesLt  = laneMaskLt();
+#pragma unroll
+    for (int i = 0; i < kSortItems; ++i)
+    {
+        unsigned d      = unsigned(key[i] >> shift) & (kRadix - 1);
+        unsigned peers  = __match_any_sync(0xffffffffu, d);
+        unsigned leader = __ffs(int(peers)) - 1;
+        uint32_t before = 0;
+        if (lane == leader)
+        {
+            before    = myHist[d];
+            myHist[d] = before + __popc(peers);
+        }
+        before  = __shfl_sync(0xffffffffu, before, leader);
+        rank[i] = uint16_t(before + __popc(peers & lanesLt));
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // ---- per digit (thread d = digit d): exclusive scan over warps, tile count, look-back
+    {
+        uint32_t run = 0;
+#pragma unroll
+        for (int w = 0; w < kSortWarps; ++w)
+        {
+            uint32_t c          = sm.warpHist[w][tid];
+            sm.warpHist[w][tid] = run;
+            run += c;
+        }
+        const uint32_t tileCount = run;
+        uint32_t* myStatus       = status + size_t(tile) * kRadix + tid;
+        if (tile == 0) stRelaxed(myStatus, kStInclusive | tileCount);
+        else stRelaxed(myStatus, kStAggregate | tileCount);
+
+        // block-wide exclusive scan of tileCount over the 256 digits
+        uint32_t incl = tileCount;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (int(lane) >= o) incl += t;
+        }
+        if (lane == 31) sm.warpSums[warp] = incl;
+        __syncthreads();
+        uint32_t off = 0;
+#pragma unroll
+        for (int w = 0; w < kSortWarps; ++w)
+            if (w < int(warp)) off += sm.warpSums[w];
+        const uint32_t dStart = off + incl - tileCount;
+        sm.digitStart[tid]    = dStart;
+
+        // decoupled look-back over earlier tiles for this digit
+        uint32_t excl = 0;
+        if (tile > 0)
+        {
+            int t = int(tile) - 1;
+            while (true)
+            {
+                uint32_t st;
+                do
+                {
+                    st = ldRelaxed(status + size_t(t) * kRadix + tid);
+                } while ((st >> kStFlagShift) == 0u);
+                excl += st & kStValueMask;
+                if ((st >> kStFlagShift) == 2u) break;
+                --t;
+            }
+            stRelaxed(myStatus, kStInclusive | (excl + tileCount));
+        }
+        sm.globalBase[tid] = binOffsets[tid] + excl - dStart;
+    }
+    __syncthreads();
+
+    // ---- reorder through shared memory
+#pragma unroll
+    for (int i = 0; i < kSortItems; ++i)
+    {
+        unsigned d   = unsigned(key[i] >> shift) & (kRadix - 1);
+        uint32_t pos = sm.digitStart[d] + sm.warpHist[warp][d] + rank[i];
+        sm.keys[pos] = key[i];
+        sm.vals[pos] = val[i];
+    }
+    __syncthreads();
+
+    // ---- write out: consecutive slots of one digit go to consecutive global addresses
+#pragma unroll
+    for (int i = 0; i < kSortItems; ++i)
+    {
+        uint32_t slot = tid + i * kSortThreads;
+        K k           = sm.keys[slot];
+        unsigned d    = unsigned(k >> shift) & (kRadix - 1);
+        uint32_t pos  = sm.globalBase[d] + slot;
+        if (pos < n)
+        {
+            keysOut[pos] = k;
+            valsOut[pos] = sm.vals[slot];
+        }
+    }
+}
+
+} // namespace csb
+
+namespace csb
+{
+
+template<class K>
+int sortByKey(K* keys, uint32_t* values, K* keyBuf, uint32_t* valueBuf, size_t n, void* temp, uint64_t tempBytes,
+              int valuesAreIota, cudaStream_t s)
+{
+    constexpr int P = numPasses<K>();
+    static_assert(P % 2 == 0, "even number of passes: the result lands in the caller's primary buffers");
+    if (n == 0) return 0;
+    if (!keys || !values || !keyBuf || !valueBuf || !temp) return CSTONE_E_INVALID_ARGUMENT;
+    if (n >= (size_t(1) << 30)) return CSTONE_E_TOO_LARGE;
+    if (tempBytes < sortTempBytes<K>(n)) return CSTONE_E_TEMP_TOO_SMALL;
+
+    SortTemp t = carveSortTemp<K>(temp, n);
+    CSB_CUDA(cudaMemsetAsync(temp, 0, t.bytes, s));
+
+    histogramKernel<K><<<gridFor(n, 512 * 8, 2), 512, 0, s>>>(keys, n, t.hist);
+    CSB_LAUNCHED();
+    binOffsetsKernel<<<P, kRadix, 0, s>>>(t.hist);
+    CSB_LAUNCHED();
+
+    static bool attrSet[2] = {false, false};
+    const size_t smemBytes = sizeof(SortSmem<K>);
+    if (!attrSet[0])
+    {
+        CSB_CUDA(cudaFuncSetAttribute(onesweepKernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      int(smemBytes)));
+        CSB_CUDA(cudaFuncSetAttribute(onesweepKernel<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      int(smemBytes)));
+        // per-device attribute: do not cache across devices (cheap call), keep the flag only as documentation
+    }
+
+    const unsigned numTiles = unsigned(sortNumTiles(n));
+    K* kSrc                 = keys;
+    K* kDst                 = keyBuf;
+    uint32_t* vSrc          = values;
+    uint32_t* vDst          = valueBuf;
+    for (int p = 0; p < P; ++p)
+    {
+        uint32_t* status = t.status + size_t(p) * numTiles * kRadix;
+        if (p == 0 && valuesAreIota)
+            onesweepKernel<K, true><<<numTiles, kSortThreads, smemBytes, s>>>(
+                kSrc, vSrc, kDst, vDst, uint32_t(n), p * kRadixBits, t.hist + p * kRadix, t.tickets + p * 32, status);
+        else
+            onesweepKernel<K, false><<<numTiles, kSortThreads, smemBytes, s>>>(
+                kSrc, vSrc, kDst, vDst, uint32_t(n), p * kRadixBits, t.hist + p * kRadix, t.tickets + p * 32, status);
+        CSB_LAUNCHED();
+        K* tk        = kSrc;
+        kSrc         = kDst;
+        kDst         = tk;
+        uint32_t* tv = vSrc;
+        vSrc         = vDst;
+        vDst         = tv;
+    }
+    return 0;
+}
+
+__global__ void __launch_bounds__(256) sequenceKernel(uint32_t* __restrict__ out, size_t n, uint32_t init)
+{
+    size_t stride = size_t(gridDim.x) * blockDim.x;
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+        out[i] = init + uint32_t(i);
+}
+
+} // namespace csb
+
+extern "C" {
+
+uint64_t cstone_b200_sort_by_key_temp_bytes_k32(uint64_t n) { return csb::sortTempBytes<uint32_t>(n); }
+uint64_t cstone_b200_sort_by_key_temp_bytes_k64(uint64_t n) { return csb::sortTempBytes<uint64_t>(n); }
+
+int cstone_b200_sort_by_key_k32(uint32_t* keys, uint32_t* values, uint32_t* keyBuf, uint32_t* valueBuf, size_t n,
+                                void* temp, uint64_t tempBytes, int iota, void* stream)
+{
+    return csb::sortByKey<uint32_t>(keys, values, keyBuf, valueBuf, n, temp, tempBytes, iota, csb::asStream(stream));
+}
+int cstone_b200_sort_by_key_k64(uint64_t* keys, uint32_t* values, uint64_t* keyBuf, uint32_t* valueBuf, size_t n,
+                                void* temp, uint64_t tempBytes, int iota, void* stream)
+{
+    return csb::sortByKey<uint64_t>(keys, values, keyBuf, valueBuf, n, temp, tempBytes, iota, csb::asStream(stream));
+}
+
+int cstone_b200_sequence_u32(uint32_t* out, size_t n, uint32_t init, void* stream)
+{
+    if (n == 0) return 0;
+    csb::sequenceKernel<<<csb::gridFor(n, 256), 256, 0, csb::asStream(stream)>>>(out, n, init);
+    CSB_LAUNCHED();
+    return 0;
+}
+
+} // extern "C"
