@@ -1,0 +1,105 @@
+"""ctypes binding of libcstone_b200.so (include/cstone_b200.h).
+
+The library is the product; this module only loads it and declares the prototypes.  There is NO fallback:
+if the shared object is missing the import fails, and every call checks the returned status and raises."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcstone_b200.so")
+
+MORTON, HILBERT = 0, 1
+OPEN, PERIODIC, FIXED = 0, 1, 2
+
+
+class BoxF32(C.Structure):
+    _fields_ = [("limits", C.c_float * 6), ("lengths", C.c_float * 3), ("inv_lengths", C.c_float * 3),
+                ("boundaries", C.c_ubyte * 3)]
+
+
+class BoxF64(C.Structure):
+    _fields_ = [("limits", C.c_double * 6), ("lengths", C.c_double * 3), ("inv_lengths", C.c_double * 3),
+                ("boundaries", C.c_ubyte * 3)]
+
+
+class CstoneError(RuntimeError):
+    def __init__(self, status, where):
+        self.status = status
+        super().__init__("%s failed with status %d: %s" % (where, status, status_string(status)))
+
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        "cornerstone_octree_b200: %s not found. Build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+        "(make -C cornerstone_octree_b200/csrc). There is no CPU fallback." % LIB_PATH)
+
+lib = C.CDLL(LIB_PATH)
+
+_vp, _sz, _i, _u32, _u64, _i32, _f = C.c_void_p, C.c_size_t, C.c_int, C.c_uint32, C.c_uint64, C.c_int32, C.c_float
+
+lib.cstone_b200_abi_version.restype = _i
+lib.cstone_b200_status_string.restype = C.c_char_p
+lib.cstone_b200_status_string.argtypes = [_i]
+lib.cstone_b200_launch_count.restype = _u64
+lib.cstone_b200_host_hilbert_table.restype = C.POINTER(C.c_uint16)
+lib.cstone_b200_host_hilbert_table.argtypes = [_i]
+
+_PROTOS = {
+    # name: (restype, argtypes)
+    "minmax_temp_bytes": (_u64, []),
+    "scan_temp_bytes": (_u64, [_u64]),
+    "sequence_u32": (_i, [_vp, _sz, _u32, _vp]),
+    "gather": (_i, [_vp, _sz, _vp, _vp, _i, _vp]),
+    "scatter": (_i, [_vp, _sz, _vp, _vp, _i, _vp]),
+    "gather_multi": (_i, [_vp, _sz, _i, _vp, _vp, _vp, _vp]),
+    "exclusive_scan_u32": (_i, [_vp, _vp, _sz, _u32, _vp, _vp]),
+    "inclusive_scan_u32": (_i, [_vp, _vp, _sz, _vp, _vp]),
+    "upsweep_sum": (_i, [_i32, _vp, _vp, _vp, _vp]),
+    "compute_node_layout": (_i, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
+}
+for ts in ("f32", "f64"):
+    _PROTOS["minmax3_" + ts] = (_i, [_vp, _vp, _vp, _sz, _vp, _vp, _vp])
+    _PROTOS["halo_radii_" + ts] = (_i, [_vp, _vp, _sz, _f, _vp, _vp])
+    _PROTOS["find_neighbors_" + ts] = (_i, [_vp, _vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _f, _u32,
+                                            _vp, _vp, _vp])
+for ks in ("k32", "k64"):
+    _PROTOS["encode_sfc_" + ks] = (_i, [_i, _vp, _vp, _vp, _vp, _sz, _vp])
+    _PROTOS["decode_sfc_" + ks] = (_i, [_i, _vp, _vp, _vp, _vp, _sz, _vp])
+    _PROTOS["sort_by_key_temp_bytes_" + ks] = (_u64, [_u64])
+    _PROTOS["sort_by_key_" + ks] = (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _u64, _i, _vp])
+    _PROTOS["compute_node_counts_" + ks] = (_i, [_vp, _vp, _i32, _vp, _vp, _u32, _i, _vp])
+    _PROTOS["compute_node_ops_" + ks] = (_i, [_vp, _i32, _vp, _u32, _vp, _vp, _vp, _vp, _vp])
+    _PROTOS["rebalance_decision_" + ks] = (_i, [_vp, _i32, _vp, _u32, _vp, _vp])
+    _PROTOS["rebalance_tree_" + ks] = (_i, [_vp, _i32, _i32, _vp, _vp, _vp])
+    _PROTOS["update_octree_" + ks] = (_i, [_vp, _vp, _u32, _u32, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp])
+    _PROTOS["compute_octree_" + ks] = (_i, [_vp, _vp, _u32, _u32, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp])
+    _PROTOS["build_octree_temp_bytes_" + ks] = (_u64, [_i32])
+    _PROTOS["build_octree_" + ks] = (_i, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp])
+    for ts in ("f32", "f64"):
+        _PROTOS["compute_sfc_keys_%s_%s" % (ks, ts)] = (_i, [_i, _vp, _vp, _vp, _vp, _sz, _vp, _vp])
+        _PROTOS["compute_geo_centers_%s_%s" % (ks, ts)] = (_i, [_i, _vp, _i32, _vp, _vp, _vp, _vp])
+        _PROTOS["find_halos_%s_%s" % (ks, ts)] = (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp])
+
+for _name, (_res, _args) in _PROTOS.items():
+    _fn = getattr(lib, "cstone_b200_" + _name)  # AttributeError here = header/library mismatch
+    _fn.restype = _res
+    _fn.argtypes = _args
+
+EXPORTED = ["abi_version", "status_string", "launch_count"] + sorted(_PROTOS)
+
+
+def status_string(status):
+    return lib.cstone_b200_status_string(int(status)).decode()
+
+
+def call(name, *args):
+    """invoke cstone_b200_<name>; raises CstoneError on a non-zero int status"""
+    fn = getattr(lib, "cstone_b200_" + name)
+    ret = fn(*args)
+    if fn.restype is _i and ret != 0:
+        raise CstoneError(ret, "cstone_b200_" + name)
+    return ret
+
+
+def launch_count():
+    return int(lib.cstone_b200_launch_count())

@@ -1,0 +1,129 @@
+"""GPU parity tests proper: the CUDA library (through its C ABI) against the CPU checkers on the same seeded
+inputs, bit-exact on every stage of the hot path, plus the reference's golden vectors (kat.py)."""
+import numpy as np
+import pytest
+
+import gen
+import kat
+import pipeline
+from oracle import loader
+from test_oracle_vs_ref import CASES, make_case
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    import gpu_adapter
+    return gpu_adapter.GpuImpl()
+
+
+KATS = [kat.check_morton, kat.check_hilbert, kat.check_sfc_keys_box, kat.check_sort, kat.check_node_counts,
+        kat.check_rebalance, kat.check_compute_octree, kat.check_octree, kat.check_find_halos]
+
+
+@pytest.mark.parametrize("check", KATS, ids=[c.__name__ for c in KATS])
+def test_known_answers(check, gpu):
+    check(gpu)
+
+
+def test_neighbors_vs_all2all(gpu):
+    kat.check_find_neighbors(gpu, n=1200)
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_pipeline_matches_port(case, gpu, port):
+    _, genname, n, kd, fd, kind, bucket, bnd = case
+    x, y, z, h, box = make_case(genname, n, fd, bnd)
+    ngmax = 150
+    a = pipeline.run(port, kind, x, y, z, h, box, kd, bucket, ngmax)
+    b = pipeline.run(gpu, kind, x, y, z, h, box, kd, bucket, ngmax)
+    assert pipeline.compare(a, b, ngmax) == []
+
+
+def test_pipeline_matches_reference_build(gpu, ref):
+    """against the reference's own code (prebuilt oracle/_ref travels to the GPU box)"""
+    x, y, z, h, box = make_case("plummer", 50000, np.float64, (0, 0, 0))
+    a = pipeline.run(ref, 1, x, y, z, h, box, np.uint64, 64, 150)
+    b = pipeline.run(gpu, 1, x, y, z, h, box, np.uint64, 64, 150)
+    assert pipeline.compare(a, b, 150) == []
+
+
+def test_ngmax_truncation_keeps_dfs_order(gpu, port):
+    """count > ngmax: the kept subset is the first ngmax in depth-first order [ref: findneighbors.hpp:138-139]"""
+    x, y, z, h, box = make_case("uniform", 20000, np.float64, (1, 1, 1))
+    h *= 1.6
+    a = pipeline.run(port, 1, x, y, z, h, box, np.uint64, 64, 32)
+    b = pipeline.run(gpu, 1, x, y, z, h, box, np.uint64, 64, 32)
+    assert (a["neighbors_count"] > 32).mean() > 0.5
+    assert pipeline.compare(a, b, 32) == []
+
+
+@pytest.mark.parametrize("kd", [np.uint32, np.uint64])
+def test_update_steps_match_port(kd, gpu, port):
+    keys = gen.gaussian_keys(200000, kd)
+    root = np.array([0, 2 ** (3 * loader.max_level(kd))], dtype=kd)
+    ta, ca = root.copy(), np.array([keys.size], dtype=np.uint32)
+    tb, cb = ta.copy(), ca.copy()
+    for _ in range(12):
+        ta, ca, conv_a = port.update_octree(keys, 16, ta, ca)
+        tb, cb, conv_b = gpu.update_octree(keys, 16, tb, cb)
+        assert np.array_equal(ta, tb) and np.array_equal(ca, cb) and conv_a == conv_b
+        if conv_a:
+            break
+    assert conv_a
+
+
+@pytest.mark.parametrize("kd", [np.uint32, np.uint64])
+@pytest.mark.parametrize("n", [0, 1, 31, 4096, 4097, 100003, 3000000])
+def test_sort_sizes(kd, n, gpu):
+    """ragged / empty sizes; stability; permutation and keys bit-exact against numpy's stable sort"""
+    rng = np.random.default_rng(n)
+    bits = 30 if kd == np.uint32 else 63
+    keys = rng.integers(0, 2 ** bits, n, dtype=np.uint64).astype(kd)
+    if n > 10:
+        keys[rng.integers(0, n, n // 3)] = keys[0]          # heavy duplicates
+        keys[rng.integers(0, n, 5)] = 2 ** bits               # removeKey sorts last
+    sk, order = gpu.sort_by_key(keys)
+    ref = np.argsort(keys, kind="stable").astype(np.uint32)
+    assert np.array_equal(order, ref) and np.array_equal(sk, keys[ref])
+    # re-sort with an existing payload (updateMap)
+    if n:
+        vals = rng.integers(0, 2 ** 31, n).astype(np.uint32)
+        sk2, v2 = gpu.sort_by_key(keys, vals)
+        assert np.array_equal(sk2, keys[ref]) and np.array_equal(v2, vals[ref])
+
+
+def test_scan_and_minmax(gpu):
+    import torch
+    from cornerstone_octree_b200 import ops
+    rng = np.random.default_rng(1)
+    for n in (1, 7, 2048, 2049, 1000003):
+        v = rng.integers(0, 1000, n).astype(np.uint32)
+        d = torch.from_numpy(v.view(np.int32)).cuda()
+        ex = ops.exclusive_scan(d, 5).cpu().numpy().view(np.uint32)
+        inc = ops.inclusive_scan(d).cpu().numpy().view(np.uint32)
+        cs = np.cumsum(v, dtype=np.uint64).astype(np.uint32)
+        assert np.array_equal(inc, cs) and np.array_equal(ex, (cs - v + 5).astype(np.uint32))
+    for fd in (np.float32, np.float64):
+        x, y, z = gen.gaussian(100001, (-3, 2), fd)
+        mm = ops.minmax3(*(torch.from_numpy(a).cuda() for a in (x, y, z)))
+        assert list(mm) == [x.min(), x.max(), y.min(), y.max(), z.min(), z.max()]
+
+
+def test_gather_multi_and_scatter(gpu):
+    import torch
+    from cornerstone_octree_b200 import ops
+    rng = np.random.default_rng(2)
+    n = 100001
+    perm = rng.permutation(n).astype(np.int32)
+    arrs = [rng.random(n), rng.random(n).astype(np.float32), rng.integers(0, 2 ** 62, n), rng.random(n)]
+    d = [torch.from_numpy(a).cuda() for a in arrs]
+    out = ops.gather_multi(torch.from_numpy(perm).cuda(), d)
+    for a, o in zip(arrs, out):
+        assert np.array_equal(o.cpu().numpy(), a[perm])
+    back = torch.empty_like(d[0])
+    ops.scatter(torch.from_numpy(perm).cuda(), out[0], back)
+    assert np.array_equal(back.cpu().numpy(), arrs[0])
