@@ -127,3 +127,35 @@ def test_gather_multi_and_scatter(gpu):
     back = torch.empty_like(d[0])
     ops.scatter(torch.from_numpy(perm).cuda(), out[0], back)
     assert np.array_equal(back.cpu().numpy(), arrs[0])
+
+
+@pytest.mark.parametrize("offset", [0.0, 1.0e6])
+@pytest.mark.parametrize("bnd", [(0, 0, 0), (1, 1, 1)])
+def test_neighbors_on_the_radius(offset, bnd, gpu, port):
+    """Lattice particles with 2h an exact multiple of the spacing: many pairs sit EXACTLY on the search radius
+    (excluded by the strict <) and many more within a few ulps of it.  The float32 filter of the double kernel
+    must hand every such pair to the exact path; with `offset` the coordinates are large, so the filter's
+    relative coordinates matter."""
+    m = 24
+    g = (np.arange(m) + 0.5) / m
+    X, Y, Z = np.meshgrid(g, g, g, indexing="ij")
+    rng = np.random.default_rng(3)
+    perm = rng.permutation(m ** 3)
+    x, y, z = (np.ascontiguousarray(a.ravel()[perm]) + offset for a in (X, Y, Z))
+    h = np.full(x.size, 1.0 / m)           # 2h = 2 spacings: (2,0,0)-type pairs have d2 == r2 in exact arithmetic
+    h[::3] = 0.5 * np.sqrt(5.0) / m        # r2 = 5 a^2: (2,1,0)-type pairs on the radius, inexact in binary
+    box = loader.make_box((offset, offset + 1.0), bnd, np.float64)
+    a = pipeline.run(port, 1, x, y, z, h, box, np.uint64, 16, 64)
+    b = pipeline.run(gpu, 1, x, y, z, h, box, np.uint64, 16, 64)
+    assert pipeline.compare(a, b, 64) == []
+    assert a["neighbors_count"].min() >= 6
+
+
+def test_neighbors_tiny_and_huge_h(gpu, port):
+    """h far below float32 range relative to the box (exact-only lanes) and h of the order of the box"""
+    x, y, z, h, box = make_case("gaussian", 8000, np.float64, (0, 0, 0))
+    h[::2] = 1e-20
+    h[1::7] = 0.4
+    a = pipeline.run(port, 1, x, y, z, h, box, np.uint64, 16, 200)
+    b = pipeline.run(gpu, 1, x, y, z, h, box, np.uint64, 16, 200)
+    assert pipeline.compare(a, b, 200) == []
