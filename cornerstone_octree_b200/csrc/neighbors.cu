@@ -34,6 +34,9 @@
 namespace csb
 {
 
+#ifndef NB_MINBLOCKS
+#define NB_MINBLOCKS 6
+#endif
 constexpr int kNbWarps     = 4;
 constexpr int kNbThreads   = kNbWarps * 32;
 constexpr int kNbStack     = 160; // >= 7 * 21 + 1 entries can be pending at any time
@@ -163,7 +166,7 @@ __device__ inline bool exactNode(const NbParams<T>& p, int idx, T xi, T yi, T zi
 }
 
 template<class T, bool AnyPbc>
-__global__ void __launch_bounds__(kNbThreads, 6) findNeighborsKernel(NbParams<T> p)
+__global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(NbParams<T> p)
 {
     constexpr bool F = NbFilter<T>::value;
     __shared__ NbWarpSmem smemAll[kNbWarps];
@@ -511,7 +514,7 @@ int findNeighbors(const T* x, const T* y, const T* z, const T* h, uint32_t first
                   sizes,     neighbors, neighborsCount, firstId, lastId,       ngmax,          ext,    makeDBox<T>(box)};
     bool anyPbc       = p.box.pbc[0] || p.box.pbc[1] || p.box.pbc[2];
     uint32_t groups   = (lastId - firstId + 31u) / 32u;
-    unsigned blocks   = gridFor(groups, kNbWarps, 6);
+    unsigned blocks   = gridFor(groups, kNbWarps, NB_MINBLOCKS);
     cudaStream_t s    = asStream(stream);
     if (anyPbc) findNeighborsKernel<T, true><<<blocks, kNbThreads, 0, s>>>(p);
     else findNeighborsKernel<T, false><<<blocks, kNbThreads, 0, s>>>(p);
