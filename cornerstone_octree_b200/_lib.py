@@ -33,6 +33,13 @@ if not os.path.exists(LIB_PATH):
         "cornerstone_octree_b200: %s not found. Build it with `python -c 'import __graft_entry__ as g; g.build()'` "
         "(make -C cornerstone_octree_b200/csrc). There is no CPU fallback." % LIB_PATH)
 
+# libcstone_b200.so links libnccl.so.2.  torch bundles a newer NCCL under the same soname: load torch's copy first
+# so that both share one NCCL (loading the system copy first would break `import torch` afterwards).
+try:
+    import torch  # noqa: F401
+except ImportError:  # pure C users of the library link the system NCCL
+    pass
+
 lib = C.CDLL(LIB_PATH)
 
 _vp, _sz, _i, _u32, _u64, _i32, _f = C.c_void_p, C.c_size_t, C.c_int, C.c_uint32, C.c_uint64, C.c_int32, C.c_float
@@ -103,3 +110,43 @@ def call(name, *args):
 
 def launch_count():
     return int(lib.cstone_b200_launch_count())
+
+
+# ------------------------------------------------------------------------------------------------ domain engine
+# include/cstone_b200_domain.h
+_i64 = C.c_int64
+lib.cstone_b200_nccl_unique_id.restype = _i
+lib.cstone_b200_nccl_unique_id.argtypes = [_vp]
+lib.cstone_b200_nccl_comm_init.restype = _i
+lib.cstone_b200_nccl_comm_init.argtypes = [_vp, _i, _i, C.POINTER(_vp)]
+lib.cstone_b200_nccl_comm_destroy.restype = _i
+lib.cstone_b200_nccl_comm_destroy.argtypes = [_vp]
+_DOMAIN_PROTOS = {
+    "create": (_vp, [_i, _i, C.c_uint, C.c_uint, _f, _vp]),
+    "destroy": (None, [_vp]),
+    "set_comm": (_i, [_vp, _vp]),
+    "sync_begin": (_i64, [_vp, _u64, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "sync_finish": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "exchange_halos": (_i, [_vp, _i, _vp, _vp]),
+    "info": (_i, [_vp, _vp]),
+    "box": (_i, [_vp, _vp]),
+    "tree_view": (_i, [_vp, _vp]),
+    "global_tree": (_i, [_vp, _vp, _vp, _vp]),
+    "find_neighbors": (_i, [_vp, _vp, _vp, _vp, _vp, _u32, _vp, _vp]),
+}
+DOMAIN_EXPORTED = ["nccl_unique_id", "nccl_comm_init", "nccl_comm_destroy", "host_assignment_k32",
+                   "host_assignment_k64", "host_limit_box_shrinking_f32", "host_limit_box_shrinking_f64"]
+for ks in ("k32", "k64"):
+    for ts in ("f32", "f64"):
+        for _name, (_res, _args) in _DOMAIN_PROTOS.items():
+            _fn = getattr(lib, "cstone_b200_domain_%s_%s_%s" % (_name, ks, ts))
+            _fn.restype = _res
+            _fn.argtypes = _args
+            DOMAIN_EXPORTED.append("domain_%s_%s_%s" % (_name, ks, ts))
+    _fn = getattr(lib, "cstone_b200_host_assignment_" + ks)
+    _fn.restype = _i
+    _fn.argtypes = [_i, _vp, _vp, _i32, _vp, _vp, _vp]
+for ts in ("f32", "f64"):
+    _fn = getattr(lib, "cstone_b200_host_limit_box_shrinking_" + ts)
+    _fn.restype = None
+    _fn.argtypes = [_vp, _vp, _vp]

@@ -1,0 +1,1080 @@
+/*
+ * domain.cu — the engine behind cstone::Domain<KeyType,T,GpuTag>: one rank's part of the SFC-sharded domain.
+ *
+ * Replaces the orchestration of Domain::sync [ref: domain/domain.hpp:196-243, :492-604], GlobalAssignmentGpu
+ * [ref: domain/assignment_gpu.cuh:78-175], exchangeParticlesGpu [ref: domain/domaindecomp_mpi_gpu.cuh:85-185] and
+ * Halos / haloExchangeGpu [ref: halos/halos.hpp:127-251, halos/exchange_halos_gpu.cuh:34-119].
+ *
+ * B200 design
+ *  - all particle data stay in HBM; the engine owns SFC-ordered copies and hands them back in sync_finish;
+ *  - the replicated global tree is updated on every GPU redundantly: local leaf counts -> ncclAllReduce(SUM) ->
+ *    max(local, sum) guard [ref: tree/update_mpi.hpp:47-69] -> same deterministic rebalance everywhere;
+ *  - particle exchange: the local particles are sorted by key, ranks own contiguous key ranges, so ONE gather puts
+ *    every outgoing message in place; messages go out as one NCCL group of send/recv per array over NVLink and are
+ *    received straight into their final slots (no staging, no unpack kernel);
+ *  - halo discovery: every rank publishes the integer halo boxes of its surface leaves (ncclAllGather), every owner
+ *    tests the foreign boxes against ITS OWN leaves (reverse collision, same integer overlap test as findHalos) and
+ *    sends the particles of the leaves that are hit; received halos land left / right of the assigned range in rank
+ *    order, which is SFC order.  The send lists are replayed by exchange_halos for arbitrary arrays.
+ *  - the search tree handed to findNeighbors is the cornerstone leaf array over assigned + halo keys
+ *    (bucketSizeFocus), linked and with node centres.
+ */
+#include <nccl.h>
+
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "../../include/cstone_b200_domain.h"
+#include "halo_box.cuh"
+#include "scan.cuh"
+#include "domain_host.hpp"
+
+namespace csb
+{
+
+#define CSB_NCCL(expr)                                                                                                 \
+    do                                                                                                                 \
+    {                                                                                                                  \
+        ncclResult_t r_ = (expr);                                                                                      \
+        if (r_ != ncclSuccess) return CSTONE_E_NCCL;                                                                   \
+    } while (0)
+
+#define CSB_TRY(expr)                                                                                                  \
+    do                                                                                                                 \
+    {                                                                                                                  \
+        int tryStatus_ = (expr);                                                                                       \
+        if (tryStatus_ != 0) return tryStatus_;                                                                        \
+    } while (0)
+
+//! grow-only device buffer (capacity grows by 5 %, as the reference's reallocate policy, util/reallocate.hpp:37-66)
+struct DevBuf
+{
+    void* p      = nullptr;
+    size_t bytes = 0;
+    int reserve(size_t need, bool keep = false, cudaStream_t s = 0)
+    {
+        if (need <= bytes) return 0;
+        size_t cap = size_t(double(need) * 1.05) + 256;
+        void* q    = nullptr;
+        CSB_CUDA(cudaMalloc(&q, cap));
+        if (keep && p && bytes)
+        {
+            CSB_CUDA(cudaMemcpyAsync(q, p, bytes, cudaMemcpyDeviceToDevice, s));
+            CSB_CUDA(cudaStreamSynchronize(s));
+        }
+        if (p) cudaFree(p);
+        p     = q;
+        bytes = cap;
+        return 0;
+    }
+    template<class U>
+    U* as() const
+    {
+        return reinterpret_cast<U*>(p);
+    }
+    ~DevBuf()
+    {
+        if (p) cudaFree(p);
+    }
+    DevBuf()                         = default;
+    DevBuf(const DevBuf&)            = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+};
+
+// ------------------------------------------------------------------------------------------------
+// small kernels of the engine
+// ------------------------------------------------------------------------------------------------
+//! out[q] = index of the first key >= queries[q]   [ref: primitives/primitives_gpu.h lowerBoundGpu]
+template<class K>
+__global__ void lowerBoundQueriesKernel(const K* __restrict__ keys, uint32_t n, const K* __restrict__ queries, int nq,
+                                        uint32_t* __restrict__ out)
+{
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    K v         = queries[q];
+    uint32_t lo = 0, len = n;
+    while (len > 0)
+    {
+        uint32_t half = len >> 1;
+        bool right    = keys[lo + half] < v;
+        lo            = right ? lo + half + 1 : lo;
+        len           = right ? len - half - 1 : half;
+    }
+    out[q] = lo;
+}
+
+//! counts[i] = max(local[i], reduced[i])   [ref: tree/update_mpi.hpp:62-65]
+__global__ void maxMergeKernel(const uint32_t* __restrict__ local, uint32_t* __restrict__ reduced, int n)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        reduced[i] = max(local[i], reduced[i]);
+}
+
+struct IBox6
+{
+    int v[6]; // xmin,xmax,ymin,ymax,zmin,zmax (integer cell coordinates, may exceed [0,2^maxLevel] for PBC)
+};
+
+
+// ------------------------------------------------------------------------------------------------
+// type dispatch onto the C ABI of the kernels (same shared library)
+// ------------------------------------------------------------------------------------------------
+template<class K, class T>
+struct Api
+{
+    static constexpr bool k64 = sizeof(K) == 8, f64 = sizeof(T) == 8;
+    using CBox = typename BoxT<T>::type;
+
+    static int keys(const T* x, const T* y, const T* z, K* keys, size_t n, const CBox* box, void* s)
+    {
+        if constexpr (k64 && f64) return cstone_b200_compute_sfc_keys_k64_f64(CSTONE_SFC_HILBERT, x, y, z, keys, n, box, s);
+        else if constexpr (k64 && !f64) return cstone_b200_compute_sfc_keys_k64_f32(CSTONE_SFC_HILBERT, x, y, z, keys, n, box, s);
+        else if constexpr (!k64 && f64) return cstone_b200_compute_sfc_keys_k32_f64(CSTONE_SFC_HILBERT, x, y, z, keys, n, box, s);
+        else return cstone_b200_compute_sfc_keys_k32_f32(CSTONE_SFC_HILBERT, x, y, z, keys, n, box, s);
+    }
+    static uint64_t sortTemp(uint64_t n)
+    {
+        if constexpr (k64) return cstone_b200_sort_by_key_temp_bytes_k64(n);
+        else return cstone_b200_sort_by_key_temp_bytes_k32(n);
+    }
+    static int sort(K* keys, uint32_t* vals, K* kb, uint32_t* vb, size_t n, void* temp, uint64_t tb, int iota, void* s)
+    {
+        if constexpr (k64) return cstone_b200_sort_by_key_k64(keys, vals, kb, vb, n, temp, tb, iota, s);
+        else return cstone_b200_sort_by_key_k32(keys, vals, kb, vb, n, temp, tb, iota, s);
+    }
+    static int updateOctree(const K* f, const K* l, unsigned bucket, K* ta, K* tb, uint32_t* counts, int32_t* ops,
+                            int32_t cap, int32_t* n, int32_t* conv, void* temp, void* s)
+    {
+        if constexpr (k64) return cstone_b200_update_octree_k64(f, l, bucket, 0xFFFFFFFFu, ta, tb, counts, ops, cap, n, conv, temp, s);
+        else return cstone_b200_update_octree_k32(f, l, bucket, 0xFFFFFFFFu, ta, tb, counts, ops, cap, n, conv, temp, s);
+    }
+    static int nodeCounts(const K* tree, uint32_t* counts, int32_t n, const K* f, const K* l, void* s)
+    {
+        if constexpr (k64) return cstone_b200_compute_node_counts_k64(tree, counts, n, f, l, 0xFFFFFFFFu, 1, s);
+        else return cstone_b200_compute_node_counts_k32(tree, counts, n, f, l, 0xFFFFFFFFu, 1, s);
+    }
+    static uint64_t octreeTemp(int32_t L)
+    {
+        if constexpr (k64) return cstone_b200_build_octree_temp_bytes_k64(L);
+        else return cstone_b200_build_octree_temp_bytes_k32(L);
+    }
+    static int buildOctree(const K* leaves, int32_t L, K* prefixes, int32_t* co, int32_t* parents, int32_t* lr,
+                           int32_t* itl, int32_t* lti, void* temp, uint64_t tb, void* s)
+    {
+        if constexpr (k64) return cstone_b200_build_octree_k64(leaves, L, prefixes, co, parents, lr, itl, lti, temp, tb, s);
+        else return cstone_b200_build_octree_k32(leaves, L, prefixes, co, parents, lr, itl, lti, temp, tb, s);
+    }
+    static int geoCenters(const K* prefixes, int32_t M, T* centers, T* sizes, const CBox* box, void* s)
+    {
+        if constexpr (k64 && f64) return cstone_b200_compute_geo_centers_k64_f64(CSTONE_SFC_HILBERT, prefixes, M, centers, sizes, box, s);
+        else if constexpr (k64 && !f64) return cstone_b200_compute_geo_centers_k64_f32(CSTONE_SFC_HILBERT, prefixes, M, centers, sizes, box, s);
+        else if constexpr (!k64 && f64) return cstone_b200_compute_geo_centers_k32_f64(CSTONE_SFC_HILBERT, prefixes, M, centers, sizes, box, s);
+        else return cstone_b200_compute_geo_centers_k32_f32(CSTONE_SFC_HILBERT, prefixes, M, centers, sizes, box, s);
+    }
+    static int minmax(const T* x, const T* y, const T* z, size_t n, T* out6, void* temp, void* s)
+    {
+        if constexpr (f64) return cstone_b200_minmax3_f64(x, y, z, n, out6, temp, s);
+        else return cstone_b200_minmax3_f32(x, y, z, n, out6, temp, s);
+    }
+    static int haloRadii(const T* h, const uint32_t* seg, size_t n, float scale, float* radii, void* s)
+    {
+        if constexpr (f64) return cstone_b200_halo_radii_f64(h, seg, n, scale, radii, s);
+        else return cstone_b200_halo_radii_f32(h, seg, n, scale, radii, s);
+    }
+    static int neighbors(const T* x, const T* y, const T* z, const T* h, uint32_t first, uint32_t last, const CBox* box,
+                         const int32_t* co, const int32_t* itl, const uint32_t* layout, const T* centers, const T* sizes,
+                         uint32_t ngmax, uint32_t* nb, uint32_t* nc, void* s)
+    {
+        if constexpr (f64) return cstone_b200_find_neighbors_f64(x, y, z, h, first, last, box, co, itl, layout, centers, sizes, 1.0f, ngmax, nb, nc, s);
+        else return cstone_b200_find_neighbors_f32(x, y, z, h, first, last, box, co, itl, layout, centers, sizes, 1.0f, ngmax, nb, nc, s);
+    }
+};
+
+//! device-resident cornerstone leaf array with ping-pong buffers  [ref: tree/update_gpu.cuh:58-82]
+template<class K, class T>
+struct LeafArrayDev
+{
+    DevBuf treeA, treeB, counts, nodeOps, temp;
+    int capacity = 0, numNodes = 0;
+
+    int ensure(int cap, cudaStream_t s)
+    {
+        if (cap <= capacity) return 0;
+        cap = int(cap * 1.05) + 64;
+        CSB_TRY(treeA.reserve(sizeof(K) * (size_t(cap) + 1), true, s));
+        CSB_TRY(treeB.reserve(sizeof(K) * (size_t(cap) + 1)));
+        CSB_TRY(counts.reserve(4 * size_t(cap), true, s));
+        CSB_TRY(nodeOps.reserve(4 * (size_t(cap) + 1)));
+        CSB_TRY(temp.reserve(cstone_b200_scan_temp_bytes(uint64_t(cap) + 1) + 1024));
+        capacity = cap;
+        return 0;
+    }
+    //! reset to the root node holding `count` particles
+    int reset(uint32_t count, cudaStream_t s)
+    {
+        CSB_TRY(ensure(1024, s));
+        K root[2] = {K(0), nodeRange<K>(0)};
+        CSB_CUDA(cudaMemcpyAsync(treeA.p, root, sizeof(root), cudaMemcpyHostToDevice, s));
+        CSB_CUDA(cudaMemcpyAsync(counts.p, &count, 4, cudaMemcpyHostToDevice, s));
+        CSB_CUDA(cudaStreamSynchronize(s));
+        numNodes = 1;
+        return 0;
+    }
+    //! one rebalance + recount step [ref: tree/csarray.hpp:429-448]; counts must hold the counts to decide on
+    int update(const K* first, const K* last, unsigned bucket, bool& converged, cudaStream_t s)
+    {
+        for (;;)
+        {
+            int32_t n = numNodes, conv = 0;
+            int st = Api<K, T>::updateOctree(first, last, bucket, treeA.as<K>(), treeB.as<K>(), counts.as<uint32_t>(),
+                                             nodeOps.as<int32_t>(), capacity, &n, &conv, temp.p, s);
+            if (st == CSTONE_E_CAPACITY)
+            {
+                CSB_TRY(ensure(n, s));
+                continue;
+            }
+            if (st) return st;
+            numNodes  = n;
+            converged = conv != 0;
+            return 0;
+        }
+    }
+};
+
+
+// ------------------------------------------------------------------------------------------------
+// halo discovery kernels (multi-rank only)
+// ------------------------------------------------------------------------------------------------
+/*! halo boxes of the local leaves that reach outside the key range [lowest, highest) of this rank
+ *  [ref: traversal/collisions.hpp:78-105: same box and the same containedIn early-out as findHalos] */
+template<class K, class T>
+__global__ void __launch_bounds__(128) surfaceBoxesKernel(const uint16_t* __restrict__ enc,
+                                                          const uint16_t* __restrict__ dec,
+                                                          const K* __restrict__ leaves,
+                                                          const uint32_t* __restrict__ counts,
+                                                          const float* __restrict__ radii,
+                                                          int numLeaves,
+                                                          K lowest,
+                                                          K highest,
+                                                          DBox<T> box,
+                                                          IBox6* __restrict__ out,
+                                                          uint32_t capacity,
+                                                          uint32_t* __restrict__ numOut)
+{
+    for (int leaf = blockIdx.x * blockDim.x + threadIdx.x; leaf < numLeaves; leaf += gridDim.x * blockDim.x)
+    {
+        if (counts[leaf] == 0) continue;
+        K start = leaves[leaf], end = leaves[leaf + 1];
+        if (start < lowest || end > highest) continue; // not one of my leaves
+        IBox nodeBox = sfcIBox<K>(CSTONE_SFC_HILBERT, dec, start, treeLevel<K>(K(end - start)));
+        IBox halo    = makeHaloBox<K, T>(nodeBox, radii[leaf], box);
+        if (containedIn<K>(CSTONE_SFC_HILBERT, enc, lowest, highest, halo)) continue;
+        uint32_t slot = atomicAdd(numOut, 1u);
+        if (slot < capacity)
+        {
+            IBox6 b;
+#pragma unroll
+            for (int d = 0; d < 3; ++d)
+                b.v[2 * d] = halo.lo[d], b.v[2 * d + 1] = halo.hi[d];
+            out[slot] = b;
+        }
+    }
+}
+
+/*! reverse collision: which of MY non-empty leaves does a foreign halo box overlap?  One thread per foreign box,
+ *  depth-first over my linked tree, nodes outside my key range are skipped.  flags[srcRank * numLeaves + leaf] = 1 */
+template<class K>
+__global__ void __launch_bounds__(128) reverseCollisionKernel(const uint16_t* __restrict__ dec,
+                                                              const K* __restrict__ prefixes,
+                                                              const int* __restrict__ childOffsets,
+                                                              const int* __restrict__ internalToLeaf,
+                                                              const uint32_t* __restrict__ counts,
+                                                              int numLeaves,
+                                                              K lowest,
+                                                              K highest,
+                                                              const IBox6* __restrict__ boxes,  // [numRanks][stride]
+                                                              const uint32_t* __restrict__ numBoxes, // [numRanks]
+                                                              uint32_t stride,
+                                                              int numRanks,
+                                                              int myRank,
+                                                              unsigned char* __restrict__ flags)
+{
+    const int src = blockIdx.y;
+    if (src == myRank) return;
+    const uint32_t nb = min(numBoxes[src], stride);
+    for (uint32_t b = blockIdx.x * blockDim.x + threadIdx.x; b < nb; b += gridDim.x * blockDim.x)
+    {
+        IBox6 fb = boxes[size_t(src) * stride + b];
+        IBox halo;
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+            halo.lo[d] = fb.v[2 * d], halo.hi[d] = fb.v[2 * d + 1];
+        unsigned char* myFlags = flags + size_t(src) * numLeaves;
+
+        auto descend = [&](int idx) -> bool
+        {
+            K prefix       = prefixes[idx];
+            unsigned level = decodePrefixLength<K>(prefix) / 3u;
+            K nodeStart    = decodePlaceholderBit<K>(prefix);
+            K nodeEnd      = nodeStart + nodeRange<K>(level);
+            if (nodeEnd <= lowest || nodeStart >= highest) return false; // nothing of mine below this node
+            return overlapBoxes<K>(sfcIBox<K>(CSTONE_SFC_HILBERT, dec, nodeStart, level), halo);
+        };
+        auto hitLeaf = [&](int idx)
+        {
+            int leaf = internalToLeaf[idx];
+            if (counts[leaf]) myFlags[leaf] = 1;
+        };
+
+        if (!descend(0)) continue;
+        if (childOffsets[0] == 0)
+        {
+            hitLeaf(0);
+            continue;
+        }
+        int stack[160];
+        int sp      = 0;
+        stack[sp++] = 0;
+        int node    = 0;
+        do
+        {
+            int firstChild = childOffsets[node];
+            for (int o = 0; o < 8; ++o)
+            {
+                int child = firstChild + o;
+                if (!descend(child)) continue;
+                if (childOffsets[child] == 0) hitLeaf(child);
+                else stack[sp++] = child;
+            }
+            node = stack[--sp];
+        } while (node != 0);
+    }
+}
+
+//! per (peer, leaf): number of particles to send = flag ? count : 0 (scanned afterwards per peer)
+struct LoadFlaggedCount
+{
+    const unsigned char* flags;
+    const uint32_t* counts;
+    int numLeaves;
+    __device__ uint32_t operator()(size_t i) const
+    {
+        return (int(i) < numLeaves && flags[i]) ? counts[i] : 0u;
+    }
+};
+
+//! expand the flagged leaves of one peer into particle indices (positions in the SFC-ordered assigned arrays)
+__global__ void __launch_bounds__(256) expandSendListKernel(const unsigned char* __restrict__ flags,
+                                                            const uint32_t* __restrict__ layout,
+                                                            const uint32_t* __restrict__ sendScan,
+                                                            int numLeaves,
+                                                            uint32_t* __restrict__ sendIdx)
+{
+    int warpsTotal = (gridDim.x * blockDim.x) >> 5;
+    for (int leaf = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; leaf < numLeaves; leaf += warpsTotal)
+    {
+        if (!flags[leaf]) continue;
+        uint32_t a = layout[leaf], b = layout[leaf + 1], o = sendScan[leaf];
+        for (uint32_t k = laneId(); k < b - a; k += 32u)
+            sendIdx[o + k] = a + k;
+    }
+}
+
+//! dst[i] = src[idx[i] + offset] for 4- or 8-byte elements (pack of halo messages)
+template<class E>
+__global__ void __launch_bounds__(256)
+    packKernel(const uint32_t* __restrict__ idx, uint32_t n, uint32_t offset, const E* __restrict__ src, E* __restrict__ dst)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        dst[i] = src[idx[i] + offset];
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// the engine
+// ------------------------------------------------------------------------------------------------
+constexpr int kMaxProps = 12;
+
+template<class K, class T>
+class Engine
+{
+public:
+    using CBox = typename BoxT<T>::type;
+
+    Engine(int rank, int nRanks, unsigned bucket, unsigned bucketFocus, float theta, const CBox& box)
+        : rank_(rank), nRanks_(nRanks), bucket_(bucket), bucketFocus_(bucketFocus), theta_(theta), box_(box)
+    {
+    }
+    void setComm(void* c) { comm_ = reinterpret_cast<ncclComm_t>(c); }
+
+    int64_t syncBegin(uint64_t nIn, const T* x, const T* y, const T* z, const T* h, int nprops, const void* const* props,
+                      const int* propBytes);
+    int syncFinish(K* keys, T* x, T* y, T* z, T* h, void* const* props);
+    int exchangeHalos(int narrays, void* const* arrays, const int* elemBytes);
+    int findNeighbors(const T* x, const T* y, const T* z, const T* h, uint32_t ngmax, uint32_t* nb, uint32_t* nc) const;
+
+    void info(int64_t* o) const
+    {
+        o[0] = start_, o[1] = end_, o[2] = nTotal_, o[3] = search_.numNodes;
+        o[4] = search_.numNodes + (search_.numNodes - 1) / 7, o[5] = global_.numNodes;
+        o[6] = nHaloSend_, o[7] = nTotal_ - (end_ - start_);
+    }
+    const CBox& box() const { return box_; }
+    void treeView(const void** p) const
+    {
+        p[0] = search_.treeA.p, p[1] = search_.counts.p, p[2] = layout_.p, p[3] = prefixes_.p, p[4] = childOffsets_.p;
+        p[5] = internalToLeaf_.p, p[6] = leafToInternal_.p, p[7] = levelRange_.p, p[8] = centers_.p, p[9] = sizes_.p;
+    }
+    void globalTree(const K** l, const uint32_t** c, const K** a) const
+    {
+        *l = hGlobalLeaves_.data(), *c = hGlobalCounts_.data(), *a = boundaries_.data();
+    }
+
+private:
+    int updateBox(const T* x, const T* y, const T* z, size_t n);
+    int updateGlobalTree(const K* keys, size_t n);
+    int allreduceCounts();
+    int linkTree(LeafArrayDev<K, T>& tree, bool withCenters);
+    int convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n, bool& fresh);
+    int discoverHalos();
+    int hostCounts(const uint32_t* dev, int n, std::vector<uint32_t>& out)
+    {
+        out.resize(n);
+        CSB_CUDA(cudaMemcpyAsync(out.data(), dev, size_t(n) * 4, cudaMemcpyDeviceToHost, s_));
+        CSB_CUDA(cudaStreamSynchronize(s_));
+        return 0;
+    }
+    int gatherMulti(const uint32_t* map, size_t n, int na, const void* const* src, void* const* dst, const int* eb)
+    {
+        return cstone_b200_gather_multi(map, n, na, src, dst, eb, s_);
+    }
+
+    int rank_, nRanks_;
+    unsigned bucket_, bucketFocus_;
+    float theta_;
+    CBox box_;
+    bool firstCall_   = true;
+    ncclComm_t comm_  = nullptr;
+    cudaStream_t s_   = nullptr; // legacy default stream: ordered with the caller's default-stream work
+
+    // particle state
+    uint64_t start_ = 0, end_ = 0, nTotal_ = 0, nAssigned_ = 0, nHaloSend_ = 0;
+    int nprops_ = 0;
+    int propBytes_[kMaxProps] = {0};
+
+    // scratch + SFC-ordered arrays
+    DevBuf keys_, keyBuf_, order_, valBuf_, sortTemp_, mmTemp_, small_;
+    DevBuf pack_[4 + kMaxProps], recv_[4 + kMaxProps], fin_[4 + kMaxProps];
+    DevBuf skeys_, fkeys_, shAssigned_;
+
+    // trees
+    LeafArrayDev<K, T> global_, focus_, search_;
+    bool globalFresh_ = true, focusFresh_ = true, searchFresh_ = true;
+    std::vector<K> hGlobalLeaves_, boundaries_, oldBoundaries_;
+    std::vector<uint32_t> hGlobalCounts_, rankCounts_;
+    DevBuf prefixes_, childOffsets_, parents_, levelRange_, internalToLeaf_, leafToInternal_, centers_, sizes_, layout_;
+    DevBuf octTemp_, scanTemp_, radii_;
+
+    // halo exchange pattern
+    DevBuf surf_, allSurf_, nSurf_, flags_, sendScan_, sendIdx_, haloPack_;
+    std::vector<uint32_t> haloSendCount_, haloSendOffset_, haloRecvCount_, haloRecvOffset_;
+};
+
+template<class K, class T>
+int Engine<K, T>::updateBox(const T* x, const T* y, const T* z, size_t n)
+{
+    // [ref: sfc/box_mpi.hpp:85-119 makeGlobalBox, domain/assignment.hpp:80-82]
+    T mm[6];
+    CSB_TRY(mmTemp_.reserve(cstone_b200_minmax_temp_bytes() + 64));
+    if (n) CSB_TRY((Api<K, T>::minmax(x, y, z, n, mm, mmTemp_.p, s_)));
+    else
+        for (int d = 0; d < 3; ++d)
+            mm[2 * d] = T(INFINITY), mm[2 * d + 1] = -T(INFINITY);
+    bool pbc[3], anyOpen = false;
+    for (int d = 0; d < 3; ++d)
+    {
+        pbc[d] = box_.boundaries[d] == CSTONE_BOUNDARY_PERIODIC;
+        if (pbc[d]) mm[2 * d] = box_.limits[2 * d], mm[2 * d + 1] = box_.limits[2 * d + 1];
+        anyOpen |= !pbc[d];
+    }
+    if (anyOpen && nRanks_ > 1)
+    {
+        T v[6] = {mm[0], -mm[1], mm[2], -mm[3], mm[4], -mm[5]};
+        CSB_TRY(small_.reserve(4096));
+        CSB_CUDA(cudaMemcpyAsync(small_.p, v, sizeof(v), cudaMemcpyHostToDevice, s_));
+        CSB_NCCL(ncclAllReduce(small_.p, small_.p, 6, sizeof(T) == 8 ? ncclDouble : ncclFloat, ncclMin, comm_, s_));
+        CSB_CUDA(cudaMemcpyAsync(v, small_.p, sizeof(v), cudaMemcpyDeviceToHost, s_));
+        CSB_CUDA(cudaStreamSynchronize(s_));
+        for (int d = 0; d < 3; ++d)
+            mm[2 * d] = v[2 * d], mm[2 * d + 1] = -v[2 * d + 1];
+    }
+    T lim[6];
+    if (firstCall_)
+        for (int k = 0; k < 6; ++k)
+            lim[k] = mm[k];
+    else limitBoxShrinking<T>(mm, box_.limits, lim);
+    for (int d = 0; d < 3; ++d)
+    {
+        box_.limits[2 * d]     = lim[2 * d];
+        box_.limits[2 * d + 1] = lim[2 * d + 1];
+        box_.lengths[d]        = lim[2 * d + 1] - lim[2 * d];
+        box_.inv_lengths[d]    = T(1) / box_.lengths[d];
+    }
+    return 0;
+}
+
+template<class K, class T>
+int Engine<K, T>::allreduceCounts()
+{
+    if (nRanks_ == 1) return 0;
+    // [ref: tree/update_mpi.hpp:58-66] counts = max(local, Allreduce(SUM)(local))
+    int n = global_.numNodes;
+    CSB_TRY(small_.reserve(size_t(n) * 4 + 4096));
+    CSB_NCCL(ncclAllReduce(global_.counts.p, small_.p, n, ncclUint32, ncclSum, comm_, s_));
+    maxMergeKernel<<<gridFor(size_t(n), 256), 256, 0, s_>>>(global_.counts.template as<uint32_t>(),
+                                                          small_.template as<uint32_t>(), n);
+    CSB_LAUNCHED();
+    CSB_CUDA(cudaMemcpyAsync(global_.counts.p, small_.p, size_t(n) * 4, cudaMemcpyDeviceToDevice, s_));
+    return 0;
+}
+
+template<class K, class T>
+int Engine<K, T>::updateGlobalTree(const K* keys, size_t n)
+{
+    // [ref: domain/assignment.hpp:92-98] one update step per sync, iterated to convergence on the first call
+    if (globalFresh_)
+    {
+        // the root count must be the GLOBAL particle count so that every rank takes the same decisions
+        CSB_TRY(global_.reset(uint32_t(n), s_));
+        CSB_TRY(allreduceCounts());
+        globalFresh_ = false;
+        bool conv    = false;
+        for (int it = 0; it < 64 && !conv; ++it)
+        {
+            CSB_TRY(global_.update(keys, keys + n, bucket_, conv, s_));
+            CSB_TRY(allreduceCounts());
+        }
+    }
+    else
+    {
+        bool conv = false;
+        CSB_TRY(global_.update(keys, keys + n, bucket_, conv, s_));
+        CSB_TRY(allreduceCounts());
+    }
+    int L = global_.numNodes;
+    hGlobalLeaves_.resize(size_t(L) + 1);
+    hGlobalCounts_.resize(L);
+    CSB_CUDA(cudaMemcpyAsync(hGlobalLeaves_.data(), global_.treeA.p, sizeof(K) * (size_t(L) + 1), cudaMemcpyDeviceToHost, s_));
+    CSB_CUDA(cudaMemcpyAsync(hGlobalCounts_.data(), global_.counts.p, 4 * size_t(L), cudaMemcpyDeviceToHost, s_));
+    CSB_CUDA(cudaStreamSynchronize(s_));
+    return 0;
+}
+
+//! iterate a local tree to convergence on the given sorted keys (from the root on the first use)
+template<class K, class T>
+int Engine<K, T>::convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n, bool& fresh)
+{
+    if (fresh)
+    {
+        CSB_TRY(tree.reset(uint32_t(n), s_));
+        fresh = false;
+    }
+    else
+    {
+        // counts of the previous tree on the NEW keys steer the first rebalance step
+        CSB_TRY((Api<K, T>::nodeCounts(tree.treeA.template as<K>(), tree.counts.template as<uint32_t>(), tree.numNodes, keys,
+                                       keys + n, s_)));
+    }
+    bool conv = false;
+    for (int it = 0; it < 64 && !conv; ++it)
+        CSB_TRY(tree.update(keys, keys + n, bucketFocus_, conv, s_));
+    return 0;
+}
+
+template<class K, class T>
+int Engine<K, T>::linkTree(LeafArrayDev<K, T>& tree, bool withCenters)
+{
+    int L = tree.numNodes, M = L + (L - 1) / 7;
+    CSB_TRY(prefixes_.reserve(sizeof(K) * size_t(M)));
+    CSB_TRY(childOffsets_.reserve(4 * (size_t(M) + 1)));
+    CSB_TRY(parents_.reserve(4 * size_t(std::max(1, (M - 1) / 8))));
+    CSB_TRY(levelRange_.reserve(4 * 32));
+    CSB_TRY(internalToLeaf_.reserve(4 * size_t(M)));
+    CSB_TRY(leafToInternal_.reserve(4 * size_t(M)));
+    uint64_t tb = Api<K, T>::octreeTemp(L);
+    CSB_TRY(octTemp_.reserve(tb + 512));
+    CSB_TRY((Api<K, T>::buildOctree(tree.treeA.template as<K>(), L, prefixes_.template as<K>(), childOffsets_.template as<int32_t>(),
+                                    parents_.template as<int32_t>(), levelRange_.template as<int32_t>(),
+                                    internalToLeaf_.template as<int32_t>(), leafToInternal_.template as<int32_t>(), octTemp_.p,
+                                    octTemp_.bytes, s_)));
+    // layout = exclusive scan of the leaf counts (every leaf of this tree is present)
+    CSB_TRY(layout_.reserve(4 * (size_t(L) + 1)));
+    CSB_TRY(scanTemp_.reserve(cstone_b200_scan_temp_bytes(uint64_t(L) + 1) + 512));
+    CSB_TRY(cstone_b200_compute_node_layout(tree.counts.template as<uint32_t>(), nullptr, 0, L, L, layout_.template as<uint32_t>(),
+                                            scanTemp_.p, s_));
+    if (withCenters)
+    {
+        CSB_TRY(centers_.reserve(sizeof(T) * 3 * size_t(M)));
+        CSB_TRY(sizes_.reserve(sizeof(T) * 3 * size_t(M)));
+        CSB_TRY((Api<K, T>::geoCenters(prefixes_.template as<K>(), M, centers_.template as<T>(), sizes_.template as<T>(), &box_, s_)));
+    }
+    return 0;
+}
+
+
+template<class K, class T>
+int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z, const T* h, int nprops,
+                                const void* const* props, const int* propBytes)
+{
+    if (nprops < 0 || nprops > kMaxProps || (nIn && (!x || !y || !z || !h))) return CSTONE_E_INVALID_ARGUMENT;
+    if (nRanks_ > 1 && !comm_) return CSTONE_E_INVALID_ARGUMENT;
+    if (nIn >= (uint64_t(1) << 30)) return CSTONE_E_TOO_LARGE;
+    uint64_t inStart = 0, inEnd = nIn;
+    if (!firstCall_)
+    {
+        if (nIn != nTotal_) return CSTONE_E_SIZE_MISMATCH; // [ref: domain/domain.hpp:130-133]
+        inStart = start_, inEnd = end_;
+    }
+    for (int a = 0; a < nprops; ++a)
+        if ((propBytes[a] != 4 && propBytes[a] != 8) || !props[a]) return CSTONE_E_INVALID_ARGUMENT;
+    const size_t np = size_t(inEnd - inStart);
+    const int na    = 4 + nprops;
+    int eb[4 + kMaxProps];
+    const void* src[4 + kMaxProps];
+    eb[0] = eb[1] = eb[2] = eb[3] = int(sizeof(T));
+    src[0] = x + inStart, src[1] = y + inStart, src[2] = z + inStart, src[3] = h + inStart;
+    nprops_ = nprops;
+    for (int a = 0; a < nprops; ++a)
+    {
+        eb[4 + a]     = propBytes[a];
+        propBytes_[a] = propBytes[a];
+        src[4 + a]    = reinterpret_cast<const char*>(props[a]) + inStart * size_t(propBytes[a]);
+    }
+
+    // 1. global box
+    CSB_TRY(updateBox(x + inStart, y + inStart, z + inStart, np));
+
+    // 2. keys of the particles this rank holds, sorted, with the permutation [ref: domain/assignment.hpp:84-90]
+    auto reserveSort = [&](size_t n) -> int
+    {
+        CSB_TRY(keyBuf_.reserve(sizeof(K) * n + 256));
+        CSB_TRY(order_.reserve(4 * n + 256));
+        CSB_TRY(valBuf_.reserve(4 * n + 256));
+        CSB_TRY(sortTemp_.reserve((Api<K, T>::sortTemp(n)) + 256));
+        return 0;
+    };
+    CSB_TRY(keys_.reserve(sizeof(K) * np + 256));
+    CSB_TRY(reserveSort(np));
+    K* keys = keys_.template as<K>();
+    if (np)
+    {
+        CSB_CUDA(cudaMemsetAsync(keys, 0, sizeof(K) * np, s_));
+        CSB_TRY((Api<K, T>::keys(x + inStart, y + inStart, z + inStart, keys, np, &box_, s_)));
+        CSB_TRY((Api<K, T>::sort(keys, order_.template as<uint32_t>(), keyBuf_.template as<K>(), valBuf_.template as<uint32_t>(), np,
+                                 sortTemp_.p, sortTemp_.bytes, 1, s_)));
+    }
+
+    // 3. replicated global tree and the assignment of its leaves to ranks
+    CSB_TRY(updateGlobalTree(keys, np));
+    makeAssignment<K>(nRanks_, hGlobalLeaves_.data(), hGlobalCounts_.data(), global_.numNodes,
+                      oldBoundaries_.empty() ? nullptr : oldBoundaries_.data(), boundaries_, rankCounts_);
+    oldBoundaries_ = boundaries_;
+
+    void* dst[4 + kMaxProps];
+    if (nRanks_ == 1)
+    {
+        // every particle stays: one gather into the final arrays, no halos
+        nAssigned_ = np, start_ = 0, end_ = np, nTotal_ = np, nHaloSend_ = 0;
+        for (int a = 0; a < na; ++a)
+        {
+            CSB_TRY(fin_[a].reserve(size_t(eb[a]) * np + 256));
+            dst[a] = fin_[a].p;
+        }
+        if (np) CSB_TRY(gatherMulti(order_.template as<uint32_t>(), np, na, src, dst, eb));
+        CSB_TRY(fkeys_.reserve(sizeof(K) * np + 256));
+        CSB_CUDA(cudaMemcpyAsync(fkeys_.p, keys, sizeof(K) * np, cudaMemcpyDeviceToDevice, s_));
+    }
+    else
+    {
+        const int P = nRanks_;
+        // 4. send ranges = positions of the rank boundaries in the sorted keys [ref: domain/domaindecomp.hpp:217-230]
+        CSB_TRY(small_.reserve(size_t(P + 1) * (sizeof(K) + 4) + size_t(P) * P * 4 + 4096));
+        K* dBound      = small_.template as<K>();
+        uint32_t* dPos = reinterpret_cast<uint32_t*>(dBound + P + 1);
+        CSB_CUDA(cudaMemcpyAsync(dBound, boundaries_.data(), sizeof(K) * (P + 1), cudaMemcpyHostToDevice, s_));
+        lowerBoundQueriesKernel<K><<<1, 64, 0, s_>>>(keys, uint32_t(np), dBound, P + 1, dPos);
+        CSB_LAUNCHED();
+        std::vector<uint32_t> sendStart(P + 1), sendCount(P);
+        CSB_CUDA(cudaMemcpyAsync(sendStart.data(), dPos, 4 * (P + 1), cudaMemcpyDeviceToHost, s_));
+        CSB_CUDA(cudaStreamSynchronize(s_));
+        sendStart[0] = 0, sendStart[P] = uint32_t(np); // keys below / above the tree range cannot occur
+        for (int q = 0; q < P; ++q)
+            sendCount[q] = sendStart[q + 1] - sendStart[q];
+
+        // 5. ONE gather orders all outgoing messages (sorted by key = grouped by destination rank)
+        for (int a = 0; a < na; ++a)
+        {
+            CSB_TRY(pack_[a].reserve(size_t(eb[a]) * np + 256));
+            dst[a] = pack_[a].p;
+        }
+        if (np) CSB_TRY(gatherMulti(order_.template as<uint32_t>(), np, na, src, dst, eb));
+
+        // 6. who sends how much to whom
+        uint32_t* dMine = dPos + P + 1;
+        uint32_t* dAll  = dMine + P;
+        CSB_CUDA(cudaMemcpyAsync(dMine, sendCount.data(), 4 * P, cudaMemcpyHostToDevice, s_));
+        CSB_NCCL(ncclAllGather(dMine, dAll, P, ncclUint32, comm_, s_));
+        std::vector<uint32_t> matrix(size_t(P) * P);
+        CSB_CUDA(cudaMemcpyAsync(matrix.data(), dAll, 4 * size_t(P) * P, cudaMemcpyDeviceToHost, s_));
+        CSB_CUDA(cudaStreamSynchronize(s_));
+        std::vector<uint32_t> recvCount(P), recvOff(P + 1, 0);
+        for (int q = 0; q < P; ++q)
+        {
+            recvCount[q]   = matrix[size_t(q) * P + rank_];
+            recvOff[q + 1] = recvOff[q] + recvCount[q];
+        }
+        nAssigned_ = recvOff[P];
+        if (nAssigned_ >= (uint64_t(1) << 30)) return CSTONE_E_TOO_LARGE;
+
+        // 7. exchange: grouped NCCL send/recv, received straight into place [ref: domaindecomp_mpi_gpu.cuh:85-185]
+        for (int a = 0; a < na; ++a)
+            CSB_TRY(recv_[a].reserve(size_t(eb[a]) * nAssigned_ + 256));
+        CSB_NCCL(ncclGroupStart());
+        for (int q = 0; q < P; ++q)
+        {
+            if (q == rank_) continue;
+            for (int a = 0; a < na; ++a)
+            {
+                if (sendCount[q])
+                    CSB_NCCL(ncclSend(pack_[a].template as<char>() + size_t(sendStart[q]) * eb[a], size_t(sendCount[q]) * eb[a],
+                                      ncclInt8, q, comm_, s_));
+                if (recvCount[q])
+                    CSB_NCCL(ncclRecv(recv_[a].template as<char>() + size_t(recvOff[q]) * eb[a], size_t(recvCount[q]) * eb[a],
+                                      ncclInt8, q, comm_, s_));
+            }
+        }
+        CSB_NCCL(ncclGroupEnd());
+        for (int a = 0; a < na; ++a)
+            if (sendCount[rank_])
+                CSB_CUDA(cudaMemcpyAsync(recv_[a].template as<char>() + size_t(recvOff[rank_]) * eb[a],
+                                         pack_[a].template as<char>() + size_t(sendStart[rank_]) * eb[a],
+                                         size_t(sendCount[rank_]) * eb[a], cudaMemcpyDeviceToDevice, s_));
+
+        // 8. keys + order of the assigned set (P sorted runs) [ref: domain/assignment.hpp:141-150]
+        const size_t n = size_t(nAssigned_);
+        CSB_TRY(skeys_.reserve(sizeof(K) * n + 256));
+        CSB_TRY(reserveSort(n));
+        K* skeys = skeys_.template as<K>();
+        if (n)
+        {
+            CSB_CUDA(cudaMemsetAsync(skeys, 0, sizeof(K) * n, s_));
+            CSB_TRY((Api<K, T>::keys(recv_[0].template as<T>(), recv_[1].template as<T>(), recv_[2].template as<T>(), skeys, n, &box_, s_)));
+            CSB_TRY((Api<K, T>::sort(skeys, order_.template as<uint32_t>(), keyBuf_.template as<K>(), valBuf_.template as<uint32_t>(), n,
+                                     sortTemp_.p, sortTemp_.bytes, 1, s_)));
+        }
+        // h in SFC order for the halo search radii
+        CSB_TRY(shAssigned_.reserve(sizeof(T) * n + 256));
+        if (n) CSB_TRY(cstone_b200_gather(order_.template as<uint32_t>(), n, recv_[3].p, shAssigned_.p, int(sizeof(T)), s_));
+
+        // 9. halos
+        CSB_TRY(discoverHalos());
+    }
+
+    // 10. search tree over assigned + halo particles, linked, with node centres and layout
+    CSB_TRY(convergeTree(search_, fkeys_.template as<K>(), size_t(nTotal_), searchFresh_));
+    CSB_TRY(linkTree(search_, true));
+    CSB_CUDA(cudaStreamSynchronize(s_));
+    firstCall_ = false;
+    return int64_t(nTotal_);
+}
+
+
+template<class K, class T>
+int Engine<K, T>::discoverHalos()
+{
+    const int P     = nRanks_;
+    const size_t n  = size_t(nAssigned_);
+    const K* skeys  = skeys_.template as<K>();
+    const K lowest  = boundaries_[rank_];
+    const K highest = boundaries_[rank_ + 1];
+    const int na    = 4 + nprops_;
+    int eb[4 + kMaxProps];
+    for (int a = 0; a < na; ++a)
+        eb[a] = a < 4 ? int(sizeof(T)) : propBytes_[a - 4];
+
+    // a. tree over the assigned particles, linked (for the reverse collision) and with its particle layout
+    CSB_TRY(convergeTree(focus_, skeys, n, focusFresh_));
+    CSB_TRY(linkTree(focus_, false));
+    const int L = focus_.numNodes;
+
+    // b. search radius per leaf [ref: halos/halos.hpp:148-160]
+    CSB_TRY(radii_.reserve(4 * size_t(L) + 256));
+    CSB_TRY((Api<K, T>::haloRadii(shAssigned_.template as<T>(), layout_.template as<uint32_t>(), size_t(L), 2.0f,
+                                  radii_.template as<float>(), s_)));
+
+    // c. halo boxes of my surface leaves
+    SfcTables tabs;
+    CSB_TRY(getSfcTables(&tabs));
+    CSB_TRY(surf_.reserve(sizeof(IBox6) * size_t(L) + 256));
+    CSB_TRY(nSurf_.reserve(4 * size_t(2 * P + 2) + size_t(P) * P * 4 + 256));
+    uint32_t* dCount = nSurf_.template as<uint32_t>();      // [0] my count, [1..P] all counts
+    CSB_CUDA(cudaMemsetAsync(dCount, 0, 4, s_));
+    surfaceBoxesKernel<K, T><<<gridFor(size_t(L), 128), 128, 0, s_>>>(
+        tabs.enc, tabs.dec, focus_.treeA.template as<K>(), focus_.counts.template as<uint32_t>(), radii_.template as<float>(), L, lowest,
+        highest, makeDBox<T>(&box_), surf_.template as<IBox6>(), uint32_t(L), dCount);
+    CSB_LAUNCHED();
+    CSB_NCCL(ncclAllGather(dCount, dCount + 1, 1, ncclUint32, comm_, s_));
+    std::vector<uint32_t> nS(P);
+    CSB_CUDA(cudaMemcpyAsync(nS.data(), dCount + 1, 4 * P, cudaMemcpyDeviceToHost, s_));
+    CSB_CUDA(cudaStreamSynchronize(s_));
+    uint32_t maxS = 1;
+    for (int q = 0; q < P; ++q)
+        maxS = std::max(maxS, nS[q]);
+
+    // d. everybody gets everybody's surface boxes (tens of MB at most: surface ~ N^(2/3))
+    CSB_TRY(surf_.reserve(sizeof(IBox6) * size_t(maxS) + 256, true, s_));
+    CSB_TRY(allSurf_.reserve(sizeof(IBox6) * size_t(maxS) * P + 256));
+    CSB_NCCL(ncclAllGather(surf_.p, allSurf_.p, sizeof(IBox6) * size_t(maxS), ncclInt8, comm_, s_));
+
+    // e. reverse collision against my own leaves
+    CSB_TRY(flags_.reserve(size_t(P) * L + 256));
+    CSB_CUDA(cudaMemsetAsync(flags_.p, 0, size_t(P) * L, s_));
+    {
+        dim3 grid(gridFor(size_t(maxS), 128, 4), P);
+        reverseCollisionKernel<K><<<grid, 128, 0, s_>>>(tabs.dec, prefixes_.template as<K>(), childOffsets_.template as<int32_t>(),
+                                                       internalToLeaf_.template as<int32_t>(), focus_.counts.template as<uint32_t>(), L,
+                                                       lowest, highest, allSurf_.template as<IBox6>(), dCount + 1, maxS, P, rank_,
+                                                       flags_.template as<unsigned char>());
+        CSB_LAUNCHED();
+    }
+
+    // f. send lists: per peer the particles of my flagged leaves, in leaf (= SFC) order
+    CSB_TRY(sendScan_.reserve(4 * (size_t(L) + 1) * P + 256));
+    CSB_TRY(scanTemp_.reserve(cstone_b200_scan_temp_bytes(uint64_t(L) + 1) + 512));
+    haloSendCount_.assign(P, 0), haloSendOffset_.assign(P + 1, 0);
+    std::vector<uint32_t> totals(P, 0);
+    for (int q = 0; q < P; ++q)
+    {
+        if (q == rank_) continue;
+        LoadFlaggedCount load{flags_.template as<unsigned char>() + size_t(q) * L, focus_.counts.template as<uint32_t>(), L};
+        uint32_t* scan = sendScan_.template as<uint32_t>() + size_t(q) * (L + 1);
+        CSB_TRY((launchScan<false>(load, scan, size_t(L) + 1, 0u, scanTemp_.p, nullptr, s_)));
+        CSB_CUDA(cudaMemcpyAsync(&totals[q], scan + L, 4, cudaMemcpyDeviceToHost, s_));
+    }
+    CSB_CUDA(cudaStreamSynchronize(s_));
+    for (int q = 0; q < P; ++q)
+    {
+        haloSendCount_[q]      = totals[q];
+        haloSendOffset_[q + 1] = haloSendOffset_[q] + totals[q];
+    }
+    nHaloSend_ = haloSendOffset_[P];
+    CSB_TRY(sendIdx_.reserve(4 * size_t(nHaloSend_) + 256));
+    for (int q = 0; q < P; ++q)
+    {
+        if (q == rank_ || !haloSendCount_[q]) continue;
+        expandSendListKernel<<<gridFor(size_t(L) * 32, 256), 256, 0, s_>>>(
+            flags_.template as<unsigned char>() + size_t(q) * L, layout_.template as<uint32_t>(),
+            sendScan_.template as<uint32_t>() + size_t(q) * (L + 1), L, sendIdx_.template as<uint32_t>() + haloSendOffset_[q]);
+        CSB_LAUNCHED();
+    }
+
+    // g. receive counts, final layout: [halos of ranks < me][assigned][halos of ranks > me], all in SFC order
+    uint32_t* dMine = dCount + 1 + P;
+    uint32_t* dAll  = dMine + P;
+    CSB_CUDA(cudaMemcpyAsync(dMine, haloSendCount_.data(), 4 * P, cudaMemcpyHostToDevice, s_));
+    CSB_NCCL(ncclAllGather(dMine, dAll, P, ncclUint32, comm_, s_));
+    std::vector<uint32_t> matrix(size_t(P) * P);
+    CSB_CUDA(cudaMemcpyAsync(matrix.data(), dAll, 4 * size_t(P) * P, cudaMemcpyDeviceToHost, s_));
+    CSB_CUDA(cudaStreamSynchronize(s_));
+    haloRecvCount_.assign(P, 0), haloRecvOffset_.assign(P, 0);
+    uint64_t left = 0, right = 0;
+    for (int q = 0; q < P; ++q)
+    {
+        haloRecvCount_[q] = q == rank_ ? 0u : matrix[size_t(q) * P + rank_];
+        if (q < rank_) left += haloRecvCount_[q];
+        if (q > rank_) right += haloRecvCount_[q];
+    }
+    start_  = left;
+    end_    = left + n;
+    nTotal_ = end_ + right;
+    if (nTotal_ >= (uint64_t(1) << 30)) return CSTONE_E_TOO_LARGE;
+    {
+        uint64_t l = 0, r = end_;
+        for (int q = 0; q < P; ++q)
+        {
+            if (q < rank_) haloRecvOffset_[q] = uint32_t(l), l += haloRecvCount_[q];
+            if (q > rank_) haloRecvOffset_[q] = uint32_t(r), r += haloRecvCount_[q];
+        }
+    }
+
+    // h. assigned particles straight to their final position, then the halos of x,y,z,h
+    const void* src[4 + kMaxProps];
+    void* dst[4 + kMaxProps];
+    for (int a = 0; a < na; ++a)
+    {
+        CSB_TRY(fin_[a].reserve(size_t(eb[a]) * nTotal_ + 256));
+        src[a] = recv_[a].p;
+        dst[a] = fin_[a].template as<char>() + size_t(start_) * eb[a];
+    }
+    if (n) CSB_TRY(gatherMulti(order_.template as<uint32_t>(), n, na, src, dst, eb));
+    void* xyzh[4] = {fin_[0].p, fin_[1].p, fin_[2].p, fin_[3].p};
+    CSB_TRY(exchangeHalos(4, xyzh, eb));
+
+    // i. keys: assigned ones are known, halo keys are computed [ref: domain/domain.hpp:530-532]
+    CSB_TRY(fkeys_.reserve(sizeof(K) * nTotal_ + 256));
+    K* fk = fkeys_.template as<K>();
+    CSB_CUDA(cudaMemsetAsync(fk, 0, sizeof(K) * nTotal_, s_));
+    CSB_CUDA(cudaMemcpyAsync(fk + start_, skeys, sizeof(K) * n, cudaMemcpyDeviceToDevice, s_));
+    const T *fx = fin_[0].template as<T>(), *fy = fin_[1].template as<T>(), *fz = fin_[2].template as<T>();
+    if (start_) CSB_TRY((Api<K, T>::keys(fx, fy, fz, fk, size_t(start_), &box_, s_)));
+    if (nTotal_ > end_)
+        CSB_TRY((Api<K, T>::keys(fx + end_, fy + end_, fz + end_, fk + end_, size_t(nTotal_ - end_), &box_, s_)));
+    return 0;
+}
+
+template<class K, class T>
+int Engine<K, T>::exchangeHalos(int narrays, void* const* arrays, const int* elemBytes)
+{
+    if (nRanks_ == 1 || narrays == 0) return 0;
+    if (narrays < 0 || !arrays || !elemBytes) return CSTONE_E_INVALID_ARGUMENT;
+    const int P = nRanks_;
+    size_t total = 0;
+    std::vector<size_t> off(narrays);
+    for (int a = 0; a < narrays; ++a)
+    {
+        if ((elemBytes[a] != 4 && elemBytes[a] != 8) || !arrays[a]) return CSTONE_E_INVALID_ARGUMENT;
+        off[a] = total;
+        total += (size_t(nHaloSend_) * elemBytes[a] + 255) / 256 * 256;
+    }
+    CSB_TRY(haloPack_.reserve(total + 256));
+    // pack [ref: halos/gather_halos_gpu.cu:25-75 gatherRanges]
+    if (nHaloSend_)
+        for (int a = 0; a < narrays; ++a)
+        {
+            unsigned grid = gridFor(size_t(nHaloSend_), 256);
+            if (elemBytes[a] == 8)
+                packKernel<uint64_t><<<grid, 256, 0, s_>>>(sendIdx_.template as<uint32_t>(), uint32_t(nHaloSend_), uint32_t(start_),
+                                                          reinterpret_cast<const uint64_t*>(arrays[a]),
+                                                          reinterpret_cast<uint64_t*>(haloPack_.template as<char>() + off[a]));
+            else
+                packKernel<uint32_t><<<grid, 256, 0, s_>>>(sendIdx_.template as<uint32_t>(), uint32_t(nHaloSend_), uint32_t(start_),
+                                                          reinterpret_cast<const uint32_t*>(arrays[a]),
+                                                          reinterpret_cast<uint32_t*>(haloPack_.template as<char>() + off[a]));
+            CSB_LAUNCHED();
+        }
+    // one NCCL group; every message is received directly in its halo range [ref: halos/exchange_halos_gpu.cuh:34-119]
+    CSB_NCCL(ncclGroupStart());
+    for (int q = 0; q < P; ++q)
+    {
+        if (q == rank_) continue;
+        for (int a = 0; a < narrays; ++a)
+        {
+            if (haloSendCount_[q])
+                CSB_NCCL(ncclSend(haloPack_.template as<char>() + off[a] + size_t(haloSendOffset_[q]) * elemBytes[a],
+                                  size_t(haloSendCount_[q]) * elemBytes[a], ncclInt8, q, comm_, s_));
+            if (haloRecvCount_[q])
+                CSB_NCCL(ncclRecv(reinterpret_cast<char*>(arrays[a]) + size_t(haloRecvOffset_[q]) * elemBytes[a],
+                                  size_t(haloRecvCount_[q]) * elemBytes[a], ncclInt8, q, comm_, s_));
+        }
+    }
+    CSB_NCCL(ncclGroupEnd());
+    return 0;
+}
+
+template<class K, class T>
+int Engine<K, T>::syncFinish(K* keys, T* x, T* y, T* z, T* h, void* const* props)
+{
+    if (nTotal_ && (!keys || !x || !y || !z || !h)) return CSTONE_E_INVALID_ARGUMENT;
+    void* out[4] = {x, y, z, h};
+    CSB_CUDA(cudaMemcpyAsync(keys, fkeys_.p, sizeof(K) * nTotal_, cudaMemcpyDeviceToDevice, s_));
+    for (int a = 0; a < 4; ++a)
+        CSB_CUDA(cudaMemcpyAsync(out[a], fin_[a].p, sizeof(T) * nTotal_, cudaMemcpyDeviceToDevice, s_));
+    for (int a = 0; a < nprops_; ++a)
+    {
+        if (!props || !props[a]) return CSTONE_E_INVALID_ARGUMENT;
+        size_t b = size_t(propBytes_[a]);
+        CSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(props[a]) + start_ * b, fin_[4 + a].template as<char>() + start_ * b,
+                                 (end_ - start_) * b, cudaMemcpyDeviceToDevice, s_));
+    }
+    CSB_CUDA(cudaStreamSynchronize(s_));
+    return 0;
+}
+
+template<class K, class T>
+int Engine<K, T>::findNeighbors(const T* x, const T* y, const T* z, const T* h, uint32_t ngmax, uint32_t* nb,
+                                uint32_t* nc) const
+{
+    return Api<K, T>::neighbors(x, y, z, h, uint32_t(start_), uint32_t(end_), &box_, childOffsets_.template as<int32_t>(),
+                                internalToLeaf_.template as<int32_t>(), layout_.template as<uint32_t>(), centers_.template as<T>(),
+                                sizes_.template as<T>(), ngmax, nb, nc, s_);
+}
+
+} // namespace csb
+
+// ------------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------------
+extern "C" {
+
+int cstone_b200_nccl_unique_id(void* id128)
+{
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId id;
+    if (ncclGetUniqueId(&id) != ncclSuccess) return CSTONE_E_NCCL;
+    std::memcpy(id128, &id, 128);
+    return 0;
+}
+int cstone_b200_nccl_comm_init(const void* id128, int nranks, int rank, void** commOut)
+{
+    ncclUniqueId id;
+    std::memcpy(&id, id128, 128);
+    ncclComm_t comm;
+    if (ncclCommInitRank(&comm, nranks, id, rank) != ncclSuccess) return CSTONE_E_NCCL;
+    *commOut = comm;
+    return 0;
+}
+int cstone_b200_nccl_comm_destroy(void* comm)
+{
+    return ncclCommDestroy(reinterpret_cast<ncclComm_t>(comm)) == ncclSuccess ? 0 : CSTONE_E_NCCL;
+}
+
+#define CSB_DOMAIN_DEF(KS, K, TS, T)                                                                                       cstone_b200_domain* cstone_b200_domain_create_##KS##_##TS(int rank, int nranks, unsigned bucket,                                                                                 unsigned bucketFocus, float theta,                                                                                     const cstone_box_##TS* box)                                  {                                                                                                                          if (!box || nranks < 1 || rank < 0 || rank >= nranks || bucket < bucketFocus || bucketFocus == 0) return nullptr;         return reinterpret_cast<cstone_b200_domain*>(new csb::Engine<K, T>(rank, nranks, bucket, bucketFocus, theta, *box));     }                                                                                                                      void cstone_b200_domain_destroy_##KS##_##TS(cstone_b200_domain* d) { delete reinterpret_cast<csb::Engine<K, T>*>(d); }     int cstone_b200_domain_set_comm_##KS##_##TS(cstone_b200_domain* d, void* comm)                                         {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              reinterpret_cast<csb::Engine<K, T>*>(d)->setComm(comm);                                                                return 0;                                                                                                          }                                                                                                                      int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n, const T* x, const T* y,                                                             const T* z, const T* h, int nprops, const void* const* props,                                                          const int* pb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncBegin(n, x, y, z, h, nprops, props, pb);                       }                                                                                                                      int cstone_b200_domain_sync_finish_##KS##_##TS(cstone_b200_domain* d, K* keys, T* x, T* y, T* z, T* h,                                                                void* const* props)                                                     {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncFinish(keys, x, y, z, h, props);                               }                                                                                                                      int cstone_b200_domain_exchange_halos_##KS##_##TS(cstone_b200_domain* d, int na, void* const* arrays,                                                                    const int* eb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              int st = reinterpret_cast<csb::Engine<K, T>*>(d)->exchangeHalos(na, arrays, eb);                                       if (st) return st;                                                                                                     cudaError_t e = cudaStreamSynchronize(nullptr);                                                                        return int(e);                                                                                                     }                                                                                                                      int cstone_b200_domain_info_##KS##_##TS(const cstone_b200_domain* d, int64_t* info8)                                   {                                                                                                                          if (!d || !info8) return CSTONE_E_INVALID_ARGUMENT;                                                                    reinterpret_cast<const csb::Engine<K, T>*>(d)->info(info8);                                                            return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_box_##KS##_##TS(const cstone_b200_domain* d, cstone_box_##TS* out)                              {                                                                                                                          if (!d || !out) return CSTONE_E_INVALID_ARGUMENT;                                                                      *out = reinterpret_cast<const csb::Engine<K, T>*>(d)->box();                                                           return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_tree_view_##KS##_##TS(const cstone_b200_domain* d, const void** ptrs10)                         {                                                                                                                          if (!d || !ptrs10) return CSTONE_E_INVALID_ARGUMENT;                                                                   reinterpret_cast<const csb::Engine<K, T>*>(d)->treeView(ptrs10);                                                       return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_global_tree_##KS##_##TS(const cstone_b200_domain* d, const K** leaves,                                                                         const uint32_t** counts, const K** assignment)                          {                                                                                                                          if (!d || !leaves || !counts || !assignment) return CSTONE_E_INVALID_ARGUMENT;                                         reinterpret_cast<const csb::Engine<K, T>*>(d)->globalTree(leaves, counts, assignment);                                 return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_find_neighbors_##KS##_##TS(const cstone_b200_domain* d, const T* x, const T* y,                                                                   const T* z, const T* h, uint32_t ngmax, uint32_t* nb,                                                                  uint32_t* nc)                                                        {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<const csb::Engine<K, T>*>(d)->findNeighbors(x, y, z, h, ngmax, nb, nc);                    }
+
+CSB_DOMAIN_DEF(k64, uint64_t, f64, double)
+CSB_DOMAIN_DEF(k64, uint64_t, f32, float)
+CSB_DOMAIN_DEF(k32, uint32_t, f64, double)
+CSB_DOMAIN_DEF(k32, uint32_t, f32, float)
+
+int cstone_b200_host_assignment_k64(int nranks, const uint64_t* leaves, const uint32_t* counts, int32_t numLeaves,
+                                    const uint64_t* oldB, uint64_t* boundaries, uint32_t* rankCounts)
+{
+    if (nranks < 1 || numLeaves < 1 || !leaves || !counts || !boundaries || !rankCounts) return CSTONE_E_INVALID_ARGUMENT;
+    std::vector<uint64_t> b;
+    std::vector<uint32_t> c;
+    csb::makeAssignment<uint64_t>(nranks, leaves, counts, numLeaves, oldB, b, c);
+    std::copy(b.begin(), b.end(), boundaries);
+    std::copy(c.begin(), c.end(), rankCounts);
+    return 0;
+}
+int cstone_b200_host_assignment_k32(int nranks, const uint32_t* leaves, const uint32_t* counts, int32_t numLeaves,
+                                    const uint32_t* oldB, uint32_t* boundaries, uint32_t* rankCounts)
+{
+    if (nranks < 1 || numLeaves < 1 || !leaves || !counts || !boundaries || !rankCounts) return CSTONE_E_INVALID_ARGUMENT;
+    std::vector<uint32_t> b;
+    std::vector<uint32_t> c;
+    csb::makeAssignment<uint32_t>(nranks, leaves, counts, numLeaves, oldB, b, c);
+    std::copy(b.begin(), b.end(), boundaries);
+    std::copy(c.begin(), c.end(), rankCounts);
+    return 0;
+}
+void cstone_b200_host_limit_box_shrinking_f64(const double* fit, const double* prev, double* out)
+{
+    csb::limitBoxShrinking<double>(fit, prev, out);
+}
+void cstone_b200_host_limit_box_shrinking_f32(const float* fit, const float* prev, float* out)
+{
+    csb::limitBoxShrinking<float>(fit, prev, out);
+}
+
+} // extern "C"

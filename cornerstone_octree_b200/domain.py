@@ -1,0 +1,184 @@
+"""Host-side mirror of cstone::Domain<KeyType,T,GpuTag> [ref: domain/domain.hpp:66-699] on torch CUDA tensors.
+
+Every method forwards to the domain engine of libcstone_b200.so (include/cstone_b200_domain.h); torch provides the
+device memory of the caller-owned particle arrays and, for multi-GPU runs, the bootstrap of the NCCL communicator
+(the unique id is broadcast through torch.distributed, all data-path communication is NCCL inside the library)."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib, ops
+from ._lib import BoxF32, BoxF64, CstoneError, lib
+
+
+def _fn(name, bits, fdtype):
+    ts = "f32" if fdtype == torch.float32 else "f64"
+    return getattr(lib, "cstone_b200_domain_%s_k%d_%s" % (name, bits, ts))
+
+
+def _check(st, where):
+    if st != 0:
+        raise CstoneError(int(st), "cstone_b200_domain_" + where)
+
+
+class Domain:
+    """Domain(rank, num_ranks, bucket_size, bucket_size_focus, theta, box)  — same arguments as the reference"""
+
+    def __init__(self, rank, num_ranks, bucket_size, bucket_size_focus, theta=0.5, box=None, key_bits=64,
+                 dtype=torch.float64):
+        if bucket_size < bucket_size_focus:
+            # [ref: domain/domain.hpp:108-112]
+            raise RuntimeError("The bucket size of the global tree must not be smaller than the bucket size of the "
+                               "focused tree")
+        self.rank, self.num_ranks, self.bits, self.fd = rank, num_ranks, key_bits, dtype
+        box = box if box is not None else ops.make_box((0.0, 1.0), dtype=dtype)
+        self._h = C.c_void_p(_fn("create", key_bits, dtype)(rank, num_ranks, bucket_size, bucket_size_focus, theta,
+                                                          C.byref(box)))
+        if not self._h:
+            raise RuntimeError("cstone_b200_domain_create failed")
+        self._comm = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _fn("destroy", self.bits, self.fd)(self._h)
+            self._h = None
+        if self._comm:
+            lib.cstone_b200_nccl_comm_destroy(self._comm)
+            self._comm = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- multi-GPU bootstrap
+    def init_comm_from_torch(self):
+        """create the NCCL communicator of this Domain; the 128-byte unique id travels over torch.distributed"""
+        import torch.distributed as dist
+        if self.num_ranks == 1:
+            return
+        ident = torch.zeros(128, dtype=torch.uint8)
+        if self.rank == 0:
+            buf = (C.c_ubyte * 128)()
+            _check(lib.cstone_b200_nccl_unique_id(buf), "nccl_unique_id")
+            ident = torch.tensor(list(buf), dtype=torch.uint8)
+        dev = ident.cuda() if dist.get_backend() == "nccl" else ident
+        dist.broadcast(dev, src=0)
+        raw = bytes(dev.cpu().tolist())
+        comm = C.c_void_p()
+        _check(lib.cstone_b200_nccl_comm_init(raw, self.num_ranks, self.rank, C.byref(comm)), "nccl_comm_init")
+        self._comm = comm
+        _check(_fn("set_comm", self.bits, self.fd)(self._h, comm), "set_comm")
+
+    # ---- sync
+    def sync(self, x, y, z, h, props=()):
+        """[ref: domain/domain.hpp:196-243] returns (keys, x, y, z, h, props) as NEW tensors of the new local size:
+        assigned particles in [start_index, end_index), halos elsewhere, everything in SFC order"""
+        for t in (x, y, z, h) + tuple(props):
+            if not t.is_cuda or not t.is_contiguous():
+                raise ValueError("Domain.sync operates on contiguous CUDA tensors (no CPU fallback)")
+        n_in = x.numel()
+        k = len(props)
+        parr = (C.c_void_p * max(k, 1))(*[p.data_ptr() for p in props])
+        pbytes = (C.c_int * max(k, 1))(*[p.element_size() for p in props])
+        n_new = _fn("sync_begin", self.bits, self.fd)(self._h, n_in, ops._p(x), ops._p(y), ops._p(z), ops._p(h), k, parr,
+                                                     pbytes)
+        if n_new < 0:
+            raise CstoneError(int(n_new), "cstone_b200_domain_sync_begin")
+        dev = x.device
+        keys = torch.empty(n_new, dtype=ops.KEY_TORCH[self.bits], device=dev)
+        out = [torch.empty(n_new, dtype=x.dtype, device=dev) for _ in range(4)]
+        pout = [torch.empty(n_new, dtype=p.dtype, device=dev) for p in props]
+        oarr = (C.c_void_p * max(k, 1))(*[p.data_ptr() for p in pout])
+        _check(_fn("sync_finish", self.bits, self.fd)(self._h, ops._p(keys), ops._p(out[0]), ops._p(out[1]), ops._p(out[2]),
+                                                    ops._p(out[3]), oarr), "sync_finish")
+        return keys, out[0], out[1], out[2], out[3], pout
+
+    def exchange_halos(self, arrays):
+        """[ref: domain/domain.hpp:381-386] fill the halo ranges of `arrays` (length n_particles_with_halos) in place"""
+        k = len(arrays)
+        if k == 0:
+            return
+        arr = (C.c_void_p * k)(*[a.data_ptr() for a in arrays])
+        eb = (C.c_int * k)(*[a.element_size() for a in arrays])
+        _check(_fn("exchange_halos", self.bits, self.fd)(self._h, k, arr, eb), "exchange_halos")
+
+    # ---- accessors [ref: domain/domain.hpp:389-437]
+    def _info(self):
+        info = (C.c_int64 * 8)()
+        _check(_fn("info", self.bits, self.fd)(self._h, info), "info")
+        return list(info)
+
+    @property
+    def start_index(self):
+        return self._info()[0]
+
+    @property
+    def end_index(self):
+        return self._info()[1]
+
+    @property
+    def n_particles(self):
+        i = self._info()
+        return i[1] - i[0]
+
+    @property
+    def n_particles_with_halos(self):
+        return self._info()[2]
+
+    def box(self):
+        b = BoxF32() if self.fd == torch.float32 else BoxF64()
+        _check(_fn("box", self.bits, self.fd)(self._h, C.byref(b)), "box")
+        return b
+
+    def global_tree(self):
+        """replicated global leaf array, its counts and the rank boundaries (numpy, host)"""
+        kt = C.c_uint64 if self.bits == 64 else C.c_uint32
+        l, c, a = C.POINTER(kt)(), C.POINTER(C.c_uint32)(), C.POINTER(kt)()
+        _check(_fn("global_tree", self.bits, self.fd)(self._h, C.byref(l), C.byref(c), C.byref(a)), "global_tree")
+        L = self._info()[5]
+        kd = np.uint64 if self.bits == 64 else np.uint32
+        return (np.ctypeslib.as_array(l, (L + 1,)).astype(kd), np.ctypeslib.as_array(c, (L,)).copy(),
+                np.ctypeslib.as_array(a, (self.num_ranks + 1,)).astype(kd))
+
+    def tree_arrays(self):
+        """device views (torch tensors that alias engine memory, valid until the next sync) of the search tree"""
+        ptrs = (C.c_void_p * 10)()
+        _check(_fn("tree_view", self.bits, self.fd)(self._h, ptrs), "tree_view")
+        i = self._info()
+        L, M = i[3], i[4]
+        ml = ops.max_level(self.bits)
+        kt, i32 = ops.KEY_TORCH[self.bits], torch.int32
+        shapes = [("leaves", kt, L + 1), ("counts", i32, L), ("layout", i32, L + 1), ("prefixes", kt, M),
+                  ("child_offsets", i32, M + 1), ("internal_to_leaf", i32, M), ("leaf_to_internal", i32, M),
+                  ("level_range", i32, ml + 2), ("centers", self.fd, 3 * M), ("sizes", self.fd, 3 * M)]
+        out = {}
+        for (name, dt, n), p in zip(shapes, ptrs):
+            out[name] = _alias(p, n, dt)
+        return out
+
+    def find_neighbors(self, x, y, z, h, ngmax, neighbors=None, neighbors_count=None):
+        """[ref: findneighbors.hpp:167-178] over [start_index, end_index) with the Domain's tree"""
+        nw = self.n_particles
+        if neighbors is None:
+            neighbors = torch.empty((nw, ngmax), dtype=torch.int32, device=x.device)
+        if neighbors_count is None:
+            neighbors_count = torch.empty(nw, dtype=torch.int32, device=x.device)
+        _check(_fn("find_neighbors", self.bits, self.fd)(self._h, ops._p(x), ops._p(y), ops._p(z), ops._p(h), ngmax,
+                                                       ops._p(neighbors), ops._p(neighbors_count)), "find_neighbors")
+        return neighbors, neighbors_count
+
+
+def _alias(ptr, n, dtype):
+    """torch tensor over `n` elements of device memory owned by the engine (copied: views must not outlive a sync)"""
+    out = torch.empty(n, dtype=dtype, device="cuda")
+    if n:
+        nbytes = n * out.element_size()
+        rt = C.CDLL("libcudart.so")
+        rt.cudaMemcpy.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]
+        st = rt.cudaMemcpy(C.c_void_p(out.data_ptr()), C.c_void_p(ptr), nbytes, 3)
+        if st != 0:
+            raise RuntimeError("cudaMemcpy failed: %d" % st)
+    return out

@@ -1,0 +1,94 @@
+/*
+ * cstone_b200_domain.h — C ABI of the domain engine of libcstone_b200.so
+ *
+ * The engine is what stands behind cstone::Domain<KeyType,T,GpuTag>
+ * [ref: domain/domain.hpp:66-699].  The C++ facade include/cstone_b200/domain.hpp
+ * keeps the reference's template signatures (sync / exchangeHalos / startIndex /
+ * endIndex / nParticles / nParticlesWithHalos / box) and forwards to the functions
+ * below; all particle data stay on the device.
+ *
+ * sync is split in two calls because the CALLER owns and resizes the particle arrays:
+ *   n_new = ..._sync_begin(d, n_in, x, y, z, h, nprops, props, prop_bytes)   // may communicate
+ *   (caller resizes keys, x, y, z, h and every property array to n_new elements; contents may be discarded)
+ *   ..._sync_finish(d, keys, x, y, z, h, props)                              // writes the SFC-ordered arrays
+ * Postconditions are the reference's [ref: domain/domain.hpp:144-179]: x,y,z,h,keys hold assigned particles in
+ * [start_index, end_index) and halos elsewhere, everything in SFC order; property arrays are valid in the assigned
+ * range and are completed by ..._exchange_halos.
+ *
+ * Multi-GPU: one process per GPU.  The caller creates the NCCL communicator (e.g. unique id broadcast through
+ * torch.distributed or MPI) and hands it over with ..._set_comm; with nranks == 1 no communicator is needed.
+ * All functions return 0, a positive cudaError_t, a negative CSTONE_E_* code, or CSTONE_E_NCCL.
+ */
+#ifndef CSTONE_B200_DOMAIN_H
+#define CSTONE_B200_DOMAIN_H
+
+#include "cstone_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CSTONE_E_NCCL (-6)
+#define CSTONE_E_SIZE_MISMATCH (-7) /* array length differs from the previous sync [ref: domain/domain.hpp:130-133] */
+
+typedef struct cstone_b200_domain cstone_b200_domain;
+
+/* NCCL bootstrap helpers (thin wrappers so that a host language without NCCL bindings can drive them) */
+int cstone_b200_nccl_unique_id(void* id128 /* 128 bytes, HOST */);
+int cstone_b200_nccl_comm_init(const void* id128, int nranks, int rank, void** comm_out);
+int cstone_b200_nccl_comm_destroy(void* comm);
+
+#define CSB_DOMAIN_DECL(KS, K, TS, T)                                                                                  \
+    /* [ref: domain/domain.hpp:95-113 Domain(rank, nRanks, bucketSize, bucketSizeFocus, theta, box)] */               \
+    cstone_b200_domain* cstone_b200_domain_create_##KS##_##TS(int rank, int nranks, unsigned bucket_size,              \
+                                                              unsigned bucket_size_focus, float theta,                 \
+                                                              const cstone_box_##TS* box);                             \
+    void cstone_b200_domain_destroy_##KS##_##TS(cstone_b200_domain* d);                                                \
+    int cstone_b200_domain_set_comm_##KS##_##TS(cstone_b200_domain* d, void* nccl_comm);                               \
+    /* [ref: domain/domain.hpp:196-243 sync]; props: HOST array of nprops device pointers, element sizes 4 or 8 */    \
+    int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n_in, const T* x, const T* y,    \
+                                                      const T* z, const T* h, int nprops, const void* const* props,    \
+                                                      const int* prop_bytes);                                          \
+    int cstone_b200_domain_sync_finish_##KS##_##TS(cstone_b200_domain* d, K* keys, T* x, T* y, T* z, T* h,             \
+                                                   void* const* props);                                                \
+    /* [ref: domain/domain.hpp:381-386 exchangeHalos] arrays: HOST array of device pointers of length n_new */        \
+    int cstone_b200_domain_exchange_halos_##KS##_##TS(cstone_b200_domain* d, int narrays, void* const* arrays,         \
+                                                      const int* elem_bytes);                                          \
+    /* [ref: domain/domain.hpp:389-437] accessors; info[8] = start, end, n_total, n_leaves(focus), n_nodes(focus),    \
+     * n_leaves(global), num halo send particles, num halo recv particles */                                           \
+    int cstone_b200_domain_info_##KS##_##TS(const cstone_b200_domain* d, int64_t* info8);                              \
+    int cstone_b200_domain_box_##KS##_##TS(const cstone_b200_domain* d, cstone_box_##TS* box_out);                     \
+    /* device views of the search tree over assigned + halo particles, valid until the next sync:                     \
+     * ptrs[10] = leaves K[L+1], counts u32[L], layout u32[L+1], prefixes K[M], child_offsets i32[M+1],                \
+     *            internal_to_leaf i32[M], leaf_to_internal i32[M], level_range i32[maxLevel+2], centers T[3M],        \
+     *            sizes T[3M]   [ref: tree/octree.hpp:296-317 OctreeNsView, domain/domain.hpp:400-420] */              \
+    int cstone_b200_domain_tree_view_##KS##_##TS(const cstone_b200_domain* d, const void** ptrs10);                    \
+    /* global (replicated) tree on the HOST: leaves K[Lg+1], counts u32[Lg], rank boundaries K[nranks+1] */            \
+    int cstone_b200_domain_global_tree_##KS##_##TS(const cstone_b200_domain* d, const K** leaves,                      \
+                                                   const uint32_t** counts, const K** assignment);                     \
+    /* findNeighbors over the assigned range with the domain's own tree [ref: findneighbors.hpp:167-178] */           \
+    int cstone_b200_domain_find_neighbors_##KS##_##TS(const cstone_b200_domain* d, const T* x, const T* y,             \
+                                                      const T* z, const T* h, uint32_t ngmax, uint32_t* neighbors,     \
+                                                      uint32_t* neighbors_count);
+
+CSB_DOMAIN_DECL(k64, uint64_t, f64, double)
+CSB_DOMAIN_DECL(k64, uint64_t, f32, float)
+CSB_DOMAIN_DECL(k32, uint32_t, f64, double)
+CSB_DOMAIN_DECL(k32, uint32_t, f32, float)
+
+/* ---- host-side decomposition logic, exported for CPU tests (no GPU needed) ------------------------------
+ * [ref: domain/domaindecomp.hpp:48-71 uniformBins, :115-124 makeSfcAssignment, :139-166 limitBoundaryShifts]
+ * leaves[L+1], counts[L] -> boundaries[nranks+1] (keys) and rank_counts[nranks];
+ * old_boundaries may be NULL (first call). */
+int cstone_b200_host_assignment_k64(int nranks, const uint64_t* leaves, const uint32_t* counts, int32_t num_leaves,
+                                    const uint64_t* old_boundaries, uint64_t* boundaries, uint32_t* rank_counts);
+int cstone_b200_host_assignment_k32(int nranks, const uint32_t* leaves, const uint32_t* counts, int32_t num_leaves,
+                                    const uint32_t* old_boundaries, uint32_t* boundaries, uint32_t* rank_counts);
+/* [ref: sfc/box.hpp:415-431 limitBoxShrinking] limits are {xmin,xmax,ymin,ymax,zmin,zmax} */
+void cstone_b200_host_limit_box_shrinking_f64(const double* fitting6, const double* previous6, double* out6);
+void cstone_b200_host_limit_box_shrinking_f32(const float* fitting6, const float* previous6, float* out6);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

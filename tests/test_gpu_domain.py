@@ -1,0 +1,85 @@
+"""Single-rank Domain (engine behind cstone::Domain<KeyType,T,GpuTag>) against the CPU checkers: after sync the
+arrays are the SFC-sorted input (bit-exact keys / permutation), the tree equals computeOctree(bucketFocus), properties
+travel with their particles, neighbour lists equal the oracle's.  The multi-rank path is tested by
+tools/domain_ranks.py under torchrun (2 GPUs) and, for the host logic, by tests/test_domain_host.py on the CPU."""
+import numpy as np
+import pytest
+
+import gen
+from oracle import loader
+from test_oracle_vs_ref import make_case
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("kd,fd", [(np.uint64, np.float64), (np.uint32, np.float32), (np.uint64, np.float32)])
+def test_single_rank_sync_matches_oracle(kd, fd, port):
+    import torch
+    from cornerstone_octree_b200 import ops
+    from cornerstone_octree_b200.domain import Domain
+    n = 60000
+    x, y, z, h, _ = make_case("gaussian", n, fd, (0, 0, 0))
+    bits = 64 if kd == np.uint64 else 32
+    td = torch.float64 if fd == np.float64 else torch.float32
+    ids = np.arange(n, dtype=np.int64)
+    mass = (np.arange(n) % 7).astype(np.float32)
+    dom = Domain(0, 1, 64, 16, 0.5, ops.make_box((-1.0, 1.0), dtype=td), key_bits=bits, dtype=td)
+    dx, dy, dz, dh = (torch.from_numpy(a).cuda() for a in (x, y, z, h))
+    keys, sx, sy, sz, sh, (sid, sm) = dom.sync(dx, dy, dz, dh, [torch.from_numpy(ids).cuda(), torch.from_numpy(mass).cuda()])
+    assert dom.start_index == 0 and dom.end_index == n and dom.n_particles_with_halos == n
+
+    # the box of an open-boundary Domain is the tight bounding box [ref: sfc/box_mpi.hpp:85-119]
+    b = dom.box()
+    lim = [x.min(), x.max(), y.min(), y.max(), z.min(), z.max()]
+    assert [b.limits[i] for i in range(6)] == [fd(v) for v in lim]
+    obox = loader.make_box(lim, (0, 0, 0), fd)
+    okeys = port.compute_sfc_keys(1, x, y, z, obox, kd)
+    oskeys, order = port.sort_by_key(okeys)
+    assert np.array_equal(keys.cpu().numpy().view(kd), oskeys)
+    assert np.array_equal(sid.cpu().numpy(), ids[order])
+    for got, src in ((sx, x), (sy, y), (sz, z), (sh, h), (sm, mass)):
+        assert np.array_equal(got.cpu().numpy(), src[order])
+
+    # search tree == computeOctree(bucketSizeFocus) on the sorted keys
+    tree, counts = port.compute_octree(oskeys, 16)
+    t = dom.tree_arrays()
+    assert np.array_equal(t["leaves"].cpu().numpy().view(kd), tree)
+    assert np.array_equal(t["counts"].cpu().numpy().view(np.uint32), counts)
+    oc = port.build_octree(tree)
+    assert np.array_equal(t["prefixes"].cpu().numpy().view(kd), oc["prefixes"])
+    assert np.array_equal(t["child_offsets"].cpu().numpy()[:oc["num_nodes"]], oc["child_offsets"][:oc["num_nodes"]])
+
+    # neighbours through the Domain's tree
+    nb, nc = dom.find_neighbors(sx, sy, sz, sh, 100)
+    centers, sizes = port.geo_centers(1, oc["prefixes"], obox, fd)
+    layout = np.zeros(tree.size, dtype=np.uint32)
+    np.cumsum(counts, out=layout[1:])
+    onb, onc = port.find_neighbors(x[order], y[order], z[order], h[order], 0, n, obox, oc, layout, centers, sizes, 100)
+    assert np.array_equal(nc.cpu().numpy().view(np.uint32), onc)
+    valid = np.arange(100)[None, :] < np.minimum(onc, 100)[:, None]
+    assert np.array_equal(np.where(valid, nb.cpu().numpy().view(np.uint32), 0), np.where(valid, onb, 0))
+
+    # second sync: particles moved a little; sizes must match, results stay consistent with a fresh computation
+    rng = np.random.default_rng(5)
+    x2 = (sx.cpu().numpy() + (0.01 * rng.standard_normal(n)).astype(fd)).astype(fd)
+    keys2, sx2, sy2, sz2, sh2, (sid2, _) = dom.sync(torch.from_numpy(x2).cuda(), sy, sz, sh, [sid, sm])
+    k2 = keys2.cpu().numpy().view(kd)
+    assert np.all(k2[1:] >= k2[:-1])
+    assert np.array_equal(np.sort(sid2.cpu().numpy()), ids)
+    b2 = dom.box()
+    obox2 = loader.make_box([b2.limits[i] for i in range(6)], (0, 0, 0), fd)
+    assert np.array_equal(port.compute_sfc_keys(1, sx2.cpu().numpy(), sy2.cpu().numpy(), sz2.cpu().numpy(), obox2, kd), k2)
+    t2 = dom.tree_arrays()
+    leaves2 = t2["leaves"].cpu().numpy().view(kd)
+    c2 = port.compute_node_counts(leaves2, k2)
+    assert np.array_equal(c2, t2["counts"].cpu().numpy().view(np.uint32)) and c2.max() <= 16 or leaves2.size > 2
+
+    with pytest.raises(Exception):
+        dom.sync(dx[:100].contiguous(), dy[:100].contiguous(), dz[:100].contiguous(), dh[:100].contiguous())
+    dom.close()
+
+
+def test_bucket_precondition():
+    from cornerstone_octree_b200.domain import Domain
+    with pytest.raises(RuntimeError):
+        Domain(0, 1, 8, 16)
