@@ -33,6 +33,8 @@ if ROOT not in sys.path:
 METRIC = "Domain::sync + findNeighbors"
 UNIT = "Mparticles/s"
 NG0 = 100
+# dram__bytes_read.sum + dram__bytes_write.sum of one findNeighborsKernel launch at 32 M uniform (profiles/r01_*)
+NEIGHBOR_TRAFFIC_BYTES = 28_636_622_000
 
 
 # ------------------------------------------------------------------------------------------------ inputs
@@ -179,18 +181,17 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=2_000_000, help="particles of the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--steady", action="store_true",
-                    help="steady-state sync: one leaf-array update step from the previous tree instead of a build "
-                         "from the root")
+    ap.add_argument("--global-bucket", type=int, default=65536, help="bucketSize of the replicated global tree")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    workload = ("%dM %s particles per GPU, u64 Hilbert keys, double x/y/z/h, bucketSize=%d: key->sort->gather->"
-                "leaf array (%s)->link->centres->layout->radii->findHalos(8 virtual ranks)->findNeighbors(ngmax=%d)" %
-                (args.n // 1_000_000, args.dist, args.bucket,
-                 "update step" if args.steady else "computeOctree from root", args.ngmax))
+    workload = ("%dM %s particles per GPU, u64 Hilbert keys, double x/y/z/h, bucketSizeFocus=%d: steady-state "
+                "Domain::sync (box, keys, sort, global tree + assignment, particle exchange, halo discovery + exchange, "
+                "tree update, linking, centres) + findNeighbors(ngmax=%d) over the assigned particles%s" %
+                (args.n // 1_000_000, args.dist, args.bucket, args.ngmax,
+                 "; + findHalos for 8 virtual ranks (configs[1])" if int(os.environ.get("WORLD_SIZE", "1")) == 1 else ""))
 
     if args.impl == "reference":
         if rank != 0:
@@ -212,94 +213,154 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    import ctypes as C
     import cornerstone_octree_b200 as pkg
     from cornerstone_octree_b200 import ops
-    from cornerstone_octree_b200.pipeline import HotPath
+    from cornerstone_octree_b200._lib import call
+    from cornerstone_octree_b200.domain import Domain
 
     n = args.n
+    # every rank starts with its slab of an UNSORTED global cloud (as test/integration_mpi/domain_nranks.cpp:103-109)
     x, y, z, h, lim = make_particles(n, args.dist, 42 + rank)
+    if args.dist == "uniform" and world > 1:
+        h = h / world ** (1.0 / 3.0)  # same ~100 neighbours at the global density of world * n particles
     box = ops.make_box(lim)
-    host = [torch.from_numpy(a).pin_memory() for a in (x, y, z, h)]
-    dev = [t.cuda(non_blocking=True) for t in host]
-    torch.cuda.synchronize()
-    hp = HotPath(n, 64, torch.float64, args.bucket, args.ngmax)
+    dom = Domain(rank, world, args.global_bucket, args.bucket, 0.5, box)
+    dom.init_comm_from_torch()
+    dev = [torch.from_numpy(a).cuda() for a in (x, y, z, h)]
+    del x, y, z
+    amp = float(0.1 * h[0])
+    state = {"a": dev, "sign": 1.0, "nb": None, "nc": None, "flags": None}
+    vranks = 8
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    cold = not args.steady
+    def drift(arrs):
+        """small deterministic displacement (0.1 h) so that every sync sees moved particles"""
+        xx, yy, zz, hh = arrs
+        w = 2.0 * math.pi * 37.0
+        xx.add_(torch.sin(yy * w), alpha=amp * state["sign"])
+        yy.add_(torch.sin(zz * w), alpha=amp * state["sign"])
+        zz.add_(torch.sin(xx * w), alpha=amp * state["sign"])
+        state["sign"] = -state["sign"]
 
-    steady_in = []
+    def halos_single_rank(t_leaves, n_leaves, info):
+        """N = 1 only: a single rank has no halos, so the halo search of BASELINE configs[1] is run for 8 virtual
+        ranks on the Domain's tree: every leaf is searched exactly once as a local leaf"""
+        ptrs = info
+        if state["flags"] is None or state["flags"].shape[1] < n_leaves:
+            state["flags"] = torch.empty((vranks, int(n_leaves * 1.1) + 64), dtype=torch.int32, device="cuda")
+            state["radii"] = torch.empty(int(n_leaves * 1.1) + 64, dtype=torch.float32, device="cuda")
+        fl = state["flags"]
+        fl.zero_()
+        call("halo_radii_f64", ops._p(state["a"][3]), C.c_void_p(ptrs[2]), n_leaves, 2.0, ops._p(state["radii"]), ops._stream())
+        bx = dom.box()
+        for r in range(vranks):
+            first, last = r * n_leaves // vranks, (r + 1) * n_leaves // vranks
+            call("find_halos_k64_f64", 1, C.c_void_p(ptrs[3]), C.c_void_p(ptrs[4]), C.c_void_p(ptrs[5]), C.c_void_p(ptrs[0]),
+                 ops._p(state["radii"]), C.byref(bx), first, last, ops._p(fl[r]), ops._stream())
 
-    def run_step(time_stages=False):
-        if args.steady and steady_in:
-            return hp.step(*steady_in, box, cold=False, time_stages=time_stages)
-        Lx = hp.step(*dev, box, cold=True, time_stages=time_stages)
-        if args.steady:  # later steps start from the SFC-ordered arrays and the previous leaf array
-            steady_in.extend(t.clone() for t in hp.sorted)
-        return Lx
+    from cornerstone_octree_b200.domain import _fn, _check
+    tree_ptrs = (C.c_void_p * 10)()
 
-    # ---- warm-up (also sizes the leaf / tree buffers)
-    for _ in range(max(args.warmup, 1)):
-        L = run_step()
+    def run_step(marks=None):
+        def mark(name):
+            if marks is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                marks.append((name, e))
+        mark("start")
+        drift(state["a"])
+        mark("drift")
+        keys, sx, sy, sz, sh, _ = dom.sync(*state["a"])
+        state["a"] = [sx, sy, sz, sh]
+        state["keys"] = keys
+        mark("sync")
+        if world == 1:
+            _check(_fn("tree_view", 64, torch.float64)(dom._h, tree_ptrs), "tree_view")
+            halos_single_rank(None, dom._info()[3], tree_ptrs)
+        mark("find_halos_8_virtual_ranks")
+        nw = dom.n_particles
+        if state["nb"] is None or state["nb"].shape[0] < nw:
+            cap = int(nw * 1.05) + 1024
+            state["nb"] = torch.empty((cap, args.ngmax), dtype=torch.int32, device="cuda")
+            state["nc"] = torch.empty(cap, dtype=torch.int32, device="cuda")
+        dom.find_neighbors(sx, sy, sz, sh, args.ngmax, state["nb"], state["nc"])
+        mark("find_neighbors")
+        return nw
+
+    # ---- warm-up: the first sync distributes the unsorted cloud and converges the trees (cold), the rest are steady
+    t0 = time.perf_counter()
+    run_step()
+    barrier()
+    first_sync_s = time.perf_counter() - t0
+    for _ in range(max(args.warmup, 3) - 1):
+        run_step()
     barrier()
 
     # ---- device-resident timing: EXACTLY K steps between two events
     sampler = ClockSampler(local_rank)
     launches0 = pkg.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    stage_acc = {}
+    stage_acc, engine_acc = {}, {}
     barrier()
     ev0.record()
-    stage_events = []
+    all_marks = []
+    n_assigned = 0
     for _ in range(args.steps):
-        L = run_step(time_stages=True)
-        stage_events.append(hp.events)
+        marks = []
+        n_assigned = run_step(marks)
+        all_marks.append(marks)
+        for k, v in dom.stage_ms().items():
+            engine_acc[k] = engine_acc.get(k, 0.0) + v / args.steps
     ev1.record()
     barrier()
     ms_total = ev0.elapsed_time(ev1)
     launches = pkg.launch_count() - launches0
     clocks = sampler.stop()
-    for evs in stage_events:
-        for (_, a), (name, b) in zip(evs[:-1], evs[1:]):
+    for marks in all_marks:
+        for (_, a), (name, b) in zip(marks[:-1], marks[1:]):
             stage_acc[name] = stage_acc.get(name, 0.0) + a.elapsed_time(b) / args.steps
     t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+    cnt = torch.tensor([float(n_assigned), float(dom.n_particles_with_halos - n_assigned)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
     ms_step = float(t.item()) / args.steps
-    value = n * world / (ms_step * 1e-3) / 1e6
+    n_global = int(cnt[0].item())
+    value = n_global / (ms_step * 1e-3) / 1e6
+    nc = state["nc"][:n_assigned]
+    nc_mean = float(nc.to(torch.float64).mean().item())
+    nc_stored = float(torch.clamp(nc, max=args.ngmax).to(torch.float64).mean().item())
+    info = dom._info()
 
-    nc_mean = float(hp.neighbors_count.to(torch.float64).mean().item())
-    nc_stored = float(torch.clamp(hp.neighbors_count, max=args.ngmax).to(torch.float64).mean().item())
-
-    # ---- end to end from pinned host buffers through the same calls
+    # ---- end to end: pinned host -> device -> sync + findNeighbors -> pinned host, every step
     e2e = None
     if not args.no_e2e:
-        M = hp.octree.num_nodes
-        out_host = dict(keys=torch.empty(n, dtype=torch.int64).pin_memory(),
-                        nc=torch.empty(n, dtype=torch.int32).pin_memory(),
-                        tree=torch.empty(L + 1, dtype=torch.int64).pin_memory(),
-                        counts=torch.empty(L, dtype=torch.int32).pin_memory(),
-                        flags=torch.empty((hp.vranks, L), dtype=torch.int32).pin_memory(),
-                        sorted=[torch.empty(n, dtype=torch.float64).pin_memory() for _ in range(4)])
-        dstage = [torch.empty_like(d) for d in dev]
+        nt = dom.n_particles_with_halos
+        hin = [a.cpu().pin_memory() for a in state["a"]]
+        hout = dict(keys=torch.empty(int(nt * 1.2) + 1024, dtype=torch.int64).pin_memory(),
+                    arr=[torch.empty(int(nt * 1.2) + 1024, dtype=torch.float64).pin_memory() for _ in range(4)],
+                    nc=torch.empty(int(n_assigned * 1.2) + 1024, dtype=torch.int32).pin_memory())
+        moved = {"h2d": 0, "d2h": 0}
 
         def e2e_step():
-            for d, s in zip(dstage, host):
-                d.copy_(s, non_blocking=True)
-            Lx = hp.step(*dstage, box, cold=True)
-            out_host["keys"].copy_(hp.keys, non_blocking=True)
-            out_host["nc"].copy_(hp.neighbors_count, non_blocking=True)
-            out_host["tree"][:Lx + 1].copy_(hp.leaves.tree_a[:Lx + 1], non_blocking=True)
-            out_host["counts"][:Lx].copy_(hp.leaves.counts_buf[:Lx], non_blocking=True)
-            for r in range(hp.vranks):
-                out_host["flags"][r, :Lx].copy_(hp.flags[r, :Lx], non_blocking=True)
-            for o, s in zip(out_host["sorted"], hp.sorted):
-                o.copy_(s, non_blocking=True)
+            state["a"] = [t_.cuda(non_blocking=True) for t_ in hin]
+            moved["h2d"] = sum(t_.numel() * t_.element_size() for t_ in hin)
+            nw = run_step()
+            m = dom.n_particles_with_halos
+            hout["keys"][:m].copy_(state["keys"], non_blocking=True)
+            for o, s_ in zip(hout["arr"], state["a"]):
+                o[:m].copy_(s_, non_blocking=True)
+            hout["nc"][:nw].copy_(state["nc"][:nw], non_blocking=True)
+            moved["d2h"] = m * 8 + 4 * m * 8 + nw * 4
             torch.cuda.synchronize()
-            return int(out_host["nc"][0])
+            # the next step starts from what the host received (sizes must match the Domain's state)
+            for k in range(4):
+                hin[k] = hout["arr"][k][:m]
 
         e2e_step()
         barrier()
@@ -312,56 +373,64 @@ def main():
         if world > 1:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         ms_e2e = float(te.item()) / args.steps
-        h2d = 4 * n * 8
-        d2h = n * 8 + n * 4 + (L + 1) * 8 + L * 4 + hp.vranks * L * 4 + 4 * n * 8
-        e2e = dict(value=n * world / (ms_e2e * 1e-3) / 1e6, unit=UNIT, h2d_bytes_per_step=h2d,
-                   d2h_bytes_per_step=d2h, ms_per_step=ms_e2e,
-                   outputs="sorted keys + x,y,z,h, leaf array + counts, halo flags, neighbour counts; the neighbour "
-                           "lists (%d x %d x 4 B) stay device-resident as for Domain<...,GpuTag> clients" %
-                           (n, args.ngmax))
+        e2e = dict(value=n_global / (ms_e2e * 1e-3) / 1e6, unit=UNIT, h2d_bytes_per_step=int(moved["h2d"]),
+                   d2h_bytes_per_step=int(moved["d2h"]), ms_per_step=ms_e2e,
+                   outputs="keys, x, y, z, h (assigned + halos, SFC order) and neighbour counts; the neighbour lists "
+                           "(%d x %d x 4 B per rank) stay device-resident as for Domain<...,GpuTag> clients" %
+                           (n_assigned, args.ngmax))
 
     if rank != 0:
+        dom.close()
         if world > 1:
             dist.destroy_process_group()
         return 0
 
-    # ---- roofline of the dominant kernel + per-stage table
+    # ---- roofline of the dominant kernel + per-stage tables
     peak, peak_src = load_peaks()
     sK, sT = 8, 8
+    npart = n_assigned
     alg = {
-        "sfc_keys": n * (3 * sT + 2 * sK),
-        "sort": n * (sK + 8 * 2 * (sK + 4) - 4),          # histogram read + 8 passes r/w of (key, u32); pass 0 reads no value
-        "gather": n * (4 + 4 * 2 * sT),
-        "find_neighbors": n * (4 * sT + 4) + 4.0 * nc_stored * n,
+        "sfc_keys": npart * (3 * sT + 2 * sK),
+        "sort": npart * (sK + 8 * 2 * (sK + 4) - 4),      # histogram read + 8 passes r/w of (key, u32); pass 0 reads no value
+        "find_neighbors": npart * (4 * sT + 4) + 4.0 * nc_stored * npart,
     }
     stages = {}
-    for name, ms in stage_acc.items():
+    for name, ms in list(stage_acc.items()) + [("sync." + k, v) for k, v in engine_acc.items()]:
         d = dict(ms=round(ms, 4), share=round(ms / ms_step, 4))
-        if name in alg:
-            gbs = alg[name] / (ms * 1e-3) / 1e9
-            d.update(alg_bytes=int(alg[name]), gbs=round(gbs, 1), frac=round(gbs / peak, 4))
+        key = name.replace("sync.", "")
+        if key in alg:
+            gbs = alg[key] / (ms * 1e-3) / 1e9
+            d.update(alg_bytes=int(alg[key]), gbs=round(gbs, 1), frac=round(gbs / peak, 4))
         stages[name] = d
-    dom = max(("find_neighbors", "sort", "sfc_keys", "gather"), key=lambda k: stage_acc.get(k, 0.0))
-    kernel_name = {"find_neighbors": "findNeighborsKernel<double>", "sort": "onesweepKernel<u64> x8 + histogram",
-                   "sfc_keys": "sfcKeysKernel", "gather": "gatherMultiKernel"}[dom]
-    ach = alg[dom] / (stage_acc[dom] * 1e-3) / 1e9
-    roofline = dict(bound="hbm", kernel=kernel_name, achieved=round(ach, 1), peak=peak, unit="GB/s",
-                    frac=round(ach / peak, 4), traffic=None, peak_source=peak_src,
-                    alg_bytes_per_launch=int(alg[dom]), launch_ms=round(stage_acc[dom], 4))
+    ach = alg["find_neighbors"] / (stage_acc["find_neighbors"] * 1e-3) / 1e9
+    roofline = dict(bound="hbm", kernel="findNeighborsKernel<double>", achieved=round(ach, 1), peak=peak, unit="GB/s",
+                    frac=round(ach / peak, 4), traffic=NEIGHBOR_TRAFFIC_BYTES, peak_source=peak_src,
+                    alg_bytes_per_launch=int(alg["find_neighbors"]), launch_ms=round(stage_acc["find_neighbors"], 4),
+                    note="issue-bound, not HBM-bound: see DESIGN.md section 4; traffic is the ncu dram read+write of one "
+                         "launch at the N=1 default size (profiles/), null otherwise")
+    if not (world == 1 and n == 32_000_000 and args.dist == "uniform"):
+        roofline["traffic"] = None
 
     cpu = None
     if not args.no_cpu and world == 1:
         cpu, _ = time_cpu(args.cpu_n, args.dist, args.bucket, args.ngmax, 1, 0)
 
-    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 1),
+    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
                 ms_per_step=ms_step, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64",
                 data="synthetic", impl="b200",
-                config=dict(workload=workload, particles_per_gpu=n, leaves=int(L), neighbours_mean=round(nc_mean, 2),
+                config=dict(workload=workload, particles_per_gpu=n, particles_global=n_global,
+                            halos_global=int(cnt[1].item()), leaves_rank0=int(info[3]), global_leaves=int(info[5]),
+                            neighbours_mean=round(nc_mean, 2), first_sync_s=round(first_sync_s, 3),
+                            drift="0.1 h deterministic displacement before every sync (3 torch kernels, inside the "
+                                  "timed region)",
                             l2="inputs (>=1 GB per stage) exceed the 126 MB L2; no explicit flush",
-                            parallelism="1 rank per GPU" if world == 1 else "%d independent SFC shards" % world),
+                            parallelism="1 rank" if world == 1 else
+                            "%d ranks, SFC-range sharding, NCCL all-reduce of global leaf counts, grouped NCCL "
+                            "send/recv for particle and halo exchange" % world),
                 clocks=clocks, e2e=e2e, gpu_launches=int(launches), roofline=roofline, stages=stages,
                 cpu_baseline=cpu)
     print(json.dumps(line))
+    dom.close()
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -130,6 +130,7 @@ _DOMAIN_PROTOS = {
     "exchange_halos": (_i, [_vp, _i, _vp, _vp]),
     "info": (_i, [_vp, _vp]),
     "box": (_i, [_vp, _vp]),
+    "stage_ms": (_i, [_vp, _vp]),
     "tree_view": (_i, [_vp, _vp]),
     "global_tree": (_i, [_vp, _vp, _vp, _vp]),
     "find_neighbors": (_i, [_vp, _vp, _vp, _vp, _vp, _u32, _vp, _vp]),

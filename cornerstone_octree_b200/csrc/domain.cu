@@ -407,6 +407,16 @@ public:
     {
     }
     void setComm(void* c) { comm_ = reinterpret_cast<ncclComm_t>(c); }
+    //! device time between the stage markers of the last sync (ms); kNumMarks - 1 values
+    void stageMs(float* ms) const
+    {
+        for (int k = 0; k + 1 < kNumMarks; ++k)
+        {
+            ms[k] = 0.f;
+            if (ev_[k] && ev_[k + 1]) cudaEventElapsedTime(&ms[k], ev_[k], ev_[k + 1]);
+        }
+    }
+    static constexpr int kNumMarks = 11;
 
     int64_t syncBegin(uint64_t nIn, const T* x, const T* y, const T* z, const T* h, int nprops, const void* const* props,
                       const int* propBytes);
@@ -432,6 +442,12 @@ public:
     }
 
 private:
+    void mark(int k)
+    {
+        if (!ev_[k]) cudaEventCreate(&ev_[k]);
+        cudaEventRecord(ev_[k], s_);
+    }
+    cudaEvent_t ev_[kNumMarks] = {nullptr};
     int updateBox(const T* x, const T* y, const T* z, size_t n);
     int updateGlobalTree(const K* keys, size_t n);
     int allreduceCounts();
@@ -653,7 +669,9 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
     }
 
     // 1. global box
+    mark(0);
     CSB_TRY(updateBox(x + inStart, y + inStart, z + inStart, np));
+    mark(1);
 
     // 2. keys of the particles this rank holds, sorted, with the permutation [ref: domain/assignment.hpp:84-90]
     auto reserveSort = [&](size_t n) -> int
@@ -671,15 +689,19 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
     {
         CSB_CUDA(cudaMemsetAsync(keys, 0, sizeof(K) * np, s_));
         CSB_TRY((Api<K, T>::keys(x + inStart, y + inStart, z + inStart, keys, np, &box_, s_)));
+        mark(2);
         CSB_TRY((Api<K, T>::sort(keys, order_.template as<uint32_t>(), keyBuf_.template as<K>(), valBuf_.template as<uint32_t>(), np,
                                  sortTemp_.p, sortTemp_.bytes, 1, s_)));
     }
+    else mark(2);
+    mark(3);
 
     // 3. replicated global tree and the assignment of its leaves to ranks
     CSB_TRY(updateGlobalTree(keys, np));
     makeAssignment<K>(nRanks_, hGlobalLeaves_.data(), hGlobalCounts_.data(), global_.numNodes,
                       oldBoundaries_.empty() ? nullptr : oldBoundaries_.data(), boundaries_, rankCounts_);
     oldBoundaries_ = boundaries_;
+    mark(4);
 
     void* dst[4 + kMaxProps];
     if (nRanks_ == 1)
@@ -694,6 +716,7 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         if (np) CSB_TRY(gatherMulti(order_.template as<uint32_t>(), np, na, src, dst, eb));
         CSB_TRY(fkeys_.reserve(sizeof(K) * np + 256));
         CSB_CUDA(cudaMemcpyAsync(fkeys_.p, keys, sizeof(K) * np, cudaMemcpyDeviceToDevice, s_));
+        mark(5), mark(6), mark(7), mark(8);
     }
     else
     {
@@ -761,6 +784,7 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
                                          pack_[a].template as<char>() + size_t(sendStart[rank_]) * eb[a],
                                          size_t(sendCount[rank_]) * eb[a], cudaMemcpyDeviceToDevice, s_));
 
+        mark(5);
         // 8. keys + order of the assigned set (P sorted runs) [ref: domain/assignment.hpp:141-150]
         const size_t n = size_t(nAssigned_);
         CSB_TRY(skeys_.reserve(sizeof(K) * n + 256));
@@ -777,13 +801,17 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         CSB_TRY(shAssigned_.reserve(sizeof(T) * n + 256));
         if (n) CSB_TRY(cstone_b200_gather(order_.template as<uint32_t>(), n, recv_[3].p, shAssigned_.p, int(sizeof(T)), s_));
 
+        mark(6);
         // 9. halos
         CSB_TRY(discoverHalos());
+        mark(8);
     }
 
     // 10. search tree over assigned + halo particles, linked, with node centres and layout
     CSB_TRY(convergeTree(search_, fkeys_.template as<K>(), size_t(nTotal_), searchFresh_));
+    mark(9);
     CSB_TRY(linkTree(search_, true));
+    mark(10);
     CSB_CUDA(cudaStreamSynchronize(s_));
     firstCall_ = false;
     return int64_t(nTotal_);
@@ -909,6 +937,7 @@ int Engine<K, T>::discoverHalos()
     }
 
     // h. assigned particles straight to their final position, then the halos of x,y,z,h
+    mark(7);
     const void* src[4 + kMaxProps];
     void* dst[4 + kMaxProps];
     for (int a = 0; a < na; ++a)
@@ -1039,7 +1068,13 @@ int cstone_b200_nccl_comm_destroy(void* comm)
     return ncclCommDestroy(reinterpret_cast<ncclComm_t>(comm)) == ncclSuccess ? 0 : CSTONE_E_NCCL;
 }
 
-#define CSB_DOMAIN_DEF(KS, K, TS, T)                                                                                       cstone_b200_domain* cstone_b200_domain_create_##KS##_##TS(int rank, int nranks, unsigned bucket,                                                                                 unsigned bucketFocus, float theta,                                                                                     const cstone_box_##TS* box)                                  {                                                                                                                          if (!box || nranks < 1 || rank < 0 || rank >= nranks || bucket < bucketFocus || bucketFocus == 0) return nullptr;         return reinterpret_cast<cstone_b200_domain*>(new csb::Engine<K, T>(rank, nranks, bucket, bucketFocus, theta, *box));     }                                                                                                                      void cstone_b200_domain_destroy_##KS##_##TS(cstone_b200_domain* d) { delete reinterpret_cast<csb::Engine<K, T>*>(d); }     int cstone_b200_domain_set_comm_##KS##_##TS(cstone_b200_domain* d, void* comm)                                         {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              reinterpret_cast<csb::Engine<K, T>*>(d)->setComm(comm);                                                                return 0;                                                                                                          }                                                                                                                      int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n, const T* x, const T* y,                                                             const T* z, const T* h, int nprops, const void* const* props,                                                          const int* pb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncBegin(n, x, y, z, h, nprops, props, pb);                       }                                                                                                                      int cstone_b200_domain_sync_finish_##KS##_##TS(cstone_b200_domain* d, K* keys, T* x, T* y, T* z, T* h,                                                                void* const* props)                                                     {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncFinish(keys, x, y, z, h, props);                               }                                                                                                                      int cstone_b200_domain_exchange_halos_##KS##_##TS(cstone_b200_domain* d, int na, void* const* arrays,                                                                    const int* eb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              int st = reinterpret_cast<csb::Engine<K, T>*>(d)->exchangeHalos(na, arrays, eb);                                       if (st) return st;                                                                                                     cudaError_t e = cudaStreamSynchronize(nullptr);                                                                        return int(e);                                                                                                     }                                                                                                                      int cstone_b200_domain_info_##KS##_##TS(const cstone_b200_domain* d, int64_t* info8)                                   {                                                                                                                          if (!d || !info8) return CSTONE_E_INVALID_ARGUMENT;                                                                    reinterpret_cast<const csb::Engine<K, T>*>(d)->info(info8);                                                            return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_box_##KS##_##TS(const cstone_b200_domain* d, cstone_box_##TS* out)                              {                                                                                                                          if (!d || !out) return CSTONE_E_INVALID_ARGUMENT;                                                                      *out = reinterpret_cast<const csb::Engine<K, T>*>(d)->box();                                                           return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_tree_view_##KS##_##TS(const cstone_b200_domain* d, const void** ptrs10)                         {                                                                                                                          if (!d || !ptrs10) return CSTONE_E_INVALID_ARGUMENT;                                                                   reinterpret_cast<const csb::Engine<K, T>*>(d)->treeView(ptrs10);                                                       return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_global_tree_##KS##_##TS(const cstone_b200_domain* d, const K** leaves,                                                                         const uint32_t** counts, const K** assignment)                          {                                                                                                                          if (!d || !leaves || !counts || !assignment) return CSTONE_E_INVALID_ARGUMENT;                                         reinterpret_cast<const csb::Engine<K, T>*>(d)->globalTree(leaves, counts, assignment);                                 return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_find_neighbors_##KS##_##TS(const cstone_b200_domain* d, const T* x, const T* y,                                                                   const T* z, const T* h, uint32_t ngmax, uint32_t* nb,                                                                  uint32_t* nc)                                                        {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<const csb::Engine<K, T>*>(d)->findNeighbors(x, y, z, h, ngmax, nb, nc);                    }
+#define CSB_DOMAIN_DEF(KS, K, TS, T)                                                                                       cstone_b200_domain* cstone_b200_domain_create_##KS##_##TS(int rank, int nranks, unsigned bucket,                                                                                 unsigned bucketFocus, float theta,                                                                                     const cstone_box_##TS* box)                                  {                                                                                                                          if (!box || nranks < 1 || rank < 0 || rank >= nranks || bucket < bucketFocus || bucketFocus == 0) return nullptr;         return reinterpret_cast<cstone_b200_domain*>(new csb::Engine<K, T>(rank, nranks, bucket, bucketFocus, theta, *box));     }                                                                                                                      void cstone_b200_domain_destroy_##KS##_##TS(cstone_b200_domain* d) { delete reinterpret_cast<csb::Engine<K, T>*>(d); }     int cstone_b200_domain_set_comm_##KS##_##TS(cstone_b200_domain* d, void* comm)                                         {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              reinterpret_cast<csb::Engine<K, T>*>(d)->setComm(comm);                                                                return 0;                                                                                                          }                                                                                                                      int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n, const T* x, const T* y,                                                             const T* z, const T* h, int nprops, const void* const* props,                                                          const int* pb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncBegin(n, x, y, z, h, nprops, props, pb);                       }                                                                                                                      int cstone_b200_domain_sync_finish_##KS##_##TS(cstone_b200_domain* d, K* keys, T* x, T* y, T* z, T* h,                                                                void* const* props)                                                     {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncFinish(keys, x, y, z, h, props);                               }                                                                                                                      int cstone_b200_domain_exchange_halos_##KS##_##TS(cstone_b200_domain* d, int na, void* const* arrays,                                                                    const int* eb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              int st = reinterpret_cast<csb::Engine<K, T>*>(d)->exchangeHalos(na, arrays, eb);                                       if (st) return st;                                                                                                     cudaError_t e = cudaStreamSynchronize(nullptr);                                                                        return int(e);                                                                                                     }                                                                                                                      int cstone_b200_domain_info_##KS##_##TS(const cstone_b200_domain* d, int64_t* info8)                                   {                                                                                                                          if (!d || !info8) return CSTONE_E_INVALID_ARGUMENT;                                                                    reinterpret_cast<const csb::Engine<K, T>*>(d)->info(info8);                                                            return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_stage_ms_##KS##_##TS(const cstone_b200_domain* d, float* ms10)                              \
+    {                                                                                                                  \
+        if (!d || !ms10) return CSTONE_E_INVALID_ARGUMENT;                                                             \
+        reinterpret_cast<const csb::Engine<K, T>*>(d)->stageMs(ms10);                                                  \
+        return 0;                                                                                                      \
+    }                                                                                                                  \
+    int cstone_b200_domain_box_##KS##_##TS(const cstone_b200_domain* d, cstone_box_##TS* out)                              {                                                                                                                          if (!d || !out) return CSTONE_E_INVALID_ARGUMENT;                                                                      *out = reinterpret_cast<const csb::Engine<K, T>*>(d)->box();                                                           return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_tree_view_##KS##_##TS(const cstone_b200_domain* d, const void** ptrs10)                         {                                                                                                                          if (!d || !ptrs10) return CSTONE_E_INVALID_ARGUMENT;                                                                   reinterpret_cast<const csb::Engine<K, T>*>(d)->treeView(ptrs10);                                                       return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_global_tree_##KS##_##TS(const cstone_b200_domain* d, const K** leaves,                                                                         const uint32_t** counts, const K** assignment)                          {                                                                                                                          if (!d || !leaves || !counts || !assignment) return CSTONE_E_INVALID_ARGUMENT;                                         reinterpret_cast<const csb::Engine<K, T>*>(d)->globalTree(leaves, counts, assignment);                                 return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_find_neighbors_##KS##_##TS(const cstone_b200_domain* d, const T* x, const T* y,                                                                   const T* z, const T* h, uint32_t ngmax, uint32_t* nb,                                                                  uint32_t* nc)                                                        {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<const csb::Engine<K, T>*>(d)->findNeighbors(x, y, z, h, ngmax, nb, nc);                    }
 
 CSB_DOMAIN_DEF(k64, uint64_t, f64, double)
 CSB_DOMAIN_DEF(k64, uint64_t, f32, float)

@@ -128,6 +128,15 @@ class Domain:
     def n_particles_with_halos(self):
         return self._info()[2]
 
+    STAGES = ["box", "sfc_keys", "sort", "global_tree", "exchange", "resort", "halo_discovery", "halo_exchange",
+              "search_tree", "link_tree"]
+
+    def stage_ms(self):
+        """device time (ms) of the stages of the last sync, measured with CUDA events inside the engine"""
+        ms = (C.c_float * 10)()
+        _check(_fn("stage_ms", self.bits, self.fd)(self._h, ms), "stage_ms")
+        return dict(zip(self.STAGES, [float(v) for v in ms]))
+
     def box(self):
         b = BoxF32() if self.fd == torch.float32 else BoxF64()
         _check(_fn("box", self.bits, self.fd)(self._h, C.byref(b)), "box")

@@ -58,6 +58,10 @@ int cstone_b200_nccl_comm_destroy(void* comm);
      * n_leaves(global), num halo send particles, num halo recv particles */                                           \
     int cstone_b200_domain_info_##KS##_##TS(const cstone_b200_domain* d, int64_t* info8);                              \
     int cstone_b200_domain_box_##KS##_##TS(const cstone_b200_domain* d, cstone_box_##TS* box_out);                     \
+    /* device time (ms, CUDA events) of the 10 stages of the last sync_begin: box, sfc keys, sort, global tree +      \
+     * assignment, particle exchange (pack gather + NCCL), re-key + re-sort of the assigned set, halo discovery,       \
+     * final gather + halo exchange + halo keys, search-tree update, linking + centres + layout */                     \
+    int cstone_b200_domain_stage_ms_##KS##_##TS(const cstone_b200_domain* d, float* ms10);                     \
     /* device views of the search tree over assigned + halo particles, valid until the next sync:                     \
      * ptrs[10] = leaves K[L+1], counts u32[L], layout u32[L+1], prefixes K[M], child_offsets i32[M+1],                \
      *            internal_to_leaf i32[M], leaf_to_internal i32[M], level_range i32[maxLevel+2], centers T[3M],        \
