@@ -136,7 +136,8 @@ _DOMAIN_PROTOS = {
     "find_neighbors": (_i, [_vp, _vp, _vp, _vp, _vp, _u32, _vp, _vp]),
 }
 DOMAIN_EXPORTED = ["nccl_unique_id", "nccl_comm_init", "nccl_comm_destroy", "host_assignment_k32",
-                   "host_assignment_k64", "host_limit_box_shrinking_f32", "host_limit_box_shrinking_f64"]
+                   "host_assignment_k64", "host_limit_box_shrinking_f32", "host_limit_box_shrinking_f64",
+                   "host_uniform_bins", "host_limit_boundary_shifts_k32", "host_limit_boundary_shifts_k64"]
 for ks in ("k32", "k64"):
     for ts in ("f32", "f64"):
         for _name, (_res, _args) in _DOMAIN_PROTOS.items():
@@ -147,6 +148,11 @@ for ks in ("k32", "k64"):
     _fn = getattr(lib, "cstone_b200_host_assignment_" + ks)
     _fn.restype = _i
     _fn.argtypes = [_i, _vp, _vp, _i32, _vp, _vp, _vp]
+    _fn = getattr(lib, "cstone_b200_host_limit_boundary_shifts_" + ks)
+    _fn.restype = _i
+    _fn.argtypes = [_i, _vp, _vp, _vp, _vp, _i32, _vp]
+lib.cstone_b200_host_uniform_bins.restype = _i
+lib.cstone_b200_host_uniform_bins.argtypes = [_vp, _i32, _i32, _vp, _vp]
 for ts in ("f32", "f64"):
     _fn = getattr(lib, "cstone_b200_host_limit_box_shrinking_" + ts)
     _fn.restype = None

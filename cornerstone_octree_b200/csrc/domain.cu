@@ -1103,6 +1103,35 @@ int cstone_b200_host_assignment_k32(int nranks, const uint32_t* leaves, const ui
     std::copy(c.begin(), c.end(), rankCounts);
     return 0;
 }
+int cstone_b200_host_uniform_bins(const uint32_t* counts, int32_t numLeaves, int32_t numBins, int32_t* bins,
+                                  uint32_t* binCounts)
+{
+    if (numBins < 1 || numLeaves < 0 || !counts || !bins || !binCounts) return CSTONE_E_INVALID_ARGUMENT;
+    std::vector<int> b;
+    std::vector<uint32_t> c;
+    csb::uniformBins(counts, numLeaves, numBins, b, c);
+    std::copy(b.begin(), b.end(), bins);
+    std::copy(c.begin(), c.end(), binCounts);
+    return 0;
+}
+int cstone_b200_host_limit_boundary_shifts_k64(int nranks, const uint64_t* oldB, uint64_t* boundaries,
+                                               const uint64_t* leaves, const uint32_t* counts, int32_t numLeaves,
+                                               uint32_t* rankCounts)
+{
+    if (nranks < 1 || numLeaves < 1 || !oldB || !leaves || !counts || !boundaries || !rankCounts)
+        return CSTONE_E_INVALID_ARGUMENT;
+    csb::limitBoundaryShifts<uint64_t>(nranks, oldB, boundaries, leaves, counts, numLeaves, rankCounts);
+    return 0;
+}
+int cstone_b200_host_limit_boundary_shifts_k32(int nranks, const uint32_t* oldB, uint32_t* boundaries,
+                                               const uint32_t* leaves, const uint32_t* counts, int32_t numLeaves,
+                                               uint32_t* rankCounts)
+{
+    if (nranks < 1 || numLeaves < 1 || !oldB || !leaves || !counts || !boundaries || !rankCounts)
+        return CSTONE_E_INVALID_ARGUMENT;
+    csb::limitBoundaryShifts<uint32_t>(nranks, oldB, boundaries, leaves, counts, numLeaves, rankCounts);
+    return 0;
+}
 void cstone_b200_host_limit_box_shrinking_f64(const double* fit, const double* prev, double* out)
 {
     csb::limitBoxShrinking<double>(fit, prev, out);

@@ -42,21 +42,12 @@ inline void uniformBins(const uint32_t* counts, int numLeaves, int numBins, std:
     binCounts.back() = uint32_t(scan.back() - scan[bins[numBins - 1]]);
 }
 
-/*! rank boundaries (SFC keys) of an equal-count split of the global leaves, with the shift of every boundary limited
- *  to the previous range of the neighbouring rank
- *  [ref: domain/domaindecomp.hpp:115-124 makeSfcAssignment, :139-166 limitBoundaryShifts] */
+/*! limit the shift of every rank boundary to the previous range of the neighbouring rank and recount if any moved
+ *  [ref: domain/domaindecomp.hpp:139-166 limitBoundaryShifts]; boundaries and rankCounts are updated in place */
 template<class K>
-inline void makeAssignment(int numRanks, const K* leaves, const uint32_t* counts, int numLeaves,
-                           const K* oldBoundaries /* may be null */, std::vector<K>& boundaries,
-                           std::vector<uint32_t>& rankCounts)
+inline void limitBoundaryShifts(int numRanks, const K* oldBoundaries, K* boundaries, const K* leaves,
+                                const uint32_t* counts, int numLeaves, uint32_t* rankCounts)
 {
-    std::vector<int> bins;
-    uniformBins(counts, numLeaves, numRanks, bins, rankCounts);
-    boundaries.resize(numRanks + 1);
-    for (int r = 0; r <= numRanks; ++r)
-        boundaries[r] = leaves[bins[r]];
-
-    if (!oldBoundaries) return;
     bool recount = false;
     for (int r = 1; r < numRanks; ++r)
     {
@@ -70,13 +61,29 @@ inline void makeAssignment(int numRanks, const K* leaves, const uint32_t* counts
     if (!recount) return;
     for (int r = 0; r < numRanks; ++r)
     {
-        int a         = findNodeAbove(leaves, numLeaves + 1, boundaries[r]);
-        int b         = findNodeAbove(leaves, numLeaves + 1, boundaries[r + 1]);
-        size_t c      = 0;
+        int a    = findNodeAbove(leaves, numLeaves + 1, boundaries[r]);
+        int b    = findNodeAbove(leaves, numLeaves + 1, boundaries[r + 1]);
+        size_t c = 0;
         for (int i = a; i < b; ++i)
             c += counts[i];
         rankCounts[r] = uint32_t(c);
     }
+}
+
+/*! rank boundaries (SFC keys) of an equal-count split of the global leaves, shifts limited against the previous
+ *  boundaries when given  [ref: domain/domaindecomp.hpp:115-124 makeSfcAssignment, domain/domain.hpp:288-290] */
+template<class K>
+inline void makeAssignment(int numRanks, const K* leaves, const uint32_t* counts, int numLeaves,
+                           const K* oldBoundaries /* may be null */, std::vector<K>& boundaries,
+                           std::vector<uint32_t>& rankCounts)
+{
+    std::vector<int> bins;
+    uniformBins(counts, numLeaves, numRanks, bins, rankCounts);
+    boundaries.resize(numRanks + 1);
+    for (int r = 0; r <= numRanks; ++r)
+        boundaries[r] = leaves[bins[r]];
+    if (oldBoundaries)
+        limitBoundaryShifts(numRanks, oldBoundaries, boundaries.data(), leaves, counts, numLeaves, rankCounts.data());
 }
 
 //! [ref: sfc/box.hpp:415-431 limitBoxShrinking] the box may lose at most 5 % of its previous extent per side

@@ -88,6 +88,16 @@ int cstone_b200_host_assignment_k64(int nranks, const uint64_t* leaves, const ui
                                     const uint64_t* old_boundaries, uint64_t* boundaries, uint32_t* rank_counts);
 int cstone_b200_host_assignment_k32(int nranks, const uint32_t* leaves, const uint32_t* counts, int32_t num_leaves,
                                     const uint32_t* old_boundaries, uint32_t* boundaries, uint32_t* rank_counts);
+/* [ref: domain/domaindecomp.hpp:48-71 uniformBins] bins[num_bins+1] (leaf indices), bin_counts[num_bins] */
+int cstone_b200_host_uniform_bins(const uint32_t* counts, int32_t num_leaves, int32_t num_bins, int32_t* bins,
+                                  uint32_t* bin_counts);
+/* [ref: domain/domaindecomp.hpp:139-166 limitBoundaryShifts] boundaries / rank_counts are updated in place */
+int cstone_b200_host_limit_boundary_shifts_k64(int nranks, const uint64_t* old_boundaries, uint64_t* boundaries,
+                                               const uint64_t* leaves, const uint32_t* counts, int32_t num_leaves,
+                                               uint32_t* rank_counts);
+int cstone_b200_host_limit_boundary_shifts_k32(int nranks, const uint32_t* old_boundaries, uint32_t* boundaries,
+                                               const uint32_t* leaves, const uint32_t* counts, int32_t num_leaves,
+                                               uint32_t* rank_counts);
 /* [ref: sfc/box.hpp:415-431 limitBoxShrinking] limits are {xmin,xmax,ymin,ymax,zmin,zmax} */
 void cstone_b200_host_limit_box_shrinking_f64(const double* fitting6, const double* previous6, double* out6);
 void cstone_b200_host_limit_box_shrinking_f32(const float* fitting6, const float* previous6, float* out6);

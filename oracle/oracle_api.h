@@ -130,6 +130,24 @@ void ORC(find_neighbors_f64)(const double* x, const double* y, const double* z, 
                              const double* sizes, float search_ext_factor, uint32_t ngmax, uint32_t* neighbors,
                              uint32_t* neighbors_count);
 
+/* --- domain decomposition, host logic (reference build only: liboracle_ref.so)
+ * [ref: domain/domaindecomp.hpp:48-71 uniformBins, :115-124 makeSfcAssignment, :139-166 limitBoundaryShifts,
+ *  sfc/box.hpp:415-431 limitBoxShrinking] --- */
+void cstone_ref_assignment_k32(int nranks, const uint32_t* leaves, const uint32_t* counts, int32_t num_leaves,
+                               const uint32_t* old_boundaries, uint32_t* boundaries, uint32_t* rank_counts);
+void cstone_ref_assignment_k64(int nranks, const uint64_t* leaves, const uint32_t* counts, int32_t num_leaves,
+                               const uint64_t* old_boundaries, uint64_t* boundaries, uint32_t* rank_counts);
+void cstone_ref_uniform_bins(const uint32_t* counts, int32_t num_leaves, int32_t num_bins, int32_t* bins,
+                             uint32_t* bin_counts);
+void cstone_ref_limit_boundary_shifts_k32(int nranks, const uint32_t* old_boundaries, uint32_t* boundaries,
+                                          const uint32_t* leaves, const uint32_t* counts, int32_t num_leaves,
+                                          uint32_t* rank_counts);
+void cstone_ref_limit_boundary_shifts_k64(int nranks, const uint64_t* old_boundaries, uint64_t* boundaries,
+                                          const uint64_t* leaves, const uint32_t* counts, int32_t num_leaves,
+                                          uint32_t* rank_counts);
+void cstone_ref_limit_box_shrinking_f32(const float* fitting6, const float* previous6, float* out6);
+void cstone_ref_limit_box_shrinking_f64(const double* fitting6, const double* previous6, double* out6);
+
 #ifdef __cplusplus
 }
 #endif

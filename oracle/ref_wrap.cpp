@@ -24,6 +24,7 @@
 #include "cstone/traversal/collisions.hpp"
 #include "cstone/domain/layout.hpp"
 #include "cstone/findneighbors.hpp"
+#include "cstone/domain/domaindecomp.hpp"
 
 #define ORACLE_PREFIX cstone_ref_
 #include "oracle_api.h"
@@ -298,3 +299,71 @@ void cstone_ref_find_neighbors_f64(const double* x, const double* y, const doubl
 { findNeighborsW(x, y, z, h, f, l, box, co, i2l, layout, c, s, ext, ngmax, nb, nc); }
 
 } // extern "C"
+
+template<class K>
+static void assignmentW(int nranks, const K* leaves, const uint32_t* counts, int32_t L, const K* oldB, K* boundaries,
+                        uint32_t* rankCounts)
+{
+    std::vector<unsigned> c(counts, counts + L);
+    SfcAssignment<K> a = makeSfcAssignment(nranks, c, leaves);
+    if (oldB)
+    {
+        SfcAssignment<K> old(nranks);
+        for (int r = 0; r <= nranks; ++r)
+            old.set(r, oldB[r], 0);
+        limitBoundaryShifts<K>(old, a, gsl::span<const K>(leaves, L + 1), gsl::span<const unsigned>(counts, L));
+    }
+    for (int r = 0; r <= nranks; ++r)
+        boundaries[r] = a[r];
+    for (int r = 0; r < nranks; ++r)
+        rankCounts[r] = a.totalCount(r);
+}
+template<class T>
+static void limitBoxW(const T* f, const T* p, T* o)
+{
+    Box<T> fit(f[0], f[1], f[2], f[3], f[4], f[5]), prev(p[0], p[1], p[2], p[3], p[4], p[5]);
+    Box<T> r = limitBoxShrinking(fit, prev);
+    o[0] = r.xmin(), o[1] = r.xmax(), o[2] = r.ymin(), o[3] = r.ymax(), o[4] = r.zmin(), o[5] = r.zmax();
+}
+
+extern "C" {
+void cstone_ref_assignment_k32(int n, const uint32_t* l, const uint32_t* c, int32_t L, const uint32_t* ob, uint32_t* b,
+                               uint32_t* rc)
+{ assignmentW(n, l, c, L, ob, b, rc); }
+void cstone_ref_assignment_k64(int n, const uint64_t* l, const uint32_t* c, int32_t L, const uint64_t* ob, uint64_t* b,
+                               uint32_t* rc)
+{ assignmentW(n, l, c, L, ob, b, rc); }
+void cstone_ref_limit_box_shrinking_f32(const float* f, const float* p, float* o) { limitBoxW(f, p, o); }
+void cstone_ref_limit_box_shrinking_f64(const double* f, const double* p, double* o) { limitBoxW(f, p, o); }
+}
+
+template<class K>
+static void limitShiftsW(int nranks, const K* oldB, K* boundaries, const K* leaves, const uint32_t* counts, int32_t L,
+                         uint32_t* rankCounts)
+{
+    SfcAssignment<K> old(nranks), cur(nranks);
+    for (int r = 0; r <= nranks; ++r)
+    {
+        old.set(r, oldB[r], 0);
+        cur.set(r, boundaries[r], r < nranks ? rankCounts[r] : 0);
+    }
+    limitBoundaryShifts<K>(old, cur, gsl::span<const K>(leaves, L + 1), gsl::span<const unsigned>(counts, L));
+    for (int r = 0; r <= nranks; ++r)
+        boundaries[r] = cur[r];
+    for (int r = 0; r < nranks; ++r)
+        rankCounts[r] = cur.totalCount(r);
+}
+
+extern "C" {
+void cstone_ref_uniform_bins(const uint32_t* counts, int32_t L, int32_t numBins, int32_t* bins, uint32_t* binCounts)
+{
+    std::vector<unsigned> c(counts, counts + L);
+    uniformBins(c, gsl::span<TreeNodeIndex>(bins, numBins + 1), gsl::span<LocalIndex>(binCounts, numBins));
+}
+void cstone_ref_limit_boundary_shifts_k32(int n, const uint32_t* ob, uint32_t* b, const uint32_t* l, const uint32_t* c,
+                                          int32_t L, uint32_t* rc)
+{ limitShiftsW(n, ob, b, l, c, L, rc); }
+void cstone_ref_limit_boundary_shifts_k64(int n, const uint64_t* ob, uint64_t* b, const uint64_t* l, const uint32_t* c,
+                                          int32_t L, uint32_t* rc)
+{ limitShiftsW(n, ob, b, l, c, L, rc); }
+}
