@@ -92,7 +92,8 @@ for _name, (_res, _args) in _PROTOS.items():
     _fn.restype = _res
     _fn.argtypes = _args
 
-EXPORTED = ["abi_version", "status_string", "launch_count"] + sorted(_PROTOS)
+EXPORTED = ["abi_version", "status_string", "launch_count", "device_malloc", "device_free", "device_memcpy",
+            "device_memset", "device_synchronize", "set_device"] + sorted(_PROTOS)
 
 
 def status_string(status):

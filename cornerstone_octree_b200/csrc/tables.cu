@@ -148,6 +148,30 @@ int cstone_b200_abi_version(void) { return CSTONE_B200_ABI_VERSION; }
 
 uint64_t cstone_b200_launch_count(void) { return csb::g_launchCount.load(); }
 
+int cstone_b200_device_malloc(void** ptr, size_t bytes)
+{
+    if (!ptr) return CSTONE_E_INVALID_ARGUMENT;
+    *ptr = nullptr;
+    if (bytes == 0) return 0;
+    return int(cudaMalloc(ptr, bytes));
+}
+int cstone_b200_device_free(void* ptr) { return ptr ? int(cudaFree(ptr)) : 0; }
+int cstone_b200_device_memcpy(void* dst, const void* src, size_t bytes, int kind)
+{
+    if (bytes == 0) return 0;
+    if (!dst || !src || kind < 0 || kind > 2) return CSTONE_E_INVALID_ARGUMENT;
+    const cudaMemcpyKind k[3] = {cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice};
+    return int(cudaMemcpy(dst, src, bytes, k[kind]));
+}
+int cstone_b200_device_memset(void* dst, int value, size_t bytes)
+{
+    if (bytes == 0) return 0;
+    if (!dst) return CSTONE_E_INVALID_ARGUMENT;
+    return int(cudaMemset(dst, value, bytes));
+}
+int cstone_b200_device_synchronize(void) { return int(cudaDeviceSynchronize()); }
+int cstone_b200_set_device(int device) { return int(cudaSetDevice(device)); }
+
 const char* cstone_b200_status_string(int status)
 {
     switch (status)
@@ -158,6 +182,8 @@ const char* cstone_b200_status_string(int status)
         case CSTONE_E_TOO_LARGE: return "cstone_b200: problem size exceeds the supported range";
         case CSTONE_E_STACK_OVERFLOW: return "cstone_b200: traversal stack exhausted";
         case CSTONE_E_CAPACITY: return "cstone_b200: output capacity too small";
+        case -6: return "cstone_b200: NCCL error";
+        case -7: return "cstone_b200: array size differs from the previous sync";
         default: break;
     }
     if (status > 0) return cudaGetErrorString(cudaError_t(status));

@@ -82,6 +82,17 @@ const char* cstone_b200_status_string(int status);
 /* number of kernels launched by this library in the calling process so far */
 uint64_t cstone_b200_launch_count(void);
 
+/* device memory behind cstone::DeviceVector<T> [ref: cuda/device_vector.h:24-62, cuda/device_vector.cu], so that a
+ * host program built with a plain C++ compiler needs no CUDA headers.  kind: 0 = host->device, 1 = device->host,
+ * 2 = device->device, on the legacy stream, complete on return. */
+int cstone_b200_device_malloc(void** ptr, size_t bytes);
+int cstone_b200_device_free(void* ptr);
+int cstone_b200_device_memcpy(void* dst, const void* src, size_t bytes, int kind);
+int cstone_b200_device_memset(void* dst, int value, size_t bytes);
+int cstone_b200_device_synchronize(void);
+/* one process per GPU: select the device of the calling thread (cudaSetDevice) */
+int cstone_b200_set_device(int device);
+
 /* ------------------------------------------------------------------------
  * a1/a2  SFC keys
  * [ref: sfc/sfc_gpu.h:38-39  computeSfcKeysGpu<KeyType,T>(x,y,z,keys,n,box)]

@@ -1,0 +1,286 @@
+/*
+ * cstone_b200/domain.hpp — cstone::Domain<KeyType, T, GpuTag> over libcstone_b200.so
+ *
+ * Source-compatible with the public surface of the reference class [ref: domain/domain.hpp:66-437] for the hot path:
+ *   Domain(rank, nRanks, bucketSize, bucketSizeFocus, theta, box)
+ *   sync(keys, x, y, z, h, std::tie(properties...), std::tie(scratch...))
+ *   exchangeHalos(std::tie(arrays...), sendBuffer, receiveBuffer)
+ *   startIndex / endIndex / nParticles / nParticlesWithHalos / box / octreeProperties / layout
+ * All vectors are cstone::DeviceVector; particle data never leave the device.  The scratch-buffer arguments are
+ * accepted for source compatibility and left untouched (the engine owns grow-only scratch).
+ * Multi-GPU: one process per GPU; hand the engine an NCCL communicator with setNcclComm() (or initNcclComm() with a
+ * unique id broadcast through the application's MPI / torch.distributed).
+ * Not provided (out of scope): syncGrav, updateExpansionCenters, focusTree(), CpuTag.
+ */
+#pragma once
+
+#include <array>
+#include <cstdint>
+#include <tuple>
+#include <vector>
+
+#include "../cstone_b200_domain.h"
+#include "box.hpp"
+#include "device_vector.hpp"
+
+namespace cstone
+{
+
+template<class T>
+struct Vec3
+{
+    T v[3];
+    T& operator[](int i) { return v[i]; }
+    const T& operator[](int i) const { return v[i]; }
+};
+
+//! [ref: tree/octree.hpp:296-317 OctreeNsView] device pointers, valid until the next sync
+template<class T, class KeyType>
+struct OctreeNsView
+{
+    TreeNodeIndex numLeafNodes;
+    TreeNodeIndex numInternalNodes;
+    TreeNodeIndex numNodes;
+    const KeyType* prefixes;
+    const TreeNodeIndex* childOffsets;
+    const TreeNodeIndex* internalToLeaf;
+    const TreeNodeIndex* levelRange;
+    const KeyType* leaves;
+    const LocalIndex* layout;
+    const Vec3<T>* centers;
+    const Vec3<T>* sizes;
+};
+
+namespace detail
+{
+template<class K, class T>
+struct DomainApi;
+
+#define CSB_DOMAIN_API(KS, K, TS, T)                                                                                   \
+    template<>                                                                                                         \
+    struct DomainApi<K, T>                                                                                             \
+    {                                                                                                                  \
+        static constexpr auto create        = cstone_b200_domain_create_##KS##_##TS;                                   \
+        static constexpr auto destroy       = cstone_b200_domain_destroy_##KS##_##TS;                                  \
+        static constexpr auto setComm       = cstone_b200_domain_set_comm_##KS##_##TS;                                 \
+        static constexpr auto syncBegin     = cstone_b200_domain_sync_begin_##KS##_##TS;                               \
+        static constexpr auto syncFinish    = cstone_b200_domain_sync_finish_##KS##_##TS;                              \
+        static constexpr auto exchangeHalos = cstone_b200_domain_exchange_halos_##KS##_##TS;                           \
+        static constexpr auto info          = cstone_b200_domain_info_##KS##_##TS;                                     \
+        static constexpr auto box           = cstone_b200_domain_box_##KS##_##TS;                                      \
+        static constexpr auto stageMs       = cstone_b200_domain_stage_ms_##KS##_##TS;                                 \
+        static constexpr auto treeView      = cstone_b200_domain_tree_view_##KS##_##TS;                                \
+        static constexpr auto globalTree    = cstone_b200_domain_global_tree_##KS##_##TS;                              \
+        static constexpr auto findNeighbors = cstone_b200_domain_find_neighbors_##KS##_##TS;                           \
+    };
+CSB_DOMAIN_API(k64, uint64_t, f64, double)
+CSB_DOMAIN_API(k64, uint64_t, f32, float)
+CSB_DOMAIN_API(k32, uint32_t, f64, double)
+CSB_DOMAIN_API(k32, uint32_t, f32, float)
+#undef CSB_DOMAIN_API
+} // namespace detail
+
+template<class KeyType, class T, class Accelerator = GpuTag>
+class Domain
+{
+    static_assert(std::is_same_v<Accelerator, GpuTag>, "this library provides the GpuTag Domain only");
+    static_assert(std::is_same_v<KeyType, uint32_t> || std::is_same_v<KeyType, uint64_t> ||
+                      (std::is_unsigned_v<KeyType> && (sizeof(KeyType) == 4 || sizeof(KeyType) == 8)),
+                  "SFC key type needs to be a 32- or 64-bit unsigned integer");
+    using K   = std::conditional_t<sizeof(KeyType) == 8, uint64_t, uint32_t>;
+    using Api = detail::DomainApi<K, T>;
+
+public:
+    using RealType = T;
+
+    Domain(int rank,
+           int nRanks,
+           unsigned bucketSize,
+           unsigned bucketSizeFocus,
+           float theta,
+           const Box<T>& box = Box<T>{0, 1})
+        : myRank_(rank)
+        , numRanks_(nRanks)
+        , box_(box)
+    {
+        if (bucketSize < bucketSizeFocus)
+        {
+            throw std::runtime_error("The bucket size of the global tree must not be smaller than the bucket size"
+                                     " of the focused tree\n");
+        }
+        d_ = Api::create(rank, nRanks, bucketSize, bucketSizeFocus, theta, box.c());
+        if (!d_) throw std::runtime_error("Domain: engine creation failed\n");
+    }
+    Domain(const Domain&)            = delete;
+    Domain& operator=(const Domain&) = delete;
+    ~Domain()
+    {
+        Api::destroy(d_);
+        if (ownedComm_) cstone_b200_nccl_comm_destroy(ownedComm_);
+    }
+
+    //! hand over an existing ncclComm_t (not owned)
+    void setNcclComm(void* ncclComm) { detail::check(Api::setComm(d_, ncclComm), "Domain::setNcclComm"); }
+    //! 128-byte id for ncclCommInitRank, to be created on rank 0 and broadcast by the application
+    static std::array<char, 128> ncclUniqueId()
+    {
+        std::array<char, 128> id{};
+        detail::check(cstone_b200_nccl_unique_id(id.data()), "ncclGetUniqueId");
+        return id;
+    }
+    //! collective over all ranks of the domain; the communicator is owned by the Domain
+    void initNcclComm(const std::array<char, 128>& id)
+    {
+        detail::check(cstone_b200_nccl_comm_init(id.data(), numRanks_, myRank_, &ownedComm_), "ncclCommInitRank");
+        setNcclComm(ownedComm_);
+    }
+
+    /*! [ref: domain/domain.hpp:196-243]  pre- and postconditions as documented there (:118-179):
+     *  on return every array has nParticlesWithHalos() elements in SFC order, x,y,z,h,keys valid everywhere,
+     *  properties valid in [startIndex(), endIndex()). */
+    template<class KeyVec, class VectorX, class VectorH, class... Vectors1, class... Vectors2>
+    void sync(KeyVec& particleKeys,
+              VectorX& x,
+              VectorX& y,
+              VectorX& z,
+              VectorH& h,
+              std::tuple<Vectors1&...> particleProperties,
+              std::tuple<Vectors2&...> /*scratchBuffers*/)
+    {
+        static_assert(sizeof(typename KeyVec::value_type) == sizeof(K), "key vector does not match KeyType");
+        static_assert(std::is_same_v<typename VectorX::value_type, T>, "coordinate vectors must hold T");
+        static_assert(std::is_same_v<typename VectorH::value_type, T>, "h must hold T");
+        static_assert(((sizeof(typename Vectors1::value_type) == 4 || sizeof(typename Vectors1::value_type) == 8) && ...),
+                      "property element size must be 4 or 8 bytes");
+
+        const std::size_t n = x.size();
+        std::apply([&](auto&... p) { checkSizesEqual(n, y, z, h, p...); }, particleProperties);
+
+        constexpr int np = sizeof...(Vectors1);
+        std::array<const void*, np + 1> in{};
+        std::array<void*, np + 1> out{};
+        std::array<int, np + 1> bytes{};
+        int i = 0;
+        std::apply([&](auto&... p) { ((in[i] = p.data(), bytes[i] = int(sizeof(*p.data())), ++i), ...); },
+                   particleProperties);
+
+        long long nNew = Api::syncBegin(d_, n, x.data(), y.data(), z.data(), h.data(), np, in.data(), bytes.data());
+        if (nNew == CSTONE_E_SIZE_MISMATCH) throw std::runtime_error("Domain sync: input array sizes are inconsistent\n");
+        detail::check(nNew < 0 ? nNew : 0, "Domain::sync");
+
+        // contents are rewritten by syncFinish; only capacity matters
+        particleKeys.resize(nNew), x.resize(nNew), y.resize(nNew), z.resize(nNew), h.resize(nNew);
+        std::apply([&](auto&... p) { (p.resize(nNew), ...); }, particleProperties);
+        i = 0;
+        std::apply([&](auto&... p) { ((out[i++] = p.data()), ...); }, particleProperties);
+        detail::check(Api::syncFinish(d_, reinterpret_cast<K*>(particleKeys.data()), x.data(), y.data(), z.data(),
+                                      h.data(), out.data()),
+                      "Domain::sync");
+        refresh();
+    }
+
+    //! [ref: domain/domain.hpp:381-386]  send/receive buffers accepted for source compatibility
+    template<class... Vectors, class SendBuffer, class ReceiveBuffer>
+    void exchangeHalos(std::tuple<Vectors&...> arrays, SendBuffer&, ReceiveBuffer&) const
+    {
+        std::apply([this](auto&... a) { checkSizesEqual(info_[2], a...); }, arrays);
+        constexpr int na = sizeof...(Vectors);
+        std::array<void*, na + 1> ptrs{};
+        std::array<int, na + 1> bytes{};
+        int i = 0;
+        std::apply([&](auto&... a) { ((ptrs[i] = a.data(), bytes[i] = int(sizeof(*a.data())), ++i), ...); }, arrays);
+        detail::check(Api::exchangeHalos(d_, na, ptrs.data(), bytes.data()), "Domain::exchangeHalos");
+    }
+
+    [[nodiscard]] LocalIndex startIndex() const { return LocalIndex(info_[0]); }
+    [[nodiscard]] LocalIndex endIndex() const { return LocalIndex(info_[1]); }
+    [[nodiscard]] LocalIndex nParticles() const { return endIndex() - startIndex(); }
+    [[nodiscard]] LocalIndex nParticlesWithHalos() const { return LocalIndex(info_[2]); }
+    const Box<T>& box() const { return box_; }
+
+    //! [ref: domain/domain.hpp:424-437] search tree over assigned + halo particles (device pointers)
+    OctreeNsView<T, KeyType> octreeProperties() const
+    {
+        const void* p[10];
+        detail::check(Api::treeView(d_, p), "Domain::octreeProperties");
+        TreeNodeIndex L = TreeNodeIndex(info_[3]), M = TreeNodeIndex(info_[4]);
+        return {L,
+                M - L,
+                M,
+                static_cast<const KeyType*>(p[3]),
+                static_cast<const TreeNodeIndex*>(p[4]),
+                static_cast<const TreeNodeIndex*>(p[5]),
+                static_cast<const TreeNodeIndex*>(p[7]),
+                static_cast<const KeyType*>(p[0]),
+                static_cast<const LocalIndex*>(p[2]),
+                static_cast<const Vec3<T>*>(p[8]),
+                static_cast<const Vec3<T>*>(p[9])};
+    }
+    //! number of particles this rank sends / receives as halos per exchange
+    std::size_t numHaloSend() const { return std::size_t(info_[6]); }
+    std::size_t numHaloRecv() const { return std::size_t(info_[7]); }
+
+    //! global (replicated) leaves, counts and rank boundaries on the host [ref: domain/domain.hpp:400 globalTree]
+    void globalTree(std::vector<KeyType>& leaves, std::vector<unsigned>& counts, std::vector<KeyType>& assignment) const
+    {
+        const K *l, *a;
+        const uint32_t* c;
+        detail::check(Api::globalTree(d_, &l, &c, &a), "Domain::globalTree");
+        std::size_t Lg = std::size_t(info_[5]);
+        leaves.assign(reinterpret_cast<const KeyType*>(l), reinterpret_cast<const KeyType*>(l) + Lg + 1);
+        counts.assign(c, c + Lg);
+        assignment.assign(reinterpret_cast<const KeyType*>(a), reinterpret_cast<const KeyType*>(a) + numRanks_ + 1);
+    }
+
+    /*! neighbour search for the assigned particles with the domain's own tree
+     *  [ref: findneighbors.hpp:167-178 findNeighbors]: neighbors[(i - startIndex) * ngmax + k], neighborsCount[i - startIndex];
+     *  both vectors are resized here */
+    void findNeighbors(const DeviceVector<T>& x,
+                       const DeviceVector<T>& y,
+                       const DeviceVector<T>& z,
+                       const DeviceVector<T>& h,
+                       unsigned ngmax,
+                       DeviceVector<LocalIndex>& neighbors,
+                       DeviceVector<unsigned>& neighborsCount) const
+    {
+        checkSizesEqual(info_[2], x, y, z, h);
+        if (neighbors.size() < std::size_t(nParticles()) * ngmax) neighbors.resize(std::size_t(nParticles()) * ngmax);
+        if (neighborsCount.size() < nParticles()) neighborsCount.resize(nParticles());
+        detail::check(Api::findNeighbors(d_, x.data(), y.data(), z.data(), h.data(), ngmax, neighbors.data(),
+                                         neighborsCount.data()),
+                      "Domain::findNeighbors");
+    }
+
+    //! device time in ms of the stages of the last sync (see cstone_b200_domain.h)
+    std::array<float, 10> stageMs() const
+    {
+        std::array<float, 10> ms{};
+        detail::check(Api::stageMs(d_, ms.data()), "Domain::stageMs");
+        return ms;
+    }
+
+private:
+    template<class... Arrays>
+    static void checkSizesEqual(std::size_t value, const Arrays&... arrays)
+    {
+        const std::size_t sizes[] = {arrays.size()..., value};
+        for (std::size_t s : sizes)
+            if (s != value) throw std::runtime_error("Domain sync: input array sizes are inconsistent\n");
+    }
+
+    void refresh()
+    {
+        detail::check(Api::info(d_, info_), "Domain::info");
+        typename Box<T>::CType b;
+        detail::check(Api::box(d_, &b), "Domain::box");
+        box_ = Box<T>(b);
+    }
+
+    int myRank_, numRanks_;
+    Box<T> box_;
+    cstone_b200_domain* d_ = nullptr;
+    void* ownedComm_       = nullptr;
+    int64_t info_[8]       = {0, 0, 0, 0, 0, 0, 0, 0};
+};
+
+} // namespace cstone
