@@ -35,12 +35,29 @@ namespace csb
 {
 
 #ifndef NB_MINBLOCKS
-#define NB_MINBLOCKS 6
+#define NB_MINBLOCKS 7
 #endif
 constexpr int kNbWarps     = 4;
 constexpr int kNbThreads   = kNbWarps * 32;
 constexpr int kNbStack     = 160; // >= 7 * 21 + 1 entries can be pending at any time
-constexpr int kNbRing      = 32;  // chunks whose hit masks are collected before they are expanded into indices
+#ifndef NB_GRIDCONST
+#define NB_GRIDCONST 1
+#endif
+#if NB_GRIDCONST
+#define NB_PARAM_QUAL const __grid_constant__
+#else
+#define NB_PARAM_QUAL
+#endif
+#ifndef NB_GROUPWALK
+#define NB_GROUPWALK 0
+#endif
+#ifndef NB_PREFETCH
+#define NB_PREFETCH 1
+#endif
+#ifndef NB_RING
+#define NB_RING 32
+#endif
+constexpr int kNbRing      = NB_RING;  // chunks whose hit masks are collected before they are expanded into indices
 
 template<class T>
 __device__ inline T absT(T v)
@@ -84,9 +101,14 @@ struct alignas(16) NbWarpSmem
     float4 candA[16];                       // staged leaf particles, two per entry: x0,x1,y0,y1 ...
     float2 candB[16];                       // ... and z0,z1 (relative float coordinates, or raw floats)
     float rec[8 * 8];                       // per child: centre xyz, size xyz, e, 8 e^2
-    int2 cinfo[8];                          // per child: leaf -> particle range [x,y); internal -> (node, -1)
-    int stackNode[kNbStack];
-    unsigned stackMask[kNbStack];
+    int2 cinfo[8];                          // per child: leaf -> particle range [x,y); internal -> (its first child, -1)
+    double c0[3];                           // warp-local origin of the float filter (target of lane 0)
+    float D;                                // max |target - origin| over the warp
+    float qMin;                             // smallest Q + D for which the filter may stand in for the ancestors' tests
+    float g[7];                             // bounding box of the 32 search spheres (min xyz, max xyz), max magnitude
+    int allNodes;                           // group box not finite: the group walk accepts every node
+    int stackFc[kNbStack];                  // pending internal nodes: index of their first child ...
+    unsigned stackMask[kNbStack];           // ... and the lanes whose walk reaches them
     uint32_t hitMask[kNbRing][32];          // per processed chunk and lane: bit k = candidate base+k is a neighbour
     uint32_t hitBase[kNbRing];              // first particle index of the chunk
 };
@@ -115,6 +137,15 @@ __device__ inline uint64_t fma2(uint64_t a, uint64_t b, uint64_t c)
     return r;
 }
 
+__device__ inline void prefetchL1(const void* ptr) { asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr)); }
+
+__device__ inline float warpMinF(float v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
 __device__ inline float warpMaxF(float v)
 {
 #pragma unroll
@@ -123,31 +154,58 @@ __device__ inline float warpMaxF(float v)
     return v;
 }
 
+//! per-target quantities of the reference's search [ref: findneighbors.hpp:104-118]
+template<class T>
+struct NbTarget
+{
+    T x, y, z, radiusSq, cellRadiusSq;
+    bool usePbc;
+};
+
+template<class T, bool AnyPbc>
+__device__ inline NbTarget<T> loadTarget(const NbParams<T>& p, uint32_t i)
+{
+    NbTarget<T> t;
+    t.x = p.x[i], t.y = p.y[i], t.z = p.z[i];
+    const T hi     = p.h[i];
+    t.radiusSq     = T(4.0) * hi * hi;
+    t.cellRadiusSq = t.radiusSq * p.ext * p.ext;
+    t.usePbc       = false;
+    if (AnyPbc)
+    {
+        T r2h       = T(2) * hi;
+        bool inside = (t.x - r2h >= p.box.lo[0]) && (t.y - r2h >= p.box.lo[1]) && (t.z - r2h >= p.box.lo[2]) &&
+                      (t.x + r2h <= p.box.hi[0]) && (t.y + r2h <= p.box.hi[1]) && (t.z + r2h <= p.box.hi[2]);
+        t.usePbc = !inside;
+    }
+    return t;
+}
+
 //! the reference's pair test, exact arithmetic  [ref: findneighbors.hpp:51-78,126-140]
 template<class T, bool AnyPbc>
-__device__ inline bool exactPair(const NbParams<T>& p, T xj, T yj, T zj, T xi, T yi, T zi, bool usePbc, T radiusSq)
+__device__ inline bool exactPair(const NbParams<T>& p, T xj, T yj, T zj, const NbTarget<T>& t)
 {
-    T dx = xj - xi;
-    T dy = yj - yi;
-    T dz = zj - zi;
-    if (AnyPbc && usePbc)
+    T dx = xj - t.x;
+    T dy = yj - t.y;
+    T dz = zj - t.z;
+    if (AnyPbc && t.usePbc)
     {
         dx -= T(p.box.pbc[0]) * p.box.len[0] * rint(dx * p.box.ilen[0]);
         dy -= T(p.box.pbc[1]) * p.box.len[1] * rint(dy * p.box.ilen[1]);
         dz -= T(p.box.pbc[2]) * p.box.len[2] * rint(dz * p.box.ilen[2]);
     }
     T d2 = dx * dx + dy * dy + dz * dz;
-    return d2 < radiusSq;
+    return d2 < t.radiusSq;
 }
 
 //! the reference's node test, exact arithmetic  [ref: traversal/boxoverlap.hpp:197-217, findneighbors.hpp:120-124]
 template<class T, bool AnyPbc>
-__device__ inline bool exactNode(const NbParams<T>& p, int idx, T xi, T yi, T zi, bool usePbc, T cellRadiusSq)
+__device__ inline bool exactNode(const NbParams<T>& p, int idx, const NbTarget<T>& t)
 {
-    T dx = p.centers[3 * idx] - xi;
-    T dy = p.centers[3 * idx + 1] - yi;
-    T dz = p.centers[3 * idx + 2] - zi;
-    if (AnyPbc && usePbc)
+    T dx = p.centers[3 * idx] - t.x;
+    T dy = p.centers[3 * idx + 1] - t.y;
+    T dz = p.centers[3 * idx + 2] - t.z;
+    if (AnyPbc && t.usePbc)
     {
         dx -= T(p.box.pbc[0]) * p.box.len[0] * rint(dx * p.box.ilen[0]);
         dy -= T(p.box.pbc[1]) * p.box.len[1] * rint(dy * p.box.ilen[1]);
@@ -162,11 +220,64 @@ __device__ inline bool exactNode(const NbParams<T>& p, int idx, T xi, T yi, T zi
     dx *= T(0.5);
     dy *= T(0.5);
     dz *= T(0.5);
-    return dx * dx + (dy * dy + dz * dz) < cellRadiusSq;
+    return dx * dx + (dy * dy + dz * dz) < t.cellRadiusSq;
+}
+
+/* Out-of-line exact decisions of the filtered (double) kernel.  They re-read the target from global memory, so that
+ * the main path keeps no double-precision target state in registers (64 registers / 8 blocks per SM). */
+template<class T, bool AnyPbc>
+__device__ __noinline__ bool exactNodeSlow(const NbParams<T>& p, int idx, uint32_t i)
+{
+    const NbTarget<T> t = loadTarget<T, AnyPbc>(p, i);
+    return exactNode<T, AnyPbc>(p, idx, t);
+}
+/*! does the reference's walk for target i reach leaf node `leafNode`?  Follows the root-to-leaf path (at every level
+ *  the child whose centre is nearest, in the L1 norm, to the leaf's centre) with the exact node test. */
+template<class T, bool AnyPbc>
+__device__ __noinline__ bool pathAcceptedSlow(const NbParams<T>& p, int leafNode, uint32_t i)
+{
+    const NbTarget<T> t = loadTarget<T, AnyPbc>(p, i);
+    int node            = 0;
+    if (!exactNode<T, AnyPbc>(p, 0, t)) return false;
+    const T lx = p.centers[3 * leafNode], ly = p.centers[3 * leafNode + 1], lz = p.centers[3 * leafNode + 2];
+    for (int level = 0; level < 24 && node != leafNode; ++level)
+    {
+        const int fc = p.childOffsets[node];
+        if (fc == 0) break;
+        int best = 0;
+        T bestD  = T(0);
+        for (int o = 0; o < 8; ++o)
+        {
+            const int c = fc + o;
+            // L1 distance: strictly smallest for the child that contains the leaf centre, also in anisotropic boxes
+            T d = absT(p.centers[3 * c] - lx) + absT(p.centers[3 * c + 1] - ly) + absT(p.centers[3 * c + 2] - lz);
+            if (o == 0 || d < bestD)
+            {
+                bestD = d;
+                best  = o;
+            }
+        }
+        node = fc + best;
+        if (!exactNode<T, AnyPbc>(p, node, t)) return false;
+    }
+    return node == leafNode;
 }
 
 template<class T, bool AnyPbc>
-__global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(NbParams<T> p)
+__device__ __noinline__ uint32_t exactChunkSlow(const NbParams<T>& p, uint32_t base, uint32_t cnt, uint32_t i)
+{
+    const NbTarget<T> t = loadTarget<T, AnyPbc>(p, i);
+    uint32_t hm         = 0;
+    for (uint32_t k = 0; k < cnt; ++k)
+    {
+        const uint32_t j = base + k;
+        if (exactPair<T, AnyPbc>(p, p.x[j], p.y[j], p.z[j], t)) hm |= 1u << k;
+    }
+    return hm;
+}
+
+template<class T, bool AnyPbc>
+__global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(NB_PARAM_QUAL NbParams<T> p)
 {
     constexpr bool F = NbFilter<T>::value;
     __shared__ NbWarpSmem smemAll[kNbWarps];
@@ -179,6 +290,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
     const uint32_t warpsTotal = gridDim.x * kNbWarps;
     constexpr float kU8       = 4.76837158203125e-7f;  // 8u = 2^-21
     constexpr float kViol     = 3145728.0f;            // 1.5 / 8u: staged magnitude limit as a multiple of e
+    constexpr float kSlack    = 1.52587890625e-05f;    // 2^-16: margin of the conservative group test
     const float4* rec4        = reinterpret_cast<const float4*>(sm.rec);
 
     for (uint32_t group = blockIdx.x * kNbWarps + (threadIdx.x >> 5); group < numGroups; group += warpsTotal)
@@ -186,57 +298,87 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
         const uint32_t w  = group * 32u + lane;
         const bool valid  = w < numTargets;
         const uint32_t i  = p.firstId + (valid ? w : numTargets - 1);
-        const T xi = p.x[i], yi = p.y[i], zi = p.z[i], hi = p.h[i];
-        const T radiusSq     = T(4.0) * hi * hi;
-        const T cellRadiusSq = radiusSq * p.ext * p.ext;
-        uint32_t count = 0;
+        uint32_t count    = 0;
 
-        bool usePbc = false;
-        if (AnyPbc)
-        {
-            T r2h       = T(2) * hi;
-            bool inside = (xi - r2h >= p.box.lo[0]) && (yi - r2h >= p.box.lo[1]) && (zi - r2h >= p.box.lo[2]) &&
-                          (xi + r2h <= p.box.hi[0]) && (yi + r2h <= p.box.hi[1]) && (zi + r2h <= p.box.hi[2]);
-            usePbc = !inside;
-        }
-
-        // ---- float filter constants of this lane (double instantiation only)
-        T c0x = 0, c0y = 0, c0z = 0;
-        float ax = 0, ay = 0, az = 0, D = 0;
-        float r2f = 0, Ap = 0, Bp = 0, c2f = 0, Ac = 0, Bc = 0;
+        // ---- per-lane constants.  Double kernel: only floats survive this block (the exact paths reload the target);
+        //      float kernel: the target itself (tg) is the working set.
+        NbTarget<T> tg;
+        float c2f = 0;
+        float Ap = 0, Bp = 0, Ac = 0, Bc = 0;
+        uint64_t nax2 = 0, nay2 = 0, naz2 = 0, nr2 = 0;
         bool exactLane = true;
-        if constexpr (F)
+        unsigned rootMask;
         {
-            c0x = __shfl_sync(full, xi, 0);
-            c0y = __shfl_sync(full, yi, 0);
-            c0z = __shfl_sync(full, zi, 0);
-            ax  = float(xi - c0x);
-            ay  = float(yi - c0y);
-            az  = float(zi - c0z);
-            D   = warpMaxF(fmaxf(fabsf(ax), fmaxf(fabsf(ay), fabsf(az))));
-            r2f = float(radiusSq);
-            Ap  = __double2float_ru(6.93 * sqrt(double(radiusSq)));
-            Bp  = __double2float_ru(double(radiusSq) * 9.5367431640625e-7);
-            c2f = float(cellRadiusSq);
-            Ac  = __double2float_ru(6.93 * sqrt(double(cellRadiusSq)));
-            Bc  = __double2float_ru(double(cellRadiusSq) * 9.5367431640625e-7);
-            exactLane = (AnyPbc && usePbc) || !(radiusSq >= T(1e-30) && cellRadiusSq >= T(1e-30) &&
-                                                 radiusSq <= T(1e30) && cellRadiusSq <= T(1e30)) ||
-                        ax != ax || ay != ay || az != az;
+            const NbTarget<T> t0 = loadTarget<T, AnyPbc>(p, i);
+            if constexpr (F)
+            {
+                const T c0x = __shfl_sync(full, t0.x, 0), c0y = __shfl_sync(full, t0.y, 0), c0z = __shfl_sync(full, t0.z, 0);
+                const float ax = float(t0.x - c0x), ay = float(t0.y - c0y), az = float(t0.z - c0z);
+                const float D  = warpMaxF(fmaxf(fabsf(ax), fmaxf(fabsf(ay), fabsf(az))));
+                // bounding box of the 32 search spheres, for the group walk
+                float rc = __double2float_ru(sqrt(double(t0.cellRadiusSq)));
+                rc       = rc * 1.000002f + 1.0e-37f;
+                const float g0 = warpMinF(ax - rc), g1 = warpMinF(ay - rc), g2 = warpMinF(az - rc);
+                const float g3 = warpMaxF(ax + rc), g4 = warpMaxF(ay + rc), g5 = warpMaxF(az + rc);
+                const float Dg = fmaxf(fmaxf(fmaxf(fabsf(g0), fabsf(g3)), fmaxf(fabsf(g1), fabsf(g4))),
+                                       fmaxf(fabsf(g2), fabsf(g5)));
+                const bool allNodes = __any_sync(full, !(Dg < 1.0e30f) || rc != rc);
+                __syncwarp();
+                if (lane == 0)
+                {
+                    sm.c0[0] = c0x, sm.c0[1] = c0y, sm.c0[2] = c0z;
+                    sm.D     = D;
+                    // 2^-19 max|origin|: e = 2^-21 (Q + D) then exceeds the rounding of double coordinates 2^11 times
+                    sm.qMin  = __double2float_ru(fmax(fabs(c0x), fmax(fabs(c0y), fabs(c0z))) * 1.9073486328125e-6);
+                    sm.g[0] = g0, sm.g[1] = g1, sm.g[2] = g2, sm.g[3] = g3, sm.g[4] = g4, sm.g[5] = g5, sm.g[6] = Dg;
+                    sm.allNodes = allNodes;
+                }
+                const float r2f = float(t0.radiusSq);
+                c2f = float(t0.cellRadiusSq);
+                const float4 lc = make_float4(__double2float_ru(6.93 * sqrt(double(t0.radiusSq))),
+                                              __double2float_ru(double(t0.radiusSq) * 9.5367431640625e-7),
+                                              __double2float_ru(6.93 * sqrt(double(t0.cellRadiusSq))),
+                                              __double2float_ru(double(t0.cellRadiusSq) * 9.5367431640625e-7));
+                Ap = lc.x, Bp = lc.y, Ac = lc.z, Bc = lc.w;
+                exactLane = (AnyPbc && t0.usePbc) ||
+                            !(t0.radiusSq >= T(1e-30) && t0.cellRadiusSq >= T(1e-30) && t0.radiusSq <= T(1e30) &&
+                              t0.cellRadiusSq <= T(1e30)) ||
+                            ax != ax || ay != ay || az != az;
+                nax2 = pack2(-ax, -ax), nay2 = pack2(-ay, -ay), naz2 = pack2(-az, -az), nr2 = pack2(-r2f, -r2f);
+            }
+            else { tg = t0; }
+            rootMask = __ballot_sync(full, valid && exactNode<T, AnyPbc>(p, 0, t0));
         }
-        const uint64_t nax2 = pack2(-ax, -ax), nay2 = pack2(-ay, -ay), naz2 = pack2(-az, -az), nr2 = pack2(-r2f, -r2f);
+        __syncwarp();
 
         uint32_t* const outRow = p.neighbors + size_t(valid ? w : 0) * p.ngmax;
 
         /* Expand the collected hit masks into neighbour indices.  Every lane walks ITS column of the ring as one
          * flat loop (next non-empty word, or next set bit), so the trip count is the per-lane total and not the sum
          * of per-chunk maxima over the warp; order = chunk order, then ascending particle index. */
-        int ring       = 0; // chunks in the ring (warp-uniform)
+        int ring        = 0; // chunks in the ring (warp-uniform)
         uint32_t ringNz = 0; // bit r: this lane has hits in ring slot r
         auto drain = [&]()
         {
             __syncwarp();
             uint32_t nz = ringNz, m = 0, b = 0;
+#if NB_FLATDRAIN
+            // branch-free refill: every trip looks at the next non-empty word and takes it if the current one is used up
+            while (m | nz)
+            {
+                const int r         = (__ffs(int(nz)) - 1) & (kNbRing - 1);
+                const uint32_t mNew = sm.hitMask[r][lane];
+                const uint32_t bNew = sm.hitBase[r];
+                const bool refill   = m == 0;
+                m                   = refill ? mNew : m;
+                b                   = refill ? bNew : b;
+                nz                  = refill ? (nz & (nz - 1u)) : nz;
+                const uint32_t k    = uint32_t(__ffs(int(m))) - 1u;
+                m &= m - 1u;
+                if (count < p.ngmax) outRow[count] = b + k;
+                ++count;
+            }
+#else
             for (;;)
             {
                 if (m == 0)
@@ -252,6 +394,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                 if (count < p.ngmax) outRow[count] = b + k;
                 ++count;
             }
+#endif
             ring   = 0;
             ringNz = 0;
             __syncwarp();
@@ -274,7 +417,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                         const T xj = p.x[j], yj = p.y[j], zj = p.z[j];
                         if constexpr (F)
                         {
-                            bx = float(xj - c0x), by = float(yj - c0y), bz = float(zj - c0z);
+                            bx = float(xj - sm.c0[0]), by = float(yj - sm.c0[1]), bz = float(zj - sm.c0[2]);
                             const float mx = fmaxf(fabsf(bx), fmaxf(fabsf(by), fabsf(bz)));
                             viol           = !(mx <= e * kViol) || bx != bx || by != by || bz != bz;
                         }
@@ -296,7 +439,41 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                         bool exact = exactLane || anyViol;
                         if (!exact)
                         {
-                            const float m    = __fmaf_rn(Ap, e, Bp) + e8;
+                            const float m = __fmaf_rn(Ap, e, Bp) + e8;
+#if NB_SIGNACC
+                            /* s = d2 - r2 + m per candidate: s < 0 is a sure hit (the sign bit is shifted into hm),
+                             * 0 <= s <= 2m is the error band (found as the smallest non-negative s, compared as
+                             * unsigned bit patterns), s > 2m a sure miss.  Rounding m - r2 costs <= u r2, inside the
+                             * slack of m. */
+                            float r2neg, dummy;
+                            unpack2(nr2, r2neg, dummy);
+                            const float cm    = m + r2neg;
+                            const uint64_t c2 = pack2(cm, cm);
+                            uint32_t minBits  = 0xffffffffu;
+#pragma unroll
+                            for (int blk = 0; blk < 4; ++blk)
+                            {
+                                if (uint32_t(8 * blk) >= cnt) break; // warp-uniform
+#pragma unroll
+                                for (int q = 0; q < 4; ++q)
+                                {
+                                    const int kk      = 4 * blk + q;
+                                    const float4 ca   = sm.candA[kk];
+                                    const float2 cb   = sm.candB[kk];
+                                    const uint64_t dx = add2(pack2(ca.x, ca.y), nax2);
+                                    const uint64_t dy = add2(pack2(ca.z, ca.w), nay2);
+                                    const uint64_t dz = add2(pack2(cb.x, cb.y), naz2);
+                                    float s0, s1;
+                                    unpack2(fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, c2))), s0, s1);
+                                    hm      = __funnelshift_l(__float_as_uint(s0), hm, 1);
+                                    hm      = __funnelshift_l(__float_as_uint(s1), hm, 1);
+                                    minBits = min(minBits, min(__float_as_uint(s0), __float_as_uint(s1)));
+                                }
+                            }
+                            // candidate k sits at bit n-1-k, n = slots processed: back to bit k
+                            hm    = __brev(hm) >> (32u - min(32u, (cnt + 7u) & ~7u));
+                            exact = !(minBits > __float_as_uint(m + m));
+#else
                             const float negm = -m;
                             float minAbs     = __int_as_float(0x7f800000);
 #pragma unroll
@@ -320,17 +497,9 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                                 }
                             }
                             exact = !(minAbs > m); // some pair inside the error band (or m is NaN): decide exactly
+#endif
                         }
-                        if (exact)
-                        {
-                            hm = 0;
-                            for (uint32_t k = 0; k < cnt; ++k)
-                            {
-                                const uint32_t j = base + k;
-                                if (exactPair<T, AnyPbc>(p, p.x[j], p.y[j], p.z[j], xi, yi, zi, usePbc, radiusSq))
-                                    hm |= 1u << k;
-                            }
-                        }
+                        if (exact) hm = exactChunkSlow<T, AnyPbc>(p, base, cnt, i);
                     }
                     else
                     {
@@ -339,8 +508,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                         {
                             const float* cA = reinterpret_cast<const float*>(sm.candA) + (k >> 1) * 4 + (k & 1u);
                             const float cz  = reinterpret_cast<const float*>(sm.candB)[k];
-                            if (exactPair<T, AnyPbc>(p, T(cA[0]), T(cA[2]), T(cz), xi, yi, zi, usePbc, radiusSq))
-                                hm |= 1u << k;
+                            if (exactPair<T, AnyPbc>(p, T(cA[0]), T(cA[2]), T(cz), tg)) hm |= 1u << k;
                         }
                     }
                     if (self >= 0 && self < 32) hm &= ~(1u << self);
@@ -353,7 +521,9 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
             }
         };
 
-        // coalesced load of the 8 children of a node (24 centre + 24 size values, child offsets, leaf ranges)
+        /* coalesced load of the 8 children fc..fc+7 of a node: 24 centre + 24 size values, child offsets and, for leaf
+         * children, their particle ranges.  All loads that do not depend on each other are issued together. */
+        unsigned groupBits = 0; // children whose box the group's bounding box overlaps (group walk)
         auto stageChildren = [&](int fc) -> unsigned
         {
             if (lane < 24u)
@@ -363,8 +533,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                 const int child = int(lane) / 3, dim = int(lane) - 3 * child;
                 if constexpr (F)
                 {
-                    const T c0                  = dim == 0 ? c0x : (dim == 1 ? c0y : c0z);
-                    sm.rec[child * 8 + dim]     = float(cd - c0);
+                    sm.rec[child * 8 + dim]     = float(cd - sm.c0[dim]);
                     sm.rec[child * 8 + 3 + dim] = __double2float_ru(sd);
                 }
                 else
@@ -376,26 +545,70 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
             int co = 1;
             if (lane < 8u)
             {
-                co = p.childOffsets[fc + int(lane)];
+                co             = p.childOffsets[fc + int(lane)];
+                const int leaf = p.internalToLeaf[fc + int(lane)]; // meaningful for leaf children only
                 if (co == 0)
                 {
-                    const int leaf = p.internalToLeaf[fc + int(lane)];
-                    sm.cinfo[lane] = make_int2(int(p.layout[leaf]), int(p.layout[leaf + 1]));
+                    const uint32_t jb = p.layout[leaf], je = p.layout[leaf + 1];
+                    sm.cinfo[lane]    = make_int2(int(jb), int(je));
+#if NB_PREFETCH
+                    // the particles of this leaf are needed next: pull their first lines into L1
+                    if (je > jb)
+                    {
+                        prefetchL1(p.x + jb), prefetchL1(p.y + jb), prefetchL1(p.z + jb);
+#if NB_PREFETCH > 1
+                        prefetchL1(p.x + je - 1), prefetchL1(p.y + je - 1), prefetchL1(p.z + je - 1);
+#endif
+                    }
+#endif
                 }
-                else { sm.cinfo[lane] = make_int2(fc + int(lane), -1); }
+                else
+                {
+                    sm.cinfo[lane] = make_int2(co, -1);
+#if NB_PREFETCH
+                    // records of the grandchildren, in case this child is pushed
+                    prefetchL1(p.centers + 3 * size_t(co)), prefetchL1(p.centers + 3 * size_t(co) + 16);
+                    prefetchL1(p.sizes + 3 * size_t(co)), prefetchL1(p.sizes + 3 * size_t(co) + 16);
+                    prefetchL1(p.childOffsets + co), prefetchL1(p.internalToLeaf + co);
+#endif
+                }
             }
             const unsigned leafBits = __ballot_sync(full, co == 0);
             __syncwarp();
             if constexpr (F)
             {
+                bool ov = false;
                 if (lane < 8u)
                 {
                     const float* r = sm.rec + lane * 8;
                     const float Q  = fmaxf(fabsf(r[0]) + r[3], fmaxf(fabsf(r[1]) + r[4], fabsf(r[2]) + r[5]));
-                    const float e  = kU8 * (Q + D);
+                    float e        = kU8 * (Q + sm.D);
+#if NB_GROUPWALK
+                    // the filter's verdict on a leaf also stands for its ancestors: needs e far above double rounding
+                    if (!(Q + sm.D >= sm.qMin)) e = __int_as_float(0x7f800000);
+                    // conservative test: can this child's box overlap the search sphere of ANY target of the warp?
+                    ov = true;
+#pragma unroll
+                    for (int d = 0; d < 3; ++d)
+                    {
+                        const float cf = r[d], sf = r[3 + d] * 1.000002f;
+                        const float mg = kSlack * (fabsf(cf) + sf + sm.g[6]);
+                        if (AnyPbc && p.box.pbc[d])
+                        {
+                            const float L  = float(p.box.len[d]);
+                            const float gc = 0.5f * (sm.g[d] + sm.g[3 + d]), gh = 0.5f * (sm.g[3 + d] - sm.g[d]);
+                            float dd       = cf - gc;
+                            dd -= L * rintf(dd * float(p.box.ilen[d]));
+                            ov = ov && (fabsf(dd) <= sf + gh + mg + kSlack * L);
+                        }
+                        else { ov = ov && (cf + sf + mg >= sm.g[d]) && (cf - sf - mg <= sm.g[3 + d]); }
+                    }
+                    ov = ov || sm.allNodes;
+#endif
                     sm.rec[lane * 8 + 6] = e;
                     sm.rec[lane * 8 + 7] = 8.0f * e * e;
                 }
+                groupBits = __ballot_sync(full, ov);
                 __syncwarp();
             }
             return leafBits;
@@ -406,22 +619,36 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
         {
             if constexpr (F)
             {
-                if (exactLane) return exactNode<T, AnyPbc>(p, child, xi, yi, zi, usePbc, cellRadiusSq);
+#if NB_GROUPWALK
+                // group walk: `child` is a leaf; outside the filter's sure range the whole root-to-leaf path is tested
+                if (exactLane) return pathAcceptedSlow<T, AnyPbc>(p, child, i);
+#else
+                if (exactLane) return exactNodeSlow<T, AnyPbc>(p, child, i);
+#endif
+                float nax, nay, naz, dummy;
+                unpack2(nax2, nax, dummy);
+                unpack2(nay2, nay, dummy);
+                unpack2(naz2, naz, dummy);
                 const float4 r0 = rec4[o * 2], r1 = rec4[o * 2 + 1];
-                const float dx  = fmaxf(fabsf(r0.x - ax) - r0.w, 0.f);
-                const float dy  = fmaxf(fabsf(r0.y - ay) - r1.x, 0.f);
-                const float dz  = fmaxf(fabsf(r0.z - az) - r1.y, 0.f);
+                const float dx  = fmaxf(fabsf(r0.x + nax) - r0.w, 0.f);
+                const float dy  = fmaxf(fabsf(r0.y + nay) - r1.x, 0.f);
+                const float dz  = fmaxf(fabsf(r0.z + naz) - r1.y, 0.f);
                 const float d2  = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
-                const float m   = __fmaf_rn(Ac, r1.z, Bc) + r1.w;
+                const float2 ab = make_float2(Ac, Bc);
+                const float m   = __fmaf_rn(ab.x, r1.z, ab.y) + r1.w;
                 if (d2 < c2f - m) return true;
                 if (d2 > c2f + m) return false;
-                return exactNode<T, AnyPbc>(p, child, xi, yi, zi, usePbc, cellRadiusSq);
+#if NB_GROUPWALK
+                return pathAcceptedSlow<T, AnyPbc>(p, child, i);
+#else
+                return exactNodeSlow<T, AnyPbc>(p, child, i);
+#endif
             }
             else
             {
                 const float* r = sm.rec + o * 8; // raw float centre / size: the exact expression on staged data
-                T dx = T(r[0]) - xi, dy = T(r[1]) - yi, dz = T(r[2]) - zi;
-                if (AnyPbc && usePbc)
+                T dx = T(r[0]) - tg.x, dy = T(r[1]) - tg.y, dz = T(r[2]) - tg.z;
+                if (AnyPbc && tg.usePbc)
                 {
                     dx -= T(p.box.pbc[0]) * p.box.len[0] * rint(dx * p.box.ilen[0]);
                     dy -= T(p.box.pbc[1]) * p.box.len[1] * rint(dy * p.box.ilen[1]);
@@ -436,15 +663,14 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                 dx *= T(0.5);
                 dy *= T(0.5);
                 dz *= T(0.5);
-                return dx * dx + (dy * dy + dz * dz) < cellRadiusSq;
+                return dx * dx + (dy * dy + dz * dz) < tg.cellRadiusSq;
             }
         };
 
-        const unsigned rootMask =
-            __ballot_sync(full, valid && exactNode<T, AnyPbc>(p, 0, xi, yi, zi, usePbc, cellRadiusSq));
         if (rootMask)
         {
-            if (p.childOffsets[0] == 0)
+            const int rootFc = p.childOffsets[0];
+            if (rootFc == 0)
             {
                 // single-node tree: decide everything exactly (infinite error terms put every pair in the band)
                 const int leaf = p.internalToLeaf[0];
@@ -455,33 +681,70 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
             {
                 if (lane == 0)
                 {
-                    sm.stackNode[0] = 0;
+                    sm.stackFc[0]   = 0; // sentinel: no internal node has first child 0
                     sm.stackMask[0] = 0;
                 }
                 int sp        = 1;
-                int node      = 0;
+                int fc        = rootFc;
                 unsigned mask = rootMask;
+#if NB_GROUPWALK
+                if constexpr (F)
+                {
+                    /* GROUP WALK: the warp walks the tree once for the bounding box of its 32 search spheres, in the
+                     * reference's order; every lane tests only the LEAVES found against its own sphere.  A leaf that
+                     * passes the filter with its margin implies that all its ancestors pass the exact test (their
+                     * boxes contain the leaf's box up to the rounding of double coordinates, which the margin exceeds
+                     * 2^11 times); anything else is decided by the exact tests along the whole path. */
+                    const bool rootOk = (rootMask >> lane) & 1u;
+                    do
+                    {
+                        const unsigned leafBits = stageChildren(fc);
+                        unsigned todo           = groupBits;
+                        while (todo)
+                        {
+                            const int o = __ffs(int(todo)) - 1;
+                            todo &= todo - 1u;
+                            const int2 r = sm.cinfo[o];
+                            if ((leafBits >> o) & 1u)
+                            {
+                                if (r.y <= r.x) continue;
+                                const unsigned cmask = __ballot_sync(full, rootOk && overlapChild(o, fc + o));
+                                if (cmask)
+                                    processLeaf(uint32_t(r.x), uint32_t(r.y), cmask, sm.rec[o * 8 + 6], sm.rec[o * 8 + 7]);
+                            }
+                            else
+                            {
+                                if (lane == 0) sm.stackFc[sp] = r.x;
+                                ++sp;
+                            }
+                        }
+                        __syncwarp();
+                        --sp;
+                        fc = sm.stackFc[sp];
+                        __syncwarp();
+                    } while (fc != 0);
+                }
+                else
+#endif
                 do
                 {
-                    const int firstChild    = p.childOffsets[node];
-                    const unsigned leafBits = stageChildren(firstChild);
+                    const unsigned leafBits = stageChildren(fc);
                     const bool mine         = (mask >> lane) & 1u;
 #pragma unroll 1
                     for (int o = 0; o < 8; ++o)
                     {
-                        const int child      = firstChild + o;
-                        const unsigned cmask = __ballot_sync(full, mine && overlapChild(o, child));
+                        const unsigned cmask = __ballot_sync(full, mine && overlapChild(o, fc + o));
                         if (!cmask) continue;
+                        const int2 r = sm.cinfo[o];
                         if ((leafBits >> o) & 1u)
                         {
-                            const int2 r = sm.cinfo[o];
                             processLeaf(uint32_t(r.x), uint32_t(r.y), cmask, sm.rec[o * 8 + 6], sm.rec[o * 8 + 7]);
                         }
                         else
                         {
                             if (lane == 0)
                             {
-                                sm.stackNode[sp] = child;
+                                sm.stackFc[sp]   = r.x;
                                 sm.stackMask[sp] = cmask;
                             }
                             ++sp;
@@ -489,10 +752,10 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                     }
                     __syncwarp();
                     --sp;
-                    node = sm.stackNode[sp];
+                    fc   = sm.stackFc[sp];
                     mask = sm.stackMask[sp];
                     __syncwarp();
-                } while (node != 0);
+                } while (fc != 0);
             }
         }
         if (ring) drain();
