@@ -40,20 +40,6 @@ namespace csb
 constexpr int kNbWarps     = 4;
 constexpr int kNbThreads   = kNbWarps * 32;
 constexpr int kNbStack     = 160; // >= 7 * 21 + 1 entries can be pending at any time
-#ifndef NB_GRIDCONST
-#define NB_GRIDCONST 1
-#endif
-#if NB_GRIDCONST
-#define NB_PARAM_QUAL const __grid_constant__
-#else
-#define NB_PARAM_QUAL
-#endif
-#ifndef NB_GROUPWALK
-#define NB_GROUPWALK 0
-#endif
-#ifndef NB_PREFETCH
-#define NB_PREFETCH 1
-#endif
 #ifndef NB_RING
 #define NB_RING 32
 #endif
@@ -104,9 +90,6 @@ struct alignas(16) NbWarpSmem
     int2 cinfo[8];                          // per child: leaf -> particle range [x,y); internal -> (its first child, -1)
     double c0[3];                           // warp-local origin of the float filter (target of lane 0)
     float D;                                // max |target - origin| over the warp
-    float qMin;                             // smallest Q + D for which the filter may stand in for the ancestors' tests
-    float g[7];                             // bounding box of the 32 search spheres (min xyz, max xyz), max magnitude
-    int allNodes;                           // group box not finite: the group walk accepts every node
     int stackFc[kNbStack];                  // pending internal nodes: index of their first child ...
     unsigned stackMask[kNbStack];           // ... and the lanes whose walk reaches them
     uint32_t hitMask[kNbRing][32];          // per processed chunk and lane: bit k = candidate base+k is a neighbour
@@ -139,13 +122,6 @@ __device__ inline uint64_t fma2(uint64_t a, uint64_t b, uint64_t c)
 
 __device__ inline void prefetchL1(const void* ptr) { asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr)); }
 
-__device__ inline float warpMinF(float v)
-{
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1)
-        v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
-    return v;
-}
 __device__ inline float warpMaxF(float v)
 {
 #pragma unroll
@@ -231,38 +207,6 @@ __device__ __noinline__ bool exactNodeSlow(const NbParams<T>& p, int idx, uint32
     const NbTarget<T> t = loadTarget<T, AnyPbc>(p, i);
     return exactNode<T, AnyPbc>(p, idx, t);
 }
-/*! does the reference's walk for target i reach leaf node `leafNode`?  Follows the root-to-leaf path (at every level
- *  the child whose centre is nearest, in the L1 norm, to the leaf's centre) with the exact node test. */
-template<class T, bool AnyPbc>
-__device__ __noinline__ bool pathAcceptedSlow(const NbParams<T>& p, int leafNode, uint32_t i)
-{
-    const NbTarget<T> t = loadTarget<T, AnyPbc>(p, i);
-    int node            = 0;
-    if (!exactNode<T, AnyPbc>(p, 0, t)) return false;
-    const T lx = p.centers[3 * leafNode], ly = p.centers[3 * leafNode + 1], lz = p.centers[3 * leafNode + 2];
-    for (int level = 0; level < 24 && node != leafNode; ++level)
-    {
-        const int fc = p.childOffsets[node];
-        if (fc == 0) break;
-        int best = 0;
-        T bestD  = T(0);
-        for (int o = 0; o < 8; ++o)
-        {
-            const int c = fc + o;
-            // L1 distance: strictly smallest for the child that contains the leaf centre, also in anisotropic boxes
-            T d = absT(p.centers[3 * c] - lx) + absT(p.centers[3 * c + 1] - ly) + absT(p.centers[3 * c + 2] - lz);
-            if (o == 0 || d < bestD)
-            {
-                bestD = d;
-                best  = o;
-            }
-        }
-        node = fc + best;
-        if (!exactNode<T, AnyPbc>(p, node, t)) return false;
-    }
-    return node == leafNode;
-}
-
 template<class T, bool AnyPbc>
 __device__ __noinline__ uint32_t exactChunkSlow(const NbParams<T>& p, uint32_t base, uint32_t cnt, uint32_t i)
 {
@@ -277,7 +221,7 @@ __device__ __noinline__ uint32_t exactChunkSlow(const NbParams<T>& p, uint32_t b
 }
 
 template<class T, bool AnyPbc>
-__global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(NB_PARAM_QUAL NbParams<T> p)
+__global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(const __grid_constant__ NbParams<T> p)
 {
     constexpr bool F = NbFilter<T>::value;
     __shared__ NbWarpSmem smemAll[kNbWarps];
@@ -290,7 +234,6 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
     const uint32_t warpsTotal = gridDim.x * kNbWarps;
     constexpr float kU8       = 4.76837158203125e-7f;  // 8u = 2^-21
     constexpr float kViol     = 3145728.0f;            // 1.5 / 8u: staged magnitude limit as a multiple of e
-    constexpr float kSlack    = 1.52587890625e-05f;    // 2^-16: margin of the conservative group test
     const float4* rec4        = reinterpret_cast<const float4*>(sm.rec);
 
     for (uint32_t group = blockIdx.x * kNbWarps + (threadIdx.x >> 5); group < numGroups; group += warpsTotal)
@@ -315,23 +258,11 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                 const T c0x = __shfl_sync(full, t0.x, 0), c0y = __shfl_sync(full, t0.y, 0), c0z = __shfl_sync(full, t0.z, 0);
                 const float ax = float(t0.x - c0x), ay = float(t0.y - c0y), az = float(t0.z - c0z);
                 const float D  = warpMaxF(fmaxf(fabsf(ax), fmaxf(fabsf(ay), fabsf(az))));
-                // bounding box of the 32 search spheres, for the group walk
-                float rc = __double2float_ru(sqrt(double(t0.cellRadiusSq)));
-                rc       = rc * 1.000002f + 1.0e-37f;
-                const float g0 = warpMinF(ax - rc), g1 = warpMinF(ay - rc), g2 = warpMinF(az - rc);
-                const float g3 = warpMaxF(ax + rc), g4 = warpMaxF(ay + rc), g5 = warpMaxF(az + rc);
-                const float Dg = fmaxf(fmaxf(fmaxf(fabsf(g0), fabsf(g3)), fmaxf(fabsf(g1), fabsf(g4))),
-                                       fmaxf(fabsf(g2), fabsf(g5)));
-                const bool allNodes = __any_sync(full, !(Dg < 1.0e30f) || rc != rc);
                 __syncwarp();
                 if (lane == 0)
                 {
                     sm.c0[0] = c0x, sm.c0[1] = c0y, sm.c0[2] = c0z;
                     sm.D     = D;
-                    // 2^-19 max|origin|: e = 2^-21 (Q + D) then exceeds the rounding of double coordinates 2^11 times
-                    sm.qMin  = __double2float_ru(fmax(fabs(c0x), fmax(fabs(c0y), fabs(c0z))) * 1.9073486328125e-6);
-                    sm.g[0] = g0, sm.g[1] = g1, sm.g[2] = g2, sm.g[3] = g3, sm.g[4] = g4, sm.g[5] = g5, sm.g[6] = Dg;
-                    sm.allNodes = allNodes;
                 }
                 const float r2f = float(t0.radiusSq);
                 c2f = float(t0.cellRadiusSq);
@@ -362,23 +293,6 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
         {
             __syncwarp();
             uint32_t nz = ringNz, m = 0, b = 0;
-#if NB_FLATDRAIN
-            // branch-free refill: every trip looks at the next non-empty word and takes it if the current one is used up
-            while (m | nz)
-            {
-                const int r         = (__ffs(int(nz)) - 1) & (kNbRing - 1);
-                const uint32_t mNew = sm.hitMask[r][lane];
-                const uint32_t bNew = sm.hitBase[r];
-                const bool refill   = m == 0;
-                m                   = refill ? mNew : m;
-                b                   = refill ? bNew : b;
-                nz                  = refill ? (nz & (nz - 1u)) : nz;
-                const uint32_t k    = uint32_t(__ffs(int(m))) - 1u;
-                m &= m - 1u;
-                if (count < p.ngmax) outRow[count] = b + k;
-                ++count;
-            }
-#else
             for (;;)
             {
                 if (m == 0)
@@ -394,7 +308,6 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                 if (count < p.ngmax) outRow[count] = b + k;
                 ++count;
             }
-#endif
             ring   = 0;
             ringNz = 0;
             __syncwarp();
@@ -440,7 +353,6 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                         if (!exact)
                         {
                             const float m = __fmaf_rn(Ap, e, Bp) + e8;
-#if NB_SIGNACC
                             /* s = d2 - r2 + m per candidate: s < 0 is a sure hit (the sign bit is shifted into hm),
                              * 0 <= s <= 2m is the error band (found as the smallest non-negative s, compared as
                              * unsigned bit patterns), s > 2m a sure miss.  Rounding m - r2 costs <= u r2, inside the
@@ -473,31 +385,6 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                             // candidate k sits at bit n-1-k, n = slots processed: back to bit k
                             hm    = __brev(hm) >> (32u - min(32u, (cnt + 7u) & ~7u));
                             exact = !(minBits > __float_as_uint(m + m));
-#else
-                            const float negm = -m;
-                            float minAbs     = __int_as_float(0x7f800000);
-#pragma unroll
-                            for (int blk = 0; blk < 4; ++blk)
-                            {
-                                if (uint32_t(8 * blk) >= cnt) break; // warp-uniform
-#pragma unroll
-                                for (int q = 0; q < 4; ++q)
-                                {
-                                    const int kk      = 4 * blk + q;
-                                    const float4 ca   = sm.candA[kk];
-                                    const float2 cb   = sm.candB[kk];
-                                    const uint64_t dx = add2(pack2(ca.x, ca.y), nax2);
-                                    const uint64_t dy = add2(pack2(ca.z, ca.w), nay2);
-                                    const uint64_t dz = add2(pack2(cb.x, cb.y), naz2);
-                                    float t0, t1; // d2 - r2 of the two candidates
-                                    unpack2(fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, nr2))), t0, t1);
-                                    if (t0 < negm) hm |= 1u << (2 * kk);
-                                    if (t1 < negm) hm |= 2u << (2 * kk);
-                                    minAbs = fminf(minAbs, fminf(fabsf(t0), fabsf(t1)));
-                                }
-                            }
-                            exact = !(minAbs > m); // some pair inside the error band (or m is NaN): decide exactly
-#endif
                         }
                         if (exact) hm = exactChunkSlow<T, AnyPbc>(p, base, cnt, i);
                     }
@@ -523,7 +410,6 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
 
         /* coalesced load of the 8 children fc..fc+7 of a node: 24 centre + 24 size values, child offsets and, for leaf
          * children, their particle ranges.  All loads that do not depend on each other are issued together. */
-        unsigned groupBits = 0; // children whose box the group's bounding box overlaps (group walk)
         auto stageChildren = [&](int fc) -> unsigned
         {
             if (lane < 24u)
@@ -551,120 +437,104 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                 {
                     const uint32_t jb = p.layout[leaf], je = p.layout[leaf + 1];
                     sm.cinfo[lane]    = make_int2(int(jb), int(je));
-#if NB_PREFETCH
                     // the particles of this leaf are needed next: pull their first lines into L1
                     if (je > jb)
                     {
                         prefetchL1(p.x + jb), prefetchL1(p.y + jb), prefetchL1(p.z + jb);
-#if NB_PREFETCH > 1
-                        prefetchL1(p.x + je - 1), prefetchL1(p.y + je - 1), prefetchL1(p.z + je - 1);
-#endif
                     }
-#endif
                 }
                 else
                 {
                     sm.cinfo[lane] = make_int2(co, -1);
-#if NB_PREFETCH
                     // records of the grandchildren, in case this child is pushed
                     prefetchL1(p.centers + 3 * size_t(co)), prefetchL1(p.centers + 3 * size_t(co) + 16);
                     prefetchL1(p.sizes + 3 * size_t(co)), prefetchL1(p.sizes + 3 * size_t(co) + 16);
                     prefetchL1(p.childOffsets + co), prefetchL1(p.internalToLeaf + co);
-#endif
                 }
             }
             const unsigned leafBits = __ballot_sync(full, co == 0);
             __syncwarp();
             if constexpr (F)
             {
-                bool ov = false;
                 if (lane < 8u)
                 {
                     const float* r = sm.rec + lane * 8;
                     const float Q  = fmaxf(fabsf(r[0]) + r[3], fmaxf(fabsf(r[1]) + r[4], fabsf(r[2]) + r[5]));
                     float e        = kU8 * (Q + sm.D);
-#if NB_GROUPWALK
-                    // the filter's verdict on a leaf also stands for its ancestors: needs e far above double rounding
-                    if (!(Q + sm.D >= sm.qMin)) e = __int_as_float(0x7f800000);
-                    // conservative test: can this child's box overlap the search sphere of ANY target of the warp?
-                    ov = true;
-#pragma unroll
-                    for (int d = 0; d < 3; ++d)
-                    {
-                        const float cf = r[d], sf = r[3 + d] * 1.000002f;
-                        const float mg = kSlack * (fabsf(cf) + sf + sm.g[6]);
-                        if (AnyPbc && p.box.pbc[d])
-                        {
-                            const float L  = float(p.box.len[d]);
-                            const float gc = 0.5f * (sm.g[d] + sm.g[3 + d]), gh = 0.5f * (sm.g[3 + d] - sm.g[d]);
-                            float dd       = cf - gc;
-                            dd -= L * rintf(dd * float(p.box.ilen[d]));
-                            ov = ov && (fabsf(dd) <= sf + gh + mg + kSlack * L);
-                        }
-                        else { ov = ov && (cf + sf + mg >= sm.g[d]) && (cf - sf - mg <= sm.g[3 + d]); }
-                    }
-                    ov = ov || sm.allNodes;
-#endif
                     sm.rec[lane * 8 + 6] = e;
                     sm.rec[lane * 8 + 7] = 8.0f * e * e;
                 }
-                groupBits = __ballot_sync(full, ov);
                 __syncwarp();
             }
             return leafBits;
         };
 
-        // does the search sphere of this lane overlap staged child o (= node `child`)?
-        auto overlapChild = [&](int o, int child) -> bool
+        /* which of the 8 staged children fc..fc+7 does the search sphere of this lane overlap?  Bit o of the result.
+         * Branch-free over the 8 children; decisions inside the filter's error band are collected and settled with
+         * the exact expression afterwards (rare). */
+        auto overlapChildren = [&](int fc, bool mine) -> uint32_t
         {
+            uint32_t bits = 0;
             if constexpr (F)
             {
-#if NB_GROUPWALK
-                // group walk: `child` is a leaf; outside the filter's sure range the whole root-to-leaf path is tested
-                if (exactLane) return pathAcceptedSlow<T, AnyPbc>(p, child, i);
-#else
-                if (exactLane) return exactNodeSlow<T, AnyPbc>(p, child, i);
-#endif
+                uint32_t band = 0;
                 float nax, nay, naz, dummy;
                 unpack2(nax2, nax, dummy);
                 unpack2(nay2, nay, dummy);
                 unpack2(naz2, naz, dummy);
-                const float4 r0 = rec4[o * 2], r1 = rec4[o * 2 + 1];
-                const float dx  = fmaxf(fabsf(r0.x + nax) - r0.w, 0.f);
-                const float dy  = fmaxf(fabsf(r0.y + nay) - r1.x, 0.f);
-                const float dz  = fmaxf(fabsf(r0.z + naz) - r1.y, 0.f);
-                const float d2  = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
-                const float2 ab = make_float2(Ac, Bc);
-                const float m   = __fmaf_rn(ab.x, r1.z, ab.y) + r1.w;
-                if (d2 < c2f - m) return true;
-                if (d2 > c2f + m) return false;
-#if NB_GROUPWALK
-                return pathAcceptedSlow<T, AnyPbc>(p, child, i);
-#else
-                return exactNodeSlow<T, AnyPbc>(p, child, i);
-#endif
+#pragma unroll
+                for (int o = 0; o < 8; ++o)
+                {
+                    const float4 r0 = rec4[o * 2], r1 = rec4[o * 2 + 1];
+                    const float dx  = fmaxf(fabsf(r0.x + nax) - r0.w, 0.f);
+                    const float dy  = fmaxf(fabsf(r0.y + nay) - r1.x, 0.f);
+                    const float dz  = fmaxf(fabsf(r0.z + naz) - r1.y, 0.f);
+                    const float d2  = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+                    const float m   = __fmaf_rn(Ac, r1.z, Bc) + r1.w;
+                    const bool in   = d2 < c2f - m;
+                    const bool out  = d2 > c2f + m;
+                    bits |= in ? (1u << o) : 0u;
+                    band |= (in || out) ? 0u : (1u << o);
+                }
+                if (exactLane) bits = 0, band = 0xffu;
+                if (!mine) bits = 0, band = 0;
+                if (__any_sync(full, band != 0))
+                {
+                    while (band)
+                    {
+                        const int o = __ffs(int(band)) - 1;
+                        band &= band - 1u;
+                        if (exactNodeSlow<T, AnyPbc>(p, fc + o, i)) bits |= 1u << o;
+                    }
+                }
             }
             else
             {
-                const float* r = sm.rec + o * 8; // raw float centre / size: the exact expression on staged data
-                T dx = T(r[0]) - tg.x, dy = T(r[1]) - tg.y, dz = T(r[2]) - tg.z;
-                if (AnyPbc && tg.usePbc)
+#pragma unroll
+                for (int o = 0; o < 8; ++o)
                 {
-                    dx -= T(p.box.pbc[0]) * p.box.len[0] * rint(dx * p.box.ilen[0]);
-                    dy -= T(p.box.pbc[1]) * p.box.len[1] * rint(dy * p.box.ilen[1]);
-                    dz -= T(p.box.pbc[2]) * p.box.len[2] * rint(dz * p.box.ilen[2]);
+                    const float* r = sm.rec + o * 8; // raw float centre / size: the exact expression on staged data
+                    T dx = T(r[0]) - tg.x, dy = T(r[1]) - tg.y, dz = T(r[2]) - tg.z;
+                    if (AnyPbc && tg.usePbc)
+                    {
+                        dx -= T(p.box.pbc[0]) * p.box.len[0] * rint(dx * p.box.ilen[0]);
+                        dy -= T(p.box.pbc[1]) * p.box.len[1] * rint(dy * p.box.ilen[1]);
+                        dz -= T(p.box.pbc[2]) * p.box.len[2] * rint(dz * p.box.ilen[2]);
+                    }
+                    dx = absT(dx) - T(r[3]);
+                    dy = absT(dy) - T(r[4]);
+                    dz = absT(dz) - T(r[5]);
+                    dx += absT(dx);
+                    dy += absT(dy);
+                    dz += absT(dz);
+                    dx *= T(0.5);
+                    dy *= T(0.5);
+                    dz *= T(0.5);
+                    bits |= (dx * dx + (dy * dy + dz * dz) < tg.cellRadiusSq) ? (1u << o) : 0u;
                 }
-                dx = absT(dx) - T(r[3]);
-                dy = absT(dy) - T(r[4]);
-                dz = absT(dz) - T(r[5]);
-                dx += absT(dx);
-                dy += absT(dy);
-                dz += absT(dz);
-                dx *= T(0.5);
-                dy *= T(0.5);
-                dz *= T(0.5);
-                return dx * dx + (dy * dy + dz * dz) < tg.cellRadiusSq;
+                if (!mine) bits = 0;
             }
+            return bits;
         };
 
         if (rootMask)
@@ -687,55 +557,17 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                 int sp        = 1;
                 int fc        = rootFc;
                 unsigned mask = rootMask;
-#if NB_GROUPWALK
-                if constexpr (F)
-                {
-                    /* GROUP WALK: the warp walks the tree once for the bounding box of its 32 search spheres, in the
-                     * reference's order; every lane tests only the LEAVES found against its own sphere.  A leaf that
-                     * passes the filter with its margin implies that all its ancestors pass the exact test (their
-                     * boxes contain the leaf's box up to the rounding of double coordinates, which the margin exceeds
-                     * 2^11 times); anything else is decided by the exact tests along the whole path. */
-                    const bool rootOk = (rootMask >> lane) & 1u;
-                    do
-                    {
-                        const unsigned leafBits = stageChildren(fc);
-                        unsigned todo           = groupBits;
-                        while (todo)
-                        {
-                            const int o = __ffs(int(todo)) - 1;
-                            todo &= todo - 1u;
-                            const int2 r = sm.cinfo[o];
-                            if ((leafBits >> o) & 1u)
-                            {
-                                if (r.y <= r.x) continue;
-                                const unsigned cmask = __ballot_sync(full, rootOk && overlapChild(o, fc + o));
-                                if (cmask)
-                                    processLeaf(uint32_t(r.x), uint32_t(r.y), cmask, sm.rec[o * 8 + 6], sm.rec[o * 8 + 7]);
-                            }
-                            else
-                            {
-                                if (lane == 0) sm.stackFc[sp] = r.x;
-                                ++sp;
-                            }
-                        }
-                        __syncwarp();
-                        --sp;
-                        fc = sm.stackFc[sp];
-                        __syncwarp();
-                    } while (fc != 0);
-                }
-                else
-#endif
                 do
                 {
                     const unsigned leafBits = stageChildren(fc);
-                    const bool mine         = (mask >> lane) & 1u;
-#pragma unroll 1
-                    for (int o = 0; o < 8; ++o)
+                    const uint32_t bits     = overlapChildren(fc, (mask >> lane) & 1u);
+                    unsigned todo           = __reduce_or_sync(full, bits);
+                    while (todo)
                     {
-                        const unsigned cmask = __ballot_sync(full, mine && overlapChild(o, fc + o));
-                        if (!cmask) continue;
-                        const int2 r = sm.cinfo[o];
+                        const int o = __ffs(int(todo)) - 1;
+                        todo &= todo - 1u;
+                        const unsigned cmask = __ballot_sync(full, (bits >> o) & 1u);
+                        const int2 r         = sm.cinfo[o];
                         if ((leafBits >> o) & 1u)
                         {
                             processLeaf(uint32_t(r.x), uint32_t(r.y), cmask, sm.rec[o * 8 + 6], sm.rec[o * 8 + 7]);
