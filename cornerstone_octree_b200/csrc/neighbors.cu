@@ -90,6 +90,7 @@ struct alignas(16) NbWarpSmem
     int2 cinfo[8];                          // per child: leaf -> particle range [x,y); internal -> (its first child, -1)
     double c0[3];                           // warp-local origin of the float filter (target of lane 0)
     float D;                                // max |target - origin| over the warp
+    float2 eMax;                            // largest e (and 8 e^2) among the 8 staged children
     int stackFc[kNbStack];                  // pending internal nodes: index of their first child ...
     unsigned stackMask[kNbStack];           // ... and the lanes whose walk reaches them
     uint32_t hitMask[kNbRing][32];          // per processed chunk and lane: bit k = candidate base+k is a neighbour
@@ -120,6 +121,14 @@ __device__ inline uint64_t fma2(uint64_t a, uint64_t b, uint64_t c)
     return r;
 }
 
+//! predicated store without a branch: *ptr = v if count < limit
+__device__ inline void storeIfBelow(uint32_t* ptr, uint32_t v, uint32_t count, uint32_t limit)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %2, %3;\n\t@p st.global.u32 [%0], %1;\n\t}"
+                 :
+                 : "l"(ptr), "r"(v), "r"(count), "r"(limit)
+                 : "memory");
+}
 __device__ inline void prefetchL1(const void* ptr) { asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr)); }
 
 __device__ inline float warpMaxF(float v)
@@ -293,6 +302,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
         {
             __syncwarp();
             uint32_t nz = ringNz, m = 0, b = 0;
+            uint32_t* optr = outRow + count; // never dereferenced beyond the row
             for (;;)
             {
                 if (m == 0)
@@ -305,7 +315,8 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                 }
                 const uint32_t k = uint32_t(__ffs(int(m))) - 1u;
                 m &= m - 1u;
-                if (count < p.ngmax) outRow[count] = b + k;
+                storeIfBelow(optr, b + k, count, p.ngmax);
+                ++optr;
                 ++count;
             }
             ring   = 0;
@@ -460,9 +471,12 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                 {
                     const float* r = sm.rec + lane * 8;
                     const float Q  = fmaxf(fabsf(r[0]) + r[3], fmaxf(fabsf(r[1]) + r[4], fabsf(r[2]) + r[5]));
-                    float e        = kU8 * (Q + sm.D);
+                    const float e  = kU8 * (Q + sm.D);
                     sm.rec[lane * 8 + 6] = e;
                     sm.rec[lane * 8 + 7] = 8.0f * e * e;
+                    // largest error term of the 8 siblings (non-negative floats order like their bit patterns)
+                    const float eMax = __uint_as_float(__reduce_max_sync(0xffu, __float_as_uint(e)));
+                    if (lane == 0) sm.eMax = make_float2(eMax, 8.0f * eMax * eMax);
                 }
                 __syncwarp();
             }
@@ -477,11 +491,15 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
             uint32_t bits = 0;
             if constexpr (F)
             {
-                uint32_t band = 0;
                 float nax, nay, naz, dummy;
                 unpack2(nax2, nax, dummy);
                 unpack2(nay2, nay, dummy);
                 unpack2(naz2, naz, dummy);
+                // one error band [lo, hi] for the 8 siblings, from their largest error term
+                const float2 em = sm.eMax;
+                const float m   = __fmaf_rn(Ac, em.x, Bc) + em.y;
+                const float lo = c2f - m, hi = c2f + m;
+                uint32_t in = 0, out = 0; // sign bits of d2 - lo and hi - d2, child o at bit 7 - o
 #pragma unroll
                 for (int o = 0; o < 8; ++o)
                 {
@@ -490,12 +508,11 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                     const float dy  = fmaxf(fabsf(r0.y + nay) - r1.x, 0.f);
                     const float dz  = fmaxf(fabsf(r0.z + naz) - r1.y, 0.f);
                     const float d2  = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
-                    const float m   = __fmaf_rn(Ac, r1.z, Bc) + r1.w;
-                    const bool in   = d2 < c2f - m;
-                    const bool out  = d2 > c2f + m;
-                    bits |= in ? (1u << o) : 0u;
-                    band |= (in || out) ? 0u : (1u << o);
+                    in              = __funnelshift_l(__float_as_uint(d2 - lo), in, 1);
+                    out             = __funnelshift_l(__float_as_uint(hi - d2), out, 1);
                 }
+                bits          = __brev(in) >> 24;
+                uint32_t band = ~(bits | (__brev(out) >> 24)) & 0xffu;
                 if (exactLane) bits = 0, band = 0xffu;
                 if (!mine) bits = 0, band = 0;
                 if (__any_sync(full, band != 0))
