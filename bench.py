@@ -266,7 +266,7 @@ def main():
     from cornerstone_octree_b200.domain import _fn, _check
     tree_ptrs = (C.c_void_p * 10)()
 
-    def run_step(marks=None):
+    def run_step(marks=None, after_sync=None):
         def mark(name):
             if marks is not None:
                 e = torch.cuda.Event(enable_timing=True)
@@ -279,6 +279,8 @@ def main():
         state["a"] = [sx, sy, sz, sh]
         state["keys"] = keys
         mark("sync")
+        if after_sync is not None:
+            after_sync()
         if world == 1:
             _check(_fn("tree_view", 64, torch.float64)(dom._h, tree_ptrs), "tree_view")
             halos_single_rank(None, dom._info()[3], tree_ptrs)
@@ -347,14 +349,26 @@ def main():
                     nc=torch.empty(int(n_assigned * 1.2) + 1024, dtype=torch.int32).pin_memory())
         moved = {"h2d": 0, "d2h": 0}
 
+        copy_stream = torch.cuda.Stream()
+
         def e2e_step():
             state["a"] = [t_.cuda(non_blocking=True) for t_ in hin]
             moved["h2d"] = sum(t_.numel() * t_.element_size() for t_ in hin)
-            nw = run_step()
+
+            def download_synced():
+                # keys, x, y, z, h are final once sync returns: their download runs on a second stream while
+                # findNeighbors computes (what a host-side client of Domain would do)
+                m_ = dom.n_particles_with_halos
+                ev = torch.cuda.Event()
+                ev.record()
+                copy_stream.wait_event(ev)
+                with torch.cuda.stream(copy_stream):
+                    hout["keys"][:m_].copy_(state["keys"], non_blocking=True)
+                    for o, s_ in zip(hout["arr"], state["a"]):
+                        o[:m_].copy_(s_, non_blocking=True)
+
+            nw = run_step(after_sync=download_synced)
             m = dom.n_particles_with_halos
-            hout["keys"][:m].copy_(state["keys"], non_blocking=True)
-            for o, s_ in zip(hout["arr"], state["a"]):
-                o[:m].copy_(s_, non_blocking=True)
             hout["nc"][:nw].copy_(state["nc"][:nw], non_blocking=True)
             moved["d2h"] = m * 8 + 4 * m * 8 + nw * 4
             torch.cuda.synchronize()
