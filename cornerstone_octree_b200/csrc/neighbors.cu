@@ -121,12 +121,13 @@ __device__ inline uint64_t fma2(uint64_t a, uint64_t b, uint64_t c)
     return r;
 }
 
-//! predicated store without a branch: *ptr = v if count < limit
-__device__ inline void storeIfBelow(uint32_t* ptr, uint32_t v, uint32_t count, uint32_t limit)
+//! predicated store without a branch: row[count] = v if count < limit
+__device__ inline void storeIfBelow(uint32_t* row, uint32_t v, uint32_t count, uint32_t limit)
 {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %2, %3;\n\t@p st.global.u32 [%0], %1;\n\t}"
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .u64 a;\n\tsetp.lt.u32 p, %2, %3;\n\tmad.wide.u32 a, %2, 4, %0;\n\t"
+                 "@p st.global.u32 [a], %1;\n\t}"
                  :
-                 : "l"(ptr), "r"(v), "r"(count), "r"(limit)
+                 : "l"(row), "r"(v), "r"(count), "r"(limit)
                  : "memory");
 }
 __device__ inline void prefetchL1(const void* ptr) { asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr)); }
@@ -302,7 +303,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
         {
             __syncwarp();
             uint32_t nz = ringNz, m = 0, b = 0;
-            uint32_t* optr = outRow + count; // never dereferenced beyond the row
+            const uint32_t ngmax = p.ngmax;
             for (;;)
             {
                 if (m == 0)
@@ -315,8 +316,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                 }
                 const uint32_t k = uint32_t(__ffs(int(m))) - 1u;
                 m &= m - 1u;
-                storeIfBelow(optr, b + k, count, p.ngmax);
-                ++optr;
+                storeIfBelow(outRow, b + k, count, ngmax);
                 ++count;
             }
             ring   = 0;
@@ -357,7 +357,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                 uint32_t hm = 0;
                 if (mine)
                 {
-                    const int self = int(i - base); // slot of the target itself, if it lives in this chunk
+                    const uint32_t self = i - base; // slot of the target itself, if it lives in this chunk (< 32)
                     if constexpr (F)
                     {
                         bool exact = exactLane || anyViol;
@@ -409,7 +409,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                             if (exactPair<T, AnyPbc>(p, T(cA[0]), T(cA[2]), T(cz), tg)) hm |= 1u << k;
                         }
                     }
-                    if (self >= 0 && self < 32) hm &= ~(1u << self);
+                    hm &= ~((self < 32u ? 1u : 0u) << (self & 31u));
                 }
                 sm.hitMask[ring][lane] = hm;
                 if (lane == 0) sm.hitBase[ring] = base;
