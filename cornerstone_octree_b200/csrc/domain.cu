@@ -104,6 +104,60 @@ __global__ void lowerBoundQueriesKernel(const K* __restrict__ keys, uint32_t n, 
     out[q] = lo;
 }
 
+/* Merge of the particles that stayed on this rank (sorted run `own`) with the sorted foreign arrivals `f`:
+ * ip[u] = number of own keys < f[u] (foreign first on ties), cnt[ip[u]]++.  With E = exclusive scan of cnt the merged
+ * position of own element t is t + E[t+1], of foreign element u it is ip[u] + u. */
+template<class K>
+__global__ void insertionPointsKernel(const K* __restrict__ own, uint32_t nOwn, const K* __restrict__ f, uint32_t nF,
+                                      uint32_t* __restrict__ ip, uint32_t* __restrict__ cnt)
+{
+    for (uint32_t u = blockIdx.x * blockDim.x + threadIdx.x; u < nF; u += gridDim.x * blockDim.x)
+    {
+        K v         = f[u];
+        uint32_t lo = 0, len = nOwn;
+        while (len > 0)
+        {
+            uint32_t half = len >> 1;
+            bool right    = own[lo + half] < v;
+            lo            = right ? lo + half + 1 : lo;
+            len           = right ? len - half - 1 : half;
+        }
+        ip[u] = lo;
+        atomicAdd(cnt + lo, 1u);
+    }
+}
+
+template<class K>
+__global__ void mergeScatterKernel(const K* __restrict__ own, uint32_t nOwn, uint32_t ownOffset,
+                                   const uint32_t* __restrict__ scanE, const K* __restrict__ f,
+                                   const uint32_t* __restrict__ fv, const uint32_t* __restrict__ ip, uint32_t nF,
+                                   K* __restrict__ outKeys, uint32_t* __restrict__ outOrder)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nOwn + nF; i += gridDim.x * blockDim.x)
+    {
+        if (i < nOwn)
+        {
+            uint32_t pos  = i + scanE[i + 1];
+            outKeys[pos]  = own[i];
+            outOrder[pos] = ownOffset + i;
+        }
+        else
+        {
+            uint32_t u    = i - nOwn;
+            uint32_t pos  = ip[u] + u;
+            outKeys[pos]  = f[u];
+            outOrder[pos] = fv[u];
+        }
+    }
+}
+
+//! v[u] = u for u < nLeft, u + gap beyond: indices of the foreign arrivals in the receive buffers
+__global__ void foreignIndexKernel(uint32_t* v, uint32_t nF, uint32_t nLeft, uint32_t gap)
+{
+    for (uint32_t u = blockIdx.x * blockDim.x + threadIdx.x; u < nF; u += gridDim.x * blockDim.x)
+        v[u] = u < nLeft ? u : u + gap;
+}
+
 //! counts[i] = max(local[i], reduced[i])   [ref: tree/update_mpi.hpp:62-65]
 __global__ void maxMergeKernel(const uint32_t* __restrict__ local, uint32_t* __restrict__ reduced, int n)
 {
@@ -352,31 +406,34 @@ __global__ void __launch_bounds__(128) reverseCollisionKernel(const uint16_t* __
     }
 }
 
-//! per (peer, leaf): number of particles to send = flag ? count : 0 (scanned afterwards per peer)
+//! per (peer, leaf), peers concatenated: number of particles to send = flag ? count : 0 (one scan for all peers)
 struct LoadFlaggedCount
 {
-    const unsigned char* flags;
+    const unsigned char* flags; // [numRanks][numLeaves]
     const uint32_t* counts;
-    int numLeaves;
+    size_t numLeaves, total;
     __device__ uint32_t operator()(size_t i) const
     {
-        return (int(i) < numLeaves && flags[i]) ? counts[i] : 0u;
+        if (i >= total || !flags[i]) return 0u;
+        return counts[i % numLeaves];
     }
 };
 
-//! expand the flagged leaves of one peer into particle indices (positions in the SFC-ordered assigned arrays)
+//! expand the flagged leaves of all peers into particle indices (positions in the SFC-ordered assigned arrays);
+//! sendScan is the exclusive scan over (peer, leaf), so the lists of the peers follow each other in rank order
 __global__ void __launch_bounds__(256) expandSendListKernel(const unsigned char* __restrict__ flags,
                                                             const uint32_t* __restrict__ layout,
                                                             const uint32_t* __restrict__ sendScan,
-                                                            int numLeaves,
+                                                            size_t numLeaves,
+                                                            size_t total,
                                                             uint32_t* __restrict__ sendIdx)
 {
-    int warpsTotal = (gridDim.x * blockDim.x) >> 5;
-    for (int leaf = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; leaf < numLeaves; leaf += warpsTotal)
+    for (size_t idx = size_t(blockIdx.x) * blockDim.x + threadIdx.x; idx < total; idx += size_t(gridDim.x) * blockDim.x)
     {
-        if (!flags[leaf]) continue;
-        uint32_t a = layout[leaf], b = layout[leaf + 1], o = sendScan[leaf];
-        for (uint32_t k = laneId(); k < b - a; k += 32u)
+        if (!flags[idx]) continue;
+        const size_t leaf = idx % numLeaves;
+        const uint32_t a = layout[leaf], b = layout[leaf + 1], o = sendScan[idx];
+        for (uint32_t k = 0; k < b - a; ++k)
             sendIdx[o + k] = a + k;
     }
 }
@@ -482,7 +539,7 @@ private:
     // scratch + SFC-ordered arrays
     DevBuf keys_, keyBuf_, order_, valBuf_, sortTemp_, mmTemp_, small_;
     DevBuf pack_[4 + kMaxProps], recv_[4 + kMaxProps], fin_[4 + kMaxProps];
-    DevBuf skeys_, fkeys_, shAssigned_;
+    DevBuf skeys_, fkeys_, shAssigned_, merge_;
 
     // trees
     LeafArrayDev<K, T> global_, focus_, search_;
@@ -790,7 +847,52 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         CSB_TRY(skeys_.reserve(sizeof(K) * n + 256));
         CSB_TRY(reserveSort(n));
         K* skeys = skeys_.template as<K>();
-        if (n)
+        const uint32_t nOwn = sendCount[rank_], nLeft = recvOff[rank_], nF = uint32_t(n) - nOwn;
+        if (n && size_t(nF) * 4 <= n)
+        {
+            /* steady state: nearly everything stayed here.  The own run is already sorted (keys are those of step 2),
+             * so only the foreign arrivals are keyed and sorted, then merged in:  O(n) streaming instead of a second
+             * 8-pass sort of all n keys. */
+            const K* ownKeys = keys + sendStart[rank_];
+            uint32_t* order  = order_.template as<uint32_t>();
+            if (nF == 0)
+            {
+                CSB_CUDA(cudaMemcpyAsync(skeys, ownKeys, sizeof(K) * n, cudaMemcpyDeviceToDevice, s_));
+                CSB_TRY(cstone_b200_sequence_u32(order, n, 0u, s_));
+            }
+            else
+            {
+                const size_t scanBytes = cstone_b200_scan_temp_bytes(uint64_t(nOwn) + 1) + 512;
+                auto up = [](size_t b) { return (b + 255) / 256 * 256; };
+                const size_t oKb = up(sizeof(K) * nF), oV = oKb + up(sizeof(K) * nF), oVb = oV + up(4 * size_t(nF)),
+                             oIp = oVb + up(4 * size_t(nF)), oCnt = oIp + up(4 * size_t(nF)),
+                             oScan = oCnt + up(4 * (size_t(nOwn) + 1));
+                CSB_TRY(merge_.reserve(oScan + scanBytes));
+                char* mb      = merge_.template as<char>();
+                K* fk         = reinterpret_cast<K*>(mb);
+                K* fkb        = reinterpret_cast<K*>(mb + oKb);
+                uint32_t* fv  = reinterpret_cast<uint32_t*>(mb + oV);
+                uint32_t* fvb = reinterpret_cast<uint32_t*>(mb + oVb);
+                uint32_t* ip  = reinterpret_cast<uint32_t*>(mb + oIp);
+                uint32_t* cnt = reinterpret_cast<uint32_t*>(mb + oCnt);
+                void* scanTmp = mb + oScan;
+                CSB_CUDA(cudaMemsetAsync(fk, 0, sizeof(K) * nF, s_));
+                const T *rx = recv_[0].template as<T>(), *ry = recv_[1].template as<T>(), *rz = recv_[2].template as<T>();
+                if (nLeft) CSB_TRY((Api<K, T>::keys(rx, ry, rz, fk, nLeft, &box_, s_)));
+                if (nF > nLeft)
+                    CSB_TRY((Api<K, T>::keys(rx + nLeft + nOwn, ry + nLeft + nOwn, rz + nLeft + nOwn, fk + nLeft, nF - nLeft, &box_, s_)));
+                foreignIndexKernel<<<gridFor(nF, 256), 256, 0, s_>>>(fv, nF, nLeft, nOwn);
+                CSB_LAUNCHED();
+                CSB_TRY((Api<K, T>::sort(fk, fv, fkb, fvb, nF, sortTemp_.p, sortTemp_.bytes, 0, s_)));
+                CSB_CUDA(cudaMemsetAsync(cnt, 0, 4 * (size_t(nOwn) + 1), s_));
+                insertionPointsKernel<K><<<gridFor(nF, 256), 256, 0, s_>>>(ownKeys, nOwn, fk, nF, ip, cnt);
+                CSB_LAUNCHED();
+                CSB_TRY(cstone_b200_exclusive_scan_u32(cnt, cnt, size_t(nOwn) + 1, 0u, scanTmp, s_));
+                mergeScatterKernel<K><<<gridFor(n, 256), 256, 0, s_>>>(ownKeys, nOwn, nLeft, cnt, fk, fv, ip, nF, skeys, order);
+                CSB_LAUNCHED();
+            }
+        }
+        else if (n)
         {
             CSB_CUDA(cudaMemsetAsync(skeys, 0, sizeof(K) * n, s_));
             CSB_TRY((Api<K, T>::keys(recv_[0].template as<T>(), recv_[1].template as<T>(), recv_[2].template as<T>(), skeys, n, &box_, s_)));
@@ -877,33 +979,28 @@ int Engine<K, T>::discoverHalos()
         CSB_LAUNCHED();
     }
 
-    // f. send lists: per peer the particles of my flagged leaves, in leaf (= SFC) order
-    CSB_TRY(sendScan_.reserve(4 * (size_t(L) + 1) * P + 256));
-    CSB_TRY(scanTemp_.reserve(cstone_b200_scan_temp_bytes(uint64_t(L) + 1) + 512));
+    // f. send lists: per peer the particles of my flagged leaves, in leaf (= SFC) order.  One scan and one expansion
+    //    over all (peer, leaf) pairs; the per-peer offsets are the scan values at the start of each peer's row.
+    const size_t PL = size_t(P) * L;
+    CSB_TRY(sendScan_.reserve(4 * (PL + 1) + 256));
+    CSB_TRY(scanTemp_.reserve(cstone_b200_scan_temp_bytes(uint64_t(PL) + 1) + 512));
     haloSendCount_.assign(P, 0), haloSendOffset_.assign(P + 1, 0);
-    std::vector<uint32_t> totals(P, 0);
-    for (int q = 0; q < P; ++q)
     {
-        if (q == rank_) continue;
-        LoadFlaggedCount load{flags_.template as<unsigned char>() + size_t(q) * L, focus_.counts.template as<uint32_t>(), L};
-        uint32_t* scan = sendScan_.template as<uint32_t>() + size_t(q) * (L + 1);
-        CSB_TRY((launchScan<false>(load, scan, size_t(L) + 1, 0u, scanTemp_.p, nullptr, s_)));
-        CSB_CUDA(cudaMemcpyAsync(&totals[q], scan + L, 4, cudaMemcpyDeviceToHost, s_));
+        LoadFlaggedCount load{flags_.template as<unsigned char>(), focus_.counts.template as<uint32_t>(), size_t(L), PL};
+        uint32_t* scan = sendScan_.template as<uint32_t>();
+        CSB_TRY((launchScan<false>(load, scan, PL + 1, 0u, scanTemp_.p, nullptr, s_)));
+        CSB_CUDA(cudaMemcpy2DAsync(haloSendOffset_.data(), 4, scan, 4 * size_t(L), 4, size_t(P) + 1, cudaMemcpyDeviceToHost, s_));
+        CSB_CUDA(cudaStreamSynchronize(s_));
     }
-    CSB_CUDA(cudaStreamSynchronize(s_));
     for (int q = 0; q < P; ++q)
-    {
-        haloSendCount_[q]      = totals[q];
-        haloSendOffset_[q + 1] = haloSendOffset_[q] + totals[q];
-    }
+        haloSendCount_[q] = haloSendOffset_[q + 1] - haloSendOffset_[q];
     nHaloSend_ = haloSendOffset_[P];
     CSB_TRY(sendIdx_.reserve(4 * size_t(nHaloSend_) + 256));
-    for (int q = 0; q < P; ++q)
+    if (nHaloSend_)
     {
-        if (q == rank_ || !haloSendCount_[q]) continue;
-        expandSendListKernel<<<gridFor(size_t(L) * 32, 256), 256, 0, s_>>>(
-            flags_.template as<unsigned char>() + size_t(q) * L, layout_.template as<uint32_t>(),
-            sendScan_.template as<uint32_t>() + size_t(q) * (L + 1), L, sendIdx_.template as<uint32_t>() + haloSendOffset_[q]);
+        expandSendListKernel<<<gridFor(PL, 256), 256, 0, s_>>>(flags_.template as<unsigned char>(), layout_.template as<uint32_t>(),
+                                                              sendScan_.template as<uint32_t>(), size_t(L), PL,
+                                                              sendIdx_.template as<uint32_t>());
         CSB_LAUNCHED();
     }
 
