@@ -34,7 +34,7 @@ METRIC = "Domain::sync + findNeighbors"
 UNIT = "Mparticles/s"
 NG0 = 100
 # dram__bytes_read.sum + dram__bytes_write.sum of one findNeighborsKernel launch at 32 M uniform (profiles/r01_*)
-NEIGHBOR_TRAFFIC_BYTES = 26_137_409_000  # dram read+write of one launch, profiles/r01b_findNeighbors_full.txt
+NEIGHBOR_TRAFFIC_BYTES = 31_562_043_000  # dram read+write of one launch, profiles/r01d_findNeighbors_full.txt
 
 
 # ------------------------------------------------------------------------------------------------ inputs
