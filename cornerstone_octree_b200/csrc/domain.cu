@@ -933,11 +933,23 @@ int Engine<K, T>::discoverHalos()
     for (int a = 0; a < na; ++a)
         eb[a] = a < 4 ? int(sizeof(T)) : propBytes_[a - 4];
 
+    // optional sub-stage timing (CSB_HALO_TIMING=1): one line per sync on stderr
+    static const bool lapOn = std::getenv("CSB_HALO_TIMING") != nullptr;
+    cudaEvent_t lapEv[8];
+    int nLap = 0;
+    auto lap = [&]()
+    {
+        if (!lapOn || nLap >= 8) return;
+        cudaEventCreate(&lapEv[nLap]);
+        cudaEventRecord(lapEv[nLap++], s_);
+    };
+    lap();
     // a. tree over the assigned particles, linked (for the reverse collision) and with its particle layout
     CSB_TRY(convergeTree(focus_, skeys, n, focusFresh_));
     CSB_TRY(linkTree(focus_, false));
     const int L = focus_.numNodes;
 
+    lap();
     // b. search radius per leaf [ref: halos/halos.hpp:148-160]
     CSB_TRY(radii_.reserve(4 * size_t(L) + 256));
     CSB_TRY((Api<K, T>::haloRadii(shAssigned_.template as<T>(), layout_.template as<uint32_t>(), size_t(L), 2.0f,
@@ -962,11 +974,13 @@ int Engine<K, T>::discoverHalos()
     for (int q = 0; q < P; ++q)
         maxS = std::max(maxS, nS[q]);
 
+    lap();
     // d. everybody gets everybody's surface boxes (tens of MB at most: surface ~ N^(2/3))
     CSB_TRY(surf_.reserve(sizeof(IBox6) * size_t(maxS) + 256, true, s_));
     CSB_TRY(allSurf_.reserve(sizeof(IBox6) * size_t(maxS) * P + 256));
     CSB_NCCL(ncclAllGather(surf_.p, allSurf_.p, sizeof(IBox6) * size_t(maxS), ncclInt8, comm_, s_));
 
+    lap();
     // e. reverse collision against my own leaves
     CSB_TRY(flags_.reserve(size_t(P) * L + 256));
     CSB_CUDA(cudaMemsetAsync(flags_.p, 0, size_t(P) * L, s_));
@@ -979,6 +993,7 @@ int Engine<K, T>::discoverHalos()
         CSB_LAUNCHED();
     }
 
+    lap();
     // f. send lists: per peer the particles of my flagged leaves, in leaf (= SFC) order.  One scan and one expansion
     //    over all (peer, leaf) pairs; the per-peer offsets are the scan values at the start of each peer's row.
     const size_t PL = size_t(P) * L;
@@ -1004,6 +1019,7 @@ int Engine<K, T>::discoverHalos()
         CSB_LAUNCHED();
     }
 
+    lap();
     // g. receive counts, final layout: [halos of ranks < me][assigned][halos of ranks > me], all in SFC order
     uint32_t* dMine = dCount + 1 + P;
     uint32_t* dAll  = dMine + P;
@@ -1033,6 +1049,18 @@ int Engine<K, T>::discoverHalos()
         }
     }
 
+    lap();
+    if (lapOn && nLap == 7)
+    {
+        cudaEventSynchronize(lapEv[6]);
+        float ms[6];
+        for (int k = 0; k < 6; ++k)
+            cudaEventElapsedTime(&ms[k], lapEv[k], lapEv[k + 1]);
+        std::fprintf(stderr, "[csb rank %d] halo discovery ms: tree %.3f radii+surface %.3f allgather %.3f collide %.3f lists %.3f counts %.3f "
+                             "(L %d, surface max %u)\n", rank_, ms[0], ms[1], ms[2], ms[3], ms[4], ms[5], L, maxS);
+        for (int k = 0; k < 7; ++k)
+            cudaEventDestroy(lapEv[k]);
+    }
     // h. assigned particles straight to their final position, then the halos of x,y,z,h
     mark(7);
     const void* src[4 + kMaxProps];
