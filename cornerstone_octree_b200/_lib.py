@@ -55,6 +55,7 @@ _PROTOS = {
     # name: (restype, argtypes)
     "minmax_temp_bytes": (_u64, []),
     "scan_temp_bytes": (_u64, [_u64]),
+    "find_neighbors_temp_bytes": (_u64, [_i32]),
     "sequence_u32": (_i, [_vp, _sz, _u32, _vp]),
     "gather": (_i, [_vp, _sz, _vp, _vp, _i, _vp]),
     "scatter": (_i, [_vp, _sz, _vp, _vp, _i, _vp]),
@@ -69,6 +70,8 @@ for ts in ("f32", "f64"):
     _PROTOS["halo_radii_" + ts] = (_i, [_vp, _vp, _sz, _f, _vp, _vp])
     _PROTOS["find_neighbors_" + ts] = (_i, [_vp, _vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _f, _u32,
                                             _vp, _vp, _vp])
+    _PROTOS["find_neighbors_ws_" + ts] = (_i, [_vp, _vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _f, _u32,
+                                               _vp, _vp, _i32, _vp, _vp])
 for ks in ("k32", "k64"):
     _PROTOS["encode_sfc_" + ks] = (_i, [_i, _vp, _vp, _vp, _vp, _sz, _vp])
     _PROTOS["decode_sfc_" + ks] = (_i, [_i, _vp, _vp, _vp, _vp, _sz, _vp])

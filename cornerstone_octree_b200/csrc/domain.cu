@@ -22,6 +22,7 @@
 #include <nccl.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -238,10 +239,15 @@ struct Api
     }
     static int neighbors(const T* x, const T* y, const T* z, const T* h, uint32_t first, uint32_t last, const CBox* box,
                          const int32_t* co, const int32_t* itl, const uint32_t* layout, const T* centers, const T* sizes,
-                         uint32_t ngmax, uint32_t* nb, uint32_t* nc, void* s)
+                         uint32_t ngmax, uint32_t* nb, uint32_t* nc, int32_t numLeaves, void* temp, void* s)
     {
-        if constexpr (f64) return cstone_b200_find_neighbors_f64(x, y, z, h, first, last, box, co, itl, layout, centers, sizes, 1.0f, ngmax, nb, nc, s);
-        else return cstone_b200_find_neighbors_f32(x, y, z, h, first, last, box, co, itl, layout, centers, sizes, 1.0f, ngmax, nb, nc, s);
+        if (!temp)
+        {
+            if constexpr (f64) return cstone_b200_find_neighbors_f64(x, y, z, h, first, last, box, co, itl, layout, centers, sizes, 1.0f, ngmax, nb, nc, s);
+            else return cstone_b200_find_neighbors_f32(x, y, z, h, first, last, box, co, itl, layout, centers, sizes, 1.0f, ngmax, nb, nc, s);
+        }
+        if constexpr (f64) return cstone_b200_find_neighbors_ws_f64(x, y, z, h, first, last, box, co, itl, layout, centers, sizes, 1.0f, ngmax, nb, nc, numLeaves, temp, s);
+        else return cstone_b200_find_neighbors_ws_f32(x, y, z, h, first, last, box, co, itl, layout, centers, sizes, 1.0f, ngmax, nb, nc, numLeaves, temp, s);
     }
 };
 
@@ -548,6 +554,7 @@ private:
     std::vector<uint32_t> hGlobalCounts_, rankCounts_;
     DevBuf prefixes_, childOffsets_, parents_, levelRange_, internalToLeaf_, leafToInternal_, centers_, sizes_, layout_;
     DevBuf octTemp_, scanTemp_, radii_;
+    mutable DevBuf nbInfo_; // node records of findNeighbors
 
     // halo exchange pattern
     DevBuf surf_, allSurf_, nSurf_, flags_, sendScan_, sendIdx_, haloPack_;
@@ -1159,9 +1166,16 @@ template<class K, class T>
 int Engine<K, T>::findNeighbors(const T* x, const T* y, const T* z, const T* h, uint32_t ngmax, uint32_t* nb,
                                 uint32_t* nc) const
 {
+    static const bool noInfo = std::getenv("CSB_NB_NOINFO") != nullptr; // measurement switch: walk without node records
+    void* temp = nullptr;
+    if (!noInfo)
+    {
+        CSB_TRY(nbInfo_.reserve(cstone_b200_find_neighbors_temp_bytes(search_.numNodes)));
+        temp = nbInfo_.p;
+    }
     return Api<K, T>::neighbors(x, y, z, h, uint32_t(start_), uint32_t(end_), &box_, childOffsets_.template as<int32_t>(),
                                 internalToLeaf_.template as<int32_t>(), layout_.template as<uint32_t>(), centers_.template as<T>(),
-                                sizes_.template as<T>(), ngmax, nb, nc, s_);
+                                sizes_.template as<T>(), ngmax, nb, nc, search_.numNodes, temp, s_);
 }
 
 } // namespace csb

@@ -73,6 +73,7 @@ struct NbParams
     const int* childOffsets;
     const int* internalToLeaf;
     const uint32_t* layout;
+    const int2* nodeInfo; // optional (workspace entry points): per node (first child, -1) or the particle range of a leaf
     const T* centers;
     const T* sizes;
     uint32_t* neighbors;
@@ -230,7 +231,25 @@ __device__ __noinline__ uint32_t exactChunkSlow(const NbParams<T>& p, uint32_t b
     return hm;
 }
 
-template<class T, bool AnyPbc>
+/* Workspace variant: one record per node that answers what the walk needs next, so that staging a node costs ONE
+ * round of independent loads instead of the chain childOffsets -> internalToLeaf -> layout. */
+__global__ void nodeInfoKernel(const int* childOffsets, const int* internalToLeaf, const uint32_t* layout, int numNodes,
+                               int2* nodeInfo)
+{
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < numNodes; idx += gridDim.x * blockDim.x)
+    {
+        const int co = childOffsets[idx];
+        int2 r       = make_int2(co, -1);
+        if (co == 0)
+        {
+            const int leaf = internalToLeaf[idx];
+            r              = make_int2(int(layout[leaf]), int(layout[leaf + 1]));
+        }
+        nodeInfo[idx] = r;
+    }
+}
+
+template<class T, bool AnyPbc, bool Info>
 __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(const __grid_constant__ NbParams<T> p)
 {
     constexpr bool F = NbFilter<T>::value;
@@ -442,25 +461,48 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
             int co = 1;
             if (lane < 8u)
             {
-                co             = p.childOffsets[fc + int(lane)];
-                const int leaf = p.internalToLeaf[fc + int(lane)]; // meaningful for leaf children only
-                if (co == 0)
+                if constexpr (Info)
                 {
-                    const uint32_t jb = p.layout[leaf], je = p.layout[leaf + 1];
-                    sm.cinfo[lane]    = make_int2(int(jb), int(je));
-                    // the particles of this leaf are needed next: pull their first lines into L1
-                    if (je > jb)
+                    const int2 inf = p.nodeInfo[fc + int(lane)];
+                    sm.cinfo[lane] = inf;
+                    co             = (inf.y == -1) ? inf.x : 0;
+                    if (co == 0)
                     {
-                        prefetchL1(p.x + jb), prefetchL1(p.y + jb), prefetchL1(p.z + jb);
+                        if (uint32_t(inf.y) > uint32_t(inf.x))
+                        {
+                            prefetchL1(p.x + uint32_t(inf.x)), prefetchL1(p.y + uint32_t(inf.x));
+                            prefetchL1(p.z + uint32_t(inf.x));
+                        }
+                    }
+                    else
+                    {
+                        prefetchL1(p.centers + 3 * size_t(co)), prefetchL1(p.centers + 3 * size_t(co) + 16);
+                        prefetchL1(p.sizes + 3 * size_t(co)), prefetchL1(p.sizes + 3 * size_t(co) + 16);
+                        prefetchL1(p.nodeInfo + co);
                     }
                 }
                 else
                 {
-                    sm.cinfo[lane] = make_int2(co, -1);
-                    // records of the grandchildren, in case this child is pushed
-                    prefetchL1(p.centers + 3 * size_t(co)), prefetchL1(p.centers + 3 * size_t(co) + 16);
-                    prefetchL1(p.sizes + 3 * size_t(co)), prefetchL1(p.sizes + 3 * size_t(co) + 16);
-                    prefetchL1(p.childOffsets + co), prefetchL1(p.internalToLeaf + co);
+                    co             = p.childOffsets[fc + int(lane)];
+                    const int leaf = p.internalToLeaf[fc + int(lane)]; // meaningful for leaf children only
+                    if (co == 0)
+                    {
+                        const uint32_t jb = p.layout[leaf], je = p.layout[leaf + 1];
+                        sm.cinfo[lane]    = make_int2(int(jb), int(je));
+                        // the particles of this leaf are needed next: pull their first lines into L1
+                        if (je > jb)
+                        {
+                            prefetchL1(p.x + jb), prefetchL1(p.y + jb), prefetchL1(p.z + jb);
+                        }
+                    }
+                    else
+                    {
+                        sm.cinfo[lane] = make_int2(co, -1);
+                        // records of the grandchildren, in case this child is pushed
+                        prefetchL1(p.centers + 3 * size_t(co)), prefetchL1(p.centers + 3 * size_t(co) + 16);
+                        prefetchL1(p.sizes + 3 * size_t(co)), prefetchL1(p.sizes + 3 * size_t(co) + 16);
+                        prefetchL1(p.childOffsets + co), prefetchL1(p.internalToLeaf + co);
+    }
                 }
             }
             const unsigned leafBits = __ballot_sync(full, co == 0);
@@ -579,6 +621,18 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                     const unsigned leafBits = stageChildren(fc);
                     const uint32_t bits     = overlapChildren(fc, (mask >> lane) & 1u);
                     unsigned todo           = __reduce_or_sync(full, bits);
+#if NB_PF2
+                    // the second cache line of the leaves that will be visited (a leaf of ~15 particles straddles two)
+                    if (lane < 8u && (((todo & leafBits) >> lane) & 1u))
+                    {
+                        const int2 r = sm.cinfo[lane];
+                        if (uint32_t(r.y) > uint32_t(r.x))
+                        {
+                            prefetchL1(p.x + uint32_t(r.y) - 1u), prefetchL1(p.y + uint32_t(r.y) - 1u);
+                            prefetchL1(p.z + uint32_t(r.y) - 1u);
+                        }
+                    }
+#endif
                     while (todo)
                     {
                         const int o = __ffs(int(todo)) - 1;
@@ -616,20 +670,33 @@ template<class T>
 int findNeighbors(const T* x, const T* y, const T* z, const T* h, uint32_t firstId, uint32_t lastId,
                   const typename BoxT<T>::type* box, const int* childOffsets, const int* internalToLeaf,
                   const uint32_t* layout, const T* centers, const T* sizes, float ext, uint32_t ngmax,
-                  uint32_t* neighbors, uint32_t* neighborsCount, void* stream)
+                  uint32_t* neighbors, uint32_t* neighborsCount, int numLeafNodes, void* temp, void* stream)
 {
     if (lastId <= firstId) return 0;
     if (!x || !y || !z || !h || !box || !childOffsets || !internalToLeaf || !layout || !centers || !sizes ||
-        !neighborsCount || (ngmax && !neighbors))
+        !neighborsCount || (ngmax && !neighbors) || (temp && numLeafNodes < 1))
         return CSTONE_E_INVALID_ARGUMENT;
-    NbParams<T> p{x,         y,         z,      h,       childOffsets, internalToLeaf, layout, centers,
-                  sizes,     neighbors, neighborsCount, firstId, lastId,       ngmax,          ext,    makeDBox<T>(box)};
+    NbParams<T> p{x,       y,     z,         h,              childOffsets, internalToLeaf, layout, static_cast<const int2*>(temp),
+                  centers, sizes, neighbors, neighborsCount, firstId,      lastId,         ngmax,  ext,
+                  makeDBox<T>(box)};
     bool anyPbc       = p.box.pbc[0] || p.box.pbc[1] || p.box.pbc[2];
     uint32_t groups   = (lastId - firstId + 31u) / 32u;
     unsigned blocks   = gridFor(groups, kNbWarps, NB_MINBLOCKS);
     cudaStream_t s    = asStream(stream);
-    if (anyPbc) findNeighborsKernel<T, true><<<blocks, kNbThreads, 0, s>>>(p);
-    else findNeighborsKernel<T, false><<<blocks, kNbThreads, 0, s>>>(p);
+    if (temp)
+    {
+        const int numNodes = numLeafNodes + (numLeafNodes - 1) / 7;
+        nodeInfoKernel<<<gridFor(uint32_t(numNodes), 256, 8), 256, 0, s>>>(childOffsets, internalToLeaf, layout, numNodes,
+                                                                           static_cast<int2*>(temp));
+        CSB_LAUNCHED();
+        if (anyPbc) findNeighborsKernel<T, true, true><<<blocks, kNbThreads, 0, s>>>(p);
+        else findNeighborsKernel<T, false, true><<<blocks, kNbThreads, 0, s>>>(p);
+    }
+    else
+    {
+        if (anyPbc) findNeighborsKernel<T, true, false><<<blocks, kNbThreads, 0, s>>>(p);
+        else findNeighborsKernel<T, false, false><<<blocks, kNbThreads, 0, s>>>(p);
+    }
     CSB_LAUNCHED();
     return 0;
 }
@@ -645,7 +712,7 @@ int cstone_b200_find_neighbors_f32(const float* x, const float* y, const float* 
                                    uint32_t* neighborsCount, void* stream)
 {
     return csb::findNeighbors<float>(x, y, z, h, firstId, lastId, box, childOffsets, internalToLeaf, layout, centers,
-                                     sizes, ext, ngmax, neighbors, neighborsCount, stream);
+                                     sizes, ext, ngmax, neighbors, neighborsCount, 0, nullptr, stream);
 }
 int cstone_b200_find_neighbors_f64(const double* x, const double* y, const double* z, const double* h,
                                    uint32_t firstId, uint32_t lastId, const cstone_box_f64* box,
@@ -654,7 +721,34 @@ int cstone_b200_find_neighbors_f64(const double* x, const double* y, const doubl
                                    uint32_t* neighbors, uint32_t* neighborsCount, void* stream)
 {
     return csb::findNeighbors<double>(x, y, z, h, firstId, lastId, box, childOffsets, internalToLeaf, layout, centers,
-                                      sizes, ext, ngmax, neighbors, neighborsCount, stream);
+                                      sizes, ext, ngmax, neighbors, neighborsCount, 0, nullptr, stream);
+}
+
+uint64_t cstone_b200_find_neighbors_temp_bytes(int32_t numLeafNodes)
+{
+    if (numLeafNodes < 1) return 0;
+    return 8ull * (uint64_t(numLeafNodes) + uint64_t(numLeafNodes - 1) / 7);
+}
+int cstone_b200_find_neighbors_ws_f32(const float* x, const float* y, const float* z, const float* h, uint32_t firstId,
+                                      uint32_t lastId, const cstone_box_f32* box, const int32_t* childOffsets,
+                                      const int32_t* internalToLeaf, const uint32_t* layout, const float* centers,
+                                      const float* sizes, float ext, uint32_t ngmax, uint32_t* neighbors,
+                                      uint32_t* neighborsCount, int32_t numLeafNodes, void* temp, void* stream)
+{
+    if (!temp) return CSTONE_E_INVALID_ARGUMENT;
+    return csb::findNeighbors<float>(x, y, z, h, firstId, lastId, box, childOffsets, internalToLeaf, layout, centers,
+                                     sizes, ext, ngmax, neighbors, neighborsCount, numLeafNodes, temp, stream);
+}
+int cstone_b200_find_neighbors_ws_f64(const double* x, const double* y, const double* z, const double* h,
+                                      uint32_t firstId, uint32_t lastId, const cstone_box_f64* box,
+                                      const int32_t* childOffsets, const int32_t* internalToLeaf, const uint32_t* layout,
+                                      const double* centers, const double* sizes, float ext, uint32_t ngmax,
+                                      uint32_t* neighbors, uint32_t* neighborsCount, int32_t numLeafNodes, void* temp,
+                                      void* stream)
+{
+    if (!temp) return CSTONE_E_INVALID_ARGUMENT;
+    return csb::findNeighbors<double>(x, y, z, h, firstId, lastId, box, childOffsets, internalToLeaf, layout, centers,
+                                      sizes, ext, ngmax, neighbors, neighborsCount, numLeafNodes, temp, stream);
 }
 
 } // extern "C"

@@ -438,7 +438,7 @@ def compute_node_layout(counts, flags, first_assigned, last_assigned, layout=Non
 
 # --------------------------------------------------------------------------------------------- neighbours
 def find_neighbors(x, y, z, h, first_id, last_id, box, octree, layout, centers, sizes, ngmax, neighbors=None,
-                   neighbors_count=None, search_ext_factor=1.0):
+                   neighbors_count=None, search_ext_factor=1.0, use_workspace=True):
     """[ref: findneighbors.hpp:167-178 findNeighbors] -> neighbors[(last-first), ngmax], neighbors_count"""
     _require_cuda(x, y, z, h, layout, centers, sizes)
     nw = last_id - first_id
@@ -446,7 +446,14 @@ def find_neighbors(x, y, z, h, first_id, last_id, box, octree, layout, centers, 
         neighbors = torch.empty((nw, ngmax), dtype=torch.int32, device=x.device)
     if neighbors_count is None:
         neighbors_count = torch.empty(nw, dtype=torch.int32, device=x.device)
-    call("find_neighbors_" + _ts(x), _p(x), _p(y), _p(z), _p(h), first_id, last_id, C.byref(box),
-         _p(octree.child_offsets), _p(octree.internal_to_leaf), _p(layout), _p(centers), _p(sizes),
-         search_ext_factor, ngmax, _p(neighbors), _p(neighbors_count), _stream())
+    num_leaves = layout.numel() - 1
+    temp = _ws(x.device).get(call("find_neighbors_temp_bytes", num_leaves)) if use_workspace else None
+    if temp is None:
+        call("find_neighbors_" + _ts(x), _p(x), _p(y), _p(z), _p(h), first_id, last_id, C.byref(box),
+             _p(octree.child_offsets), _p(octree.internal_to_leaf), _p(layout), _p(centers), _p(sizes),
+             search_ext_factor, ngmax, _p(neighbors), _p(neighbors_count), _stream())
+    else:
+        call("find_neighbors_ws_" + _ts(x), _p(x), _p(y), _p(z), _p(h), first_id, last_id, C.byref(box),
+             _p(octree.child_offsets), _p(octree.internal_to_leaf), _p(layout), _p(centers), _p(sizes),
+             search_ext_factor, ngmax, _p(neighbors), _p(neighbors_count), num_leaves, _p(temp), _stream())
     return neighbors, neighbors_count

@@ -351,6 +351,24 @@ int cstone_b200_find_neighbors_f64(const double* x, const double* y, const doubl
                                    float search_ext_factor, uint32_t ngmax, uint32_t* neighbors,
                                    uint32_t* neighbors_count, void* stream);
 
+/* a15 with caller-provided workspace (same results; the preferred entry point): temp holds one 8-byte record
+ * per tree node (first child / particle range of a leaf), rebuilt on every call, so that staging a node during the
+ * walk is one round of independent loads [replaces the OctreeNsView member walk of findneighbors.hpp:120-141].
+ * temp >= cstone_b200_find_neighbors_temp_bytes(num_leaf_nodes), num_leaf_nodes = OctreeNsView::numLeafNodes. */
+uint64_t cstone_b200_find_neighbors_temp_bytes(int32_t num_leaf_nodes);
+int cstone_b200_find_neighbors_ws_f32(const float* x, const float* y, const float* z, const float* h,
+                                      uint32_t first_id, uint32_t last_id, const cstone_box_f32* box,
+                                      const int32_t* child_offsets, const int32_t* internal_to_leaf,
+                                      const uint32_t* layout, const float* centers, const float* sizes,
+                                      float search_ext_factor, uint32_t ngmax, uint32_t* neighbors,
+                                      uint32_t* neighbors_count, int32_t num_leaf_nodes, void* temp, void* stream);
+int cstone_b200_find_neighbors_ws_f64(const double* x, const double* y, const double* z, const double* h,
+                                      uint32_t first_id, uint32_t last_id, const cstone_box_f64* box,
+                                      const int32_t* child_offsets, const int32_t* internal_to_leaf,
+                                      const uint32_t* layout, const double* centers, const double* sizes,
+                                      float search_ext_factor, uint32_t ngmax, uint32_t* neighbors,
+                                      uint32_t* neighbors_count, int32_t num_leaf_nodes, void* temp, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
