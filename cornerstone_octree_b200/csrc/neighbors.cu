@@ -43,6 +43,15 @@ constexpr int kNbStack     = 160; // >= 7 * 21 + 1 entries can be pending at any
 #ifndef NB_RING
 #define NB_RING 32
 #endif
+#ifndef NB_ASYNC
+#define NB_ASYNC 1 // workspace kernels: cp.async pipeline for candidate chunks and node records
+#endif
+#ifndef NB_PFNODE
+#define NB_PFNODE 0
+#endif
+#ifndef NB_PFLEAF
+#define NB_PFLEAF 0
+#endif
 constexpr int kNbRing      = NB_RING;  // chunks whose hit masks are collected before they are expanded into indices
 
 template<class T>
@@ -98,6 +107,17 @@ struct alignas(16) NbWarpSmem
     uint32_t hitBase[kNbRing];              // first particle index of the chunk
 };
 
+/* Landing zones of the asynchronous copies (workspace kernels only): the raw coordinates of the NEXT chunk of
+ * candidates and the raw records of the NEXT node arrive here (cp.async) while the current chunk is tested. */
+template<class T>
+struct alignas(16) NbWarpRaw
+{
+    T cand[3][32];
+    T centers[24];
+    T sizes[24];
+    int2 info[8];
+};
+
 // packed 2 x f32 arithmetic of sm_100 (FADD2 / FMUL2 / FFMA2): two candidates per instruction
 __device__ inline uint64_t pack2(float lo, float hi)
 {
@@ -132,6 +152,20 @@ __device__ inline void storeIfBelow(uint32_t* row, uint32_t v, uint32_t count, u
                  : "memory");
 }
 __device__ inline void prefetchL1(const void* ptr) { asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr)); }
+
+template<int Bytes>
+__device__ inline void cpAsync(void* smemDst, const void* src)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(uint32_t(__cvta_generic_to_shared(smemDst))), "l"(src),
+                 "n"(Bytes)
+                 : "memory");
+}
+__device__ inline void cpAsyncCommit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template<int N>
+__device__ inline void cpAsyncWait()
+{
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
 
 __device__ inline float warpMaxF(float v)
 {
@@ -252,9 +286,12 @@ __global__ void nodeInfoKernel(const int* childOffsets, const int* internalToLea
 template<class T, bool AnyPbc, bool Info>
 __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(const __grid_constant__ NbParams<T> p)
 {
-    constexpr bool F = NbFilter<T>::value;
+    constexpr bool F     = NbFilter<T>::value;
+    constexpr bool Async = Info && NB_ASYNC;
     __shared__ NbWarpSmem smemAll[kNbWarps];
-    NbWarpSmem& sm = smemAll[threadIdx.x >> 5];
+    __shared__ NbWarpRaw<T> rawAll[Async ? kNbWarps : 1];
+    NbWarpSmem& sm    = smemAll[threadIdx.x >> 5];
+    NbWarpRaw<T>& raw = rawAll[Async ? (threadIdx.x >> 5) : 0];
 
     const unsigned lane       = laneId();
     const unsigned full       = 0xffffffffu;
@@ -343,6 +380,99 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
             __syncwarp();
         };
 
+        /* stage one chunk of <= 32 candidates: pairs of candidates as (x0,x1,y0,y1) + (z0,z1), relative float
+         * coordinates (or raw floats); slots >= cnt hold a far-away dummy.  Returns whether a staged value violates
+         * the magnitude limit of the filter bound (then the chunk is decided exactly). */
+        auto stageChunk = [&](uint32_t cnt, T xj, T yj, T zj, float e) -> bool
+        {
+            bool viol = false;
+            float bx = 1.0e18f, by = 1.0e18f, bz = 1.0e18f;
+            if (lane < cnt)
+            {
+                if constexpr (F)
+                {
+                    bx = float(xj - sm.c0[0]), by = float(yj - sm.c0[1]), bz = float(zj - sm.c0[2]);
+                    const float mx = fmaxf(fabsf(bx), fmaxf(fabsf(by), fabsf(bz)));
+                    viol           = !(mx <= e * kViol) || bx != bx || by != by || bz != bz;
+                }
+                else { bx = float(xj), by = float(yj), bz = float(zj); }
+            }
+            float* cA = reinterpret_cast<float*>(sm.candA) + (lane >> 1) * 4 + (lane & 1u);
+            cA[0]     = bx;
+            cA[2]     = by;
+            reinterpret_cast<float*>(sm.candB)[lane] = bz;
+            const bool anyViol = F ? bool(__any_sync(full, viol)) : false;
+            __syncwarp();
+            return anyViol;
+        };
+
+        // the staged chunk [base, base + cnt) against this lane (if `mine`); the hit mask goes into the ring
+        auto testChunk = [&](uint32_t base, uint32_t cnt, bool mine, bool anyViol, float e, float e8)
+        {
+            uint32_t hm = 0;
+            if (mine)
+            {
+                const uint32_t self = i - base; // slot of the target itself, if it lives in this chunk (< 32)
+                if constexpr (F)
+                {
+                    bool exact = exactLane || anyViol;
+                    if (!exact)
+                    {
+                        const float m = __fmaf_rn(Ap, e, Bp) + e8;
+                        /* s = d2 - r2 + m per candidate: s < 0 is a sure hit (the sign bit is shifted into hm),
+                         * 0 <= s <= 2m is the error band (found as the smallest non-negative s, compared as
+                         * unsigned bit patterns), s > 2m a sure miss.  Rounding m - r2 costs <= u r2, inside the
+                         * slack of m. */
+                        float r2neg, dummy;
+                        unpack2(nr2, r2neg, dummy);
+                        const float cm    = m + r2neg;
+                        const uint64_t c2 = pack2(cm, cm);
+                        uint32_t minBits  = 0xffffffffu;
+#pragma unroll
+                        for (int blk = 0; blk < 4; ++blk)
+                        {
+                            if (uint32_t(8 * blk) >= cnt) break; // warp-uniform
+#pragma unroll
+                            for (int q = 0; q < 4; ++q)
+                            {
+                                const int kk      = 4 * blk + q;
+                                const float4 ca   = sm.candA[kk];
+                                const float2 cb   = sm.candB[kk];
+                                const uint64_t dx = add2(pack2(ca.x, ca.y), nax2);
+                                const uint64_t dy = add2(pack2(ca.z, ca.w), nay2);
+                                const uint64_t dz = add2(pack2(cb.x, cb.y), naz2);
+                                float s0, s1;
+                                unpack2(fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, c2))), s0, s1);
+                                hm      = __funnelshift_l(__float_as_uint(s0), hm, 1);
+                                hm      = __funnelshift_l(__float_as_uint(s1), hm, 1);
+                                minBits = min(minBits, min(__float_as_uint(s0), __float_as_uint(s1)));
+                            }
+                        }
+                        // candidate k sits at bit n-1-k, n = slots processed: back to bit k
+                        hm    = __brev(hm) >> (32u - min(32u, (cnt + 7u) & ~7u));
+                        exact = !(minBits > __float_as_uint(m + m));
+                    }
+                    if (exact) hm = exactChunkSlow<T, AnyPbc>(p, base, cnt, i);
+                }
+                else
+                {
+#pragma unroll 4
+                    for (uint32_t k = 0; k < cnt; ++k)
+                    {
+                        const float* cA = reinterpret_cast<const float*>(sm.candA) + (k >> 1) * 4 + (k & 1u);
+                        const float cz  = reinterpret_cast<const float*>(sm.candB)[k];
+                        if (exactPair<T, AnyPbc>(p, T(cA[0]), T(cA[2]), T(cz), tg)) hm |= 1u << k;
+                    }
+                }
+                hm &= ~((self < 32u ? 1u : 0u) << (self & 31u));
+            }
+            sm.hitMask[ring][lane] = hm;
+            if (lane == 0) sm.hitBase[ring] = base;
+            ringNz |= (hm ? 1u : 0u) << ring;
+            if (++ring == kNbRing) drain();
+            else __syncwarp();
+        };
+
         // all particles of one leaf against the lanes in `mask`; e / e8 = filter error terms of the leaf node
         auto processLeaf = [&](uint32_t jBeg, uint32_t jEnd, unsigned mask, float e, float e8)
         {
@@ -350,92 +480,77 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
             for (uint32_t base = jBeg; base < jEnd; base += 32u)
             {
                 const uint32_t cnt = min(32u, jEnd - base);
-                bool viol          = false;
+                T xj = 0, yj = 0, zj = 0;
+                if (lane < cnt)
                 {
-                    // stage: pairs of candidates as (x0,x1,y0,y1) + (z0,z1); slots >= cnt hold a far-away dummy
-                    float bx = 1.0e18f, by = 1.0e18f, bz = 1.0e18f;
-                    if (lane < cnt)
-                    {
-                        const uint32_t j = base + lane;
-                        const T xj = p.x[j], yj = p.y[j], zj = p.z[j];
-                        if constexpr (F)
-                        {
-                            bx = float(xj - sm.c0[0]), by = float(yj - sm.c0[1]), bz = float(zj - sm.c0[2]);
-                            const float mx = fmaxf(fabsf(bx), fmaxf(fabsf(by), fabsf(bz)));
-                            viol           = !(mx <= e * kViol) || bx != bx || by != by || bz != bz;
-                        }
-                        else { bx = float(xj), by = float(yj), bz = float(zj); }
-                    }
-                    float* cA = reinterpret_cast<float*>(sm.candA) + (lane >> 1) * 4 + (lane & 1u);
-                    cA[0]     = bx;
-                    cA[2]     = by;
-                    reinterpret_cast<float*>(sm.candB)[lane] = bz;
+                    const uint32_t j = base + lane;
+                    xj = p.x[j], yj = p.y[j], zj = p.z[j];
                 }
-                const bool anyViol = F ? bool(__any_sync(full, viol)) : false;
-                __syncwarp();
-                uint32_t hm = 0;
-                if (mine)
-                {
-                    const uint32_t self = i - base; // slot of the target itself, if it lives in this chunk (< 32)
-                    if constexpr (F)
-                    {
-                        bool exact = exactLane || anyViol;
-                        if (!exact)
-                        {
-                            const float m = __fmaf_rn(Ap, e, Bp) + e8;
-                            /* s = d2 - r2 + m per candidate: s < 0 is a sure hit (the sign bit is shifted into hm),
-                             * 0 <= s <= 2m is the error band (found as the smallest non-negative s, compared as
-                             * unsigned bit patterns), s > 2m a sure miss.  Rounding m - r2 costs <= u r2, inside the
-                             * slack of m. */
-                            float r2neg, dummy;
-                            unpack2(nr2, r2neg, dummy);
-                            const float cm    = m + r2neg;
-                            const uint64_t c2 = pack2(cm, cm);
-                            uint32_t minBits  = 0xffffffffu;
-#pragma unroll
-                            for (int blk = 0; blk < 4; ++blk)
-                            {
-                                if (uint32_t(8 * blk) >= cnt) break; // warp-uniform
-#pragma unroll
-                                for (int q = 0; q < 4; ++q)
-                                {
-                                    const int kk      = 4 * blk + q;
-                                    const float4 ca   = sm.candA[kk];
-                                    const float2 cb   = sm.candB[kk];
-                                    const uint64_t dx = add2(pack2(ca.x, ca.y), nax2);
-                                    const uint64_t dy = add2(pack2(ca.z, ca.w), nay2);
-                                    const uint64_t dz = add2(pack2(cb.x, cb.y), naz2);
-                                    float s0, s1;
-                                    unpack2(fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, c2))), s0, s1);
-                                    hm      = __funnelshift_l(__float_as_uint(s0), hm, 1);
-                                    hm      = __funnelshift_l(__float_as_uint(s1), hm, 1);
-                                    minBits = min(minBits, min(__float_as_uint(s0), __float_as_uint(s1)));
-                                }
-                            }
-                            // candidate k sits at bit n-1-k, n = slots processed: back to bit k
-                            hm    = __brev(hm) >> (32u - min(32u, (cnt + 7u) & ~7u));
-                            exact = !(minBits > __float_as_uint(m + m));
-                        }
-                        if (exact) hm = exactChunkSlow<T, AnyPbc>(p, base, cnt, i);
-                    }
-                    else
-                    {
-#pragma unroll 4
-                        for (uint32_t k = 0; k < cnt; ++k)
-                        {
-                            const float* cA = reinterpret_cast<const float*>(sm.candA) + (k >> 1) * 4 + (k & 1u);
-                            const float cz  = reinterpret_cast<const float*>(sm.candB)[k];
-                            if (exactPair<T, AnyPbc>(p, T(cA[0]), T(cA[2]), T(cz), tg)) hm |= 1u << k;
-                        }
-                    }
-                    hm &= ~((self < 32u ? 1u : 0u) << (self & 31u));
-                }
-                sm.hitMask[ring][lane] = hm;
-                if (lane == 0) sm.hitBase[ring] = base;
-                ringNz |= (hm ? 1u : 0u) << ring;
-                if (++ring == kNbRing) drain();
-                else __syncwarp();
+                const bool anyViol = stageChunk(cnt, xj, yj, zj, e);
+                testChunk(base, cnt, mine, anyViol, e, e8);
             }
+        };
+
+        /* Workspace kernels: the reached leaf children of the staged node, chunk by chunk.  The raw coordinates of
+         * chunk k+1 travel (cp.async) while chunk k is tested; `bits` = reached children of this lane. */
+        auto advanceChunk = [&](unsigned& lt, int& o, uint32_t& base, uint32_t& end) -> bool
+        {
+            if (o >= 0 && base + 32u < end)
+            {
+                base += 32u;
+                return true;
+            }
+            while (lt)
+            {
+                o = __ffs(int(lt)) - 1;
+                lt &= lt - 1u;
+                const int2 r = sm.cinfo[o];
+                base = uint32_t(r.x), end = uint32_t(r.y);
+                if (end > base) return true;
+            }
+            return false;
+        };
+        auto issueChunk = [&](uint32_t base, uint32_t end)
+        {
+            const uint32_t j = base + lane;
+            if (j < end && lane < 32u)
+            {
+                cpAsync<sizeof(T)>(&raw.cand[0][lane], p.x + j);
+                cpAsync<sizeof(T)>(&raw.cand[1][lane], p.y + j);
+                cpAsync<sizeof(T)>(&raw.cand[2][lane], p.z + j);
+            }
+        };
+        // precondition: the copies of the first chunk (if any) were committed as the second-youngest group
+        auto processLeaves = [&](unsigned lt, int o, uint32_t base, uint32_t end, bool have, uint32_t bits)
+        {
+            bool first = true;
+            while (have)
+            {
+                const uint32_t cbase = base, cnt = min(32u, end - base);
+                const int co = o;
+                if (first) cpAsyncWait<1>();
+                else cpAsyncWait<0>();
+                first = false;
+                __syncwarp();
+                const float e = sm.rec[co * 8 + 6], e8 = sm.rec[co * 8 + 7];
+                T xj = 0, yj = 0, zj = 0;
+                if (lane < cnt) xj = raw.cand[0][lane], yj = raw.cand[1][lane], zj = raw.cand[2][lane];
+                const bool anyViol = stageChunk(cnt, xj, yj, zj, e);
+                have = advanceChunk(lt, o, base, end);
+                if (have) issueChunk(base, end);
+                cpAsyncCommit();
+                testChunk(cbase, cnt, (bits >> co) & 1u, anyViol, e, e8);
+            }
+        };
+        // raw records of the 8 children fc..fc+7 (centres, sizes, node records) on their way to shared memory
+        auto issueNode = [&](int fc)
+        {
+            if (lane < 24u)
+            {
+                cpAsync<sizeof(T)>(&raw.centers[lane], p.centers + 3 * size_t(fc) + lane);
+                cpAsync<sizeof(T)>(&raw.sizes[lane], p.sizes + 3 * size_t(fc) + lane);
+            }
+            if (lane < 8u) cpAsync<8>(&raw.info[lane], p.nodeInfo + fc + int(lane));
         };
 
         /* coalesced load of the 8 children fc..fc+7 of a node: 24 centre + 24 size values, child offsets and, for leaf
@@ -444,8 +559,9 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
         {
             if (lane < 24u)
             {
-                const T cd      = p.centers[3 * size_t(fc) + lane];
-                const T sd      = p.sizes[3 * size_t(fc) + lane];
+                T cd, sd;
+                if constexpr (Async) { cd = raw.centers[lane], sd = raw.sizes[lane]; }
+                else { cd = p.centers[3 * size_t(fc) + lane], sd = p.sizes[3 * size_t(fc) + lane]; }
                 const int child = int(lane) / 3, dim = int(lane) - 3 * child;
                 if constexpr (F)
                 {
@@ -461,7 +577,28 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
             int co = 1;
             if (lane < 8u)
             {
-                if constexpr (Info)
+                if constexpr (Async)
+                {
+                    const int2 inf = raw.info[lane];
+                    sm.cinfo[lane] = inf;
+                    co             = (inf.y == -1) ? inf.x : 0;
+#if NB_PFLEAF
+                    if (co == 0 && uint32_t(inf.y) > uint32_t(inf.x))
+                    {
+                        prefetchL1(p.x + uint32_t(inf.x)), prefetchL1(p.y + uint32_t(inf.x));
+                        prefetchL1(p.z + uint32_t(inf.x));
+                    }
+#endif
+#if NB_PFNODE
+                    if (co != 0)
+                    {
+                        prefetchL1(p.centers + 3 * size_t(co)), prefetchL1(p.centers + 3 * size_t(co) + 16);
+                        prefetchL1(p.sizes + 3 * size_t(co)), prefetchL1(p.sizes + 3 * size_t(co) + 16);
+                        prefetchL1(p.nodeInfo + co);
+                    }
+#endif
+                }
+                else if constexpr (Info)
                 {
                     const int2 inf = p.nodeInfo[fc + int(lane)];
                     sm.cinfo[lane] = inf;
@@ -596,6 +733,84 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
             return bits;
         };
 
+        if constexpr (Async)
+        {
+            if (rootMask)
+            {
+                const int2 rootInf = p.nodeInfo[0];
+                if (rootInf.y != -1)
+                {
+                    // single-node tree: decide everything exactly (infinite error terms put every pair in the band)
+                    if (lane == 0)
+                    {
+                        sm.cinfo[0] = rootInf;
+                        sm.rec[6] = sm.rec[7] = __int_as_float(0x7f800000);
+                    }
+                    __syncwarp();
+                    unsigned lt = 1u;
+                    int o       = -1;
+                    uint32_t base = 0, end = 0;
+                    const bool have = advanceChunk(lt, o, base, end);
+                    if (have) issueChunk(base, end);
+                    cpAsyncCommit();
+                    cpAsyncCommit(); // (empty) stands in for the node group
+                    processLeaves(lt, o, base, end, have, (rootMask >> lane) & 1u);
+                }
+                else
+                {
+                    if (lane == 0)
+                    {
+                        sm.stackFc[0]   = 0; // sentinel: no internal node has first child 0
+                        sm.stackMask[0] = 0;
+                    }
+                    int sp        = 1;
+                    int fc        = rootInf.x;
+                    unsigned mask = rootMask;
+                    issueNode(fc);
+                    cpAsyncCommit();
+                    do
+                    {
+                        cpAsyncWait<0>();
+                        __syncwarp();
+                        const unsigned leafBits = stageChildren(fc);
+                        const uint32_t bits     = overlapChildren(fc, (mask >> lane) & 1u);
+                        const unsigned todo     = __reduce_or_sync(full, bits);
+                        // first chunk of the reached leaf children: on its way before anything else
+                        unsigned lt = todo & leafBits;
+                        int o       = -1;
+                        uint32_t base = 0, end = 0;
+                        const bool have = advanceChunk(lt, o, base, end);
+                        if (have) issueChunk(base, end);
+                        cpAsyncCommit();
+                        // reached internal children go onto the stack (the leaves of this node are visited first)
+                        unsigned pushTodo = todo & ~leafBits;
+                        while (pushTodo)
+                        {
+                            const int q = __ffs(int(pushTodo)) - 1;
+                            pushTodo &= pushTodo - 1u;
+                            const unsigned cmask = __ballot_sync(full, (bits >> q) & 1u);
+                            if (lane == 0)
+                            {
+                                sm.stackFc[sp]   = sm.cinfo[q].x;
+                                sm.stackMask[sp] = cmask;
+                            }
+                            ++sp;
+                        }
+                        __syncwarp();
+                        // the node that will be popped next is known now: fetch its records while the leaves are tested
+                        --sp;
+                        fc = sm.stackFc[sp];
+                        if (fc != 0) issueNode(fc);
+                        cpAsyncCommit();
+                        processLeaves(lt, o, base, end, have, bits);
+                        mask = sm.stackMask[sp];
+                        __syncwarp();
+                    } while (fc != 0);
+                }
+            }
+        }
+        else
+        {
         if (rootMask)
         {
             const int rootFc = p.childOffsets[0];
@@ -621,18 +836,6 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                     const unsigned leafBits = stageChildren(fc);
                     const uint32_t bits     = overlapChildren(fc, (mask >> lane) & 1u);
                     unsigned todo           = __reduce_or_sync(full, bits);
-#if NB_PF2
-                    // the second cache line of the leaves that will be visited (a leaf of ~15 particles straddles two)
-                    if (lane < 8u && (((todo & leafBits) >> lane) & 1u))
-                    {
-                        const int2 r = sm.cinfo[lane];
-                        if (uint32_t(r.y) > uint32_t(r.x))
-                        {
-                            prefetchL1(p.x + uint32_t(r.y) - 1u), prefetchL1(p.y + uint32_t(r.y) - 1u);
-                            prefetchL1(p.z + uint32_t(r.y) - 1u);
-                        }
-                    }
-#endif
                     while (todo)
                     {
                         const int o = __ffs(int(todo)) - 1;
@@ -661,6 +864,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                 } while (fc != 0);
             }
         }
+        }
         if (ring) drain();
         if (valid) p.neighborsCount[w] = count;
     }
@@ -685,6 +889,14 @@ int findNeighbors(const T* x, const T* y, const T* z, const T* h, uint32_t first
     cudaStream_t s    = asStream(stream);
     if (temp)
     {
+        static const bool carved = []()
+        {
+            // 7 blocks of 31 KB per SM: ask for the largest shared-memory carve-out
+            cudaFuncSetAttribute(findNeighborsKernel<T, true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            cudaFuncSetAttribute(findNeighborsKernel<T, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            return true;
+        }();
+        (void)carved;
         const int numNodes = numLeafNodes + (numLeafNodes - 1) / 7;
         nodeInfoKernel<<<gridFor(uint32_t(numNodes), 256, 8), 256, 0, s>>>(childOffsets, internalToLeaf, layout, numNodes,
                                                                            static_cast<int2*>(temp));
