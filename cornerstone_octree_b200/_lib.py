@@ -129,6 +129,7 @@ _DOMAIN_PROTOS = {
     "create": (_vp, [_i, _i, C.c_uint, C.c_uint, _f, _vp]),
     "destroy": (None, [_vp]),
     "set_comm": (_i, [_vp, _vp]),
+    "set_fields_ready_event": (_i, [_vp, _vp]),
     "sync_begin": (_i64, [_vp, _u64, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "sync_finish": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "exchange_halos": (_i, [_vp, _i, _vp, _vp]),

@@ -469,6 +469,8 @@ public:
         : rank_(rank), nRanks_(nRanks), bucket_(bucket), bucketFocus_(bucketFocus), theta_(theta), box_(box)
     {
     }
+    //! one-shot: the stream waits for `e` before h and the properties are first read (their upload may still run)
+    void setFieldsReadyEvent(void* e) { fieldsReady_ = reinterpret_cast<cudaEvent_t>(e); }
     void setComm(void* c) { comm_ = reinterpret_cast<ncclComm_t>(c); }
     //! device time between the stage markers of the last sync (ms); kNumMarks - 1 values
     void stageMs(float* ms) const
@@ -535,6 +537,7 @@ private:
     CBox box_;
     bool firstCall_   = true;
     ncclComm_t comm_  = nullptr;
+    cudaEvent_t fieldsReady_ = nullptr;
     cudaStream_t s_   = nullptr; // legacy default stream: ordered with the caller's default-stream work
 
     // particle state
@@ -777,6 +780,11 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
             CSB_TRY(fin_[a].reserve(size_t(eb[a]) * np + 256));
             dst[a] = fin_[a].p;
         }
+        if (fieldsReady_)
+        {
+            CSB_CUDA(cudaStreamWaitEvent(s_, fieldsReady_, 0));
+            fieldsReady_ = nullptr;
+        }
         if (np) CSB_TRY(gatherMulti(order_.template as<uint32_t>(), np, na, src, dst, eb));
         CSB_TRY(fkeys_.reserve(sizeof(K) * np + 256));
         CSB_CUDA(cudaMemcpyAsync(fkeys_.p, keys, sizeof(K) * np, cudaMemcpyDeviceToDevice, s_));
@@ -804,6 +812,11 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         {
             CSB_TRY(pack_[a].reserve(size_t(eb[a]) * np + 256));
             dst[a] = pack_[a].p;
+        }
+        if (fieldsReady_)
+        {
+            CSB_CUDA(cudaStreamWaitEvent(s_, fieldsReady_, 0));
+            fieldsReady_ = nullptr;
         }
         if (np) CSB_TRY(gatherMulti(order_.template as<uint32_t>(), np, na, src, dst, eb));
 
@@ -1207,7 +1220,7 @@ int cstone_b200_nccl_comm_destroy(void* comm)
     return ncclCommDestroy(reinterpret_cast<ncclComm_t>(comm)) == ncclSuccess ? 0 : CSTONE_E_NCCL;
 }
 
-#define CSB_DOMAIN_DEF(KS, K, TS, T)                                                                                       cstone_b200_domain* cstone_b200_domain_create_##KS##_##TS(int rank, int nranks, unsigned bucket,                                                                                 unsigned bucketFocus, float theta,                                                                                     const cstone_box_##TS* box)                                  {                                                                                                                          if (!box || nranks < 1 || rank < 0 || rank >= nranks || bucket < bucketFocus || bucketFocus == 0) return nullptr;         return reinterpret_cast<cstone_b200_domain*>(new csb::Engine<K, T>(rank, nranks, bucket, bucketFocus, theta, *box));     }                                                                                                                      void cstone_b200_domain_destroy_##KS##_##TS(cstone_b200_domain* d) { delete reinterpret_cast<csb::Engine<K, T>*>(d); }     int cstone_b200_domain_set_comm_##KS##_##TS(cstone_b200_domain* d, void* comm)                                         {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              reinterpret_cast<csb::Engine<K, T>*>(d)->setComm(comm);                                                                return 0;                                                                                                          }                                                                                                                      int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n, const T* x, const T* y,                                                             const T* z, const T* h, int nprops, const void* const* props,                                                          const int* pb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncBegin(n, x, y, z, h, nprops, props, pb);                       }                                                                                                                      int cstone_b200_domain_sync_finish_##KS##_##TS(cstone_b200_domain* d, K* keys, T* x, T* y, T* z, T* h,                                                                void* const* props)                                                     {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncFinish(keys, x, y, z, h, props);                               }                                                                                                                      int cstone_b200_domain_exchange_halos_##KS##_##TS(cstone_b200_domain* d, int na, void* const* arrays,                                                                    const int* eb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              int st = reinterpret_cast<csb::Engine<K, T>*>(d)->exchangeHalos(na, arrays, eb);                                       if (st) return st;                                                                                                     cudaError_t e = cudaStreamSynchronize(nullptr);                                                                        return int(e);                                                                                                     }                                                                                                                      int cstone_b200_domain_info_##KS##_##TS(const cstone_b200_domain* d, int64_t* info8)                                   {                                                                                                                          if (!d || !info8) return CSTONE_E_INVALID_ARGUMENT;                                                                    reinterpret_cast<const csb::Engine<K, T>*>(d)->info(info8);                                                            return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_stage_ms_##KS##_##TS(const cstone_b200_domain* d, float* ms10)                              \
+#define CSB_DOMAIN_DEF(KS, K, TS, T)                                                                                       cstone_b200_domain* cstone_b200_domain_create_##KS##_##TS(int rank, int nranks, unsigned bucket,                                                                                 unsigned bucketFocus, float theta,                                                                                     const cstone_box_##TS* box)                                  {                                                                                                                          if (!box || nranks < 1 || rank < 0 || rank >= nranks || bucket < bucketFocus || bucketFocus == 0) return nullptr;         return reinterpret_cast<cstone_b200_domain*>(new csb::Engine<K, T>(rank, nranks, bucket, bucketFocus, theta, *box));     }                                                                                                                      void cstone_b200_domain_destroy_##KS##_##TS(cstone_b200_domain* d) { delete reinterpret_cast<csb::Engine<K, T>*>(d); }     int cstone_b200_domain_set_comm_##KS##_##TS(cstone_b200_domain* d, void* comm)                                         {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              reinterpret_cast<csb::Engine<K, T>*>(d)->setComm(comm);                                                                return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_set_fields_ready_event_##KS##_##TS(cstone_b200_domain* d, void* event)                                         {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              reinterpret_cast<csb::Engine<K, T>*>(d)->setFieldsReadyEvent(event);                                                                return 0;                                                                                                          }                                                                                                                      int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n, const T* x, const T* y,                                                             const T* z, const T* h, int nprops, const void* const* props,                                                          const int* pb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncBegin(n, x, y, z, h, nprops, props, pb);                       }                                                                                                                      int cstone_b200_domain_sync_finish_##KS##_##TS(cstone_b200_domain* d, K* keys, T* x, T* y, T* z, T* h,                                                                void* const* props)                                                     {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncFinish(keys, x, y, z, h, props);                               }                                                                                                                      int cstone_b200_domain_exchange_halos_##KS##_##TS(cstone_b200_domain* d, int na, void* const* arrays,                                                                    const int* eb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              int st = reinterpret_cast<csb::Engine<K, T>*>(d)->exchangeHalos(na, arrays, eb);                                       if (st) return st;                                                                                                     cudaError_t e = cudaStreamSynchronize(nullptr);                                                                        return int(e);                                                                                                     }                                                                                                                      int cstone_b200_domain_info_##KS##_##TS(const cstone_b200_domain* d, int64_t* info8)                                   {                                                                                                                          if (!d || !info8) return CSTONE_E_INVALID_ARGUMENT;                                                                    reinterpret_cast<const csb::Engine<K, T>*>(d)->info(info8);                                                            return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_stage_ms_##KS##_##TS(const cstone_b200_domain* d, float* ms10)                              \
     {                                                                                                                  \
         if (!d || !ms10) return CSTONE_E_INVALID_ARGUMENT;                                                             \
         reinterpret_cast<const csb::Engine<K, T>*>(d)->stageMs(ms10);                                                  \

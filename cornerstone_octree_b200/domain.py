@@ -73,9 +73,12 @@ class Domain:
         _check(_fn("set_comm", self.bits, self.fd)(self._h, comm), "set_comm")
 
     # ---- sync
-    def sync(self, x, y, z, h, props=()):
+    def sync(self, x, y, z, h, props=(), fields_ready=None):
         """[ref: domain/domain.hpp:196-243] returns (keys, x, y, z, h, props) as NEW tensors of the new local size:
-        assigned particles in [start_index, end_index), halos elsewhere, everything in SFC order"""
+        assigned particles in [start_index, end_index), halos elsewhere, everything in SFC order.
+        fields_ready: optional torch.cuda.Event after which h and props are valid (e.g. the end of their upload on
+        another stream); x, y, z must be valid at the call, the engine waits for the event before it first reads
+        h / props, so that box, keys and sort overlap the rest of the upload."""
         for t in (x, y, z, h) + tuple(props):
             if not t.is_cuda or not t.is_contiguous():
                 raise ValueError("Domain.sync operates on contiguous CUDA tensors (no CPU fallback)")
@@ -83,6 +86,9 @@ class Domain:
         k = len(props)
         parr = (C.c_void_p * max(k, 1))(*[p.data_ptr() for p in props])
         pbytes = (C.c_int * max(k, 1))(*[p.element_size() for p in props])
+        if fields_ready is not None:
+            _check(_fn("set_fields_ready_event", self.bits, self.fd)(self._h, C.c_void_p(fields_ready.cuda_event)),
+                   "set_fields_ready_event")
         n_new = _fn("sync_begin", self.bits, self.fd)(self._h, n_in, ops._p(x), ops._p(y), ops._p(z), ops._p(h), k, parr,
                                                      pbytes)
         if n_new < 0:

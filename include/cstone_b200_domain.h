@@ -45,6 +45,7 @@ int cstone_b200_nccl_comm_destroy(void* comm);
                                                               const cstone_box_##TS* box);                             \
     void cstone_b200_domain_destroy_##KS##_##TS(cstone_b200_domain* d);                                                \
     int cstone_b200_domain_set_comm_##KS##_##TS(cstone_b200_domain* d, void* nccl_comm);                               \
+    int cstone_b200_domain_set_fields_ready_event_##KS##_##TS(cstone_b200_domain* d, void* cuda_event);                \
     /* [ref: domain/domain.hpp:196-243 sync]; props: HOST array of nprops device pointers, element sizes 4 or 8 */    \
     int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n_in, const T* x, const T* y,    \
                                                       const T* z, const T* h, int nprops, const void* const* props,    \

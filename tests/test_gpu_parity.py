@@ -129,6 +129,20 @@ def test_gather_multi_and_scatter(gpu):
     assert np.array_equal(back.cpu().numpy(), arrs[0])
 
 
+@pytest.mark.parametrize("narr", [1, 3, 4, 8, 9])
+@pytest.mark.parametrize("n", [4095, 4096, 100003])
+def test_gather_multi_all_double(narr, n, gpu):
+    """the four-elements-per-thread kernel (8-byte arrays only, n >= 4096, tail of n % 4) and its fallbacks"""
+    import torch
+    from cornerstone_octree_b200 import ops
+    rng = np.random.default_rng(narr * 7 + n)
+    perm = rng.permutation(n).astype(np.int32)
+    arrs = [rng.integers(0, 2 ** 63, n).view(np.float64) if k % 2 else rng.integers(0, 2 ** 63, n) for k in range(narr)]
+    out = ops.gather_multi(torch.from_numpy(perm).cuda(), [torch.from_numpy(a).cuda() for a in arrs])
+    for a, o in zip(arrs, out):
+        assert np.array_equal(o.cpu().numpy().view(np.int64), a.view(np.int64)[perm])
+
+
 @pytest.mark.parametrize("offset", [0.0, 1.0e6])
 @pytest.mark.parametrize("bnd", [(0, 0, 0), (1, 1, 1)])
 def test_neighbors_on_the_radius(offset, bnd, gpu, port):
