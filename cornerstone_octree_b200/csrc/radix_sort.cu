@@ -26,6 +26,7 @@ constexpr int kRadix        = 1 << kRadixBits;
 constexpr int kSortThreads  = 256; // == kRadix: thread d owns digit d in the look-back
 constexpr int kSortWarps    = kSortThreads / 32;
 constexpr int kSortItems    = 16;
+constexpr int kLookBack     = 4;  // predecessor tiles fetched per look-back round
 constexpr int kSortTile     = kSortThreads * kSortItems;
 constexpr uint32_t kStFlagShift     = 30;
 constexpr uint32_t kStValueMask     = (1u << kStFlagShift) - 1u;
@@ -77,6 +78,22 @@ __device__ inline uint32_t ldRelaxed(const uint32_t* p)
 __device__ inline void stRelaxed(uint32_t* p, uint32_t v)
 {
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+/* Lanes of the warp that hold the same 8-bit digit.  Eight ballots instead of match.any: MATCH runs on the ADU pipe at
+ * ~1 warp instruction per 64 cycles per SM (measured: 72 % ADU utilisation was the limiter of the whole pass), a
+ * VOTE + LOP3 pair per bit is an order of magnitude cheaper. */
+__device__ inline unsigned matchDigit(unsigned d)
+{
+    unsigned peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < kRadixBits; ++b)
+    {
+        const bool bit   = (d >> b) & 1u;
+        const unsigned m = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? m : ~m;
+    }
+    return peers;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -136,23 +153,29 @@ struct SortSmem
 {
     K keys[kSortTile];
     uint32_t vals[kSortTile];
-    uint32_t warpHist[kSortWarps][kRadix];
-    uint32_t digitStart[kRadix]; // exclusive scan of the tile's digit counts
-    uint32_t globalBase[kRadix]; // global position of local slot 0 of each digit, minus digitStart
+    uint32_t stage[kSortTile];            // values in load order: cp.async landing zone (no registers while ranking)
+    uint32_t warpHist[kSortWarps][kRadix]; // per warp digit counts, then first tile-local slot of (warp, digit)
+    uint32_t globalBase[kRadix];           // global position of local slot 0 of each digit, minus its tile-local start
     uint32_t warpSums[kSortWarps];
     uint32_t tile;
 };
 
+__device__ inline void cpAsync4(void* smemDst, const void* src)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(uint32_t(__cvta_generic_to_shared(smemDst))), "l"(src)
+                 : "memory");
+}
+
 template<class K, bool Iota>
-__global__ void __launch_bounds__(kSortThreads) onesweepKernel(const K* __restrict__ keysIn,
-                                                                const uint32_t* __restrict__ valsIn,
-                                                                K* __restrict__ keysOut,
-                                                                uint32_t* __restrict__ valsOut,
-                                                                uint32_t n,
-                                                                int shift,
-                                                                const uint32_t* __restrict__ binOffsets,
-                                                                uint32_t* __restrict__ ticket,
-                                                                uint32_t* __restrict__ status)
+__global__ void __launch_bounds__(kSortThreads, 3) onesweepKernel(const K* __restrict__ keysIn,
+                                                                   const uint32_t* __restrict__ valsIn,
+                                                                   K* __restrict__ keysOut,
+                                                                   uint32_t* __restrict__ valsOut,
+                                                                   uint32_t n,
+                                                                   int shift,
+                                                                   const uint32_t* __restrict__ binOffsets,
+                                                                   uint32_t* __restrict__ ticket,
+                                                                   uint32_t* __restrict__ status)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     SortSmem<K>& sm = *reinterpret_cast<SortSmem<K>*>(smemRaw);
@@ -168,34 +191,47 @@ __global__ void __launch_bounds__(kSortThreads) onesweepKernel(const K* __restri
     __syncthreads();
     const uint32_t tile     = sm.tile;
     const uint32_t tileBase = tile * uint32_t(kSortTile);
-    const uint32_t warpBase = tileBase + warp * (32u * kSortItems);
+    const uint32_t warpOff  = warp * (32u * kSortItems) + lane; // tile-local index of item 0 of this thread
+    const bool fullTile     = tileBase + uint32_t(kSortTile) <= n;
 
-    // ---- load (warp-striped: item i of lane l is element warpBase + 32 i + l); order = (warp, i, lane)
+    // ---- load (warp-striped: item i of lane l is element tileBase + warpOff + 32 i); order = (warp, i, lane).
+    //      Values travel straight to shared memory (cp.async) and are picked up by the same thread at the reorder.
     K key[kSortItems];
-    uint32_t val[kSortItems];
-#pragma unroll
-    for (int i = 0; i < kSortItems; ++i)
+    if (fullTile)
     {
-        uint32_t idx = warpBase + 32u * i + lane;
-        key[i]       = (idx < n) ? keysIn[idx] : K(~K(0)); // padding sorts behind everything, never written
-    }
+        const K* src = keysIn + tileBase + warpOff;
 #pragma unroll
-    for (int i = 0; i < kSortItems; ++i)
-    {
-        uint32_t idx = warpBase + 32u * i + lane;
-        if (Iota) val[i] = idx;
-        else val[i] = (idx < n) ? valsIn[idx] : 0u;
+        for (int i = 0; i < kSortItems; ++i)
+            key[i] = src[32 * i];
+        if (!Iota)
+        {
+            const uint32_t* vsrc = valsIn + tileBase + warpOff;
+#pragma unroll
+            for (int i = 0; i < kSortItems; ++i)
+                cpAsync4(&sm.stage[warpOff + 32u * i], vsrc + 32 * i);
+        }
     }
+    else
+    {
+#pragma unroll
+        for (int i = 0; i < kSortItems; ++i)
+        {
+            const uint32_t idx = tileBase + warpOff + 32u * i;
+            key[i]             = (idx < n) ? keysIn[idx] : K(~K(0)); // padding sorts behind everything, never written
+            if (!Iota && idx < n) cpAsync4(&sm.stage[warpOff + 32u * i], valsIn + idx);
+        }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
 
     // ---- stable ranking inside the warp
     uint16_t rank[kSortItems];
-    uint32_t* myHist        = sm.warpHist[warp];
-    const unsigned lanesLt  = laneMaskLt();
+    uint32_t* myHist       = sm.warpHist[warp];
+    const unsigned lanesLt = laneMaskLt();
 #pragma unroll
     for (int i = 0; i < kSortItems; ++i)
     {
         unsigned d      = unsigned(key[i] >> shift) & (kRadix - 1);
-        unsigned peers  = __match_any_sync(0xffffffffu, d);
+        unsigned peers  = matchDigit(d);
         unsigned leader = __ffs(int(peers)) - 1;
         uint32_t before = 0;
         if (lane == leader)
@@ -209,18 +245,20 @@ __global__ void __launch_bounds__(kSortThreads) onesweepKernel(const K* __restri
     }
     __syncthreads();
 
-    // ---- per digit (thread d = digit d): exclusive scan over warps, tile count, look-back
+    // ---- per digit (thread d = digit d): tile count, aggregate published, tile-local starts of every (warp, digit)
+    uint32_t st[kLookBack];
+    uint32_t tileCount, dStart;
+    uint32_t* const myStatus = status + size_t(tile) * kRadix + tid;
     {
+        uint32_t c[kSortWarps];
         uint32_t run = 0;
 #pragma unroll
         for (int w = 0; w < kSortWarps; ++w)
         {
-            uint32_t c          = sm.warpHist[w][tid];
-            sm.warpHist[w][tid] = run;
-            run += c;
+            c[w] = sm.warpHist[w][tid];
+            run += c[w];
         }
-        const uint32_t tileCount = run;
-        uint32_t* myStatus       = status + size_t(tile) * kRadix + tid;
+        tileCount = run;
         if (tile == 0) stRelaxed(myStatus, kStInclusive | tileCount);
         else stRelaxed(myStatus, kStAggregate | tileCount);
 
@@ -238,29 +276,26 @@ __global__ void __launch_bounds__(kSortThreads) onesweepKernel(const K* __restri
 #pragma unroll
         for (int w = 0; w < kSortWarps; ++w)
             if (w < int(warp)) off += sm.warpSums[w];
-        const uint32_t dStart = off + incl - tileCount;
-        sm.digitStart[tid]    = dStart;
-
-        // decoupled look-back over earlier tiles for this digit
-        uint32_t excl = 0;
+        dStart = off + incl - tileCount;
+        run    = dStart;
+#pragma unroll
+        for (int w = 0; w < kSortWarps; ++w)
+        {
+            sm.warpHist[w][tid] = run;
+            run += c[w];
+        }
+        /* first window of the decoupled look-back: the status words of the kLookBack preceding tiles are requested
+         * now and consumed after the reorder, so their L2 round trip (and part of the wait for the predecessors)
+         * overlaps the shared-memory traffic.  Indices below tile 0 are clamped; tile 0 is always inclusive, so a
+         * clamped copy is never consumed. */
         if (tile > 0)
         {
-            int t = int(tile) - 1;
-            while (true)
-            {
-                uint32_t st;
-                do
-                {
-                    st = ldRelaxed(status + size_t(t) * kRadix + tid);
-                } while ((st >> kStFlagShift) == 0u);
-                excl += st & kStValueMask;
-                if ((st >> kStFlagShift) == 2u) break;
-                --t;
-            }
-            stRelaxed(myStatus, kStInclusive | (excl + tileCount));
+#pragma unroll
+            for (int k = 0; k < kLookBack; ++k)
+                st[k] = ldRelaxed(status + size_t(max(int(tile) - 1 - k, 0)) * kRadix + tid);
         }
-        sm.globalBase[tid] = binOffsets[tid] + excl - dStart;
     }
+    asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
 
     // ---- reorder through shared memory
@@ -268,9 +303,41 @@ __global__ void __launch_bounds__(kSortThreads) onesweepKernel(const K* __restri
     for (int i = 0; i < kSortItems; ++i)
     {
         unsigned d   = unsigned(key[i] >> shift) & (kRadix - 1);
-        uint32_t pos = sm.digitStart[d] + sm.warpHist[warp][d] + rank[i];
+        uint32_t pos = sm.warpHist[warp][d] + rank[i];
         sm.keys[pos] = key[i];
-        sm.vals[pos] = val[i];
+        sm.vals[pos] = Iota ? tileBase + warpOff + 32u * i : sm.stage[warpOff + 32u * i];
+    }
+
+    // ---- look-back: consume the window in order up to the first tile that is not ready or is inclusive
+    {
+        uint32_t excl = 0;
+        if (tile > 0)
+        {
+            int t     = int(tile) - 1;
+            bool done = false;
+            for (;;)
+            {
+                bool open = true;
+#pragma unroll
+                for (int k = 0; k < kLookBack; ++k)
+                {
+                    const uint32_t flag = st[k] >> kStFlagShift;
+                    open                = open && flag != 0u;
+                    if (open)
+                    {
+                        excl += st[k] & kStValueMask;
+                        --t;
+                        if (flag == 2u) done = true, open = false;
+                    }
+                }
+                if (done) break;
+#pragma unroll
+                for (int k = 0; k < kLookBack; ++k)
+                    st[k] = ldRelaxed(status + size_t(max(t - k, 0)) * kRadix + tid);
+            }
+            stRelaxed(myStatus, kStInclusive | (excl + tileCount));
+        }
+        sm.globalBase[tid] = binOffsets[tid] + excl - dStart;
     }
     __syncthreads();
 
@@ -282,7 +349,7 @@ __global__ void __launch_bounds__(kSortThreads) onesweepKernel(const K* __restri
         K k           = sm.keys[slot];
         unsigned d    = unsigned(k >> shift) & (kRadix - 1);
         uint32_t pos  = sm.globalBase[d] + slot;
-        if (pos < n)
+        if (fullTile || pos < n)
         {
             keysOut[pos] = k;
             valsOut[pos] = sm.vals[slot];
