@@ -26,7 +26,8 @@ constexpr int kRadix        = 1 << kRadixBits;
 constexpr int kSortThreads  = 256; // == kRadix: thread d owns digit d in the look-back
 constexpr int kSortWarps    = kSortThreads / 32;
 constexpr int kSortItems    = 16;
-constexpr int kLookBack     = 4;  // predecessor tiles fetched per look-back round
+constexpr int kLookBack     = 4;  // predecessor tiles requested before the reorder
+constexpr int kLookBackWide = 16; // ... and per round afterwards
 constexpr int kSortTile     = kSortThreads * kSortItems;
 constexpr uint32_t kStFlagShift     = 30;
 constexpr uint32_t kStValueMask     = (1u << kStFlagShift) - 1u;
@@ -83,17 +84,22 @@ __device__ inline void stRelaxed(uint32_t* p, uint32_t v)
 /* Lanes of the warp that hold the same 8-bit digit.  Eight ballots instead of match.any: MATCH runs on the ADU pipe at
  * ~1 warp instruction per 64 cycles per SM (measured: 72 % ADU utilisation was the limiter of the whole pass), a
  * VOTE + LOP3 pair per bit is an order of magnitude cheaper. */
+template<int Bit>
+__device__ inline unsigned sameBitLanes(unsigned d)
+{
+    // lanes whose bit `Bit` of d equals mine: ballot of the bit, inverted where my bit is clear (LOP3.P, VOTE, @!p LOP3)
+    unsigned m;
+    asm("{\n\t.reg .pred p;\n\t.reg .b32 t;\n\tand.b32 t, %1, %2;\n\tsetp.ne.u32 p, t, 0;\n\t"
+        "vote.sync.ballot.b32 %0, p, 0xffffffff;\n\t@!p not.b32 %0, %0;\n\t}"
+        : "=r"(m)
+        : "r"(d), "n"(1u << Bit));
+    return m;
+}
 __device__ inline unsigned matchDigit(unsigned d)
 {
-    unsigned peers = 0xffffffffu;
-#pragma unroll
-    for (int b = 0; b < kRadixBits; ++b)
-    {
-        const bool bit   = (d >> b) & 1u;
-        const unsigned m = __ballot_sync(0xffffffffu, bit);
-        peers &= bit ? m : ~m;
-    }
-    return peers;
+    static_assert(kRadixBits == 8, "eight ballots");
+    return (sameBitLanes<0>(d) & sameBitLanes<1>(d) & sameBitLanes<2>(d)) &
+           (sameBitLanes<3>(d) & sameBitLanes<4>(d) & sameBitLanes<5>(d)) & (sameBitLanes<6>(d) & sameBitLanes<7>(d));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -166,6 +172,33 @@ __device__ inline void cpAsync4(void* smemDst, const void* src)
                  : "memory");
 }
 
+__device__ inline void cpAsync16(void* smemDst, const void* src)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(uint32_t(__cvta_generic_to_shared(smemDst))), "l"(src)
+                 : "memory");
+}
+
+/* One round of the look-back: consume W status words (tiles t, t-1, ...) in order up to the first tile that is not
+ * ready (flag 0) or carries an inclusive prefix (flag 2).  Returns true when the inclusive prefix was reached. */
+template<int W>
+__device__ inline bool consumeWindow(const uint32_t (&st)[W], uint32_t& excl, int& t)
+{
+    bool open = true, done = false;
+#pragma unroll
+    for (int k = 0; k < W; ++k)
+    {
+        const uint32_t flag = st[k] >> kStFlagShift;
+        open                = open && flag != 0u;
+        if (open)
+        {
+            excl += st[k] & kStValueMask;
+            --t;
+            if (flag == 2u) done = true, open = false;
+        }
+    }
+    return done;
+}
+
 template<class K, bool Iota>
 __global__ void __launch_bounds__(kSortThreads, 3) onesweepKernel(const K* __restrict__ keysIn,
                                                                    const uint32_t* __restrict__ valsIn,
@@ -205,10 +238,20 @@ __global__ void __launch_bounds__(kSortThreads, 3) onesweepKernel(const K* __res
             key[i] = src[32 * i];
         if (!Iota)
         {
-            const uint32_t* vsrc = valsIn + tileBase + warpOff;
+            if ((reinterpret_cast<uintptr_t>(valsIn) & 15u) == 0)
+            {
+                // 16 bytes per copy, tile order; the reorder reads them after cp.async.wait_all + the block barrier
 #pragma unroll
-            for (int i = 0; i < kSortItems; ++i)
-                cpAsync4(&sm.stage[warpOff + 32u * i], vsrc + 32 * i);
+                for (int r = 0; r < kSortItems / 4; ++r)
+                    cpAsync16(&sm.stage[4u * (tid + r * kSortThreads)], valsIn + tileBase + 4u * (tid + r * kSortThreads));
+            }
+            else
+            {
+                const uint32_t* vsrc = valsIn + tileBase + warpOff;
+#pragma unroll
+                for (int i = 0; i < kSortItems; ++i)
+                    cpAsync4(&sm.stage[warpOff + 32u * i], vsrc + 32 * i);
+            }
         }
     }
     else
@@ -308,32 +351,21 @@ __global__ void __launch_bounds__(kSortThreads, 3) onesweepKernel(const K* __res
         sm.vals[pos] = Iota ? tileBase + warpOff + 32u * i : sm.stage[warpOff + 32u * i];
     }
 
-    // ---- look-back: consume the window in order up to the first tile that is not ready or is inclusive
+    // ---- look-back: the pre-fetched window first, then wider windows (the key registers are free by now)
     {
         uint32_t excl = 0;
         if (tile > 0)
         {
-            int t     = int(tile) - 1;
-            bool done = false;
-            for (;;)
+            int t = int(tile) - 1;
+            if (!consumeWindow<kLookBack>(st, excl, t))
             {
-                bool open = true;
-#pragma unroll
-                for (int k = 0; k < kLookBack; ++k)
+                uint32_t wide[kLookBackWide];
+                do
                 {
-                    const uint32_t flag = st[k] >> kStFlagShift;
-                    open                = open && flag != 0u;
-                    if (open)
-                    {
-                        excl += st[k] & kStValueMask;
-                        --t;
-                        if (flag == 2u) done = true, open = false;
-                    }
-                }
-                if (done) break;
 #pragma unroll
-                for (int k = 0; k < kLookBack; ++k)
-                    st[k] = ldRelaxed(status + size_t(max(t - k, 0)) * kRadix + tid);
+                    for (int k = 0; k < kLookBackWide; ++k)
+                        wide[k] = ldRelaxed(status + size_t(max(t - k, 0)) * kRadix + tid);
+                } while (!consumeWindow<kLookBackWide>(wide, excl, t));
             }
             stRelaxed(myStatus, kStInclusive | (excl + tileCount));
         }
