@@ -118,9 +118,29 @@ __global__ void __launch_bounds__(512) histogramKernel(const K* __restrict__ key
     for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
     {
         K key = keys[i];
+        /* SFC keys of a time-stepping code arrive almost sorted: the upper digits of 32 consecutive keys are then
+         * identical and a plain atomicAdd would serialise 32 ways on one address.  One vote on the upper half of the
+         * key decides for P/2 digits at once: if it is warp-uniform, lane p adds the warp's count to digit p.
+         * (Full warps only; the ragged tail takes the plain path.) */
+        constexpr int PH    = P / 2;
+        const unsigned top  = unsigned(key >> (PH * kRadixBits));
+        bool uniform        = false;
+        if (__activemask() == 0xffffffffu) uniform = __all_sync(0xffffffffu, top == __shfl_sync(0xffffffffu, top, 0));
 #pragma unroll
-        for (int p = 0; p < P; ++p)
+        for (int p = 0; p < PH; ++p)
             atomicAdd(&sHist[p * kRadix + (unsigned(key >> (p * kRadixBits)) & (kRadix - 1))], 1u);
+        if (uniform)
+        {
+            const unsigned l = threadIdx.x & 31u;
+            if (l < unsigned(P - PH))
+                atomicAdd(&sHist[(PH + l) * kRadix + ((top >> (l * kRadixBits)) & (kRadix - 1))], 32u);
+        }
+        else
+        {
+#pragma unroll
+            for (int p = PH; p < P; ++p)
+                atomicAdd(&sHist[p * kRadix + (unsigned(key >> (p * kRadixBits)) & (kRadix - 1))], 1u);
+        }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < P * kRadix; i += blockDim.x)
