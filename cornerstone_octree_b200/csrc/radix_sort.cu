@@ -379,11 +379,19 @@ __global__ void __launch_bounds__(kSortThreads, 3) onesweepKernel(const K* __res
             int t = int(tile) - 1;
             if (!consumeWindow<kLookBack>(st, excl, t))
             {
+                /* wait on ONE word (the first tile that was not ready), then fetch the window behind it: polling with
+                 * the whole window floods the L2 when many tiles reach the look-back together (small or digit-uniform
+                 * sorts: 5x slower passes) */
                 uint32_t wide[kLookBackWide];
                 do
                 {
+                    const uint32_t* sp = status + size_t(t) * kRadix + tid;
+                    do
+                    {
+                        wide[0] = ldRelaxed(sp);
+                    } while ((wide[0] >> kStFlagShift) == 0u);
 #pragma unroll
-                    for (int k = 0; k < kLookBackWide; ++k)
+                    for (int k = 1; k < kLookBackWide; ++k)
                         wide[k] = ldRelaxed(status + size_t(max(t - k, 0)) * kRadix + tid);
                 } while (!consumeWindow<kLookBackWide>(wide, excl, t));
             }

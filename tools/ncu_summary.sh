@@ -2,7 +2,7 @@
 # Summary of one `ncu --set full --import-source on` capture of findNeighborsKernel: headline metrics + per-line shares.
 # usage: tools/ncu_summary.sh <report.ncu-rep> <lib with the same build> "<header line>"
 set -e
-rep=$1; lib=$2; hdr=$3
+rep=$1; lib=$(realpath $2); hdr=$3
 tmp=$(mktemp -d)
 ncu -i $rep --page raw --csv 2>/dev/null > $tmp/raw.csv
 ncu -i $rep --page source --csv 2>/dev/null > $tmp/sass.csv
@@ -19,5 +19,5 @@ for k in keys:
 PY
 echo
 echo "# per source line (tools/ncu_lines.py on --page source --csv; cubin of the same build)"
-python tools/ncu_lines.py $tmp/sass.csv $tmp/neighbors.sm_100a.cubin _ZN3csb19findNeighborsKernelIdLb0EEEvNS_8NbParamsIT_EE 45 | cut -c1-170
+python tools/ncu_lines.py $tmp/sass.csv $tmp/neighbors.sm_100a.cubin ${KERN:-_ZN3csb19findNeighborsKernelIdLb0ELb1EEEvNS_8NbParamsIT_EE} 45 | cut -c1-170
 rm -rf $tmp
