@@ -29,12 +29,15 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
+# stdout carries exactly one JSON line: NCCL's own banner / debug output (NCCL_DEBUG=VERSION|INFO in the environment)
+# goes to stderr.  Must be set before the first communicator is created.
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 METRIC = "Domain::sync + findNeighbors"
 UNIT = "Mparticles/s"
 NG0 = 100
-# dram__bytes_read.sum + dram__bytes_write.sum of one findNeighborsKernel launch at 32 M uniform (profiles/r01_*)
-NEIGHBOR_TRAFFIC_BYTES = 31_562_043_000  # dram read+write of one launch, profiles/r01d_findNeighbors_full.txt
+# dram__bytes_read.sum + dram__bytes_write.sum of one findNeighborsKernel launch at 32 M uniform (ncu --set full)
+NEIGHBOR_TRAFFIC_BYTES = 24_110_202_000  # dram read (9.145 GB) + write (14.965 GB) of one launch, profiles/r01e_findNeighbors_full.txt
 
 
 # ------------------------------------------------------------------------------------------------ inputs
