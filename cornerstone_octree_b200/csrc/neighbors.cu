@@ -46,6 +46,9 @@ constexpr int kNbStack     = 160; // >= 7 * 21 + 1 entries can be pending at any
 #ifndef NB_ASYNC
 #define NB_ASYNC 1 // workspace kernels: cp.async pipeline for candidate chunks and node records
 #endif
+#ifndef NB_MERGE
+#define NB_MERGE 1 // workspace kernels: consecutive reached leaf children that fit into one chunk are tested together
+#endif
 #ifndef NB_PFNODE
 #define NB_PFNODE 0
 #endif
@@ -407,7 +410,8 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
         };
 
         // the staged chunk [base, base + cnt) against this lane (if `mine`); the hit mask goes into the ring
-        auto testChunk = [&](uint32_t base, uint32_t cnt, bool mine, bool anyViol, float e, float e8)
+        auto testChunk = [&](uint32_t base, uint32_t cnt, bool mine, bool anyViol, float e, float e8,
+                             uint32_t vmask = 0xffffffffu)
         {
             uint32_t hm = 0;
             if (mine)
@@ -464,7 +468,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                         if (exactPair<T, AnyPbc>(p, T(cA[0]), T(cA[2]), T(cz), tg)) hm |= 1u << k;
                     }
                 }
-                hm &= ~((self < 32u ? 1u : 0u) << (self & 31u));
+                hm &= vmask & ~((self < 32u ? 1u : 0u) << (self & 31u));
             }
             sm.hitMask[ring][lane] = hm;
             if (lane == 0) sm.hitBase[ring] = base;
@@ -493,7 +497,11 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
 
         /* Workspace kernels: the reached leaf children of the staged node, chunk by chunk.  The raw coordinates of
          * chunk k+1 travel (cp.async) while chunk k is tested; `bits` = reached children of this lane. */
-        auto advanceChunk = [&](unsigned& lt, int& o, uint32_t& base, uint32_t& end) -> bool
+        /* Next chunk.  Consecutive reached leaf children whose particles are contiguous and fit into ONE chunk of 32
+         * are merged into a run (`run` = their child bits): one staging + one test for the whole run, every lane
+         * keeps only the candidates of the leaves its own walk reaches (same order: leaf children are visited in
+         * ascending child order before any internal child). */
+        auto advanceChunk = [&](unsigned& lt, int& o, unsigned& run, uint32_t& base, uint32_t& end) -> bool
         {
             if (o >= 0 && base + 32u < end)
             {
@@ -506,6 +514,17 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                 lt &= lt - 1u;
                 const int2 r = sm.cinfo[o];
                 base = uint32_t(r.x), end = uint32_t(r.y);
+                run = 1u << o;
+#if NB_MERGE
+                for (int q = o + 1; (lt >> q) & 1u; ++q)
+                {
+                    const int2 rn = sm.cinfo[q];
+                    if (uint32_t(rn.x) != end || uint32_t(rn.y) - base > 32u) break;
+                    end = uint32_t(rn.y);
+                    run |= 1u << q;
+                    lt &= ~(1u << q);
+                }
+#endif
                 if (end > base) return true;
             }
             return false;
@@ -521,25 +540,43 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
             }
         };
         // precondition: the copies of the first chunk (if any) were committed as the second-youngest group
-        auto processLeaves = [&](unsigned lt, int o, uint32_t base, uint32_t end, bool have, uint32_t bits)
+        auto processLeaves = [&](unsigned lt, int o, unsigned run, uint32_t base, uint32_t end, bool have, uint32_t bits)
         {
             bool first = true;
             while (have)
             {
                 const uint32_t cbase = base, cnt = min(32u, end - base);
                 const int co = o;
+                const unsigned crun = run;
                 if (first) cpAsyncWait<1>();
                 else cpAsyncWait<0>();
                 first = false;
                 __syncwarp();
-                const float e = sm.rec[co * 8 + 6], e8 = sm.rec[co * 8 + 7];
+                float e = sm.rec[co * 8 + 6], e8 = sm.rec[co * 8 + 7];
+                bool mine      = (bits >> co) & 1u;
+                uint32_t vmask = 0xffffffffu;
+                if (crun & (crun - 1u)) // merged run (warp-uniform): per-lane mask of the candidates in reached leaves
+                {
+                    vmask = 0;
+                    for (unsigned rb = crun; rb; rb &= rb - 1u)
+                    {
+                        const int q      = __ffs(int(rb)) - 1;
+                        const int2 r     = sm.cinfo[q];
+                        const uint32_t n = uint32_t(r.y - r.x);
+                        e                = fmaxf(e, sm.rec[q * 8 + 6]);
+                        e8               = fmaxf(e8, sm.rec[q * 8 + 7]);
+                        const uint32_t m = n ? ((0xffffffffu >> (32u - n)) << (uint32_t(r.x) - cbase)) : 0u;
+                        if ((bits >> q) & 1u) vmask |= m;
+                    }
+                    mine = vmask != 0;
+                }
                 T xj = 0, yj = 0, zj = 0;
                 if (lane < cnt) xj = raw.cand[0][lane], yj = raw.cand[1][lane], zj = raw.cand[2][lane];
                 const bool anyViol = stageChunk(cnt, xj, yj, zj, e);
-                have = advanceChunk(lt, o, base, end);
+                have = advanceChunk(lt, o, run, base, end);
                 if (have) issueChunk(base, end);
                 cpAsyncCommit();
-                testChunk(cbase, cnt, (bits >> co) & 1u, anyViol, e, e8);
+                testChunk(cbase, cnt, mine, anyViol, e, e8, vmask);
             }
         };
         // raw records of the 8 children fc..fc+7 (centres, sizes, node records) on their way to shared memory
@@ -747,14 +784,14 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                         sm.rec[6] = sm.rec[7] = __int_as_float(0x7f800000);
                     }
                     __syncwarp();
-                    unsigned lt = 1u;
+                    unsigned lt = 1u, run = 0;
                     int o       = -1;
                     uint32_t base = 0, end = 0;
-                    const bool have = advanceChunk(lt, o, base, end);
+                    const bool have = advanceChunk(lt, o, run, base, end);
                     if (have) issueChunk(base, end);
                     cpAsyncCommit();
                     cpAsyncCommit(); // (empty) stands in for the node group
-                    processLeaves(lt, o, base, end, have, (rootMask >> lane) & 1u);
+                    processLeaves(lt, o, run, base, end, have, (rootMask >> lane) & 1u);
                 }
                 else
                 {
@@ -776,10 +813,10 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                         const uint32_t bits     = overlapChildren(fc, (mask >> lane) & 1u);
                         const unsigned todo     = __reduce_or_sync(full, bits);
                         // first chunk of the reached leaf children: on its way before anything else
-                        unsigned lt = todo & leafBits;
+                        unsigned lt = todo & leafBits, run = 0;
                         int o       = -1;
                         uint32_t base = 0, end = 0;
-                        const bool have = advanceChunk(lt, o, base, end);
+                        const bool have = advanceChunk(lt, o, run, base, end);
                         if (have) issueChunk(base, end);
                         cpAsyncCommit();
                         // reached internal children go onto the stack (the leaves of this node are visited first)
@@ -802,7 +839,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                         fc = sm.stackFc[sp];
                         if (fc != 0) issueNode(fc);
                         cpAsyncCommit();
-                        processLeaves(lt, o, base, end, have, bits);
+                        processLeaves(lt, o, run, base, end, have, bits);
                         mask = sm.stackMask[sp];
                         __syncwarp();
                     } while (fc != 0);
