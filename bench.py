@@ -32,6 +32,8 @@ if ROOT not in sys.path:
 # stdout carries exactly one JSON line: NCCL's own banner / debug output (NCCL_DEBUG=VERSION|INFO in the environment)
 # goes to stderr.  Must be set before the first communicator is created.
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":  # NCCL honours NCCL_DEBUG_FILE only above level VERSION
+    os.environ["NCCL_DEBUG"] = "WARN"
 
 METRIC = "Domain::sync + findNeighbors"
 UNIT = "Mparticles/s"
@@ -110,8 +112,12 @@ def time_cpu(n, dist, bucket, ngmax, steps, warmup):
 
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
+    """nvidia-smi sampling of SM clocks / throttle reasons.  Started BEFORE the steady warm-up steps (nvidia-smi needs
+    up to a second to come up on an 8-GPU box, longer than a short timed region); every sample carries a timestamp and
+    stop(t0, t1) keeps the samples inside the timed region [t0, t1] (host clock).  If the region was too short to catch
+    one, the samples of the steady warm-up steps (same load) are used and `window` says so."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,timestamp")
 
     def __init__(self, index):
         self.path = "/tmp/cstone_clocks_%d_%d.csv" % (os.getpid(), index)
@@ -119,12 +125,13 @@ class ClockSampler:
         try:
             self.f = open(self.path, "w")
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                          "--format=csv,noheader,nounits", "-lms", "50"], stdout=self.f,
                                          stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
+        import datetime
         out = dict(sm_mhz=None, sm_max_mhz=None, reasons=[])
         if self.proc is None:
             return out
@@ -134,20 +141,28 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         self.f.close()
-        sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = []
         for line in open(self.path):
             p = [s.strip() for s in line.split(",")]
-            if len(p) < 7:
+            if len(p) < 8:
                 continue
             try:
-                sm.append(float(p[0]))
-                mx.append(float(p[1]))
+                row = (float(p[0]), float(p[1]), [nm for k, nm in enumerate(names) if p[3 + k].lower().startswith("active")])
             except ValueError:
                 continue
-            for k, nm in enumerate(names):
-                if p[3 + k].lower().startswith("active"):
-                    reasons.add(nm)
+            try:
+                ts = datetime.datetime.strptime(p[7], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+            except ValueError:
+                ts = None
+            rows.append((ts,) + row)
+        inside = [r for r in rows if t0 is not None and r[0] is not None and t0 <= r[0] <= t1]
+        out["window"] = "timed region" if inside else "steady warm-up + timed region"
+        sm, mx, reasons = [], [], set()
+        for _, a, b, rs in (inside or rows):
+            sm.append(a)
+            mx.append(b)
+            reasons.update(rs)
         try:
             os.remove(self.path)
         except OSError:
@@ -302,16 +317,17 @@ def main():
     run_step()
     barrier()
     first_sync_s = time.perf_counter() - t0
+    sampler = ClockSampler(local_rank)
     for _ in range(max(args.warmup, 3) - 1):
         run_step()
     barrier()
 
     # ---- device-resident timing: EXACTLY K steps between two events
-    sampler = ClockSampler(local_rank)
     launches0 = pkg.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     stage_acc, engine_acc = {}, {}
     barrier()
+    wall0 = time.time()
     ev0.record()
     all_marks = []
     n_assigned = 0
@@ -323,9 +339,10 @@ def main():
             engine_acc[k] = engine_acc.get(k, 0.0) + v / args.steps
     ev1.record()
     barrier()
+    wall1 = time.time()
     ms_total = ev0.elapsed_time(ev1)
     launches = pkg.launch_count() - launches0
-    clocks = sampler.stop()
+    clocks = sampler.stop(wall0, wall1)
     for marks in all_marks:
         for (_, a), (name, b) in zip(marks[:-1], marks[1:]):
             stage_acc[name] = stage_acc.get(name, 0.0) + a.elapsed_time(b) / args.steps
