@@ -65,6 +65,34 @@ _PROTOS = {
     "upsweep_sum": (_i, [_i32, _vp, _vp, _vp, _vp]),
     "compute_node_layout": (_i, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
 }
+_PROTOS.update({
+    "reduce_temp_bytes": (_u64, []),
+    "fill": (_i, [_vp, _sz, _vp, _i, _vp]),
+    "scale_f32": (_i, [_vp, _sz, _f, _vp]),
+    "scale_f64": (_i, [_vp, _sz, C.c_double, _vp]),
+    "increment_u32": (_i, [_vp, _vp, _sz, _u32, _vp]),
+    "increment_u64": (_i, [_vp, _vp, _sz, _u64, _vp]),
+    "reduce_sum_u32": (_i, [_vp, _sz, _u64, _vp, _vp, _vp]),
+    "count_u32": (_i, [_vp, _sz, _u32, _vp, _vp, _vp]),
+    "count_u64": (_i, [_vp, _sz, _u64, _vp, _vp, _vp]),
+    "lower_bound_u32": (_i, [_vp, _sz, _u32, _vp, _vp, _vp]),
+    "lower_bound_u64": (_i, [_vp, _sz, _u64, _vp, _vp, _vp]),
+    "lower_bound_i32": (_i, [_vp, _sz, _i32, _vp, _vp, _vp]),
+    "lower_bound_i64": (_i, [_vp, _sz, C.c_int64, _vp, _vp, _vp]),
+    "lower_bound_f32": (_i, [_vp, _sz, _f, _vp, _vp, _vp]),
+    "gather_ranges": (_i, [_vp, _vp, _i, _i32, _vp, _vp, _sz, _i, _vp]),
+})
+for ts in ("f32", "f64"):
+    _PROTOS["max_norm_square_" + ts] = (_i, [_vp, _vp, _vp, _sz, _vp, _vp, _vp])
+for tt in ("f32_f32", "f64_f32", "f64_f64"):
+    _PROTOS["segment_max_" + tt] = (_i, [_vp, _vp, _i, _sz, _sz, _vp, _vp])
+for ks in ("k32", "k64"):
+    _PROTOS["sort_keys_temp_bytes_" + ks] = (_u64, [_u64])
+    _PROTOS["sort_keys_" + ks] = (_i, [_vp, _vp, _sz, _vp, _u64, _vp])
+    _PROTOS["count_sfc_gaps_" + ks] = (_i, [_vp, _i32, _vp, _vp])
+    _PROTOS["fill_sfc_gaps_" + ks] = (_i, [_vp, _i32, _vp, _vp, _vp])
+    for its in ("u32", "u64"):
+        _PROTOS["lower_bound_many_%s_%s" % (ks, its)] = (_i, [_vp, _sz, _vp, _sz, _vp, _vp])
 for ts in ("f32", "f64"):
     _PROTOS["minmax3_" + ts] = (_i, [_vp, _vp, _vp, _sz, _vp, _vp, _vp])
     _PROTOS["halo_radii_" + ts] = (_i, [_vp, _vp, _sz, _f, _vp, _vp])

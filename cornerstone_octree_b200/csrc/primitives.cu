@@ -19,9 +19,6 @@
 namespace csb
 {
 
-int sortByKeyDispatch32(uint32_t*, uint32_t*, uint32_t*, uint32_t*, size_t, void*, uint64_t, int, cudaStream_t);
-int sortByKeyDispatch64(uint64_t*, uint32_t*, uint64_t*, uint32_t*, size_t, void*, uint64_t, int, cudaStream_t);
-
 constexpr int kPrimThreads   = 256;
 constexpr int kReduceBlocks  = kNumSMs * 4;
 
@@ -217,11 +214,11 @@ struct LoadEquals
 };
 
 // ------------------------------------------------------------------------------------------------ SFC gaps
-//! last non-zero octal digit place of a key, 0 for key 0  [ref: sfc/common.hpp lastNzPlace]
+//! last non-zero octal digit place of a key, maxLevel for key 0  [ref: sfc/common.hpp:339-346]
 template<class K>
 __device__ inline int lastNzPlace(K key)
 {
-    if (key == 0) return 0;
+    if (key == 0) return int(KeyTraits<K>::maxLevel);
     const int tz = (sizeof(K) == 8) ? (__ffsll((long long)key) - 1) : (__ffs(int(key)) - 1);
     return int(KeyTraits<K>::maxLevel) - tz / 3;
 }

@@ -457,3 +457,143 @@ def find_neighbors(x, y, z, h, first_id, last_id, box, octree, layout, centers, 
              _p(octree.child_offsets), _p(octree.internal_to_leaf), _p(layout), _p(centers), _p(sizes),
              search_ext_factor, ngmax, _p(neighbors), _p(neighbors_count), num_leaves, _p(temp), _stream())
     return neighbors, neighbors_count
+
+
+# --------------------------------------------------------------------------------------------- small primitives
+# [ref: primitives/primitives_gpu.h:39-125, tree/csarray_gpu.h:86-89, halos/gather_halos_gpu.h:21-27]
+_INT_SFX = {torch.int32: "u32", torch.int64: "u64"}
+
+
+def _host_scalar(ctype, v=0):
+    return ctype(v)
+
+
+def fill(t, value):
+    """fillGpu: every element of a 1-, 4- or 8-byte tensor = value"""
+    _require_cuda(t)
+    v = np.array([value], dtype={torch.uint8: np.uint8, torch.int8: np.int8, torch.int32: np.int32, torch.int64: np.int64,
+                                 torch.float32: np.float32, torch.float64: np.float64}[t.dtype])
+    call("fill", _p(t), t.numel(), v.ctypes.data_as(C.c_void_p), t.element_size(), _stream())
+    return t
+
+
+def scale(t, value):
+    """scaleGpu: t *= value in place"""
+    _require_cuda(t)
+    call("scale_" + _ts(t), _p(t), t.numel(), value, _stream())
+    return t
+
+
+def increment(src, value, out=None):
+    """incrementGpu: out[i] = src[i] + value (wrapping, 32- or 64-bit integers)"""
+    _require_cuda(src, out)
+    out = torch.empty_like(src) if out is None else out
+    bits = 32 if src.dtype == torch.int32 else 64
+    call("increment_" + _INT_SFX[src.dtype], _p(src), _p(out), src.numel(), int(value) & ((1 << bits) - 1), _stream())
+    return out
+
+
+def max_norm_square(x, y, z, ws=None):
+    _require_cuda(x, y, z)
+    ws = ws or _ws(x.device)
+    temp = ws.get(call("reduce_temp_bytes"))
+    out = np.zeros(1, dtype=np.float32 if x.dtype == torch.float32 else np.float64)
+    call("max_norm_square_" + _ts(x), _p(x), _p(y), _p(z), x.numel(), out.ctypes.data_as(C.c_void_p), _p(temp), _stream())
+    return out[0]
+
+
+def reduce_sum(t, init=0, ws=None):
+    """reduceGpu<unsigned, size_t>: 64-bit sum of a u32 array (int32 bit patterns)"""
+    _require_cuda(t)
+    ws = ws or _ws(t.device)
+    temp = ws.get(call("reduce_temp_bytes"))
+    out = C.c_uint64(0)
+    call("reduce_sum_u32", _p(t), t.numel(), int(init), C.byref(out), _p(temp), _stream())
+    return int(out.value)
+
+
+def count(t, value, ws=None):
+    """countGpu: number of elements equal to value"""
+    _require_cuda(t)
+    ws = ws or _ws(t.device)
+    temp = ws.get(call("reduce_temp_bytes"))
+    out = C.c_uint64(0)
+    bits = 32 if t.dtype == torch.int32 else 64
+    call("count_" + _INT_SFX[t.dtype], _p(t), t.numel(), int(value) & ((1 << bits) - 1), C.byref(out), _p(temp), _stream())
+    return int(out.value)
+
+
+def lower_bound(sorted_t, value, unsigned=True, ws=None):
+    """lowerBoundGpu(first, last, value): index of the first element >= value"""
+    _require_cuda(sorted_t)
+    ws = ws or _ws(sorted_t.device)
+    temp = ws.get(call("reduce_temp_bytes"))
+    out = C.c_uint64(0)
+    if sorted_t.dtype == torch.float32:
+        sfx, v = "f32", float(value)
+    else:
+        bits = 32 if sorted_t.dtype == torch.int32 else 64
+        sfx = ("u" if unsigned else "i") + str(bits)
+        v = int(value) & ((1 << bits) - 1) if unsigned else int(value)
+    call("lower_bound_" + sfx, _p(sorted_t), sorted_t.numel(), v, C.byref(out), _p(temp), _stream())
+    return int(out.value)
+
+
+def lower_bound_many(sorted_keys, values, index_bits=32):
+    """lowerBoundGpu(first, last, valueFirst, valueLast, result) on unsigned keys (signed torch bit patterns)"""
+    _require_cuda(sorted_keys, values)
+    res = torch.empty(values.numel(), dtype=KEY_TORCH[index_bits], device=values.device)
+    call("lower_bound_many_%s_u%d" % (_ks(sorted_keys), index_bits), _p(sorted_keys), sorted_keys.numel(), _p(values),
+         values.numel(), _p(res), _stream())
+    return res
+
+
+def segment_max(inp, segments, out_dtype=None):
+    """segmentMax<Tin, Tout, IndexType>: segments int32 / int64 (unsigned bit patterns), num_segments+1 entries"""
+    _require_cuda(inp, segments)
+    out_dtype = out_dtype or inp.dtype
+    nseg = segments.numel() - 1
+    out = torch.empty(max(nseg, 0), dtype=out_dtype, device=inp.device)
+    if nseg > 0:
+        call("segment_max_%s_%s" % (_ts(inp), _ts(out)), _p(inp), _p(segments), segments.element_size(), nseg,
+             inp.numel(), _p(out), _stream())
+    return out
+
+
+def sort_keys(keys, ws=None):
+    """sortGpu(first, last, keyBuf): in-place ascending sort of unsigned keys"""
+    _require_cuda(keys)
+    ws = ws or _ws(keys.device)
+    ks = _ks(keys)
+    nbytes = call("sort_keys_temp_bytes_" + ks, keys.numel())
+    temp = ws.get(nbytes)
+    buf = torch.empty_like(keys)
+    call("sort_keys_" + ks, _p(keys), _p(buf), keys.numel(), _p(temp), nbytes, _stream())
+    return keys
+
+
+def count_sfc_gaps(tree):
+    """countSfcGapsGpu: node_ops[i] = nodes needed to span [tree[i], tree[i+1]); num_nodes+1 entries, last = 0"""
+    _require_cuda(tree)
+    n = tree.numel() - 1
+    ops_ = torch.zeros(n + 1, dtype=torch.int32, device=tree.device)
+    call("count_sfc_gaps_" + _ks(tree), _p(tree), n, _p(ops_), _stream())
+    return ops_
+
+
+def fill_sfc_gaps(tree, scanned_ops, new_num_nodes):
+    """fillSfcGapsGpu with the exclusive scan of count_sfc_gaps"""
+    _require_cuda(tree, scanned_ops)
+    new_tree = torch.empty(new_num_nodes + 1, dtype=tree.dtype, device=tree.device)
+    call("fill_sfc_gaps_" + _ks(tree), _p(tree), tree.numel() - 1, _p(scanned_ops), _p(new_tree), _stream())
+    return new_tree
+
+
+def gather_ranges(range_scan, range_offsets, src, buffer_size):
+    """gatherRanges<T, IndexType>: pack index ranges of src (rows of 4/8/12/16 bytes) into one send buffer"""
+    _require_cuda(range_scan, range_offsets, src)
+    row_bytes = src.element_size() * (src.shape[1] if src.dim() == 2 else 1)
+    out = torch.empty((buffer_size,) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
+    call("gather_ranges", _p(range_scan), _p(range_offsets), range_scan.element_size(), range_scan.numel(), _p(src),
+         _p(out), buffer_size, row_bytes, _stream())
+    return out

@@ -369,6 +369,87 @@ int cstone_b200_find_neighbors_ws_f64(const double* x, const double* y, const do
                                       float search_ext_factor, uint32_t ngmax, uint32_t* neighbors,
                                       uint32_t* neighbors_count, int32_t num_leaf_nodes, void* temp, void* stream);
 
+/* ------------------------------------------------------------------------
+ * small primitives used by the callers of the hot path between its stages
+ * [ref: primitives/primitives_gpu.h:39-125; tree/csarray_gpu.h:86-89;
+ *       halos/gather_halos_gpu.h:21-27]
+ * Results returned through a HOST pointer synchronise the stream (the
+ * reference returns them by value).  temp >= cstone_b200_reduce_temp_bytes().
+ * ---------------------------------------------------------------------- */
+uint64_t cstone_b200_reduce_temp_bytes(void);
+/* fillGpu(first, first+n, value): elem_bytes in {1,4,8}, value_host points to one element */
+int cstone_b200_fill(void* first, size_t n, const void* value_host, int elem_bytes, void* stream);
+/* scaleGpu: first[i] *= value */
+int cstone_b200_scale_f32(float* first, size_t n, float value, void* stream);
+int cstone_b200_scale_f64(double* first, size_t n, double value, void* stream);
+/* incrementGpu: out[i] = in[i] + value (wrapping) */
+int cstone_b200_increment_u32(const uint32_t* in, uint32_t* out, size_t n, uint32_t value, void* stream);
+int cstone_b200_increment_u64(const uint64_t* in, uint64_t* out, size_t n, uint64_t value, void* stream);
+/* maxNormSquareGpu: max_i (x*x + y*y + z*z), 0 for n = 0 */
+int cstone_b200_max_norm_square_f32(const float* x, const float* y, const float* z, size_t n, float* out_host,
+                                    void* temp, void* stream);
+int cstone_b200_max_norm_square_f64(const double* x, const double* y, const double* z, size_t n, double* out_host,
+                                    void* temp, void* stream);
+/* reduceGpu<unsigned,size_t>: init + sum of in[0..n) in 64 bits */
+int cstone_b200_reduce_sum_u32(const uint32_t* in, size_t n, uint64_t init, uint64_t* out_host, void* temp,
+                               void* stream);
+/* countGpu: number of elements equal to value (int arrays: pass the bit pattern to _u32) */
+int cstone_b200_count_u32(const uint32_t* first, size_t n, uint32_t value, uint64_t* out_host, void* temp,
+                          void* stream);
+int cstone_b200_count_u64(const uint64_t* first, size_t n, uint64_t value, uint64_t* out_host, void* temp,
+                          void* stream);
+/* lowerBoundGpu(first, last, value) -> index of the first element >= value of a sorted array */
+int cstone_b200_lower_bound_u32(const uint32_t* first, size_t n, uint32_t value, uint64_t* out_host, void* temp,
+                                void* stream);
+int cstone_b200_lower_bound_u64(const uint64_t* first, size_t n, uint64_t value, uint64_t* out_host, void* temp,
+                                void* stream);
+int cstone_b200_lower_bound_i32(const int32_t* first, size_t n, int32_t value, uint64_t* out_host, void* temp,
+                                void* stream);
+int cstone_b200_lower_bound_i64(const int64_t* first, size_t n, int64_t value, uint64_t* out_host, void* temp,
+                                void* stream);
+int cstone_b200_lower_bound_f32(const float* first, size_t n, float value, uint64_t* out_host, void* temp,
+                                void* stream);
+/* lowerBoundGpu(first, last, valueFirst, valueLast, result): one search per value, result index type u32 / u64
+ * [used by createSendRangesGpu, domain/domaindecomp_gpu.cuh:55-69] */
+int cstone_b200_lower_bound_many_k32_u32(const uint32_t* first, size_t n, const uint32_t* values, size_t num_values,
+                                         uint32_t* result, void* stream);
+int cstone_b200_lower_bound_many_k64_u32(const uint64_t* first, size_t n, const uint64_t* values, size_t num_values,
+                                         uint32_t* result, void* stream);
+int cstone_b200_lower_bound_many_k32_u64(const uint32_t* first, size_t n, const uint32_t* values, size_t num_values,
+                                         uint64_t* result, void* stream);
+int cstone_b200_lower_bound_many_k64_u64(const uint64_t* first, size_t n, const uint64_t* values, size_t num_values,
+                                         uint64_t* result, void* stream);
+/* segmentMax<Tin,Tout,IndexType>: out[s] = Tout(max(0, max in[segments[s] .. segments[s+1])));
+ * index_bytes = sizeof(IndexType) in {4,8}; num_elements = segments[num_segments] (a hint that only selects the
+ * thread mapping, the result does not depend on it) */
+int cstone_b200_segment_max_f32_f32(const float* in, const void* segments, int index_bytes, size_t num_segments,
+                                    size_t num_elements, float* out, void* stream);
+int cstone_b200_segment_max_f64_f32(const double* in, const void* segments, int index_bytes, size_t num_segments,
+                                    size_t num_elements, float* out, void* stream);
+int cstone_b200_segment_max_f64_f64(const double* in, const void* segments, int index_bytes, size_t num_segments,
+                                    size_t num_elements, double* out, void* stream);
+/* sortGpu(first, last, keyBuf): ascending key-only sort (onesweep with a scratch permutation in temp) */
+uint64_t cstone_b200_sort_keys_temp_bytes_k32(uint64_t n);
+uint64_t cstone_b200_sort_keys_temp_bytes_k64(uint64_t n);
+int cstone_b200_sort_keys_k32(uint32_t* keys, uint32_t* key_buf, size_t n, void* temp, uint64_t temp_bytes,
+                              void* stream);
+int cstone_b200_sort_keys_k64(uint64_t* keys, uint64_t* key_buf, size_t n, void* temp, uint64_t temp_bytes,
+                              void* stream);
+/* countSfcGapsGpu / fillSfcGapsGpu: node_ops[i] = number of cornerstone nodes needed to span [tree[i], tree[i+1])
+ * [ref: sfc/common.hpp:392-438 spanSfcRange]; after an exclusive scan of node_ops (num_nodes+1 entries),
+ * fill writes those nodes to new_tree + node_ops[i] and new_tree[node_ops[num_nodes]] = tree[num_nodes] */
+int cstone_b200_count_sfc_gaps_k32(const uint32_t* tree, int32_t num_nodes, int32_t* node_ops, void* stream);
+int cstone_b200_count_sfc_gaps_k64(const uint64_t* tree, int32_t num_nodes, int32_t* node_ops, void* stream);
+int cstone_b200_fill_sfc_gaps_k32(const uint32_t* tree, int32_t num_nodes, const int32_t* node_ops,
+                                  uint32_t* new_tree, void* stream);
+int cstone_b200_fill_sfc_gaps_k64(const uint64_t* tree, int32_t num_nodes, const int32_t* node_ops,
+                                  uint64_t* new_tree, void* stream);
+/* gatherRanges<T,IndexType>: buffer[t] = src[range_offsets[r] + t - range_scan[r]] for the range r with
+ * range_scan[r] <= t < range_scan[r+1] (range_scan has num_ranges entries, the last range ends at buffer_size);
+ * index_bytes in {4,8}, elem_bytes in {4,8,12,16}  [halo send-buffer packing, halos/exchange_halos_gpu.cuh:71] */
+int cstone_b200_gather_ranges(const void* range_scan, const void* range_offsets, int index_bytes, int32_t num_ranges,
+                              const void* src, void* buffer, size_t buffer_size, int elem_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

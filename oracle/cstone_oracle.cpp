@@ -923,6 +923,34 @@ void cstone_oracle_gather(const uint32_t* map, size_t n, const void* src, void* 
 TREEFUNCS(k32, uint32_t)
 TREEFUNCS(k64, uint64_t)
 
+/* [ref: sfc/common.hpp:392-430 spanSfcRange, :339-346 lastNzPlace]: walk up from a in growing powers of 8 until the
+ * first octal place where a and b differ, then down towards b in shrinking powers of 8 */
+extern "C++" {
+template<class K>
+static int spanSfcRangeT(K a, K b, K* out)
+{
+    auto lastNz = [](K x) { return x ? int(KT<K>::maxLevel) - KT<K>::ctz(x) / 3 : int(KT<K>::maxLevel); };
+    int n             = 0;
+    const int diffPos = (KT<K>::clz(K(a ^ b)) + 3 - int(KT<K>::unused)) / 3;
+    const int aLast = lastNz(a), bLast = lastNz(b);
+    for (int pos = aLast; pos > diffPos; --pos)
+        for (int d = (8 - int(octalDigit<K>(a, unsigned(pos)))) % 8; d > 0; --d, ++n)
+        {
+            if (out) out[n] = a;
+            a += nodeRange<K>(unsigned(pos));
+        }
+    for (int pos = diffPos; pos <= bLast; ++pos)
+        for (int d = int(octalDigit<K>(b, unsigned(pos))) - int(octalDigit<K>(a, unsigned(pos))); d > 0; --d, ++n)
+        {
+            if (out) out[n] = a;
+            a += nodeRange<K>(unsigned(pos));
+        }
+    return n;
+}
+}
+int cstone_oracle_span_sfc_range_k32(uint32_t a, uint32_t b, uint32_t* out) { return spanSfcRangeT<uint32_t>(a, b, out); }
+int cstone_oracle_span_sfc_range_k64(uint64_t a, uint64_t b, uint64_t* out) { return spanSfcRangeT<uint64_t>(a, b, out); }
+
 void cstone_oracle_upsweep_sum(int32_t numLevels, const int32_t* lr, const int32_t* co, uint32_t* counts)
 {
     upsweepSum(numLevels, lr, co, counts);

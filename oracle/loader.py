@@ -213,6 +213,16 @@ class Oracle:
         out["num_leaf_nodes"], out["num_internal_nodes"], out["num_nodes"] = L, I, M
         return out
 
+    def span_sfc_range(self, a, b, kdtype=np.uint64):
+        """keys of the fewest cornerstone nodes spanning [a, b) [ref: sfc/common.hpp:392-438]"""
+        kt = C.c_uint32 if np.dtype(kdtype) == np.uint32 else C.c_uint64
+        f = self._f("span_sfc_range_" + _ks(kdtype), C.c_int)
+        n = f(kt(int(a)), kt(int(b)), None)
+        out = np.zeros(n, dtype=kdtype)
+        if n:
+            f(kt(int(a)), kt(int(b)), _ptr(out))
+        return out
+
     def upsweep_sum(self, level_range, child_offsets, counts):
         counts = counts.copy()
         self._f("upsweep_sum")(C.c_int32(level_range.size - 1), _ptr(level_range), _ptr(child_offsets), _ptr(counts))

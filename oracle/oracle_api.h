@@ -90,6 +90,10 @@ void ORC(build_octree_k32)(const uint32_t* leaves, int32_t num_leaf_nodes, uint3
 void ORC(build_octree_k64)(const uint64_t* leaves, int32_t num_leaf_nodes, uint64_t* prefixes, int32_t* child_offsets,
                            int32_t* parents, int32_t* level_range, int32_t* internal_to_leaf,
                            int32_t* leaf_to_internal);
+/* cornerstone keys spanning [a, b) with the fewest nodes; out may be NULL (count only)
+ * [ref: sfc/common.hpp:392-438 spanSfcRange; used by countSfcGapsGpu / fillSfcGapsGpu, tree/csarray_gpu.cu:231-265] */
+int ORC(span_sfc_range_k32)(uint32_t a, uint32_t b, uint32_t* out);
+int ORC(span_sfc_range_k64)(uint64_t a, uint64_t b, uint64_t* out);
 void ORC(upsweep_sum)(int32_t num_levels, const int32_t* level_range, const int32_t* child_offsets, uint32_t* counts);
 void ORC(geo_centers_k32_f32)(int kind, const uint32_t* prefixes, int32_t n, float* centers, float* sizes,
                               const cstone_box_f32* box);

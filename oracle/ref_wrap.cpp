@@ -250,6 +250,10 @@ void cstone_ref_build_octree_k32(const uint32_t* leaves, int32_t L, uint32_t* p,
                                  int32_t* i2l, int32_t* l2i) { buildOctreeW(leaves, L, p, co, pa, lr, i2l, l2i); }
 void cstone_ref_build_octree_k64(const uint64_t* leaves, int32_t L, uint64_t* p, int32_t* co, int32_t* pa, int32_t* lr,
                                  int32_t* i2l, int32_t* l2i) { buildOctreeW(leaves, L, p, co, pa, lr, i2l, l2i); }
+int cstone_ref_span_sfc_range_k32(uint32_t a, uint32_t b, uint32_t* out)
+{ return out ? spanSfcRange(a, b, out) : spanSfcRange(a, b); }
+int cstone_ref_span_sfc_range_k64(uint64_t a, uint64_t b, uint64_t* out)
+{ return out ? spanSfcRange(a, b, out) : spanSfcRange(a, b); }
 void cstone_ref_upsweep_sum(int32_t numLevels, const int32_t* levelRange, const int32_t* childOffsets, uint32_t* counts)
 {
     // as used by FocusedOctree::updateCounts: upsweep(levelRange, childOffsets, counts, NodeCount<unsigned>{})

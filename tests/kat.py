@@ -170,6 +170,23 @@ def check_node_counts(impl):
         assert c[0] == 2 and c[-1] == 2 and c.sum() == 4
 
 
+def check_span_sfc_range(impl):
+    """[ref: test/unit/sfc/common.cpp:376-419 spanSfcRange32 / spanSfcRange64]"""
+    for kd in (np.uint32, np.uint64):
+        span = lambda a, b: [int(v) for v in impl.span_sfc_range(a, b, kd)]
+        assert span(0, 0o7777) == [0, 0o1000, 0o2000, 0o3000, 0o4000, 0o5000, 0o6000, 0o7000, 0o7100, 0o7200, 0o7300,
+                                   0o7400, 0o7500, 0o7600, 0o7700, 0o7710, 0o7720, 0o7730, 0o7740, 0o7750, 0o7760,
+                                   0o7770, 0o7771, 0o7772, 0o7773, 0o7774, 0o7775, 0o7776]
+        assert span(1, 0o742) == [1, 2, 3, 4, 5, 6, 7, 0o10, 0o20, 0o30, 0o40, 0o50, 0o60, 0o70, 0o100, 0o200, 0o300,
+                                  0o400, 0o500, 0o600, 0o700, 0o710, 0o720, 0o730, 0o740, 0o741]
+        assert span(0o41305, 0o46000) == [0o41305, 0o41306, 0o41307, 0o41310, 0o41320, 0o41330, 0o41340, 0o41350,
+                                          0o41360, 0o41370, 0o41400, 0o41500, 0o41600, 0o41700, 0o42000, 0o43000,
+                                          0o44000, 0o45000]
+        assert len(span(0o40000, 0o50000)) == 1 and len(span(0o40000, 0o60000)) == 2
+        assert span(int(pad(1, 3, kd)), node_range(0, kd)) == [int(pad(k, 3, kd)) for k in range(1, 8)]
+        assert span(0, 0) == [] and span(1, 1) == []
+
+
 def _spanning_like(kd):
     """cornerstone tree resolving key 1 and key 2^(3L)-1 at maximum depth (same tree computeSpanningTree
     {0,1,R-1,R} yields)"""

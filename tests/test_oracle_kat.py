@@ -4,7 +4,7 @@ import pytest
 import kat
 
 CHECKS = [kat.check_morton, kat.check_hilbert, kat.check_sfc_keys_box, kat.check_sort, kat.check_node_counts,
-          kat.check_rebalance, kat.check_compute_octree, kat.check_octree, kat.check_find_halos]
+          kat.check_rebalance, kat.check_compute_octree, kat.check_octree, kat.check_find_halos, kat.check_span_sfc_range]
 
 
 @pytest.mark.parametrize("check", CHECKS, ids=[c.__name__ for c in CHECKS])
