@@ -14,8 +14,8 @@ namespace csb
 // ------------------------------------------------------------------------------------------------
 // a6 counts.  counts[i] = min(lb(tree[i+1]) - lb(tree[i]), maxCount)  [ref: tree/csarray.hpp:93-103]
 // Each block resolves 257 consecutive leaf boundaries into shared memory with one binary search per boundary
-// (the reference does two per leaf), then differences them.  The search runs over the sorted particle keys;
-// its upper levels are shared by neighbouring boundaries and stay in L2/L1.
+// (the reference does two per leaf), then differences them.  The key range of the block is staged in shared memory
+// by TMA bulk copies (nodeCountsTmaKernel below).
 // ------------------------------------------------------------------------------------------------
 template<class K>
 __device__ inline uint32_t lowerBound(const K* __restrict__ keys, uint32_t n, K value)
@@ -34,6 +34,7 @@ __device__ inline uint32_t lowerBound(const K* __restrict__ keys, uint32_t n, K 
 
 constexpr int kCountThreads = 256;
 
+//! fallback (key array not 16-byte aligned): one global binary search per boundary
 template<class K>
 __global__ void __launch_bounds__(kCountThreads) nodeCountsKernel(const K* __restrict__ tree,
                                                                    uint32_t* __restrict__ counts,
@@ -62,6 +63,147 @@ __global__ void __launch_bounds__(kCountThreads) nodeCountsKernel(const K* __res
     }
 }
 
+/* TMA-staged variant.  The 257 boundaries of 256 consecutive leaves fall into ONE contiguous range [lo, hi) of the
+ * sorted particle keys.  Two warps find lo and hi with a 32-ary cooperative search (5 dependent rounds instead of 25),
+ * the range travels to shared memory as bulk-copy tiles (cp.async.bulk + mbarrier, one elected thread), and every
+ * thread resolves its boundary with a binary search in shared memory.  Each particle key is read from HBM once
+ * (sK per particle) instead of ~25 dependent L2 probes per leaf.  Ranges that are far longer than the leaves they
+ * serve (saturated global-tree leaves) keep the direct search, restricted to [lo, hi). */
+constexpr int kCountTileKeys = 4096;
+constexpr uint32_t kCountMaxChunks = 4;
+
+__device__ inline void mbarInit(uint64_t* bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(uint32_t(__cvta_generic_to_shared(bar))), "r"(count));
+}
+__device__ inline void mbarExpectTx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(uint32_t(__cvta_generic_to_shared(bar))),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ inline void mbarWait(uint64_t* bar, uint32_t phase)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@!p bra WAIT_%=;\n\t}" ::"r"(
+                     uint32_t(__cvta_generic_to_shared(bar))),
+                 "r"(phase)
+                 : "memory");
+}
+__device__ inline void bulkCopyToShared(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     uint32_t(__cvta_generic_to_shared(dst))),
+                 "l"(src), "r"(bytes), "r"(uint32_t(__cvta_generic_to_shared(bar)))
+                 : "memory");
+}
+__device__ inline void fenceProxyAsync() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+//! lower bound of value in keys[0, n) found by one warp: 32 probes per round
+template<class K>
+__device__ inline uint32_t warpLowerBound(const K* __restrict__ keys, uint32_t n, K value)
+{
+    const unsigned lane = threadIdx.x & 31u;
+    uint32_t lo = 0, len = n;
+    while (len > 32u)
+    {
+        const uint32_t p   = lo + uint32_t((uint64_t(lane + 1u) * len) / 33u);
+        const unsigned lt  = __ballot_sync(0xffffffffu, keys[p] < value); // a prefix of the lanes (sorted keys)
+        const unsigned cnt = __popc(lt);
+        const uint32_t pPrev = __shfl_sync(0xffffffffu, p, (cnt + 31u) & 31u); // probe cnt-1
+        const uint32_t pNext = __shfl_sync(0xffffffffu, p, cnt & 31u);         // probe cnt
+        const uint32_t newLo = cnt ? pPrev + 1u : lo;
+        const uint32_t newHi = cnt < 32u ? pNext : lo + len;                   // answer in [newLo, newHi]
+        lo  = newLo;
+        len = newHi - newLo;
+    }
+    const bool lt = lane < len && keys[lo + lane] < value;
+    return lo + __popc(__ballot_sync(0xffffffffu, lt));
+}
+
+template<class K>
+__global__ void __launch_bounds__(kCountThreads) nodeCountsTmaKernel(const K* __restrict__ tree,
+                                                                      uint32_t* __restrict__ counts,
+                                                                      int numNodes,
+                                                                      const K* __restrict__ keys,
+                                                                      uint32_t numKeys,
+                                                                      uint32_t maxCount)
+{
+    constexpr uint32_t E = 16u / sizeof(K); // keys per 16 bytes: bulk copies start and end on 16-byte boundaries
+    __shared__ alignas(128) K sKeys[kCountTileKeys];
+    __shared__ uint32_t sLb[kCountThreads + 1];
+    __shared__ uint32_t sRange[2];
+    __shared__ alignas(8) uint64_t sBar;
+
+    const unsigned tid = threadIdx.x;
+    if (tid == 0)
+    {
+        mbarInit(&sBar, 1);
+        fenceProxyAsync();
+    }
+    __syncthreads();
+    uint32_t phase = 0;
+    const uint32_t numKeysAligned = numKeys & ~(E - 1u);
+
+    for (int blockBase = blockIdx.x * kCountThreads; blockBase < numNodes; blockBase += gridDim.x * kCountThreads)
+    {
+        const int nb = min(kCountThreads, numNodes - blockBase); // leaves of this tile; boundaries blockBase .. +nb
+        if (tid < 32u)
+        {
+            const uint32_t r = warpLowerBound(keys, numKeys, tree[blockBase]);
+            if (tid == 0) sRange[0] = r;
+        }
+        else if (tid < 64u)
+        {
+            const uint32_t r = warpLowerBound(keys, numKeys, tree[blockBase + nb]);
+            if (tid == 32u) sRange[1] = r;
+        }
+        __syncthreads();
+        const uint32_t lo = sRange[0], hi = sRange[1];
+        const bool mine   = int(tid) < nb;
+        const K v         = mine ? tree[blockBase + int(tid)] : K(0);
+        uint32_t ans      = hi;
+        if (tid == 0) sLb[nb] = hi;
+        if (hi - lo > kCountMaxChunks * uint32_t(kCountTileKeys) - E)
+        {
+            if (mine) ans = lo + lowerBound(keys + lo, hi - lo, v);
+        }
+        else
+        {
+            bool open = mine;
+            for (uint32_t start = lo & ~(E - 1u); start < hi; start += uint32_t(kCountTileKeys))
+            {
+                const uint32_t len  = min(uint32_t(kCountTileKeys), hi - start);
+                const uint32_t want = min((len + E - 1u) & ~(E - 1u), numKeysAligned - min(start, numKeysAligned));
+                if (tid == 0 && want)
+                {
+                    fenceProxyAsync();
+                    mbarExpectTx(&sBar, want * uint32_t(sizeof(K)));
+                    bulkCopyToShared(sKeys, keys + start, want * uint32_t(sizeof(K)), &sBar);
+                }
+                if (want + tid < len) sKeys[want + tid] = keys[start + want + tid]; // < E keys behind the last 16-byte unit
+                if (want)
+                {
+                    mbarWait(&sBar, phase);
+                    phase ^= 1u;
+                }
+                __syncthreads();
+                if (open)
+                {
+                    const uint32_t off = start < lo ? lo - start : 0u;
+                    const uint32_t pos = off + lowerBound(sKeys + off, len - off, v);
+                    if (pos < len) ans = start + pos, open = false;
+                }
+                __syncthreads();
+            }
+        }
+        if (mine) sLb[tid] = ans;
+        __syncthreads();
+        if (mine) counts[blockBase + int(tid)] = min(sLb[tid + 1] - sLb[tid], maxCount);
+        __syncthreads();
+    }
+}
+
 template<class K>
 int computeNodeCounts(const K* tree, uint32_t* counts, int numNodes, const K* first, const K* last,
                       uint32_t maxCount, cudaStream_t s)
@@ -70,8 +212,10 @@ int computeNodeCounts(const K* tree, uint32_t* counts, int numNodes, const K* fi
     if (!tree || !counts || last < first) return CSTONE_E_INVALID_ARGUMENT;
     size_t numKeys = size_t(last - first);
     if (numKeys > 0xFFFFFFFFull) return CSTONE_E_TOO_LARGE;
-    unsigned grid = gridFor(size_t(numNodes), kCountThreads, 8);
-    nodeCountsKernel<K><<<grid, kCountThreads, 0, s>>>(tree, counts, numNodes, first, uint32_t(numKeys), maxCount);
+    unsigned grid = gridFor(size_t(numNodes), kCountThreads, 4);
+    if ((reinterpret_cast<uintptr_t>(first) & 15u) == 0)
+        nodeCountsTmaKernel<K><<<grid, kCountThreads, 0, s>>>(tree, counts, numNodes, first, uint32_t(numKeys), maxCount);
+    else nodeCountsKernel<K><<<grid, kCountThreads, 0, s>>>(tree, counts, numNodes, first, uint32_t(numKeys), maxCount);
     CSB_LAUNCHED();
     return 0;
 }
