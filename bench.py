@@ -39,7 +39,7 @@ METRIC = "Domain::sync + findNeighbors"
 UNIT = "Mparticles/s"
 NG0 = 100
 # dram__bytes_read.sum + dram__bytes_write.sum of one findNeighborsKernel launch at 32 M uniform (ncu --set full)
-NEIGHBOR_TRAFFIC_BYTES = 24_110_202_000  # dram read (9.145 GB) + write (14.965 GB) of one launch, profiles/r01e_findNeighbors_full.txt
+NEIGHBOR_TRAFFIC_BYTES = 23_073_595_000  # dram read (8.378 GB) + write (14.696 GB) of one launch, profiles/r01f_findNeighbors_full.txt
 
 
 # ------------------------------------------------------------------------------------------------ inputs

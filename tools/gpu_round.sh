@@ -1,5 +1,6 @@
 #!/bin/bash
-# One GPU-box pass: gpu tests, default bench line, ncu launch list, one full capture of findNeighborsKernel.
+# One GPU-box pass: gpu tests, default bench line, ncu launch list, one full capture of findNeighborsKernel and one
+# full capture of every other kernel of one steady-state step.
 # usage (under gpurun): bash tools/gpu_round.sh <tag> [skip-tests]
 tag=${1:-rXX}; out=gpurun_out
 mkdir -p $out
@@ -13,3 +14,6 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --
   python bench.py --steps 2 --warmup 3 --no-cpu --no-e2e > $out/${tag}_ncu_launch.log 2>&1; echo "ncu list exit $?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:findNeighborsKernel -s 3 -c 1 -f -o $out/${tag}_nb \
   python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e > $out/${tag}_ncu_full.log 2>&1; echo "ncu full exit $?"
+# every other library kernel of the last (steady-state) steps: skip the launches of the cold first sync
+timeout 900 ncu --set full --clock-control none -k regex:'^(?!.*findNeighbors)(csb::|void csb::)' -s 150 -c 70 -f -o $out/${tag}_kernels \
+  python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e > $out/${tag}_ncu_kernels.log 2>&1; echo "ncu kernels exit $?"
