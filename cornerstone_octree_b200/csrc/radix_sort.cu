@@ -25,7 +25,13 @@ constexpr int kRadixBits    = 8;
 constexpr int kRadix        = 1 << kRadixBits;
 constexpr int kSortThreads  = 256; // == kRadix: thread d owns digit d in the look-back
 constexpr int kSortWarps    = kSortThreads / 32;
-constexpr int kSortItems    = 16;
+#ifndef RS_ITEMS
+#define RS_ITEMS 20 // measured at 32 M pairs (tools/sort_variants.sh): u64 12/16/20/24 items = 2.14/2.07/1.98/2.00 ms
+#endif
+#ifndef RS_MINBLOCKS
+#define RS_MINBLOCKS(K) (sizeof(K) == 8 ? 2 : 3) // 91 KB (u64) / 71 KB (u32) of shared memory per block
+#endif
+constexpr int kSortItems    = RS_ITEMS;
 constexpr int kLookBack     = 4;  // predecessor tiles requested before the reorder
 constexpr int kLookBackWide = 16; // ... and per round afterwards
 constexpr int kSortTile     = kSortThreads * kSortItems;
@@ -114,18 +120,16 @@ __global__ void __launch_bounds__(512) histogramKernel(const K* __restrict__ key
         sHist[i] = 0;
     __syncthreads();
 
-    size_t stride = size_t(gridDim.x) * blockDim.x;
-    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    /* SFC keys of a time-stepping code arrive almost sorted: the upper digits of 32 consecutive keys are then
+     * identical and a plain atomicAdd would serialise 32 ways on one address.  One vote on the upper half of the
+     * key decides for P/2 digits at once: if it is warp-uniform, lane p adds the warp's count to digit p.
+     * (Full warps only; the ragged tail takes the plain path.) */
+    auto addKey = [&](K key, bool fullWarp)
     {
-        K key = keys[i];
-        /* SFC keys of a time-stepping code arrive almost sorted: the upper digits of 32 consecutive keys are then
-         * identical and a plain atomicAdd would serialise 32 ways on one address.  One vote on the upper half of the
-         * key decides for P/2 digits at once: if it is warp-uniform, lane p adds the warp's count to digit p.
-         * (Full warps only; the ragged tail takes the plain path.) */
         constexpr int PH    = P / 2;
         const unsigned top  = unsigned(key >> (PH * kRadixBits));
         bool uniform        = false;
-        if (__activemask() == 0xffffffffu) uniform = __all_sync(0xffffffffu, top == __shfl_sync(0xffffffffu, top, 0));
+        if (fullWarp) uniform = __all_sync(0xffffffffu, top == __shfl_sync(0xffffffffu, top, 0));
 #pragma unroll
         for (int p = 0; p < PH; ++p)
             atomicAdd(&sHist[p * kRadix + (unsigned(key >> (p * kRadixBits)) & (kRadix - 1))], 1u);
@@ -141,6 +145,26 @@ __global__ void __launch_bounds__(512) histogramKernel(const K* __restrict__ key
             for (int p = PH; p < P; ++p)
                 atomicAdd(&sHist[p * kRadix + (unsigned(key >> (p * kRadixBits)) & (kRadix - 1))], 1u);
         }
+    };
+    // kHistUnroll independent coalesced loads per thread are in flight before the first shared-memory atomic
+    constexpr int kHistUnroll = 4;
+    const size_t chunk        = size_t(blockDim.x) * kHistUnroll;
+    const size_t stride       = size_t(gridDim.x) * chunk;
+    size_t base               = size_t(blockIdx.x) * chunk;
+    for (; base + chunk <= n; base += stride)
+    {
+        K key[kHistUnroll];
+#pragma unroll
+        for (int k = 0; k < kHistUnroll; ++k)
+            key[k] = keys[base + size_t(k) * blockDim.x + threadIdx.x];
+#pragma unroll
+        for (int k = 0; k < kHistUnroll; ++k)
+            addKey(key[k], true);
+    }
+    if (base < n) // the ragged last chunk (one block only)
+    {
+        for (size_t i = base + threadIdx.x; i < n; i += blockDim.x)
+            addKey(keys[i], __activemask() == 0xffffffffu);
     }
     __syncthreads();
     for (int i = threadIdx.x; i < P * kRadix; i += blockDim.x)
@@ -220,7 +244,7 @@ __device__ inline bool consumeWindow(const uint32_t (&st)[W], uint32_t& excl, in
 }
 
 template<class K, bool Iota>
-__global__ void __launch_bounds__(kSortThreads, 3) onesweepKernel(const K* __restrict__ keysIn,
+__global__ void __launch_bounds__(kSortThreads, RS_MINBLOCKS(K)) onesweepKernel(const K* __restrict__ keysIn,
                                                                    const uint32_t* __restrict__ valsIn,
                                                                    K* __restrict__ keysOut,
                                                                    uint32_t* __restrict__ valsOut,
