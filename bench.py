@@ -39,7 +39,7 @@ METRIC = "Domain::sync + findNeighbors"
 UNIT = "Mparticles/s"
 NG0 = 100
 # dram__bytes_read.sum + dram__bytes_write.sum of one findNeighborsKernel launch at 32 M uniform (ncu --set full)
-NEIGHBOR_TRAFFIC_BYTES = 23_073_595_000  # dram read (8.378 GB) + write (14.696 GB) of one launch, profiles/r01f_findNeighbors_full.txt
+NEIGHBOR_TRAFFIC_BYTES = 23_385_864_000  # dram read (8.688 GB) + write (14.698 GB) of one launch, profiles/r01g_findNeighbors_full.txt
 
 
 # ------------------------------------------------------------------------------------------------ inputs
@@ -276,10 +276,22 @@ def main():
         fl.zero_()
         call("halo_radii_f64", ops._p(state["a"][3]), C.c_void_p(ptrs[2]), n_leaves, 2.0, ops._p(state["radii"]), ops._stream())
         bx = dom.box()
+        # the 8 searches are independent (own flag arrays): one stream each, so that a 262 k-leaf launch (less than
+        # one wave of threads) does not leave the GPU idle; the main stream waits for all of them
+        if state.get("hstreams") is None:
+            state["hstreams"] = [torch.cuda.Stream() for _ in range(vranks)]
+        main = torch.cuda.current_stream()
+        ready = torch.cuda.Event()
+        ready.record(main)
         for r in range(vranks):
             first, last = r * n_leaves // vranks, (r + 1) * n_leaves // vranks
+            st = state["hstreams"][r]
+            st.wait_event(ready)
             call("find_halos_k64_f64", 1, C.c_void_p(ptrs[3]), C.c_void_p(ptrs[4]), C.c_void_p(ptrs[5]), C.c_void_p(ptrs[0]),
-                 ops._p(state["radii"]), C.byref(bx), first, last, ops._p(fl[r]), ops._stream())
+                 ops._p(state["radii"]), C.byref(bx), first, last, ops._p(fl[r]), C.c_void_p(st.cuda_stream))
+            done = torch.cuda.Event()
+            done.record(st)
+            main.wait_event(done)
 
     from cornerstone_octree_b200.domain import _fn, _check
     tree_ptrs = (C.c_void_p * 10)()

@@ -14,6 +14,8 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --
   python bench.py --steps 2 --warmup 3 --no-cpu --no-e2e > $out/${tag}_ncu_launch.log 2>&1; echo "ncu list exit $?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:findNeighborsKernel -s 3 -c 1 -f -o $out/${tag}_nb \
   python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e > $out/${tag}_ncu_full.log 2>&1; echo "ncu full exit $?"
-# every other library kernel of the last (steady-state) steps: skip the launches of the cold first sync
-timeout 900 ncu --set full --clock-control none -k regex:'^(?!.*findNeighbors)(csb::|void csb::)' -s 150 -c 70 -f -o $out/${tag}_kernels \
+# the large streaming kernels of one steady-state step (full set; the small tree kernels: see gpu_kernels_small below)
+if [ -n "$3" ]; then
+timeout 900 ncu --set full --clock-control none -k 'regex:onesweep|sfcKeys|gather8x4|gatherMulti|minMaxPartial|histogram|nodeCounts|haloRadii|geoCenters|findHalos' -s 90 -c 36 -f -o $out/${tag}_kernels \
   python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e > $out/${tag}_ncu_kernels.log 2>&1; echo "ncu kernels exit $?"
+fi
