@@ -158,6 +158,7 @@ _DOMAIN_PROTOS = {
     "destroy": (None, [_vp]),
     "set_comm": (_i, [_vp, _vp]),
     "set_fields_ready_event": (_i, [_vp, _vp]),
+    "set_sfc_kind": (_i, [_vp, _i]),
     "sync_begin": (_i64, [_vp, _u64, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "sync_finish": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "exchange_halos": (_i, [_vp, _i, _vp, _vp]),

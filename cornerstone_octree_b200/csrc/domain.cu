@@ -181,12 +181,12 @@ struct Api
     static constexpr bool k64 = sizeof(K) == 8, f64 = sizeof(T) == 8;
     using CBox = typename BoxT<T>::type;
 
-    static int keys(const T* x, const T* y, const T* z, K* keys, size_t n, const CBox* box, void* s)
+    static int keys(int kind, const T* x, const T* y, const T* z, K* keys, size_t n, const CBox* box, void* s)
     {
-        if constexpr (k64 && f64) return cstone_b200_compute_sfc_keys_k64_f64(CSTONE_SFC_HILBERT, x, y, z, keys, n, box, s);
-        else if constexpr (k64 && !f64) return cstone_b200_compute_sfc_keys_k64_f32(CSTONE_SFC_HILBERT, x, y, z, keys, n, box, s);
-        else if constexpr (!k64 && f64) return cstone_b200_compute_sfc_keys_k32_f64(CSTONE_SFC_HILBERT, x, y, z, keys, n, box, s);
-        else return cstone_b200_compute_sfc_keys_k32_f32(CSTONE_SFC_HILBERT, x, y, z, keys, n, box, s);
+        if constexpr (k64 && f64) return cstone_b200_compute_sfc_keys_k64_f64(kind, x, y, z, keys, n, box, s);
+        else if constexpr (k64 && !f64) return cstone_b200_compute_sfc_keys_k64_f32(kind, x, y, z, keys, n, box, s);
+        else if constexpr (!k64 && f64) return cstone_b200_compute_sfc_keys_k32_f64(kind, x, y, z, keys, n, box, s);
+        else return cstone_b200_compute_sfc_keys_k32_f32(kind, x, y, z, keys, n, box, s);
     }
     static uint64_t sortTemp(uint64_t n)
     {
@@ -220,12 +220,12 @@ struct Api
         if constexpr (k64) return cstone_b200_build_octree_k64(leaves, L, prefixes, co, parents, lr, itl, lti, temp, tb, s);
         else return cstone_b200_build_octree_k32(leaves, L, prefixes, co, parents, lr, itl, lti, temp, tb, s);
     }
-    static int geoCenters(const K* prefixes, int32_t M, T* centers, T* sizes, const CBox* box, void* s)
+    static int geoCenters(int kind, const K* prefixes, int32_t M, T* centers, T* sizes, const CBox* box, void* s)
     {
-        if constexpr (k64 && f64) return cstone_b200_compute_geo_centers_k64_f64(CSTONE_SFC_HILBERT, prefixes, M, centers, sizes, box, s);
-        else if constexpr (k64 && !f64) return cstone_b200_compute_geo_centers_k64_f32(CSTONE_SFC_HILBERT, prefixes, M, centers, sizes, box, s);
-        else if constexpr (!k64 && f64) return cstone_b200_compute_geo_centers_k32_f64(CSTONE_SFC_HILBERT, prefixes, M, centers, sizes, box, s);
-        else return cstone_b200_compute_geo_centers_k32_f32(CSTONE_SFC_HILBERT, prefixes, M, centers, sizes, box, s);
+        if constexpr (k64 && f64) return cstone_b200_compute_geo_centers_k64_f64(kind, prefixes, M, centers, sizes, box, s);
+        else if constexpr (k64 && !f64) return cstone_b200_compute_geo_centers_k64_f32(kind, prefixes, M, centers, sizes, box, s);
+        else if constexpr (!k64 && f64) return cstone_b200_compute_geo_centers_k32_f64(kind, prefixes, M, centers, sizes, box, s);
+        else return cstone_b200_compute_geo_centers_k32_f32(kind, prefixes, M, centers, sizes, box, s);
     }
     static int minmax(const T* x, const T* y, const T* z, size_t n, T* out6, void* temp, void* s)
     {
@@ -309,7 +309,8 @@ struct LeafArrayDev
 /*! halo boxes of the local leaves that reach outside the key range [lowest, highest) of this rank
  *  [ref: traversal/collisions.hpp:78-105: same box and the same containedIn early-out as findHalos] */
 template<class K, class T>
-__global__ void __launch_bounds__(128) surfaceBoxesKernel(const uint16_t* __restrict__ enc,
+__global__ void __launch_bounds__(128) surfaceBoxesKernel(int kind,
+                                                          const uint16_t* __restrict__ enc,
                                                           const uint16_t* __restrict__ dec,
                                                           const K* __restrict__ leaves,
                                                           const uint32_t* __restrict__ counts,
@@ -327,9 +328,9 @@ __global__ void __launch_bounds__(128) surfaceBoxesKernel(const uint16_t* __rest
         if (counts[leaf] == 0) continue;
         K start = leaves[leaf], end = leaves[leaf + 1];
         if (start < lowest || end > highest) continue; // not one of my leaves
-        IBox nodeBox = sfcIBox<K>(CSTONE_SFC_HILBERT, dec, start, treeLevel<K>(K(end - start)));
+        IBox nodeBox = sfcIBox<K>(kind, dec, start, treeLevel<K>(K(end - start)));
         IBox halo    = makeHaloBox<K, T>(nodeBox, radii[leaf], box);
-        if (containedIn<K>(CSTONE_SFC_HILBERT, enc, lowest, highest, halo)) continue;
+        if (containedIn<K>(kind, enc, lowest, highest, halo)) continue;
         uint32_t slot = atomicAdd(numOut, 1u);
         if (slot < capacity)
         {
@@ -345,7 +346,8 @@ __global__ void __launch_bounds__(128) surfaceBoxesKernel(const uint16_t* __rest
 /*! reverse collision: which of MY non-empty leaves does a foreign halo box overlap?  One thread per foreign box,
  *  depth-first over my linked tree, nodes outside my key range are skipped.  flags[srcRank * numLeaves + leaf] = 1 */
 template<class K>
-__global__ void __launch_bounds__(128) reverseCollisionKernel(const uint16_t* __restrict__ dec,
+__global__ void __launch_bounds__(128) reverseCollisionKernel(int kind,
+                                                              const uint16_t* __restrict__ dec,
                                                               const K* __restrict__ prefixes,
                                                               const int* __restrict__ childOffsets,
                                                               const int* __restrict__ internalToLeaf,
@@ -379,7 +381,7 @@ __global__ void __launch_bounds__(128) reverseCollisionKernel(const uint16_t* __
             K nodeStart    = decodePlaceholderBit<K>(prefix);
             K nodeEnd      = nodeStart + nodeRange<K>(level);
             if (nodeEnd <= lowest || nodeStart >= highest) return false; // nothing of mine below this node
-            return overlapBoxes<K>(sfcIBox<K>(CSTONE_SFC_HILBERT, dec, nodeStart, level), halo);
+            return overlapBoxes<K>(sfcIBox<K>(kind, dec, nodeStart, level), halo);
         };
         auto hitLeaf = [&](int idx)
         {
@@ -472,6 +474,13 @@ public:
     //! one-shot: the stream waits for `e` before h and the properties are first read (their upload may still run)
     void setFieldsReadyEvent(void* e) { fieldsReady_ = reinterpret_cast<cudaEvent_t>(e); }
     void setComm(void* c) { comm_ = reinterpret_cast<ncclComm_t>(c); }
+    //! space-filling curve of the keys (the reference's Domain hard-wires Hilbert, sfc/sfc.hpp:54-55); before the first sync
+    int setSfcKind(int kind)
+    {
+        if (kind != CSTONE_SFC_MORTON && kind != CSTONE_SFC_HILBERT) return CSTONE_E_INVALID_ARGUMENT;
+        sfcKind_ = kind;
+        return 0;
+    }
     //! device time between the stage markers of the last sync (ms); kNumMarks - 1 values
     void stageMs(float* ms) const
     {
@@ -538,6 +547,7 @@ private:
     bool firstCall_   = true;
     ncclComm_t comm_  = nullptr;
     cudaEvent_t fieldsReady_ = nullptr;
+    int sfcKind_      = CSTONE_SFC_HILBERT;
     cudaStream_t s_   = nullptr; // legacy default stream: ordered with the caller's default-stream work
 
     // particle state
@@ -700,7 +710,7 @@ int Engine<K, T>::linkTree(LeafArrayDev<K, T>& tree, bool withCenters)
     {
         CSB_TRY(centers_.reserve(sizeof(T) * 3 * size_t(M)));
         CSB_TRY(sizes_.reserve(sizeof(T) * 3 * size_t(M)));
-        CSB_TRY((Api<K, T>::geoCenters(prefixes_.template as<K>(), M, centers_.template as<T>(), sizes_.template as<T>(), &box_, s_)));
+        CSB_TRY((Api<K, T>::geoCenters(sfcKind_, prefixes_.template as<K>(), M, centers_.template as<T>(), sizes_.template as<T>(), &box_, s_)));
     }
     return 0;
 }
@@ -755,7 +765,7 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
     if (np)
     {
         CSB_CUDA(cudaMemsetAsync(keys, 0, sizeof(K) * np, s_));
-        CSB_TRY((Api<K, T>::keys(x + inStart, y + inStart, z + inStart, keys, np, &box_, s_)));
+        CSB_TRY((Api<K, T>::keys(sfcKind_, x + inStart, y + inStart, z + inStart, keys, np, &box_, s_)));
         mark(2);
         CSB_TRY((Api<K, T>::sort(keys, order_.template as<uint32_t>(), keyBuf_.template as<K>(), valBuf_.template as<uint32_t>(), np,
                                  sortTemp_.p, sortTemp_.bytes, 1, s_)));
@@ -898,9 +908,9 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
                 void* scanTmp = mb + oScan;
                 CSB_CUDA(cudaMemsetAsync(fk, 0, sizeof(K) * nF, s_));
                 const T *rx = recv_[0].template as<T>(), *ry = recv_[1].template as<T>(), *rz = recv_[2].template as<T>();
-                if (nLeft) CSB_TRY((Api<K, T>::keys(rx, ry, rz, fk, nLeft, &box_, s_)));
+                if (nLeft) CSB_TRY((Api<K, T>::keys(sfcKind_, rx, ry, rz, fk, nLeft, &box_, s_)));
                 if (nF > nLeft)
-                    CSB_TRY((Api<K, T>::keys(rx + nLeft + nOwn, ry + nLeft + nOwn, rz + nLeft + nOwn, fk + nLeft, nF - nLeft, &box_, s_)));
+                    CSB_TRY((Api<K, T>::keys(sfcKind_, rx + nLeft + nOwn, ry + nLeft + nOwn, rz + nLeft + nOwn, fk + nLeft, nF - nLeft, &box_, s_)));
                 foreignIndexKernel<<<gridFor(nF, 256), 256, 0, s_>>>(fv, nF, nLeft, nOwn);
                 CSB_LAUNCHED();
                 CSB_TRY((Api<K, T>::sort(fk, fv, fkb, fvb, nF, sortTemp_.p, sortTemp_.bytes, 0, s_)));
@@ -915,7 +925,7 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         else if (n)
         {
             CSB_CUDA(cudaMemsetAsync(skeys, 0, sizeof(K) * n, s_));
-            CSB_TRY((Api<K, T>::keys(recv_[0].template as<T>(), recv_[1].template as<T>(), recv_[2].template as<T>(), skeys, n, &box_, s_)));
+            CSB_TRY((Api<K, T>::keys(sfcKind_, recv_[0].template as<T>(), recv_[1].template as<T>(), recv_[2].template as<T>(), skeys, n, &box_, s_)));
             CSB_TRY((Api<K, T>::sort(skeys, order_.template as<uint32_t>(), keyBuf_.template as<K>(), valBuf_.template as<uint32_t>(), n,
                                      sortTemp_.p, sortTemp_.bytes, 1, s_)));
         }
@@ -983,7 +993,7 @@ int Engine<K, T>::discoverHalos()
     uint32_t* dCount = nSurf_.template as<uint32_t>();      // [0] my count, [1..P] all counts
     CSB_CUDA(cudaMemsetAsync(dCount, 0, 4, s_));
     surfaceBoxesKernel<K, T><<<gridFor(size_t(L), 128), 128, 0, s_>>>(
-        tabs.enc, tabs.dec, focus_.treeA.template as<K>(), focus_.counts.template as<uint32_t>(), radii_.template as<float>(), L, lowest,
+        sfcKind_,         tabs.enc, tabs.dec, focus_.treeA.template as<K>(), focus_.counts.template as<uint32_t>(), radii_.template as<float>(), L, lowest,
         highest, makeDBox<T>(&box_), surf_.template as<IBox6>(), uint32_t(L), dCount);
     CSB_LAUNCHED();
     CSB_NCCL(ncclAllGather(dCount, dCount + 1, 1, ncclUint32, comm_, s_));
@@ -1006,7 +1016,7 @@ int Engine<K, T>::discoverHalos()
     CSB_CUDA(cudaMemsetAsync(flags_.p, 0, size_t(P) * L, s_));
     {
         dim3 grid(gridFor(size_t(maxS), 128, 4), P);
-        reverseCollisionKernel<K><<<grid, 128, 0, s_>>>(tabs.dec, prefixes_.template as<K>(), childOffsets_.template as<int32_t>(),
+        reverseCollisionKernel<K><<<grid, 128, 0, s_>>>(sfcKind_, tabs.dec, prefixes_.template as<K>(), childOffsets_.template as<int32_t>(),
                                                        internalToLeaf_.template as<int32_t>(), focus_.counts.template as<uint32_t>(), L,
                                                        lowest, highest, allSurf_.template as<IBox6>(), dCount + 1, maxS, P, rank_,
                                                        flags_.template as<unsigned char>());
@@ -1101,9 +1111,9 @@ int Engine<K, T>::discoverHalos()
     CSB_CUDA(cudaMemsetAsync(fk, 0, sizeof(K) * nTotal_, s_));
     CSB_CUDA(cudaMemcpyAsync(fk + start_, skeys, sizeof(K) * n, cudaMemcpyDeviceToDevice, s_));
     const T *fx = fin_[0].template as<T>(), *fy = fin_[1].template as<T>(), *fz = fin_[2].template as<T>();
-    if (start_) CSB_TRY((Api<K, T>::keys(fx, fy, fz, fk, size_t(start_), &box_, s_)));
+    if (start_) CSB_TRY((Api<K, T>::keys(sfcKind_, fx, fy, fz, fk, size_t(start_), &box_, s_)));
     if (nTotal_ > end_)
-        CSB_TRY((Api<K, T>::keys(fx + end_, fy + end_, fz + end_, fk + end_, size_t(nTotal_ - end_), &box_, s_)));
+        CSB_TRY((Api<K, T>::keys(sfcKind_, fx + end_, fy + end_, fz + end_, fk + end_, size_t(nTotal_ - end_), &box_, s_)));
     return 0;
 }
 
@@ -1220,7 +1230,12 @@ int cstone_b200_nccl_comm_destroy(void* comm)
     return ncclCommDestroy(reinterpret_cast<ncclComm_t>(comm)) == ncclSuccess ? 0 : CSTONE_E_NCCL;
 }
 
-#define CSB_DOMAIN_DEF(KS, K, TS, T)                                                                                       cstone_b200_domain* cstone_b200_domain_create_##KS##_##TS(int rank, int nranks, unsigned bucket,                                                                                 unsigned bucketFocus, float theta,                                                                                     const cstone_box_##TS* box)                                  {                                                                                                                          if (!box || nranks < 1 || rank < 0 || rank >= nranks || bucket < bucketFocus || bucketFocus == 0) return nullptr;         return reinterpret_cast<cstone_b200_domain*>(new csb::Engine<K, T>(rank, nranks, bucket, bucketFocus, theta, *box));     }                                                                                                                      void cstone_b200_domain_destroy_##KS##_##TS(cstone_b200_domain* d) { delete reinterpret_cast<csb::Engine<K, T>*>(d); }     int cstone_b200_domain_set_comm_##KS##_##TS(cstone_b200_domain* d, void* comm)                                         {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              reinterpret_cast<csb::Engine<K, T>*>(d)->setComm(comm);                                                                return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_set_fields_ready_event_##KS##_##TS(cstone_b200_domain* d, void* event)                                         {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              reinterpret_cast<csb::Engine<K, T>*>(d)->setFieldsReadyEvent(event);                                                                return 0;                                                                                                          }                                                                                                                      int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n, const T* x, const T* y,                                                             const T* z, const T* h, int nprops, const void* const* props,                                                          const int* pb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncBegin(n, x, y, z, h, nprops, props, pb);                       }                                                                                                                      int cstone_b200_domain_sync_finish_##KS##_##TS(cstone_b200_domain* d, K* keys, T* x, T* y, T* z, T* h,                                                                void* const* props)                                                     {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncFinish(keys, x, y, z, h, props);                               }                                                                                                                      int cstone_b200_domain_exchange_halos_##KS##_##TS(cstone_b200_domain* d, int na, void* const* arrays,                                                                    const int* eb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              int st = reinterpret_cast<csb::Engine<K, T>*>(d)->exchangeHalos(na, arrays, eb);                                       if (st) return st;                                                                                                     cudaError_t e = cudaStreamSynchronize(nullptr);                                                                        return int(e);                                                                                                     }                                                                                                                      int cstone_b200_domain_info_##KS##_##TS(const cstone_b200_domain* d, int64_t* info8)                                   {                                                                                                                          if (!d || !info8) return CSTONE_E_INVALID_ARGUMENT;                                                                    reinterpret_cast<const csb::Engine<K, T>*>(d)->info(info8);                                                            return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_stage_ms_##KS##_##TS(const cstone_b200_domain* d, float* ms10)                              \
+#define CSB_DOMAIN_DEF(KS, K, TS, T)                                                                                       cstone_b200_domain* cstone_b200_domain_create_##KS##_##TS(int rank, int nranks, unsigned bucket,                                                                                 unsigned bucketFocus, float theta,                                                                                     const cstone_box_##TS* box)                                  {                                                                                                                          if (!box || nranks < 1 || rank < 0 || rank >= nranks || bucket < bucketFocus || bucketFocus == 0) return nullptr;         return reinterpret_cast<cstone_b200_domain*>(new csb::Engine<K, T>(rank, nranks, bucket, bucketFocus, theta, *box));     }                                                                                                                      void cstone_b200_domain_destroy_##KS##_##TS(cstone_b200_domain* d) { delete reinterpret_cast<csb::Engine<K, T>*>(d); }     int cstone_b200_domain_set_comm_##KS##_##TS(cstone_b200_domain* d, void* comm)                                         {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              reinterpret_cast<csb::Engine<K, T>*>(d)->setComm(comm);                                                                return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_set_sfc_kind_##KS##_##TS(cstone_b200_domain* d, int kind)                                   \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return reinterpret_cast<csb::Engine<K, T>*>(d)->setSfcKind(kind);                                              \
+    }                                                                                                                  \
+    int cstone_b200_domain_set_fields_ready_event_##KS##_##TS(cstone_b200_domain* d, void* event)                                         {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              reinterpret_cast<csb::Engine<K, T>*>(d)->setFieldsReadyEvent(event);                                                                return 0;                                                                                                          }                                                                                                                      int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n, const T* x, const T* y,                                                             const T* z, const T* h, int nprops, const void* const* props,                                                          const int* pb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncBegin(n, x, y, z, h, nprops, props, pb);                       }                                                                                                                      int cstone_b200_domain_sync_finish_##KS##_##TS(cstone_b200_domain* d, K* keys, T* x, T* y, T* z, T* h,                                                                void* const* props)                                                     {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncFinish(keys, x, y, z, h, props);                               }                                                                                                                      int cstone_b200_domain_exchange_halos_##KS##_##TS(cstone_b200_domain* d, int na, void* const* arrays,                                                                    const int* eb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              int st = reinterpret_cast<csb::Engine<K, T>*>(d)->exchangeHalos(na, arrays, eb);                                       if (st) return st;                                                                                                     cudaError_t e = cudaStreamSynchronize(nullptr);                                                                        return int(e);                                                                                                     }                                                                                                                      int cstone_b200_domain_info_##KS##_##TS(const cstone_b200_domain* d, int64_t* info8)                                   {                                                                                                                          if (!d || !info8) return CSTONE_E_INVALID_ARGUMENT;                                                                    reinterpret_cast<const csb::Engine<K, T>*>(d)->info(info8);                                                            return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_stage_ms_##KS##_##TS(const cstone_b200_domain* d, float* ms10)                              \
     {                                                                                                                  \
         if (!d || !ms10) return CSTONE_E_INVALID_ARGUMENT;                                                             \
         reinterpret_cast<const csb::Engine<K, T>*>(d)->stageMs(ms10);                                                  \

@@ -26,7 +26,7 @@ class Domain:
     """Domain(rank, num_ranks, bucket_size, bucket_size_focus, theta, box)  — same arguments as the reference"""
 
     def __init__(self, rank, num_ranks, bucket_size, bucket_size_focus, theta=0.5, box=None, key_bits=64,
-                 dtype=torch.float64):
+                 dtype=torch.float64, sfc_kind=ops.HILBERT):
         if bucket_size < bucket_size_focus:
             # [ref: domain/domain.hpp:108-112]
             raise RuntimeError("The bucket size of the global tree must not be smaller than the bucket size of the "
@@ -38,6 +38,9 @@ class Domain:
         if not self._h:
             raise RuntimeError("cstone_b200_domain_create failed")
         self._comm = None
+        self.sfc_kind = sfc_kind
+        if sfc_kind != ops.HILBERT:  # the reference's Domain hard-wires Hilbert; Morton is an extension
+            _check(_fn("set_sfc_kind", key_bits, dtype)(self._h, int(sfc_kind)), "set_sfc_kind")
 
     def close(self):
         if getattr(self, "_h", None):

@@ -63,6 +63,7 @@ struct DomainApi;
         static constexpr auto create        = cstone_b200_domain_create_##KS##_##TS;                                   \
         static constexpr auto destroy       = cstone_b200_domain_destroy_##KS##_##TS;                                  \
         static constexpr auto setComm       = cstone_b200_domain_set_comm_##KS##_##TS;                                 \
+        static constexpr auto setSfcKind    = cstone_b200_domain_set_sfc_kind_##KS##_##TS;                             \
         static constexpr auto syncBegin     = cstone_b200_domain_sync_begin_##KS##_##TS;                               \
         static constexpr auto syncFinish    = cstone_b200_domain_sync_finish_##KS##_##TS;                              \
         static constexpr auto exchangeHalos = cstone_b200_domain_exchange_halos_##KS##_##TS;                           \
@@ -121,6 +122,8 @@ public:
 
     //! hand over an existing ncclComm_t (not owned)
     void setNcclComm(void* ncclComm) { detail::check(Api::setComm(d_, ncclComm), "Domain::setNcclComm"); }
+    //! extension: CSTONE_SFC_MORTON instead of the Hilbert curve the reference's Domain hard-wires; before sync
+    void setSfcKind(int sfcKind) { detail::check(Api::setSfcKind(d_, sfcKind), "Domain::setSfcKind"); }
     //! 128-byte id for ncclCommInitRank, to be created on rank 0 and broadcast by the application
     static std::array<char, 128> ncclUniqueId()
     {

@@ -46,6 +46,9 @@ int cstone_b200_nccl_comm_destroy(void* comm);
     void cstone_b200_domain_destroy_##KS##_##TS(cstone_b200_domain* d);                                                \
     int cstone_b200_domain_set_comm_##KS##_##TS(cstone_b200_domain* d, void* nccl_comm);                               \
     int cstone_b200_domain_set_fields_ready_event_##KS##_##TS(cstone_b200_domain* d, void* cuda_event);                \
+    /* CSTONE_SFC_HILBERT (default, what the reference's Domain hard-wires: sfc/sfc.hpp:54-55) or CSTONE_SFC_MORTON;  \
+     * call before the first sync */                                                                                   \
+    int cstone_b200_domain_set_sfc_kind_##KS##_##TS(cstone_b200_domain* d, int sfc_kind);                              \
     /* [ref: domain/domain.hpp:196-243 sync]; props: HOST array of nprops device pointers, element sizes 4 or 8 */    \
     int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n_in, const T* x, const T* y,    \
                                                       const T* z, const T* h, int nprops, const void* const* props,    \

@@ -12,8 +12,10 @@ from test_oracle_vs_ref import make_case
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("kd,fd", [(np.uint64, np.float64), (np.uint32, np.float32), (np.uint64, np.float32)])
-def test_single_rank_sync_matches_oracle(kd, fd, port):
+@pytest.mark.parametrize("kd,fd,kind", [(np.uint64, np.float64, 1), (np.uint32, np.float32, 1), (np.uint64, np.float32, 1),
+                                        (np.uint64, np.float64, 0), (np.uint32, np.float64, 0)])
+def test_single_rank_sync_matches_oracle(kd, fd, kind, port):
+    """kind 1 = Hilbert (what the reference's Domain uses), 0 = Morton (Domain-level curve selection)"""
     import torch
     from cornerstone_octree_b200 import ops
     from cornerstone_octree_b200.domain import Domain
@@ -23,7 +25,7 @@ def test_single_rank_sync_matches_oracle(kd, fd, port):
     td = torch.float64 if fd == np.float64 else torch.float32
     ids = np.arange(n, dtype=np.int64)
     mass = (np.arange(n) % 7).astype(np.float32)
-    dom = Domain(0, 1, 64, 16, 0.5, ops.make_box((-1.0, 1.0), dtype=td), key_bits=bits, dtype=td)
+    dom = Domain(0, 1, 64, 16, 0.5, ops.make_box((-1.0, 1.0), dtype=td), key_bits=bits, dtype=td, sfc_kind=kind)
     dx, dy, dz, dh = (torch.from_numpy(a).cuda() for a in (x, y, z, h))
     keys, sx, sy, sz, sh, (sid, sm) = dom.sync(dx, dy, dz, dh, [torch.from_numpy(ids).cuda(), torch.from_numpy(mass).cuda()])
     assert dom.start_index == 0 and dom.end_index == n and dom.n_particles_with_halos == n
@@ -33,7 +35,7 @@ def test_single_rank_sync_matches_oracle(kd, fd, port):
     lim = [x.min(), x.max(), y.min(), y.max(), z.min(), z.max()]
     assert [b.limits[i] for i in range(6)] == [fd(v) for v in lim]
     obox = loader.make_box(lim, (0, 0, 0), fd)
-    okeys = port.compute_sfc_keys(1, x, y, z, obox, kd)
+    okeys = port.compute_sfc_keys(kind, x, y, z, obox, kd)
     oskeys, order = port.sort_by_key(okeys)
     assert np.array_equal(keys.cpu().numpy().view(kd), oskeys)
     assert np.array_equal(sid.cpu().numpy(), ids[order])
@@ -51,7 +53,7 @@ def test_single_rank_sync_matches_oracle(kd, fd, port):
 
     # neighbours through the Domain's tree
     nb, nc = dom.find_neighbors(sx, sy, sz, sh, 100)
-    centers, sizes = port.geo_centers(1, oc["prefixes"], obox, fd)
+    centers, sizes = port.geo_centers(kind, oc["prefixes"], obox, fd)
     layout = np.zeros(tree.size, dtype=np.uint32)
     np.cumsum(counts, out=layout[1:])
     onb, onc = port.find_neighbors(x[order], y[order], z[order], h[order], 0, n, obox, oc, layout, centers, sizes, 100)
@@ -68,7 +70,7 @@ def test_single_rank_sync_matches_oracle(kd, fd, port):
     assert np.array_equal(np.sort(sid2.cpu().numpy()), ids)
     b2 = dom.box()
     obox2 = loader.make_box([b2.limits[i] for i in range(6)], (0, 0, 0), fd)
-    assert np.array_equal(port.compute_sfc_keys(1, sx2.cpu().numpy(), sy2.cpu().numpy(), sz2.cpu().numpy(), obox2, kd), k2)
+    assert np.array_equal(port.compute_sfc_keys(kind, sx2.cpu().numpy(), sy2.cpu().numpy(), sz2.cpu().numpy(), obox2, kd), k2)
     t2 = dom.tree_arrays()
     leaves2 = t2["leaves"].cpu().numpy().view(kd)
     c2 = port.compute_node_counts(leaves2, k2)
