@@ -173,3 +173,14 @@ def test_neighbors_tiny_and_huge_h(gpu, port):
     a = pipeline.run(port, 1, x, y, z, h, box, np.uint64, 16, 200)
     b = pipeline.run(gpu, 1, x, y, z, h, box, np.uint64, 16, 200)
     assert pipeline.compare(a, b, 200) == []
+
+
+@pytest.mark.parametrize("bucket", [1, 2, 4])
+@pytest.mark.parametrize("genname,bnd", [("gaussian", (0, 0, 0)), ("uniform", (1, 1, 1))])
+def test_neighbors_merged_leaf_runs(bucket, genname, bnd, gpu, port):
+    """tiny buckets: up to 8 sibling leaves (some empty) share one 32-candidate chunk of the neighbour search; every
+    lane must keep exactly the candidates of the leaves its own walk reaches [neighbors.cu advanceChunk]"""
+    x, y, z, h, box = make_case(genname, 6000, np.float64, bnd)
+    a = pipeline.run(port, 1, x, y, z, h, box, np.uint64, bucket, 150)
+    b = pipeline.run(gpu, 1, x, y, z, h, box, np.uint64, bucket, 150)
+    assert pipeline.compare(a, b, 150) == []
