@@ -138,6 +138,12 @@ __device__ inline uint64_t add2(uint64_t a, uint64_t b)
     asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
     return r;
 }
+__device__ inline uint64_t mul2(uint64_t a, uint64_t b)
+{
+    uint64_t r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
 __device__ inline uint64_t fma2(uint64_t a, uint64_t b, uint64_t c)
 {
     uint64_t r;
@@ -458,7 +464,7 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                     }
                     if (exact) hm = exactChunkSlow<T, AnyPbc>(p, base, cnt, i);
                 }
-                else
+                else if (AnyPbc && tg.usePbc)
                 {
 #pragma unroll 4
                     for (uint32_t k = 0; k < cnt; ++k)
@@ -467,6 +473,37 @@ __global__ void __launch_bounds__(kNbThreads, NB_MINBLOCKS) findNeighborsKernel(
                         const float cz  = reinterpret_cast<const float*>(sm.candB)[k];
                         if (exactPair<T, AnyPbc>(p, T(cA[0]), T(cA[2]), T(cz), tg)) hm |= 1u << k;
                     }
+                }
+                else
+                {
+                    /* float coordinates: the reference's own expression ((dx*dx + dy*dy) + dz*dz < r2, round to nearest,
+                     * no contraction) on two candidates per instruction; the sign bit of d2 - r2 is the hit bit (the
+                     * difference of two floats is negative exactly when the first is smaller; NaNs come out of the
+                     * arithmetic with a clear sign bit = no hit, like the comparison) */
+                    const uint64_t ntx = pack2(-float(tg.x), -float(tg.x)), nty = pack2(-float(tg.y), -float(tg.y));
+                    const uint64_t ntz = pack2(-float(tg.z), -float(tg.z));
+                    const uint64_t nr  = pack2(-float(tg.radiusSq), -float(tg.radiusSq));
+#pragma unroll
+                    for (int blk = 0; blk < 4; ++blk)
+                    {
+                        if (uint32_t(8 * blk) >= cnt) break; // warp-uniform
+#pragma unroll
+                        for (int q = 0; q < 4; ++q)
+                        {
+                            const int kk      = 4 * blk + q;
+                            const float4 ca   = sm.candA[kk];
+                            const float2 cb   = sm.candB[kk];
+                            const uint64_t dx = add2(pack2(ca.x, ca.y), ntx);
+                            const uint64_t dy = add2(pack2(ca.z, ca.w), nty);
+                            const uint64_t dz = add2(pack2(cb.x, cb.y), ntz);
+                            float s0, s1;
+                            unpack2(add2(add2(add2(mul2(dx, dx), mul2(dy, dy)), mul2(dz, dz)), nr), s0, s1);
+                            hm = __funnelshift_l(__float_as_uint(s0), hm, 1);
+                            hm = __funnelshift_l(__float_as_uint(s1), hm, 1);
+                        }
+                    }
+                    hm = __brev(hm) >> (32u - min(32u, (cnt + 7u) & ~7u));
+                    if (cnt < 32u) hm &= (1u << cnt) - 1u; // padding slots hold a far-away dummy, not a non-candidate
                 }
                 hm &= vmask & ~((self < 32u ? 1u : 0u) << (self & 31u));
             }
