@@ -157,7 +157,10 @@ class ClockSampler:
                 ts = None
             rows.append((ts,) + row)
         inside = [r for r in rows if t0 is not None and r[0] is not None and t0 <= r[0] <= t1]
-        out["window"] = "timed region" if inside else "steady warm-up + timed region"
+        out["window"] = "timed region" if inside else "warm-up + timed region"
+        if not inside and t0 is not None:  # prefer the samples closest to the timed region (steady warm-up steps)
+            late = [r for r in rows if r[0] is not None and r[0] >= t0 - 1.0]
+            rows = late or rows
         sm, mx, reasons = [], [], set()
         for _, a, b, rs in (inside or rows):
             sm.append(a)
@@ -325,11 +328,11 @@ def main():
         return nw
 
     # ---- warm-up: the first sync distributes the unsorted cloud and converges the trees (cold), the rest are steady
+    sampler = ClockSampler(local_rank)  # before the cold step: 8 concurrent nvidia-smi need seconds to come up
     t0 = time.perf_counter()
     run_step()
     barrier()
     first_sync_s = time.perf_counter() - t0
-    sampler = ClockSampler(local_rank)
     for _ in range(max(args.warmup, 3) - 1):
         run_step()
     barrier()
