@@ -82,6 +82,18 @@ _PROTOS.update({
     "lower_bound_f32": (_i, [_vp, _sz, _f, _vp, _vp, _vp]),
     "gather_ranges": (_i, [_vp, _vp, _i, _i32, _vp, _vp, _sz, _i, _vp]),
 })
+for ks, kt in (("k32", _u32), ("k64", _u64)):
+    _PROTOS["rebalance_decision_essential_" + ks] = (_i, [_vp, _vp, _vp, _vp, _vp, kt, kt, _u32, _vp, _i32, _vp])
+    _PROTOS["mac_refine_decision_" + ks] = (_i, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp])
+    _PROTOS["protect_ancestors_" + ks] = (_i, [_vp, _vp, _vp, _i32, _vp, _vp, _vp])
+    _PROTOS["enforce_keys_" + ks] = (_i, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp])
+    _PROTOS["range_count_" + ks] = (_i, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp])
+    for ts in ("f32", "f64"):
+        _PROTOS["geo_mac_spheres_%s_%s" % (ks, ts)] = (_i, [_i, _vp, _i32, _vp, _f, _vp, _vp])
+        _PROTOS["set_mac_%s_%s" % (ks, ts)] = (_i, [_i, _vp, _i32, _vp, _f, _vp, _vp])
+        _PROTOS["mark_macs_%s_%s" % (ks, ts)] = (_i, [_i, _vp, _vp, _vp, _vp, _vp, _i32, _i, _vp, _vp])
+for ts in ("f32", "f64"):
+    _PROTOS["move_centers_" + ts] = (_i, [_vp, _i32, _vp, _vp])
 for ts in ("f32", "f64"):
     _PROTOS["max_norm_square_" + ts] = (_i, [_vp, _vp, _vp, _sz, _vp, _vp, _vp])
 for tt in ("f32_f32", "f64_f32", "f64_f64"):

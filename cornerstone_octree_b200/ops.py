@@ -597,3 +597,89 @@ def gather_ranges(range_scan, range_offsets, src, buffer_size):
     call("gather_ranges", _p(range_scan), _p(range_offsets), range_scan.element_size(), range_scan.numel(), _p(src),
          _p(out), buffer_size, row_bytes, _stream())
     return out
+
+
+# --------------------------------------------------------------------------------------------- focus-tree kernels
+# [ref: focus/rebalance_gpu.h:39-85, traversal/collisions_gpu.h markMacsGpu, focus/source_center_gpu.h:72-89]
+def _key_arg(t, v):
+    return int(v) & ((1 << key_bits(t)) - 1)
+
+
+def rebalance_decision_essential(octree, counts, macs, focus_start, focus_end, bucket_size):
+    """rebalanceDecisionEssentialGpu: op per NODE (0 merge / 1 keep / 8 split); macs is an int8 tensor"""
+    p = octree.prefixes
+    _require_cuda(p, counts, macs)
+    n = octree.num_nodes
+    node_ops = torch.empty(n, dtype=torch.int32, device=p.device)
+    call("rebalance_decision_essential_" + _ks(p), _p(p), _p(octree.child_offsets), _p(octree.parents), _p(counts),
+         _p(macs), _key_arg(p, focus_start), _key_arg(p, focus_end), bucket_size, _p(node_ops), n, _stream())
+    return node_ops
+
+
+def mac_refine_decision(octree, macs, focus_first, focus_last):
+    p = octree.prefixes
+    L = octree.num_leaf_nodes
+    node_ops = torch.empty(L, dtype=torch.int32, device=p.device)
+    l2i = octree.leaf_to_internal[octree.num_internal_nodes:]  # the OctreeView span [ref: tree/octree.hpp:355]
+    call("mac_refine_decision_" + _ks(p), _p(p), _p(macs), _p(l2i), L, focus_first, focus_last,
+         _p(node_ops), _stream())
+    return node_ops
+
+
+def protect_ancestors(octree, node_ops, ws=None):
+    """protectAncestorsGpu, in place on node_ops -> converged"""
+    p = octree.prefixes
+    temp = (ws or _ws(p.device)).get(64)
+    conv = C.c_int32(0)
+    call("protect_ancestors_" + _ks(p), _p(p), _p(octree.parents), _p(node_ops), octree.num_nodes, C.byref(conv),
+         _p(temp), _stream())
+    return bool(conv.value)
+
+
+def enforce_keys(forced_keys, octree, node_ops, ws=None):
+    """enforceKeysGpu, in place on node_ops -> ResolutionStatus (0 converged, 1 cancelMerge, 2 rebalance, 3 failed)"""
+    p = octree.prefixes
+    temp = (ws or _ws(p.device)).get(64)
+    st = C.c_int32(0)
+    call("enforce_keys_" + _ks(p), _p(forced_keys), forced_keys.numel(), _p(p), _p(octree.child_offsets),
+         _p(octree.parents), _p(node_ops), C.byref(st), _p(temp), _stream())
+    return int(st.value)
+
+
+def range_count(leaves, counts, leaves_focus, leaves_focus_idx, counts_focus=None):
+    """rangeCountGpu"""
+    _require_cuda(leaves, counts, leaves_focus, leaves_focus_idx)
+    if counts_focus is None:
+        counts_focus = torch.zeros(leaves_focus.numel() - 1, dtype=torch.int32, device=leaves.device)
+    call("range_count_" + _ks(leaves), _p(leaves), leaves.numel(), _p(counts), _p(leaves_focus), _p(leaves_focus_idx),
+         leaves_focus_idx.numel(), _p(counts_focus), _stream())
+    return counts_focus
+
+
+def geo_mac_spheres(prefixes, inv_theta, box, dtype=torch.float64, kind=HILBERT):
+    c4 = torch.empty((prefixes.numel(), 4), dtype=dtype, device=prefixes.device)
+    call("geo_mac_spheres_%s_%s" % (_ks(prefixes), _ts(c4)), kind, _p(prefixes), prefixes.numel(), _p(c4), inv_theta,
+         C.byref(box), _stream())
+    return c4
+
+
+def set_mac(prefixes, mac_spheres, inv_theta, box, kind=HILBERT):
+    call("set_mac_%s_%s" % (_ks(prefixes), _ts(mac_spheres)), kind, _p(prefixes), prefixes.numel(), _p(mac_spheres),
+         inv_theta, C.byref(box), _stream())
+    return mac_spheres
+
+
+def mark_macs(octree, centers4, box, focus_nodes, limit_source, markings=None, kind=HILBERT):
+    """markMacsGpu: focus_nodes = cornerstone keys of the focus leaves (n + 1 entries); markings int8[num_nodes]"""
+    p = octree.prefixes
+    if markings is None:
+        markings = torch.zeros(octree.num_nodes, dtype=torch.int8, device=p.device)
+    call("mark_macs_%s_%s" % (_ks(p), _ts(centers4)), kind, _p(p), _p(octree.child_offsets), _p(centers4), C.byref(box),
+         _p(focus_nodes), focus_nodes.numel() - 1, int(limit_source), _p(markings), _stream())
+    return markings
+
+
+def move_centers(src3):
+    dst = torch.empty((src3.shape[0], 4), dtype=src3.dtype, device=src3.device)
+    call("move_centers_" + _ts(src3), _p(src3), src3.shape[0], _p(dst), _stream())
+    return dst

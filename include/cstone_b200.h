@@ -450,6 +450,60 @@ int cstone_b200_fill_sfc_gaps_k64(const uint64_t* tree, int32_t num_nodes, const
 int cstone_b200_gather_ranges(const void* range_scan, const void* range_offsets, int index_bytes, int32_t num_ranges,
                               const void* src, void* buffer, size_t buffer_size, int elem_bytes, void* stream);
 
+/* ------------------------------------------------------------------------
+ * a19 (device kernels of the focus-tree update)
+ * [ref: focus/rebalance_gpu.h:39-85, traversal/collisions_gpu.h:69-77 markMacsGpu,
+ *       focus/source_center_gpu.h:72-89 geoMacSpheresGpu / setMacGpu / moveCenters]
+ * Tree arrays as in OctreeView (prefixes[M], child_offsets[M], parents[(M-1)/8]); macs / markings are char[M];
+ * MAC spheres / source centres are Vec4<T>[M] = (x, y, z, mac^2).  temp >= 4 bytes of device scratch.
+ * ---------------------------------------------------------------------- */
+#define CSTONE_B200_FOCUS_DECL(KS, K)                                                                                  \
+    /* rebalanceDecisionEssentialGpu: node_ops[i] in {0 merge, 1 keep, 8 split} for every node */                     \
+    int cstone_b200_rebalance_decision_essential_##KS(const K* prefixes, const int32_t* child_offsets,                 \
+                                                      const int32_t* parents, const uint32_t* counts,                  \
+                                                      const char* macs, K focus_start, K focus_end,                    \
+                                                      uint32_t bucket_size, int32_t* node_ops, int32_t num_nodes,      \
+                                                      void* stream);                                                   \
+    /* macRefineDecisionGpu: per LEAF, 8 if outside [focus_first, focus_last) and the MAC failed, else 1;           \
+     * leaf_to_internal = the OctreeView span (build_octree's array + num_internal_nodes) */                          \
+    int cstone_b200_mac_refine_decision_##KS(const K* prefixes, const char* macs, const int32_t* leaf_to_internal,     \
+                                             int32_t num_leaf_nodes, int32_t focus_first, int32_t focus_last,          \
+                                             int32_t* node_ops, void* stream);                                         \
+    /* protectAncestorsGpu: *converged_host = 1 iff every resulting op is 1 */                                         \
+    int cstone_b200_protect_ancestors_##KS(const K* prefixes, const int32_t* parents, int32_t* node_ops,               \
+                                           int32_t num_nodes, int32_t* converged_host, void* temp, void* stream);      \
+    /* enforceKeysGpu: *status_host = ResolutionStatus (0 converged, 1 cancelMerge, 2 rebalance, 3 failed) */          \
+    int cstone_b200_enforce_keys_##KS(const K* forced_keys, int32_t num_forced_keys, const K* node_keys,               \
+                                      const int32_t* child_offsets, const int32_t* parents, int32_t* node_ops,         \
+                                      int32_t* status_host, void* temp, void* stream);                                 \
+    /* rangeCountGpu: counts_focus[idx] = saturated sum of the global counts inside focus leaf idx, for idx in         \
+     * leaves_focus_idx; num_leaf_keys = number of keys of the global leaf array (nodes + 1) */                         \
+    int cstone_b200_range_count_##KS(const K* leaves, int32_t num_leaf_keys, const uint32_t* counts,                   \
+                                     const K* leaves_focus, const int32_t* leaves_focus_idx, int32_t num_idx,          \
+                                     uint32_t* counts_focus, void* stream);
+CSTONE_B200_FOCUS_DECL(k32, uint32_t)
+CSTONE_B200_FOCUS_DECL(k64, uint64_t)
+
+#define CSTONE_B200_MAC_DECL(KS, K, TS, T)                                                                             \
+    /* geoMacSpheresGpu: centres4[i] = (geometric centre, (2 max(size) inv_theta)^2) */                                \
+    int cstone_b200_geo_mac_spheres_##KS##_##TS(int sfc_kind, const K* prefixes, int32_t num_nodes, T* centers4,       \
+                                                float inv_theta, const cstone_box_##TS* box, void* stream);            \
+    /* setMacGpu: mac_spheres4[i][3] = (2 max(size) inv_theta + |centre - geometric centre|)^2 unless it was 0 */      \
+    int cstone_b200_set_mac_##KS##_##TS(int sfc_kind, const K* prefixes, int32_t num_nodes, T* mac_spheres4,           \
+                                        float inv_theta, const cstone_box_##TS* box, void* stream);                    \
+    /* markMacsGpu: markings[i] = 1 for every node outside the focus that fails the MAC w.r.t. one of the              \
+     * focus leaves focus_nodes[0..num_focus_nodes] (cornerstone keys, num_focus_nodes + 1 entries) */                 \
+    int cstone_b200_mark_macs_##KS##_##TS(int sfc_kind, const K* prefixes, const int32_t* child_offsets,               \
+                                          const T* centers4, const cstone_box_##TS* box, const K* focus_nodes,         \
+                                          int32_t num_focus_nodes, int limit_source, char* markings, void* stream);
+CSTONE_B200_MAC_DECL(k32, uint32_t, f32, float)
+CSTONE_B200_MAC_DECL(k32, uint32_t, f64, double)
+CSTONE_B200_MAC_DECL(k64, uint64_t, f32, float)
+CSTONE_B200_MAC_DECL(k64, uint64_t, f64, double)
+/* moveCenters: dst4[i] = (src3[i], 1) */
+int cstone_b200_move_centers_f32(const float* src3, int32_t num_nodes, float* dst4, void* stream);
+int cstone_b200_move_centers_f64(const double* src3, int32_t num_nodes, double* dst4, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

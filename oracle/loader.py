@@ -223,6 +223,71 @@ class Oracle:
             f(kt(int(a)), kt(int(b)), _ptr(out))
         return out
 
+    # ---- focus-tree update functions (reference build only: oracle/ref_wrap.cpp, prefix cstone_ref_)
+    def rebalance_decision_essential(self, oc, counts, macs, focus_start, focus_end, bucket):
+        """[ref: focus/rebalance.hpp:140-166]"""
+        p = oc["prefixes"]
+        kt = C.c_uint32 if p.dtype == np.uint32 else C.c_uint64
+        ops = np.zeros(p.size, dtype=np.int32)
+        self._f("rebalance_decision_essential_" + _ks(p.dtype))(
+            _ptr(p), _ptr(oc["child_offsets"]), _ptr(oc["parents"]), _ptr(counts), _ptr(macs), kt(int(focus_start)),
+            kt(int(focus_end)), C.c_uint32(bucket), _ptr(ops), C.c_int32(p.size))
+        return ops
+
+    def mac_refine_decision(self, oc, macs, focus_first, focus_last):
+        p = oc["prefixes"]
+        L = oc["num_leaf_nodes"]
+        ops = np.zeros(L, dtype=np.int32)
+        self._f("mac_refine_decision_" + _ks(p.dtype))(_ptr(p), _ptr(macs), _ptr(np.ascontiguousarray(oc["leaf_to_internal"][oc["num_internal_nodes"]:])), C.c_int32(L),
+                                                       C.c_int32(focus_first), C.c_int32(focus_last), _ptr(ops))
+        return ops
+
+    def protect_ancestors(self, oc, ops):
+        """[ref: focus/rebalance.hpp:168-181] -> (nodeOps, converged)"""
+        p = oc["prefixes"]
+        ops = ops.copy()
+        conv = self._f("protect_ancestors_" + _ks(p.dtype), C.c_int)(_ptr(p), _ptr(oc["parents"]), _ptr(ops),
+                                                                     C.c_int32(p.size))
+        return ops, bool(conv)
+
+    def enforce_keys(self, keys, oc, ops):
+        """[ref: focus/rebalance.hpp:252-266] -> (nodeOps, ResolutionStatus as int)"""
+        p = oc["prefixes"]
+        ops = ops.copy()
+        st = self._f("enforce_keys_" + _ks(p.dtype), C.c_int)(_ptr(keys), C.c_int32(keys.size), _ptr(p),
+                                                              _ptr(oc["child_offsets"]), _ptr(oc["parents"]), _ptr(ops))
+        return ops, int(st)
+
+    def range_count(self, leaves, counts, leaves_focus, idx):
+        """[ref: focus/rebalance.hpp:277-299]"""
+        out = np.zeros(leaves_focus.size - 1, dtype=np.uint32)
+        self._f("range_count_" + _ks(leaves.dtype))(_ptr(leaves), C.c_int32(leaves.size), _ptr(counts), _ptr(leaves_focus),
+                                                    C.c_int32(leaves_focus.size), _ptr(idx), C.c_int32(idx.size), _ptr(out))
+        return out
+
+    def geo_mac_spheres(self, prefixes, inv_theta, box, fdtype=np.float64):
+        """[ref: traversal/macs.hpp:58-71 computeMinMacR2 per node]"""
+        c4 = np.zeros((prefixes.size, 4), dtype=fdtype)
+        self._f("geo_mac_spheres_%s_%s" % (_ks(prefixes.dtype), _ts(fdtype)))(
+            _ptr(prefixes), C.c_int32(prefixes.size), _ptr(c4), C.c_float(inv_theta), C.byref(box))
+        return c4
+
+    def set_mac(self, prefixes, spheres, inv_theta, box):
+        """[ref: focus/source_center_gpu.cu setMacKernel over traversal/macs.hpp:84-100 computeVecMacR2]"""
+        c4 = spheres.copy()
+        self._f("set_mac_%s_%s" % (_ks(prefixes.dtype), _ts(c4.dtype)))(
+            _ptr(prefixes), C.c_int32(prefixes.size), _ptr(c4), C.c_float(inv_theta), C.byref(box))
+        return c4
+
+    def mark_macs(self, oc, centers4, box, focus_nodes, limit_source):
+        """[ref: traversal/macs.hpp:236-269 markMacs]"""
+        p = oc["prefixes"]
+        marks = np.zeros(p.size, dtype=np.int8)
+        self._f("mark_macs_%s_%s" % (_ks(p.dtype), _ts(centers4.dtype)))(
+            _ptr(p), _ptr(oc["child_offsets"]), _ptr(centers4), C.byref(box), _ptr(focus_nodes),
+            C.c_int32(focus_nodes.size - 1), C.c_int(int(limit_source)), _ptr(marks))
+        return marks
+
     def upsweep_sum(self, level_range, child_offsets, counts):
         counts = counts.copy()
         self._f("upsweep_sum")(C.c_int32(level_range.size - 1), _ptr(level_range), _ptr(child_offsets), _ptr(counts))

@@ -371,3 +371,87 @@ void cstone_ref_limit_boundary_shifts_k64(int n, const uint64_t* ob, uint64_t* b
                                           int32_t L, uint32_t* rc)
 { limitShiftsW(n, ob, b, l, c, L, rc); }
 }
+
+// ------------------------------------------------------------------------------------------------
+// a19 device-kernel counterparts: the reference's CPU functions of the focus-tree update (reference build only)
+// ------------------------------------------------------------------------------------------------
+#include "cstone/focus/rebalance.hpp"
+#include "cstone/traversal/macs.hpp"
+
+template<class K>
+static void rebalanceEssentialW(const K* p, const int32_t* co, const int32_t* pa, const uint32_t* c, const char* macs,
+                                K fs, K fe, uint32_t bucket, int32_t* ops, int32_t n)
+{
+    rebalanceDecisionEssential<K>(gsl::span<const K>(p, size_t(n)), co, pa, c, macs, fs, fe, bucket, ops);
+}
+template<class K>
+static void macRefineW(const K* p, const char* macs, const int32_t* l2i, int32_t L, int32_t f0, int32_t f1, int32_t* ops)
+{
+    // the loop of macRefineDecisionGpu [focus/rebalance_gpu.cu:93-104] over the CPU macRefineOp
+    for (int32_t i = 0; i < L; ++i)
+        ops[i] = (i < f0 || i >= f1) ? macRefineOp(p[l2i[i]], macs[l2i[i]]) : 1;
+}
+template<class K, class T, class CB>
+static void geoMacSpheresW(const K* p, int32_t n, T* c4, float invTheta, const CB* box)
+{
+    for (int32_t i = 0; i < n; ++i)
+    {
+        Vec4<T> v = computeMinMacR2(p[i], invTheta, asBox<T>(box));
+        for (int d = 0; d < 4; ++d)
+            c4[4 * i + d] = v[d];
+    }
+}
+template<class K, class T, class CB>
+static void setMacW(const K* p, int32_t n, T* c4, float invTheta, const CB* box)
+{
+    // setMacKernel [focus/source_center_gpu.cu] over the CPU computeVecMacR2
+    for (int32_t i = 0; i < n; ++i)
+    {
+        Vec3<T> c{c4[4 * i], c4[4 * i + 1], c4[4 * i + 2]};
+        T mac         = computeVecMacR2(p[i], c, invTheta, asBox<T>(box));
+        c4[4 * i + 3] = (c4[4 * i + 3] != T(0)) ? mac : T(0);
+    }
+}
+template<class K, class T, class CB>
+static void markMacsW(const K* p, const int32_t* co, const T* c4, const CB* box, const K* focus, int32_t nf, int limit,
+                      char* markings)
+{
+    markMacs(p, co, reinterpret_cast<const Vec4<T>*>(c4), asBox<T>(box), focus, nf, bool(limit), markings);
+}
+
+extern "C" {
+#define REF_FOCUS(KS, K)                                                                                               \
+    void cstone_ref_rebalance_decision_essential_##KS(const K* p, const int32_t* co, const int32_t* pa,                \
+                                                      const uint32_t* c, const char* macs, K fs, K fe,                 \
+                                                      uint32_t bucket, int32_t* ops, int32_t n)                        \
+    { rebalanceEssentialW<K>(p, co, pa, c, macs, fs, fe, bucket, ops, n); }                                            \
+    void cstone_ref_mac_refine_decision_##KS(const K* p, const char* macs, const int32_t* l2i, int32_t L, int32_t f0,  \
+                                             int32_t f1, int32_t* ops)                                                 \
+    { macRefineW<K>(p, macs, l2i, L, f0, f1, ops); }                                                                   \
+    int cstone_ref_protect_ancestors_##KS(const K* p, const int32_t* pa, int32_t* ops, int32_t n)                      \
+    { return protectAncestors<K>(gsl::span<const K>(p, size_t(n)), pa, ops) ? 1 : 0; }                                 \
+    int cstone_ref_enforce_keys_##KS(const K* keys, int32_t nk, const K* p, const int32_t* co, const int32_t* pa,      \
+                                     int32_t* ops)                                                                     \
+    { return int(enforceKeys<K>(gsl::span<const K>(keys, size_t(nk)), p, co, pa, ops)); }                              \
+    void cstone_ref_range_count_##KS(const K* leaves, int32_t nKeys, const uint32_t* counts, const K* lf, int32_t nf,  \
+                                     const int32_t* idx, int32_t ni, uint32_t* cf)                                     \
+    {                                                                                                                  \
+        rangeCount<K>(gsl::span<const K>(leaves, size_t(nKeys)), gsl::span<const unsigned>(counts, size_t(nKeys - 1)), \
+                      gsl::span<const K>(lf, size_t(nf)), gsl::span<const TreeNodeIndex>(idx, size_t(ni)),             \
+                      gsl::span<unsigned>(cf, size_t(nf - 1)));                                                        \
+    }
+REF_FOCUS(k32, uint32_t)
+REF_FOCUS(k64, uint64_t)
+#define REF_MAC(KS, K, TS, T)                                                                                          \
+    void cstone_ref_geo_mac_spheres_##KS##_##TS(const K* p, int32_t n, T* c4, float it, const cstone_box_##TS* box)    \
+    { geoMacSpheresW<K, T>(p, n, c4, it, box); }                                                                       \
+    void cstone_ref_set_mac_##KS##_##TS(const K* p, int32_t n, T* c4, float it, const cstone_box_##TS* box)            \
+    { setMacW<K, T>(p, n, c4, it, box); }                                                                              \
+    void cstone_ref_mark_macs_##KS##_##TS(const K* p, const int32_t* co, const T* c4, const cstone_box_##TS* box,      \
+                                          const K* focus, int32_t nf, int limit, char* markings)                       \
+    { markMacsW<K, T>(p, co, c4, box, focus, nf, limit, markings); }
+REF_MAC(k32, uint32_t, f32, float)
+REF_MAC(k32, uint32_t, f64, double)
+REF_MAC(k64, uint64_t, f32, float)
+REF_MAC(k64, uint64_t, f64, double)
+}
