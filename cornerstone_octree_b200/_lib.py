@@ -94,6 +94,15 @@ for ks, kt in (("k32", _u32), ("k64", _u64)):
         _PROTOS["mark_macs_%s_%s" % (ks, ts)] = (_i, [_i, _vp, _vp, _vp, _vp, _vp, _i32, _i, _vp, _vp])
 for ts in ("f32", "f64"):
     _PROTOS["move_centers_" + ts] = (_i, [_vp, _i32, _vp, _vp])
+    _PROTOS["upsweep_centers_" + ts] = (_i, [_i32, _vp, _vp, _vp, _vp])
+for tt in ("f64_f64_f64", "f64_f32_f64", "f32_f32_f32"):
+    _PROTOS["compute_leaf_source_center_" + tt] = (_i, [_vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp])
+_PROTOS["compute_fixed_groups"] = (_i, [_u32, _u32, _u32, _vp, _vp])
+_PROTOS["group_splits_temp_bytes"] = (_u64, [_u32, _u32])
+for ks in ("k32", "k64"):
+    for tt in ("f64_f64", "f64_f32", "f32_f32"):
+        _PROTOS["compute_group_splits_%s_%s" % (ks, tt)] = (
+            _i, [_u32, _u32, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _u32, _f, _vp, _u64, _vp, _vp, _u64, _vp])
 for ts in ("f32", "f64"):
     _PROTOS["max_norm_square_" + ts] = (_i, [_vp, _vp, _vp, _sz, _vp, _vp, _vp])
 for tt in ("f32_f32", "f64_f32", "f64_f64"):

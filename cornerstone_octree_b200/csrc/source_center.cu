@@ -1,0 +1,151 @@
+/*
+ * source_center.cu — n3 (first part): expansion (mass) centres of the tree nodes.
+ *
+ * Replaces computeLeafSourceCenterGpu / upsweepCentersGpu [ref: focus/source_center_gpu.h:51-74,
+ * focus/source_center_gpu.cu:38-111]; semantics follow the CPU functions
+ *   addBody / normalizeMass / massCenter     [ref: focus/source_center.hpp:44-78]
+ *   CombineSourceCenter                      [ref: focus/source_center.hpp:81-96]
+ *   computeLeafMassCenter                    [ref: focus/source_center.hpp:110-126]
+ *
+ * Parity: the accumulation order IS the result (floating point sums), so a leaf is summed by one thread, particle
+ * after particle, and an internal node adds its eight children in index order; no contraction (-fmad=false), the
+ * normalisation multiplies by 1/sum like the reference.  Neighbouring threads own neighbouring particle runs, so the
+ * four coordinate streams are read once through L1 (algorithmic bytes: 3 sizeof(Tc) + sizeof(Tm) per particle +
+ * 4 sizeof(Tf) per leaf).
+ */
+#include "common.cuh"
+
+namespace csb
+{
+
+constexpr int kCenterThreads = 256;
+
+template<class T>
+__device__ __forceinline__ void addBody(T (&c)[4], T sx, T sy, T sz, T sm)
+{
+    T w = fabs(sm);
+    c[0] += w * sx;
+    c[1] += w * sy;
+    c[2] += w * sz;
+    c[3] += w;
+}
+
+template<class T>
+__device__ __forceinline__ void normalizeMass(T (&c)[4])
+{
+    T invM = (c[3] != T(0.0)) ? T(1.0) / c[3] : T(1.0);
+    c[0] *= invM;
+    c[1] *= invM;
+    c[2] *= invM;
+}
+
+template<class T>
+struct alignas(16) Quad
+{
+    T v[4];
+};
+
+template<class Tc, class Tm, class Tf>
+__global__ void __launch_bounds__(kCenterThreads)
+    leafSourceCenterKernel(const Tc* __restrict__ x, const Tc* __restrict__ y, const Tc* __restrict__ z,
+                           const Tm* __restrict__ m, const int* __restrict__ leafToInternal, int numLeaves,
+                           const uint32_t* __restrict__ layout, Quad<Tf>* __restrict__ centers)
+{
+    for (int leaf = blockIdx.x * blockDim.x + threadIdx.x; leaf < numLeaves; leaf += gridDim.x * blockDim.x)
+    {
+        uint32_t first = layout[leaf], last = layout[leaf + 1];
+        Tf c[4] = {0, 0, 0, 0};
+        for (uint32_t i = first; i < last; ++i)
+            addBody<Tf>(c, Tf(x[i]), Tf(y[i]), Tf(z[i]), Tf(m[i]));
+        normalizeMass(c);
+        Quad<Tf> q;
+        q.v[0] = c[0], q.v[1] = c[1], q.v[2] = c[2], q.v[3] = c[3];
+        centers[leafToInternal[leaf]] = q;
+    }
+}
+
+template<class T>
+__global__ void __launch_bounds__(kCenterThreads)
+    upsweepCentersKernel(int first, int last, const int* __restrict__ childOffsets, Quad<T>* centers)
+{
+    for (int cell = first + blockIdx.x * blockDim.x + threadIdx.x; cell < last; cell += gridDim.x * blockDim.x)
+    {
+        int child = childOffsets[cell];
+        if (!child) continue;
+        T c[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+        {
+            Quad<T> s = centers[child + k];
+            addBody<T>(c, s.v[0], s.v[1], s.v[2], s.v[3]);
+        }
+        normalizeMass(c);
+        Quad<T> q;
+        q.v[0] = c[0], q.v[1] = c[1], q.v[2] = c[2], q.v[3] = c[3];
+        centers[cell] = q;
+    }
+}
+
+template<class Tc, class Tm, class Tf>
+int leafSourceCenter(const Tc* x, const Tc* y, const Tc* z, const Tm* m, const int* l2i, int numLeaves,
+                     const uint32_t* layout, Tf* centers, void* stream)
+{
+    if (numLeaves <= 0) return 0;
+    if (!x || !y || !z || !m || !l2i || !layout || !centers) return CSTONE_E_INVALID_ARGUMENT;
+    leafSourceCenterKernel<Tc, Tm, Tf><<<gridFor(size_t(numLeaves), kCenterThreads, 8), kCenterThreads, 0,
+                                         asStream(stream)>>>(x, y, z, m, l2i, numLeaves, layout,
+                                                             reinterpret_cast<Quad<Tf>*>(centers));
+    CSB_LAUNCHED();
+    return 0;
+}
+
+template<class T>
+int upsweepCenters(int numLevels, const int* levelRangeHost, const int* childOffsets, T* centers, void* stream)
+{
+    if (numLevels <= 0) return 0;
+    if (!levelRangeHost || !childOffsets || !centers) return CSTONE_E_INVALID_ARGUMENT;
+    for (int level = numLevels - 1; level >= 0; --level)
+    {
+        int first = levelRangeHost[level], last = levelRangeHost[level + 1];
+        if (last <= first) continue;
+        upsweepCentersKernel<T><<<gridFor(size_t(last - first), kCenterThreads, 8), kCenterThreads, 0,
+                                  asStream(stream)>>>(first, last, childOffsets, reinterpret_cast<Quad<T>*>(centers));
+        CSB_LAUNCHED();
+    }
+    return 0;
+}
+
+} // namespace csb
+
+extern "C" {
+
+int cstone_b200_compute_leaf_source_center_f64_f64_f64(const double* x, const double* y, const double* z,
+                                                       const double* m, const int32_t* l2i, int32_t numLeaves,
+                                                       const uint32_t* layout, double* centers4, void* stream)
+{
+    return csb::leafSourceCenter<double, double, double>(x, y, z, m, l2i, numLeaves, layout, centers4, stream);
+}
+int cstone_b200_compute_leaf_source_center_f64_f32_f64(const double* x, const double* y, const double* z,
+                                                       const float* m, const int32_t* l2i, int32_t numLeaves,
+                                                       const uint32_t* layout, double* centers4, void* stream)
+{
+    return csb::leafSourceCenter<double, float, double>(x, y, z, m, l2i, numLeaves, layout, centers4, stream);
+}
+int cstone_b200_compute_leaf_source_center_f32_f32_f32(const float* x, const float* y, const float* z, const float* m,
+                                                       const int32_t* l2i, int32_t numLeaves, const uint32_t* layout,
+                                                       float* centers4, void* stream)
+{
+    return csb::leafSourceCenter<float, float, float>(x, y, z, m, l2i, numLeaves, layout, centers4, stream);
+}
+int cstone_b200_upsweep_centers_f32(int32_t numLevels, const int32_t* levelRangeHost, const int32_t* childOffsets,
+                                    float* centers4, void* stream)
+{
+    return csb::upsweepCenters<float>(numLevels, levelRangeHost, childOffsets, centers4, stream);
+}
+int cstone_b200_upsweep_centers_f64(int32_t numLevels, const int32_t* levelRangeHost, const int32_t* childOffsets,
+                                    double* centers4, void* stream)
+{
+    return csb::upsweepCenters<double>(numLevels, levelRangeHost, childOffsets, centers4, stream);
+}
+
+} // extern "C"

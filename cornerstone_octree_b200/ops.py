@@ -683,3 +683,48 @@ def move_centers(src3):
     dst = torch.empty((src3.shape[0], 4), dtype=src3.dtype, device=src3.device)
     call("move_centers_" + _ts(src3), _p(src3), src3.shape[0], _p(dst), _stream())
     return dst
+
+
+# --------------------------------------------------------------------------------------------- expansion centres
+def compute_leaf_source_center(x, y, z, m, octree, layout, centers4=None):
+    """computeLeafSourceCenterGpu [ref: focus/source_center_gpu.h:51-66]: centers4[leaf node] = (mass centre, mass)"""
+    _require_cuda(x, y, z, m, layout)
+    tf = x.dtype
+    if centers4 is None:
+        centers4 = torch.zeros((octree.num_nodes, 4), dtype=tf, device=x.device)
+    l2i = octree.leaf_to_internal[octree.num_internal_nodes:]
+    call("compute_leaf_source_center_%s_%s_%s" % (_ts(x), _ts(m), _ts(centers4)), _p(x), _p(y), _p(z), _p(m), _p(l2i),
+         octree.num_leaf_nodes, _p(layout), _p(centers4), _stream())
+    return centers4
+
+
+def upsweep_centers(level_range_host, child_offsets, centers4):
+    """upsweepCentersGpu [ref: focus/source_center_gpu.h:68-74], in place; level_range_host = numpy int32 (host)"""
+    lr = np.ascontiguousarray(level_range_host, dtype=np.int32)
+    call("upsweep_centers_" + _ts(centers4), lr.size - 1, lr.ctypes.data_as(C.c_void_p), _p(child_offsets),
+         _p(centers4), _stream())
+    return centers4
+
+
+# --------------------------------------------------------------------------------------------- target groups
+def compute_fixed_groups(first, last, group_size, device="cuda"):
+    """computeFixedGroups [ref: traversal/groups_gpu.h:60]: group starts, last entry = last"""
+    n = (last - first + group_size - 1) // group_size
+    groups = torch.empty(n + 1, dtype=torch.int32, device=device)
+    call("compute_fixed_groups", first, last, group_size, _p(groups), _stream())
+    return groups
+
+
+def compute_group_splits(first, last, x, y, z, h, leaves, layout, box, group_size, tol_factor, ws=None):
+    """computeGroupSplits [ref: traversal/groups_gpu.h:75-88] -> int32 tensor of num_groups + 1 group starts"""
+    _require_cuda(x, y, z, leaves, layout)
+    n = max(last - first, 0)
+    tb = int(call("group_splits_temp_bytes", n, group_size))
+    temp = (ws or _ws(x.device)).get(max(tb, 16))
+    hs = _ts(h) if h is not None else _ts(x)
+    groups = torch.empty(n + 1, dtype=torch.int32, device=x.device)
+    ng = C.c_uint32(0)
+    call("compute_group_splits_%s_%s_%s" % (_ks(leaves), _ts(x), hs), first, last, _p(x), _p(y), _p(z),
+         _p(h) if h is not None else None, _p(leaves), leaves.numel() - 1, _p(layout), C.byref(box), group_size,
+         tol_factor, _p(groups), groups.numel(), C.byref(ng), _p(temp), temp.numel(), _stream())
+    return groups[:ng.value + 1]

@@ -504,6 +504,57 @@ CSTONE_B200_MAC_DECL(k64, uint64_t, f64, double)
 int cstone_b200_move_centers_f32(const float* src3, int32_t num_nodes, float* dst4, void* stream);
 int cstone_b200_move_centers_f64(const double* src3, int32_t num_nodes, double* dst4, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Expansion (mass) centres [ref: focus/source_center_gpu.h:51-74 computeLeafSourceCenterGpu, upsweepCentersGpu;
+ * CPU: focus/source_center.hpp:44-126].  centers4 = num_nodes x (x, y, z, mass); suffixes = coordinate type, mass
+ * type, centre type — the reference's three instantiations.  leaf_to_internal = the OctreeView span (L entries);
+ * layout[i] = index of the first particle of leaf i (L + 1 entries).  Sums run in the reference's order (particle
+ * by particle inside a leaf, child 0..7 inside a node): results are bit-identical to the CPU functions.
+ * upsweep: level_range is a HOST pointer (num_levels + 1 entries), as in the reference. */
+int cstone_b200_compute_leaf_source_center_f64_f64_f64(const double* x, const double* y, const double* z,
+                                                       const double* m, const int32_t* leaf_to_internal,
+                                                       int32_t num_leaves, const uint32_t* layout, double* centers4,
+                                                       void* stream);
+int cstone_b200_compute_leaf_source_center_f64_f32_f64(const double* x, const double* y, const double* z,
+                                                       const float* m, const int32_t* leaf_to_internal,
+                                                       int32_t num_leaves, const uint32_t* layout, double* centers4,
+                                                       void* stream);
+int cstone_b200_compute_leaf_source_center_f32_f32_f32(const float* x, const float* y, const float* z, const float* m,
+                                                       const int32_t* leaf_to_internal, int32_t num_leaves,
+                                                       const uint32_t* layout, float* centers4, void* stream);
+int cstone_b200_upsweep_centers_f32(int32_t num_levels, const int32_t* level_range_host, const int32_t* child_offsets,
+                                    float* centers4, void* stream);
+int cstone_b200_upsweep_centers_f64(int32_t num_levels, const int32_t* level_range_host, const int32_t* child_offsets,
+                                    double* centers4, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Target groups [ref: traversal/groups_gpu.h:60-88 computeFixedGroups, computeGroupSplits; GroupView
+ * traversal/groups.hpp:19-27].  groups = group start indices, num_groups + 1 entries, groups[num_groups] = last
+ * (GroupView::groupStart = groups, groupEnd = groups + 1).
+ * fixed groups: num_groups = ceil((last-first)/group_size).
+ * group splits: group_size 32 or 64 (else CSTONE_E_INVALID_ARGUMENT, the reference throws); suffixes = coordinate
+ * type, smoothing-length type; h may be NULL (unused by the split criterion, as in the reference).  *num_groups_host
+ * receives the number of groups; CSTONE_E_CAPACITY (with *num_groups_host set) if capacity < num_groups + 1 —
+ * (last-first) + 1 entries always suffice.  temp >= cstone_b200_group_splits_temp_bytes(last-first, group_size).
+ * The reference has no CPU twin; behaviour is pinned on test/unit_cuda/traversal/groups.cu. */
+int cstone_b200_compute_fixed_groups(uint32_t first, uint32_t last, uint32_t group_size, uint32_t* groups,
+                                     void* stream);
+uint64_t cstone_b200_group_splits_temp_bytes(uint32_t num_particles, uint32_t group_size);
+#define CSTONE_B200_GROUPS_DECL(KS, K, TS, TC, TH)                                                                     \
+    int cstone_b200_compute_group_splits_##KS##_##TS(                                                                  \
+        uint32_t first, uint32_t last, const TC* x, const TC* y, const TC* z, const TH* h, const K* leaves,            \
+        int32_t num_leaves, const uint32_t* layout, const cstone_box_##TC##_t* box, uint32_t group_size,               \
+        float tol_factor, uint32_t* groups, uint64_t capacity, uint32_t* num_groups_host, void* temp,                  \
+        uint64_t temp_bytes, void* stream);
+typedef cstone_box_f64 cstone_box_double_t;
+typedef cstone_box_f32 cstone_box_float_t;
+CSTONE_B200_GROUPS_DECL(k32, uint32_t, f64_f64, double, double)
+CSTONE_B200_GROUPS_DECL(k32, uint32_t, f64_f32, double, float)
+CSTONE_B200_GROUPS_DECL(k32, uint32_t, f32_f32, float, float)
+CSTONE_B200_GROUPS_DECL(k64, uint64_t, f64_f64, double, double)
+CSTONE_B200_GROUPS_DECL(k64, uint64_t, f64_f32, double, float)
+CSTONE_B200_GROUPS_DECL(k64, uint64_t, f32_f32, float, float)
+
 #ifdef __cplusplus
 }
 #endif

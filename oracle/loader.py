@@ -288,6 +288,23 @@ class Oracle:
             C.c_int32(focus_nodes.size - 1), C.c_int(int(limit_source)), _ptr(marks))
         return marks
 
+    def compute_leaf_source_center(self, x, y, z, m, oc, layout, fdtype=None):
+        """[ref: focus/source_center.hpp:110-126 computeLeafMassCenter] (reference build only)"""
+        fdtype = np.dtype(fdtype or x.dtype)
+        c4 = np.zeros((oc["num_nodes"], 4), dtype=fdtype)
+        l2i = np.ascontiguousarray(oc["leaf_to_internal"][oc["num_internal_nodes"]:])
+        self._f("compute_leaf_source_center_%s_%s_%s" % (_ts(x.dtype), _ts(m.dtype), _ts(fdtype)))(
+            _ptr(x), _ptr(y), _ptr(z), _ptr(m), C.c_size_t(x.size), _ptr(l2i), C.c_int32(l2i.size), _ptr(layout),
+            _ptr(c4))
+        return c4
+
+    def upsweep_centers(self, level_range, child_offsets, centers4):
+        """[ref: tree/octree.hpp:583-601 upsweep with focus/source_center.hpp:81-96 CombineSourceCenter]"""
+        c4 = centers4.copy()
+        lr = np.ascontiguousarray(level_range, dtype=np.int32)
+        self._f("upsweep_centers_" + _ts(c4.dtype))(C.c_int32(lr.size - 1), _ptr(lr), _ptr(child_offsets), _ptr(c4))
+        return c4
+
     def upsweep_sum(self, level_range, child_offsets, counts):
         counts = counts.copy()
         self._f("upsweep_sum")(C.c_int32(level_range.size - 1), _ptr(level_range), _ptr(child_offsets), _ptr(counts))

@@ -455,3 +455,40 @@ REF_MAC(k32, uint32_t, f64, double)
 REF_MAC(k64, uint64_t, f32, float)
 REF_MAC(k64, uint64_t, f64, double)
 }
+
+// ------------------------------------------------------------------------------------------------
+// n3 device-kernel counterparts: expansion centres (reference build only)
+// ------------------------------------------------------------------------------------------------
+template<class Tc, class Tm, class Tf>
+static void leafMassCenterW(const Tc* x, const Tc* y, const Tc* z, const Tm* m, size_t n, const int32_t* l2i, int32_t L,
+                            const uint32_t* layout, Tf* c4)
+{
+    computeLeafMassCenter<Tc, Tm, Tf>({x, n}, {y, n}, {z, n}, {m, n}, {l2i, size_t(L)}, layout,
+                                      reinterpret_cast<SourceCenterType<Tf>*>(c4));
+}
+template<class T>
+static void upsweepCentersW(int32_t numLevels, const int32_t* levelRange, const int32_t* co, T* c4)
+{
+    // as FocusedOctree::updateCenters does [focus/octree_focus_mpi.hpp:421]
+    upsweep(gsl::span<const TreeNodeIndex>(levelRange, size_t(numLevels + 1)),
+            gsl::span<const TreeNodeIndex>(co, size_t(levelRange[numLevels])),
+            reinterpret_cast<SourceCenterType<T>*>(c4), CombineSourceCenter<T>{});
+}
+extern "C" {
+void cstone_ref_compute_leaf_source_center_f64_f64_f64(const double* x, const double* y, const double* z,
+                                                       const double* m, size_t n, const int32_t* l2i, int32_t L,
+                                                       const uint32_t* layout, double* c4)
+{ leafMassCenterW<double, double, double>(x, y, z, m, n, l2i, L, layout, c4); }
+void cstone_ref_compute_leaf_source_center_f64_f32_f64(const double* x, const double* y, const double* z,
+                                                       const float* m, size_t n, const int32_t* l2i, int32_t L,
+                                                       const uint32_t* layout, double* c4)
+{ leafMassCenterW<double, float, double>(x, y, z, m, n, l2i, L, layout, c4); }
+void cstone_ref_compute_leaf_source_center_f32_f32_f32(const float* x, const float* y, const float* z, const float* m,
+                                                       size_t n, const int32_t* l2i, int32_t L, const uint32_t* layout,
+                                                       float* c4)
+{ leafMassCenterW<float, float, float>(x, y, z, m, n, l2i, L, layout, c4); }
+void cstone_ref_upsweep_centers_f32(int32_t nl, const int32_t* lr, const int32_t* co, float* c4)
+{ upsweepCentersW<float>(nl, lr, co, c4); }
+void cstone_ref_upsweep_centers_f64(int32_t nl, const int32_t* lr, const int32_t* co, double* c4)
+{ upsweepCentersW<double>(nl, lr, co, c4); }
+}

@@ -166,3 +166,35 @@ def test_move_centers(fd):
     got = ops.move_centers(ga.to_dev(src)).cpu().numpy()
     np.testing.assert_array_equal(got[:, :3], src)
     np.testing.assert_array_equal(got[:, 3], np.ones(1000, dtype=fd))
+
+
+@pytest.mark.parametrize("types", [(np.float64, np.float64, np.float64), (np.float64, np.float32, np.float64),
+                                   (np.float32, np.float32, np.float32)])
+@pytest.mark.parametrize("kd", KD)
+def test_source_centers(ref, kd, types):
+    """computeLeafSourceCenterGpu + upsweepCentersGpu: sums in the reference's order, bit-identical"""
+    tc, tm, tf = types
+    n = 50000
+    box = loader.make_box((-1, 1), dtype=tc)
+    x, y, z = _cloud(n, 9, tc)
+    keys = ref.compute_sfc_keys(loader.HILBERT, x, y, z, box, kdtype=kd)
+    order = np.argsort(keys, kind="stable")
+    keys, x, y, z = keys[order], x[order].copy(), y[order].copy(), z[order].copy()
+    rng = np.random.default_rng(4)
+    m = rng.uniform(0.1, 2.0, size=n).astype(tm)
+    m[::17] *= -1  # addBody weighs with |m|
+    tree, counts = ref.compute_octree(keys, 32)
+    oc = ref.build_octree(tree)
+    layout = np.concatenate(([0], np.cumsum(counts, dtype=np.uint64))).astype(np.uint32)
+    d = ga.oct_to_dev(oc)
+
+    want_leaf = ref.compute_leaf_source_center(x, y, z, m, oc, layout, fdtype=tf)
+    got = ops.compute_leaf_source_center(ga.to_dev(x), ga.to_dev(y), ga.to_dev(z), ga.to_dev(m), d, ga.to_dev(layout))
+    np.testing.assert_array_equal(got.cpu().numpy(), want_leaf)
+
+    want = ref.upsweep_centers(oc["level_range"], oc["child_offsets"], want_leaf)
+    ops.upsweep_centers(oc["level_range"], d.child_offsets, got)
+    np.testing.assert_array_equal(got.cpu().numpy(), want)
+    # the root holds the total |mass| up to summation order and a centre inside the cloud
+    assert abs(want[0, 3] - np.abs(m.astype(np.float64)).sum()) < 1e-3 * n
+    assert np.all(np.abs(want[0, :3]) < 0.1)
