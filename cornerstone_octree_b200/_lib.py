@@ -97,6 +97,12 @@ for ts in ("f32", "f64"):
     _PROTOS["upsweep_centers_" + ts] = (_i, [_i32, _vp, _vp, _vp, _vp])
 for tt in ("f64_f64_f64", "f64_f32_f64", "f32_f32_f32"):
     _PROTOS["compute_leaf_source_center_" + tt] = (_i, [_vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp])
+for ks, kt in (("k32", _u32), ("k64", _u64)):
+    _PROTOS["focus_tree_create_" + ks] = (_vp, [_i, _u32, _f])
+    _PROTOS["focus_tree_destroy_" + ks] = (None, [_vp])
+    _PROTOS["focus_tree_view_" + ks] = (_i, [_vp, _vp])
+    for ts in ("f32", "f64"):
+        _PROTOS["focus_tree_update_%s_%s" % (ks, ts)] = (_i, [_vp, _vp, _vp, _u64, kt, kt, _vp, _i32, _vp, _vp])
 _PROTOS["compute_fixed_groups"] = (_i, [_u32, _u32, _u32, _vp, _vp])
 _PROTOS["group_splits_temp_bytes"] = (_u64, [_u32, _u32])
 for ks in ("k32", "k64"):

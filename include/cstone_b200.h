@@ -555,6 +555,44 @@ CSTONE_B200_GROUPS_DECL(k64, uint64_t, f64_f64, double, double)
 CSTONE_B200_GROUPS_DECL(k64, uint64_t, f64_f32, double, float)
 CSTONE_B200_GROUPS_DECL(k64, uint64_t, f32_f32, float, float)
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Single-rank focus tree, device resident [ref: focus/octree_focus.hpp:349-427 FocusedOctreeSingleNode<KeyType>;
+ * CombinedUpdate::updateFocus :83-135].  create: bucket_size = maximum particle count of a leaf inside the focus,
+ * theta = opening angle outside (NULL on invalid arguments).  update = one step of the reference's update():
+ * rebalance by counts inside [focus_start, focus_end) and by MAC outside, focus boundaries and mandatory keys (HOST
+ * array, may be unsorted / contain duplicates) enforced or injected, then MAC marks and particle counts of the new
+ * tree from the sorted particle keys (DEVICE).  *converged_host = 1 iff the tree structure did not change.
+ * view: device pointers owned by the tree, valid until the next update / destroy; leaf_to_internal is the full
+ * array of build_octree (the OctreeView span starts at + num_internal_nodes). */
+typedef struct cstone_b200_focus_tree_view
+{
+    int32_t num_leaf_nodes, num_internal_nodes, num_nodes, reserved;
+    const void* leaves;          /* K[num_leaf_nodes + 1] */
+    const uint32_t* leaf_counts; /* [num_leaf_nodes], NULL before the first update */
+    const void* prefixes;        /* K[num_nodes] */
+    const int32_t* child_offsets;
+    const int32_t* parents;
+    const int32_t* level_range; /* device copy, max_tree_level + 2 entries */
+    const int32_t* internal_to_leaf;
+    const int32_t* leaf_to_internal;
+    const uint32_t* counts; /* [num_nodes] */
+    const char* macs;       /* [num_nodes] */
+} cstone_b200_focus_tree_view;
+#define CSTONE_B200_FOCUS_TREE_DECL(KS, K)                                                                             \
+    void* cstone_b200_focus_tree_create_##KS(int sfc_kind, uint32_t bucket_size, float theta);                         \
+    void cstone_b200_focus_tree_destroy_##KS(void* handle);                                                            \
+    int cstone_b200_focus_tree_update_##KS##_f32(void* handle, const cstone_box_f32* box, const K* particle_keys,      \
+                                                 uint64_t num_keys, K focus_start, K focus_end,                        \
+                                                 const K* mandatory_keys_host, int32_t num_mandatory,                  \
+                                                 int32_t* converged_host, void* stream);                               \
+    int cstone_b200_focus_tree_update_##KS##_f64(void* handle, const cstone_box_f64* box, const K* particle_keys,      \
+                                                 uint64_t num_keys, K focus_start, K focus_end,                        \
+                                                 const K* mandatory_keys_host, int32_t num_mandatory,                  \
+                                                 int32_t* converged_host, void* stream);                               \
+    int cstone_b200_focus_tree_view_##KS(void* handle, cstone_b200_focus_tree_view* out);
+CSTONE_B200_FOCUS_TREE_DECL(k32, uint32_t)
+CSTONE_B200_FOCUS_TREE_DECL(k64, uint64_t)
+
 #ifdef __cplusplus
 }
 #endif

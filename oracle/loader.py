@@ -358,3 +358,37 @@ def load(which="port"):
     if which not in _cache:
         _cache[which] = Oracle(which)
     return _cache[which]
+
+
+class RefFocusTree:
+    """the reference's FocusedOctreeSingleNode<KeyType> [ref: focus/octree_focus.hpp:349-427], compiled from its own
+    headers into oracle/_ref (reference build only)"""
+
+    def __init__(self, oracle, bucket_size, theta, kdtype=np.uint64):
+        assert oracle.which == "ref"
+        self.o = oracle
+        self.kd = np.dtype(kdtype)
+        self.ks = _ks(kdtype)
+        self.h = C.c_void_p(oracle._f("focus_tree_create_" + self.ks, C.c_void_p)(C.c_uint32(bucket_size),
+                                                                                  C.c_float(theta)))
+
+    def close(self):
+        if self.h:
+            self.o._f("focus_tree_destroy_" + self.ks)(self.h)
+            self.h = None
+
+    def update(self, box, keys, focus_start, focus_end, mandatory=()):
+        kt = C.c_uint32 if self.kd == np.uint32 else C.c_uint64
+        mand = np.ascontiguousarray(np.asarray(list(mandatory), dtype=self.kd))
+        ts = "f32" if isinstance(box, BoxF32) else "f64"
+        r = self.o._f("focus_tree_update_%s_%s" % (self.ks, ts), C.c_int)(
+            self.h, C.byref(box), _ptr(keys), C.c_size_t(keys.size), kt(int(focus_start)), kt(int(focus_end)),
+            _ptr(mand), C.c_int32(mand.size))
+        return bool(r)
+
+    def leaves_and_counts(self):
+        n = self.o._f("focus_tree_num_leaves_" + self.ks, C.c_int32)(self.h)
+        leaves = np.zeros(n + 1, dtype=self.kd)
+        counts = np.zeros(n, dtype=np.uint32)
+        self.o._f("focus_tree_get_" + self.ks)(self.h, _ptr(leaves), _ptr(counts))
+        return leaves, counts

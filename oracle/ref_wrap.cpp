@@ -492,3 +492,39 @@ void cstone_ref_upsweep_centers_f32(int32_t nl, const int32_t* lr, const int32_t
 void cstone_ref_upsweep_centers_f64(int32_t nl, const int32_t* lr, const int32_t* co, double* c4)
 { upsweepCentersW<double>(nl, lr, co, c4); }
 }
+
+// ------------------------------------------------------------------------------------------------
+// a19: the reference's single-rank focus tree (reference build only)
+// ------------------------------------------------------------------------------------------------
+#include "cstone/focus/octree_focus.hpp"
+
+template<class K, class T, class CB>
+static int focusUpdateW(void* h, const CB* box, const K* keys, size_t n, K fs, K fe, const K* mand, int32_t nm)
+{
+    auto* t = static_cast<FocusedOctreeSingleNode<K>*>(h);
+    return t->update(asBox<T>(box), gsl::span<const K>(keys, n), fs, fe, gsl::span<const K>(mand, size_t(nm))) ? 1 : 0;
+}
+extern "C" {
+#define REF_FOCUS_TREE(KS, K)                                                                                          \
+    void* cstone_ref_focus_tree_create_##KS(uint32_t bucket, float theta)                                              \
+    { return new FocusedOctreeSingleNode<K>(bucket, theta); }                                                          \
+    void cstone_ref_focus_tree_destroy_##KS(void* h) { delete static_cast<FocusedOctreeSingleNode<K>*>(h); }           \
+    int cstone_ref_focus_tree_update_##KS##_f32(void* h, const cstone_box_f32* box, const K* keys, size_t n, K fs,     \
+                                                K fe, const K* mand, int32_t nm)                                       \
+    { return focusUpdateW<K, float>(h, box, keys, n, fs, fe, mand, nm); }                                              \
+    int cstone_ref_focus_tree_update_##KS##_f64(void* h, const cstone_box_f64* box, const K* keys, size_t n, K fs,     \
+                                                K fe, const K* mand, int32_t nm)                                       \
+    { return focusUpdateW<K, double>(h, box, keys, n, fs, fe, mand, nm); }                                             \
+    int32_t cstone_ref_focus_tree_num_leaves_##KS(void* h)                                                             \
+    { return int32_t(static_cast<FocusedOctreeSingleNode<K>*>(h)->treeLeaves().size()) - 1; }                          \
+    void cstone_ref_focus_tree_get_##KS(void* h, K* leaves, uint32_t* counts)                                          \
+    {                                                                                                                  \
+        auto* t = static_cast<FocusedOctreeSingleNode<K>*>(h);                                                         \
+        auto l  = t->treeLeaves();                                                                                     \
+        auto c  = t->leafCounts();                                                                                     \
+        std::copy(l.begin(), l.end(), leaves);                                                                         \
+        std::copy(c.begin(), c.end(), counts);                                                                         \
+    }
+REF_FOCUS_TREE(k32, uint32_t)
+REF_FOCUS_TREE(k64, uint64_t)
+}
