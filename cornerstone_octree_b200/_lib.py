@@ -101,6 +101,9 @@ for ks, kt in (("k32", _u32), ("k64", _u64)):
     _PROTOS["focus_tree_create_" + ks] = (_vp, [_i, _u32, _f])
     _PROTOS["focus_tree_destroy_" + ks] = (None, [_vp])
     _PROTOS["focus_tree_view_" + ks] = (_i, [_vp, _vp])
+    _PROTOS["focus_tree_set_leaves_" + ks] = (_i, [_vp, _vp, _i32, _vp])
+    for ts in ("f32", "f64"):
+        _PROTOS["focus_tree_mac_refine_%s_%s" % (ks, ts)] = (_i, [_vp, _vp, kt, kt, kt, kt, _f, _vp, _vp])
     for ts in ("f32", "f64"):
         _PROTOS["focus_tree_update_%s_%s" % (ks, ts)] = (_i, [_vp, _vp, _vp, _u64, kt, kt, _vp, _i32, _vp, _vp])
 _PROTOS["compute_fixed_groups"] = (_i, [_u32, _u32, _u32, _vp, _vp])

@@ -76,6 +76,7 @@ struct FocusApi;
         static constexpr auto decision = cstone_b200_rebalance_decision_essential_##KS;                                \
         static constexpr auto enforce  = cstone_b200_enforce_keys_##KS;                                                \
         static constexpr auto protect  = cstone_b200_protect_ancestors_##KS;                                           \
+        static constexpr auto refine   = cstone_b200_mac_refine_decision_##KS;                                         \
         static constexpr auto rebal    = cstone_b200_rebalance_tree_##KS;                                              \
         static constexpr auto sortKeys = cstone_b200_sort_keys_##KS;                                                   \
         static constexpr auto sortTemp = cstone_b200_sort_keys_temp_bytes_##KS;                                        \
@@ -148,6 +149,28 @@ public:
     template<class T>
     int update(const typename BoxT<T>::type* box, const K* keys, size_t numKeys, K focusStart, K focusEnd,
                const K* mandatoryHost, int numMandatory, int* convergedHost, cudaStream_t s);
+
+    //! replace the leaf array (e.g. a tree received from elsewhere) and relink; counts and macs are zeroed
+    int setLeaves(const K* leavesDev, int numLeaves, cudaStream_t s)
+    {
+        CSB_TRY(leaves_.reserve((size_t(numLeaves) + 1) * sizeof(K)));
+        CSB_CUDA(cudaMemcpyAsync(leaves_.p, leavesDev, (size_t(numLeaves) + 1) * sizeof(K), cudaMemcpyDeviceToDevice, s));
+        numLeaves_ = numLeaves;
+        CSB_TRY(link(s));
+        CSB_TRY(counts_.reserve(size_t(numNodes_) * 4));
+        CSB_TRY(macs_.reserve(size_t(numNodes_)));
+        CSB_CUDA(cudaMemsetAsync(counts_.p, 0, size_t(numNodes_) * 4, s));
+        CSB_CUDA(cudaMemsetAsync(macs_.p, 0, size_t(numNodes_), s));
+        leafCounts_.reserve(size_t(numLeaves_) * 4);
+        CSB_CUDA(cudaMemsetAsync(leafCounts_.p, 0, size_t(numLeaves_) * 4, s));
+        CSB_CUDA(cudaStreamSynchronize(s));
+        ready_ = true;
+        return 0;
+    }
+
+    template<class T>
+    int macRefine(const typename BoxT<T>::type* box, K oldFocusStart, K oldFocusEnd, K focusStart, K focusEnd,
+                  float invTheta, int* convergedHost, cudaStream_t s);
 
     int kind_;
     unsigned bucket_;
@@ -304,6 +327,72 @@ int FocusTree<K>::update(const typename BoxT<T>::type* box, const K* keys, size_
     return 0;
 }
 
+/*! one step of macRefineGpu / updateMacRefineGpu [ref: focus/octree_focus.hpp:297-342]: after the focus moved from
+ *  [oldFocusStart, oldFocusEnd) to [focusStart, focusEnd), leaves OUTSIDE the focus that fail the minimum-distance MAC
+ *  w.r.t. the newly covered part of the focus are split by one level.  converged = no leaf was split. */
+template<class K>
+template<class T>
+int FocusTree<K>::macRefine(const typename BoxT<T>::type* box, K oldFocusStart, K oldFocusEnd, K focusStart,
+                            K focusEnd, float invTheta, int* convergedHost, cudaStream_t s)
+{
+    using A = FocusApi<K>;
+    if (!ready_) CSB_TRY(init(s));
+    if (oldFocusStart == focusStart && oldFocusEnd == focusEnd)
+    {
+        if (convergedHost) *convergedHost = 1;
+        return 0;
+    }
+    const int L = numLeaves_, M = numNodes_;
+    CSB_TRY(temp_.reserve(size_t(cstone_b200_scan_temp_bytes(uint64_t(M) + 1)) + cstone_b200_reduce_temp_bytes() + 4096));
+    CSB_TRY(centers_.reserve(size_t(M) * 4 * sizeof(T)));
+    CSB_TRY(A::geoMac(kind_, prefixes_.as<K>(), M, centers_.as<T>(), invTheta, box, s));
+    CSB_TRY(macs_.reserve(size_t(M)));
+    CSB_CUDA(cudaMemsetAsync(macs_.p, 0, size_t(M), s));
+
+    K growthLower = focusStart < oldFocusStart ? oldFocusStart : focusStart;
+    K growthUpper = oldFocusEnd < focusEnd ? oldFocusEnd : focusEnd;
+    uint64_t fGrowL = 0, fGrowU = 0, fStart = 0, fEnd = 0;
+    CSB_TRY(lowerBoundKey(leaves_.as<K>(), size_t(L), growthLower, &fGrowL, temp_.p, s));
+    CSB_TRY(lowerBoundKey(leaves_.as<K>(), size_t(L), growthUpper, &fGrowU, temp_.p, s));
+    CSB_TRY(lowerBoundKey(leaves_.as<K>(), size_t(L), focusStart, &fStart, temp_.p, s));
+    CSB_TRY(lowerBoundKey(leaves_.as<K>(), size_t(L), focusEnd, &fEnd, temp_.p, s));
+    if (fGrowL > fStart)
+        CSB_TRY(A::mark(kind_, prefixes_.as<K>(), childOffsets_.as<int>(), centers_.as<T>(), box,
+                        leaves_.as<K>() + fStart, int(fGrowL - fStart), 1, macs_.as<char>(), s));
+    if (fEnd > fGrowU)
+        CSB_TRY(A::mark(kind_, prefixes_.as<K>(), childOffsets_.as<int>(), centers_.as<T>(), box,
+                        leaves_.as<K>() + fGrowU, int(fEnd - fGrowU), 1, macs_.as<char>(), s));
+
+    CSB_TRY(leafOps_.reserve((size_t(L) + 1) * 4));
+    CSB_TRY(nodeOps_.reserve((size_t(M) + 1) * 4));
+    CSB_CUDA(cudaMemsetAsync(leafOps_.as<int>() + L, 0, 4, s));
+    CSB_TRY(A::refine(prefixes_.as<K>(), macs_.as<char>(), l2i_.as<int>() + numInternal_, L, int(fStart), int(fEnd),
+                      leafOps_.as<int>(), s));
+    uint64_t ones = 0;
+    CSB_TRY(cstone_b200_count_u32(leafOps_.as<uint32_t>(), size_t(L), 1u, &ones, temp_.p, s));
+    const bool converged = ones == uint64_t(L);
+    CSB_TRY(cstone_b200_exclusive_scan_u32(leafOps_.as<uint32_t>(), nodeOps_.as<uint32_t>(), size_t(L) + 1, 0u,
+                                           temp_.p, s));
+    int newL = 0;
+    CSB_CUDA(cudaMemcpyAsync(&newL, nodeOps_.as<int>() + L, 4, cudaMemcpyDeviceToHost, s));
+    CSB_CUDA(cudaStreamSynchronize(s));
+    CSB_TRY(newLeaves_.reserve((size_t(newL) + 1) * sizeof(K)));
+    CSB_TRY(A::rebal(leaves_.as<K>(), L, newL, nodeOps_.as<int>(), newLeaves_.as<K>(), s));
+    leaves_.swap(newLeaves_);
+    numLeaves_ = newL;
+    CSB_TRY(link(s));
+    // node arrays of the new tree: sized, zeroed (the caller refreshes them with update())
+    CSB_TRY(counts_.reserve(size_t(numNodes_) * 4));
+    CSB_TRY(macs_.reserve(size_t(numNodes_)));
+    CSB_TRY(leafCounts_.reserve(size_t(numLeaves_) * 4));
+    CSB_CUDA(cudaMemsetAsync(counts_.p, 0, size_t(numNodes_) * 4, s));
+    CSB_CUDA(cudaMemsetAsync(macs_.p, 0, size_t(numNodes_), s));
+    CSB_CUDA(cudaMemsetAsync(leafCounts_.p, 0, size_t(numLeaves_) * 4, s));
+    CSB_CUDA(cudaStreamSynchronize(s));
+    if (convergedHost) *convergedHost = converged ? 1 : 0;
+    return 0;
+}
+
 } // namespace csb
 
 extern "C" {
@@ -336,6 +425,27 @@ extern "C" {
         return static_cast<csb::FocusTree<K>*>(handle)->update<double>(box, particleKeys, numKeys, focusStart,         \
                                                                        focusEnd, mandatoryKeysHost, numMandatory,      \
                                                                        convergedHost, csb::asStream(stream));          \
+    }                                                                                                                  \
+    int cstone_b200_focus_tree_set_leaves_##KS(void* handle, const K* leaves, int32_t numLeafNodes, void* stream)      \
+    {                                                                                                                  \
+        if (!handle || !leaves || numLeafNodes < 1) return CSTONE_E_INVALID_ARGUMENT;                                  \
+        return static_cast<csb::FocusTree<K>*>(handle)->setLeaves(leaves, numLeafNodes, csb::asStream(stream));        \
+    }                                                                                                                  \
+    int cstone_b200_focus_tree_mac_refine_##KS##_f32(void* handle, const cstone_box_f32* box, K oldFocusStart,         \
+                                                     K oldFocusEnd, K focusStart, K focusEnd, float invTheta,          \
+                                                     int32_t* convergedHost, void* stream)                             \
+    {                                                                                                                  \
+        if (!handle || !box) return CSTONE_E_INVALID_ARGUMENT;                                                         \
+        return static_cast<csb::FocusTree<K>*>(handle)->macRefine<float>(                                              \
+            box, oldFocusStart, oldFocusEnd, focusStart, focusEnd, invTheta, convergedHost, csb::asStream(stream));    \
+    }                                                                                                                  \
+    int cstone_b200_focus_tree_mac_refine_##KS##_f64(void* handle, const cstone_box_f64* box, K oldFocusStart,         \
+                                                     K oldFocusEnd, K focusStart, K focusEnd, float invTheta,          \
+                                                     int32_t* convergedHost, void* stream)                             \
+    {                                                                                                                  \
+        if (!handle || !box) return CSTONE_E_INVALID_ARGUMENT;                                                         \
+        return static_cast<csb::FocusTree<K>*>(handle)->macRefine<double>(                                             \
+            box, oldFocusStart, oldFocusEnd, focusStart, focusEnd, invTheta, convergedHost, csb::asStream(stream));    \
     }                                                                                                                  \
     int cstone_b200_focus_tree_view_##KS(void* handle, cstone_b200_focus_tree_view* out)                               \
     {                                                                                                                  \

@@ -61,6 +61,21 @@ class FocusedOctreeSingleNode:
              torch.cuda.current_stream().cuda_stream)
         return bool(conv.value)
 
+    def set_leaves(self, leaves):
+        """replace the leaf array (device tensor, num_leaf_nodes + 1 keys)"""
+        call("focus_tree_set_leaves_" + self.ks, self.h, leaves.data_ptr(), leaves.numel() - 1,
+             torch.cuda.current_stream().cuda_stream)
+
+    def mac_refine(self, box, old_focus_start, old_focus_end, focus_start, focus_end, inv_theta):
+        """one step of macRefineGpu [ref: focus/octree_focus.hpp:318-342] -> converged"""
+        mask = (1 << (32 if self.ks == "k32" else 64)) - 1
+        conv = C.c_int32(0)
+        ts = "f32" if box.__class__.__name__ == "BoxF32" else "f64"
+        call("focus_tree_mac_refine_%s_%s" % (self.ks, ts), self.h, C.byref(box), int(old_focus_start) & mask,
+             int(old_focus_end) & mask, int(focus_start) & mask, int(focus_end) & mask, inv_theta, C.byref(conv),
+             torch.cuda.current_stream().cuda_stream)
+        return bool(conv.value)
+
     def _view(self):
         v = _View()
         call("focus_tree_view_" + self.ks, self.h, C.byref(v))

@@ -589,6 +589,17 @@ typedef struct cstone_b200_focus_tree_view
                                                  uint64_t num_keys, K focus_start, K focus_end,                        \
                                                  const K* mandatory_keys_host, int32_t num_mandatory,                  \
                                                  int32_t* converged_host, void* stream);                               \
+    /* replace the leaf array (device, num_leaf_nodes + 1 keys) and relink; counts and macs are zeroed */             \
+    int cstone_b200_focus_tree_set_leaves_##KS(void* handle, const K* leaves, int32_t num_leaf_nodes, void* stream);   \
+    /* one step of macRefineGpu [ref: focus/octree_focus.hpp:297-342]: the focus moved from [old_focus_start,          \
+     * old_focus_end) to [focus_start, focus_end); leaves outside the focus failing the min-distance MAC w.r.t. the    \
+     * newly covered focus leaves are split by one level.  *converged_host = 1 iff nothing was split. */               \
+    int cstone_b200_focus_tree_mac_refine_##KS##_f32(void* handle, const cstone_box_f32* box, K old_focus_start,       \
+                                                     K old_focus_end, K focus_start, K focus_end, float inv_theta,     \
+                                                     int32_t* converged_host, void* stream);                           \
+    int cstone_b200_focus_tree_mac_refine_##KS##_f64(void* handle, const cstone_box_f64* box, K old_focus_start,       \
+                                                     K old_focus_end, K focus_start, K focus_end, float inv_theta,     \
+                                                     int32_t* converged_host, void* stream);                           \
     int cstone_b200_focus_tree_view_##KS(void* handle, cstone_b200_focus_tree_view* out);
 CSTONE_B200_FOCUS_TREE_DECL(k32, uint32_t)
 CSTONE_B200_FOCUS_TREE_DECL(k64, uint64_t)

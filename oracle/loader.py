@@ -305,6 +305,20 @@ class Oracle:
         self._f("upsweep_centers_" + _ts(c4.dtype))(C.c_int32(lr.size - 1), _ptr(lr), _ptr(child_offsets), _ptr(c4))
         return c4
 
+    def mac_refine_step(self, leaves, old_fs, old_fe, fs, fe, inv_theta, box):
+        """one step of macRefine [ref: focus/octree_focus.hpp:260-295] -> (new leaves, converged)"""
+        kt = C.c_uint32 if leaves.dtype == np.uint32 else C.c_uint64
+        cap = 8 * (leaves.size - 1) + 8
+        buf = np.zeros(cap + 1, dtype=leaves.dtype)
+        buf[:leaves.size] = leaves
+        n = C.c_int32(leaves.size - 1)
+        ts = "f32" if isinstance(box, BoxF32) else "f64"
+        r = self._f("mac_refine_step_%s_%s" % (_ks(leaves.dtype), ts), C.c_int)(
+            _ptr(buf), C.byref(n), C.c_int32(cap), kt(int(old_fs)), kt(int(old_fe)), kt(int(fs)), kt(int(fe)),
+            C.c_float(inv_theta), C.byref(box))
+        assert r >= 0
+        return buf[:n.value + 1].copy(), bool(r)
+
     def upsweep_sum(self, level_range, child_offsets, counts):
         counts = counts.copy()
         self._f("upsweep_sum")(C.c_int32(level_range.size - 1), _ptr(level_range), _ptr(child_offsets), _ptr(counts))

@@ -528,3 +528,32 @@ extern "C" {
 REF_FOCUS_TREE(k32, uint32_t)
 REF_FOCUS_TREE(k64, uint64_t)
 }
+
+// one step of the reference's macRefine on a leaf array [focus/octree_focus.hpp:260-295]; leaves has room for
+// capacity + 1 keys, *numLeaves is updated; returns converged, or -1 if the new tree does not fit
+template<class K, class T, class CB>
+static int macRefineStepW(K* leavesIo, int32_t* numLeaves, int32_t capacity, K ofs, K ofe, K fs, K fe, float invTheta,
+                          const CB* box)
+{
+    std::vector<K> leaves(leavesIo, leavesIo + *numLeaves + 1);
+    OctreeData<K, CpuTag> tree;
+    tree.resize(nNodes(leaves));
+    updateInternalTree<K>(leaves, tree.data());
+    std::vector<SourceCenterType<T>> centers;
+    std::vector<char> macs;
+    bool conv = macRefine(tree, leaves, centers, macs, ofs, ofe, fs, fe, invTheta, asBox<T>(box));
+    if (int32_t(nNodes(leaves)) > capacity) return -1;
+    std::copy(leaves.begin(), leaves.end(), leavesIo);
+    *numLeaves = int32_t(nNodes(leaves));
+    return conv ? 1 : 0;
+}
+extern "C" {
+#define REF_MAC_REFINE(KS, K, TS, T)                                                                                   \
+    int cstone_ref_mac_refine_step_##KS##_##TS(K* leaves, int32_t* n, int32_t cap, K ofs, K ofe, K fs, K fe,           \
+                                               float invTheta, const cstone_box_##TS* box)                             \
+    { return macRefineStepW<K, T>(leaves, n, cap, ofs, ofe, fs, fe, invTheta, box); }
+REF_MAC_REFINE(k32, uint32_t, f32, float)
+REF_MAC_REFINE(k32, uint32_t, f64, double)
+REF_MAC_REFINE(k64, uint64_t, f32, float)
+REF_MAC_REFINE(k64, uint64_t, f64, double)
+}

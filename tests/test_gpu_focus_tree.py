@@ -115,3 +115,52 @@ def test_focus_tree_cloud_with_mandatory_keys(ref, kd, fd):
         assert steps < 120
     rt.close()
     gt.close()
+
+
+def _mac_refinement_tree(kd):
+    """OctreeMaker{}.divide().divide(0).divide(0,j) for j in 0..7 .divide(0,0,0): level 3 in the first octant (level 4
+    in its first cell), level 1 elsewhere  [ref: test/unit/focus/octree_focus.cpp:436-447]"""
+    ml = loader.max_level(kd)
+    r = [1 << (3 * (ml - l)) for l in range(6)]
+    keys = set(i * r[1] for i in range(9))
+    keys |= set(i * r[2] for i in range(8))
+    keys |= set(i * r[3] for i in range(64))
+    keys |= set(i * r[4] for i in range(8))
+    return np.array(sorted(keys), dtype=kd)
+
+
+@pytest.mark.parametrize("kd", [np.uint32, np.uint64])
+@pytest.mark.parametrize("fd", [np.float32, np.float64])
+def test_mac_refinement(ref, kd, fd):
+    ml = loader.max_level(kd)
+    leaves0 = _mac_refinement_tree(kd)
+    assert leaves0.size - 1 == 78
+    rbox = loader.make_box((0, 1), dtype=fd)
+    gbox = ga.conv_box(rbox)
+    inv_theta = float(np.float32(np.sqrt(3) / 2 + 1e-6))
+    td = torch.int32 if kd == np.uint32 else torch.int64
+    oct1 = 1 << (3 * (ml - 1))  # decodePlaceholderBit(011): end of the first octant
+    o0101 = 1 << (3 * (ml - 2))  # decodePlaceholderBit(0101)
+    o0107 = 7 << (3 * (ml - 2))  # decodePlaceholderBit(0107)
+    cases = {"fullSurface": (oct1, oct1, 64 + 7 + 3 * (4 + 4 * 8) + 3 * (6 + 2 * 8) + (7 + 8)),
+             "noSurface": (o0101, oct1, 78),
+             "partialSurface": (0, o0107, 78 + 5 * 7)}
+    for name, (old_fs, old_fe, want_leaves) in cases.items():
+        gt = FocusedOctreeSingleNode(16, 0.5, key_dtype=td)
+        gt.set_leaves(ga.to_dev(leaves0))
+        leaves = leaves0
+        steps = 0
+        while True:
+            leaves, want_conv = ref.mac_refine_step(leaves, old_fs, old_fe, 0, oct1, inv_theta, rbox)
+            got_conv = gt.mac_refine(gbox, old_fs, old_fe, 0, oct1, inv_theta)
+            np.testing.assert_array_equal(_keys_np(gt.tree_leaves(), kd), leaves, err_msg=name)
+            assert got_conv == want_conv
+            steps += 1
+            assert steps < 20
+            if want_conv:
+                break
+        if fd == np.float64:
+            assert leaves.size - 1 == want_leaves, name  # the reference test's known answers (double)
+        # unchanged focus: nothing to do
+        assert gt.mac_refine(gbox, 0, oct1, 0, oct1, inv_theta)
+        gt.close()
