@@ -161,7 +161,7 @@ public:
         CSB_TRY(macs_.reserve(size_t(numNodes_)));
         CSB_CUDA(cudaMemsetAsync(counts_.p, 0, size_t(numNodes_) * 4, s));
         CSB_CUDA(cudaMemsetAsync(macs_.p, 0, size_t(numNodes_), s));
-        leafCounts_.reserve(size_t(numLeaves_) * 4);
+        CSB_TRY(leafCounts_.reserve(size_t(numLeaves_) * 4));
         CSB_CUDA(cudaMemsetAsync(leafCounts_.p, 0, size_t(numLeaves_) * 4, s));
         CSB_CUDA(cudaStreamSynchronize(s));
         ready_ = true;

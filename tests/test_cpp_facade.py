@@ -8,10 +8,11 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SRC = os.path.join(ROOT, "tests", "cpp", "domain_facade_test.cpp")
+FOCUS_SRC = os.path.join(ROOT, "tests", "cpp", "focus_facade_test.cpp")
 
 
-def build_facade_test(out_dir):
-    exe = os.path.join(str(out_dir), "domain_facade_test")
+def build_facade_test(out_dir, SRC=SRC):
+    exe = os.path.join(str(out_dir), os.path.basename(SRC)[:-4])
     libdir = os.path.join(ROOT, "cornerstone_octree_b200")
     cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"), SRC,
            "-L" + libdir, "-lcstone_b200", "-Wl,-rpath," + libdir, "-o", exe]
@@ -24,6 +25,21 @@ def test_facade_compiles_with_host_compiler(tmp_path):
     # no arguments: prints the usage and returns 2 without touching a device
     r = subprocess.run([exe], capture_output=True, text=True)
     assert r.returncode == 2 and "usage" in r.stdout
+
+
+def test_focus_facade_compiles_with_host_compiler(tmp_path):
+    exe = build_facade_test(tmp_path, FOCUS_SRC)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 2 and "usage" in r.stdout
+
+
+@pytest.mark.gpu
+def test_focus_facade_known_answers(tmp_path):
+    """groups + single-rank focus tree through focus.hpp on the reference tests' known answers"""
+    exe = build_facade_test(tmp_path, FOCUS_SRC)
+    r = subprocess.run([exe, "run"], capture_output=True, text=True, timeout=600)
+    print(r.stdout[-3000:], r.stderr[-2000:])
+    assert r.returncode == 0 and "FOCUS_FACADE_OK" in r.stdout
 
 
 @pytest.mark.gpu

@@ -64,7 +64,7 @@ def test_compute_essential_tree(ref, kd):
     while not _step_both(rt, gt, rbox, gbox, keys, dkeys, fs, fe):
         steps += 1
         assert steps < 40
-    if kd == np.uint64:
+    if kd is not None:  # both key widths give the reference test's known answer
         assert _octant_node_count(_keys_np(gt.tree_leaves(), kd), kd) == ref_counts
 
     fs, fe = pad(7, 3), top - 1
@@ -75,7 +75,7 @@ def test_compute_essential_tree(ref, kd):
     while not _step_both(rt, gt, rbox, gbox, keys, dkeys, fs, fe):
         steps += 1
         assert steps < 120
-    if kd == np.uint64:
+    if kd is not None:  # both key widths give the reference test's known answer
         assert _octant_node_count(_keys_np(gt.tree_leaves(), kd), kd) == ref_counts
     # node arrays are consistent: root count = all particles, marks only outside of nothing-but-the-focus
     prefixes, child_offsets, counts, macs = gt.node_arrays()
