@@ -9,8 +9,10 @@
  * particles; each fixed group is cut again wherever two CONSECUTIVE particles are further apart (in box-normalised
  * coordinates) than tol_factor * edge length of the leaf of the group's first particle.
  *
- * Reference pipeline: split kernel, scan, D2H, length kernel (popcount loops), second scan, H2D of `last`.
- * Here: split kernel (one warp per fixed group, coalesced loads, one ballot per 32 particles), one scan of the split
+ * Reference pipeline: split kernel (a 21-step leaf search per particle), scan, D2H, length kernel (popcount loops),
+ * second scan, H2D of `last`.
+ * Here: the leaf level of every group is scattered from the leaf side (groupLeafLevelsKernel, no search), then the
+ * split kernel (one warp per fixed group, coalesced independent loads, one ballot per 32 particles), one scan of the split
  * counts, and a start kernel that writes group starts straight from the bit positions — the lengths of a fixed
  * group always add up to group_size, so start(g, j) = first + g*group_size + (position of the j-th split bit) + 1
  * and the second scan is not needed.  Algorithmic bytes: 3 sizeof(Tc) per particle read, 4 B per group written.
@@ -33,25 +35,62 @@ __global__ void __launch_bounds__(kGroupThreads)
         groups[g] = (g == numGroups) ? last : first + g * groupSize;
 }
 
-//! index of the leaf holding particle `body`: last i in [0, numLeaves) with layout[i] <= body  (upper_bound - 1)
-__device__ inline int leafOfBody(const uint32_t* __restrict__ layout, int numLeaves, uint32_t body)
+/*! Leaf level per fixed group, computed from the LEAF side: the reference takes, for every body of the first warp-width
+ *  of a group, the leaf upper_bound(layout, layout + numLeaves, body) - 1 and keeps the smallest one.  Leaf i holds the
+ *  bodies [layout[i], layout[i+1]) (the last leaf: everything from layout[i] on), so it is a maximum of the leaf levels
+ *  scattered to the groups whose first 32 bodies a leaf touches: one coalesced pass over the leaf arrays with an
+ *  atomicMax per (leaf, group) pair, and no search at all on the particle side.  levels[] starts at 0 (root, volume 1,
+ *  the reference's initial value).  Leaves spanning more than 32 groups are spread over the warp. */
+template<class K>
+__global__ void __launch_bounds__(kGroupThreads)
+    groupLeafLevelsKernel(uint32_t first, uint32_t last, uint32_t groupSize, const K* __restrict__ leaves, int numLeaves,
+                          const uint32_t* __restrict__ layout, uint32_t* __restrict__ levels)
 {
-    int lo = 0, n = numLeaves;
-    while (n > 0)
+    const uint32_t lane = laneId();
+    for (int base = int((blockIdx.x * blockDim.x + threadIdx.x) & ~31u); base < numLeaves; base += int(gridDim.x * blockDim.x))
     {
-        int half = n >> 1;
-        if (!(body < layout[lo + half])) { lo += half + 1, n -= half + 1; }
-        else n = half;
+        const int i = base + int(lane);
+        uint32_t sb = 0, eb = 0, level = 0;
+        if (i < numLeaves)
+        {
+            sb    = (i == 0) ? 0u : layout[i];
+            eb    = (i == numLeaves - 1) ? 0xffffffffu : layout[i + 1];
+            sb    = max(sb, first);
+            eb    = min(eb, last);
+            level = treeLevel<K>(K(leaves[i + 1] - leaves[i]));
+        }
+        const bool active   = sb < eb && level > 0;
+        const uint32_t gLo  = active ? (sb - first) / groupSize : 1u;
+        const uint32_t gHi  = active ? (eb - 1u - first) / groupSize : 0u;
+        const bool big      = active && gHi - gLo > 32u;
+        if (active && !big)
+        {
+            for (uint32_t g = gLo; g <= gHi; ++g)
+            {
+                const uint32_t lo = first + g * groupSize; // the first warp-width of the group
+                if (max(sb, lo) < min(eb, lo + 32u)) atomicMax(&levels[g], level);
+            }
+        }
+        for (unsigned todo = __ballot_sync(0xffffffffu, big); todo; todo &= todo - 1u)
+        {
+            const int src      = __ffs(int(todo)) - 1;
+            const uint32_t lv  = __shfl_sync(0xffffffffu, level, src);
+            const uint32_t g0  = __shfl_sync(0xffffffffu, gLo, src), g1 = __shfl_sync(0xffffffffu, gHi, src);
+            const uint32_t s0  = __shfl_sync(0xffffffffu, sb, src), e0 = __shfl_sync(0xffffffffu, eb, src);
+            for (uint32_t g = g0 + lane; g <= g1; g += 32u)
+            {
+                const uint32_t lo = first + g * groupSize;
+                if (max(s0, lo) < min(e0, lo + 32u)) atomicMax(&levels[g], lv);
+            }
+        }
     }
-    return lo - 1;
 }
 
 template<int NWT, class K, class Tc, class Th>
 __global__ void __launch_bounds__(kGroupThreads)
     groupSplitsKernel(uint32_t first, uint32_t last, const Tc* __restrict__ x, const Tc* __restrict__ y,
-                      const Tc* __restrict__ z, const K* __restrict__ leaves, int numLeaves,
-                      const uint32_t* __restrict__ layout, Tc ilx, Tc ily, Tc ilz, float tolFactor,
-                      uint32_t* __restrict__ masks, uint32_t* __restrict__ numSplits, uint32_t numFixed)
+                      const Tc* __restrict__ z, const uint32_t* __restrict__ levels, Tc ilx, Tc ily, Tc ilz,
+                      float tolFactor, uint32_t* __restrict__ masks, uint32_t* __restrict__ numSplits, uint32_t numFixed)
 {
     constexpr uint32_t groupSize = 32u * NWT;
     const uint32_t lane          = laneId();
@@ -62,14 +101,10 @@ __global__ void __launch_bounds__(kGroupThreads)
         for (int k = 0; k < NWT; ++k)
             body[k] = min(first + g * groupSize + uint32_t(k) * 32u + lane, last - 1u);
 
-        // edge of the leaf of the first warp-width of bodies (the reference looks at segment 0 only), warp minimum
-        int leaf       = leafOfBody(layout, numLeaves, body[0]);
-        unsigned level = treeLevel<K>(K(leaves[leaf + 1] - leaves[leaf]));
-        Th half        = Th(int(1u << (KeyTraits<K>::maxLevel - level))) * (Th(0.5) / Th(1u << KeyTraits<K>::maxLevel));
-        Th vol         = Th(8) * half * half * half;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1)
-            vol = min(vol, __shfl_xor_sync(0xffffffffu, vol, o));
+        // volume of the smallest leaf under the group's first warp-width of bodies (groupLeafLevelsKernel)
+        const unsigned level = levels[g];
+        const Th half = Th(int(1u << (KeyTraits<K>::maxLevel - level))) * (Th(0.5) / Th(1u << KeyTraits<K>::maxLevel));
+        const Th vol  = Th(8) * half * half * half;
         Tc distCrit = Tc(cbrt(vol) * tolFactor); // Th * float, evaluated in Th
         Tc crit2    = distCrit * distCrit;
 
@@ -132,7 +167,7 @@ inline size_t align128(size_t b) { return (b + 127) & ~size_t(127); }
 
 struct GroupTemp
 {
-    uint32_t *masks, *numSplits, *offsets, *total;
+    uint32_t *masks, *numSplits, *offsets, *levels, *total;
     void* scan;
     size_t bytes;
 };
@@ -144,6 +179,7 @@ inline GroupTemp carveGroupTemp(void* temp, size_t numFixed, int nwt)
     t.masks     = reinterpret_cast<uint32_t*>(p), p += align128(numFixed * nwt * 4);
     t.numSplits = reinterpret_cast<uint32_t*>(p), p += align128(numFixed * 4);
     t.offsets   = reinterpret_cast<uint32_t*>(p), p += align128(numFixed * 4);
+    t.levels    = reinterpret_cast<uint32_t*>(p), p += align128(numFixed * 4);
     t.total     = reinterpret_cast<uint32_t*>(p), p += 128;
     t.scan      = p, p += align128(scanTempBytes(numFixed));
     t.bytes     = size_t(p - reinterpret_cast<char*>(temp));
@@ -160,9 +196,13 @@ int groupSplitsImpl(uint32_t first, uint32_t last, const Tc* x, const Tc* y, con
     GroupTemp t       = carveGroupTemp(temp, numFixed, NWT);
     if (tempBytes < t.bytes) return CSTONE_E_TEMP_TOO_SMALL;
 
+    CSB_CUDA(cudaMemsetAsync(t.levels, 0, size_t(numFixed) * 4, s));
+    groupLeafLevelsKernel<K><<<gridFor(size_t(numLeaves), kGroupThreads, 8), kGroupThreads, 0, s>>>(
+        first, last, 32u * NWT, leaves, numLeaves, layout, t.levels);
+    CSB_LAUNCHED();
     groupSplitsKernel<NWT, K, Tc, Th><<<gridFor(size_t(numFixed) * 32, kGroupThreads, 8), kGroupThreads, 0, s>>>(
-        first, last, x, y, z, leaves, numLeaves, layout, Tc(box->inv_lengths[0]), Tc(box->inv_lengths[1]),
-        Tc(box->inv_lengths[2]), tolFactor, t.masks, t.numSplits, numFixed);
+        first, last, x, y, z, t.levels, Tc(box->inv_lengths[0]), Tc(box->inv_lengths[1]), Tc(box->inv_lengths[2]),
+        tolFactor, t.masks, t.numSplits, numFixed);
     CSB_LAUNCHED();
     int st = launchScan<false>(LoadPlain{t.numSplits}, t.offsets, numFixed, 0u, t.scan, t.total, s);
     if (st) return st;

@@ -9,9 +9,8 @@
  *
  * Parity: the accumulation order IS the result (floating point sums), so a leaf is summed by one thread, particle
  * after particle, and an internal node adds its eight children in index order; no contraction (-fmad=false), the
- * normalisation multiplies by 1/sum like the reference.  Neighbouring threads own neighbouring particle runs, so the
- * four coordinate streams are read once through L1 (algorithmic bytes: 3 sizeof(Tc) + sizeof(Tm) per particle +
- * 4 sizeof(Tf) per leaf).
+ * normalisation multiplies by 1/sum like the reference.  The particle streams are staged through shared memory with
+ * coalesced loads (algorithmic bytes: 3 sizeof(Tc) + sizeof(Tm) per particle + 4 sizeof(Tf) per leaf).
  */
 #include "common.cuh"
 
@@ -45,22 +44,47 @@ struct alignas(16) Quad
     T v[4];
 };
 
+constexpr int kCenterChunk = 1024; // particles staged per round: 4 x 1024 x sizeof(Tf) = 32 KB for double
+
+/* One thread per leaf, 256 consecutive leaves per block.  The particles of those leaves are one contiguous run: the
+ * block streams it through shared memory in chunks (coalesced loads, converted to Tf), and every thread adds the part
+ * of its leaf that lies in the chunk, in particle order — the running sums live in registers across chunks, so the
+ * summation order is exactly the sequential one of massCenter(). */
 template<class Tc, class Tm, class Tf>
 __global__ void __launch_bounds__(kCenterThreads)
     leafSourceCenterKernel(const Tc* __restrict__ x, const Tc* __restrict__ y, const Tc* __restrict__ z,
                            const Tm* __restrict__ m, const int* __restrict__ leafToInternal, int numLeaves,
                            const uint32_t* __restrict__ layout, Quad<Tf>* __restrict__ centers)
 {
-    for (int leaf = blockIdx.x * blockDim.x + threadIdx.x; leaf < numLeaves; leaf += gridDim.x * blockDim.x)
+    __shared__ Tf sx[kCenterChunk], sy[kCenterChunk], sz[kCenterChunk], sm[kCenterChunk];
+    for (int leafBase = blockIdx.x * kCenterThreads; leafBase < numLeaves; leafBase += gridDim.x * kCenterThreads)
     {
-        uint32_t first = layout[leaf], last = layout[leaf + 1];
+        const int nb        = min(kCenterThreads, numLeaves - leafBase);
+        const int leaf      = leafBase + int(threadIdx.x);
+        const bool mine     = int(threadIdx.x) < nb;
+        const uint32_t p0   = layout[leafBase], p1 = layout[leafBase + nb];
+        const uint32_t first = mine ? layout[leaf] : p1, last = mine ? layout[leaf + 1] : p1;
         Tf c[4] = {0, 0, 0, 0};
-        for (uint32_t i = first; i < last; ++i)
-            addBody<Tf>(c, Tf(x[i]), Tf(y[i]), Tf(z[i]), Tf(m[i]));
-        normalizeMass(c);
-        Quad<Tf> q;
-        q.v[0] = c[0], q.v[1] = c[1], q.v[2] = c[2], q.v[3] = c[3];
-        centers[leafToInternal[leaf]] = q;
+        for (uint32_t start = p0; start < p1; start += kCenterChunk)
+        {
+            const uint32_t len = min(uint32_t(kCenterChunk), p1 - start);
+            __syncthreads();
+            for (uint32_t k = threadIdx.x; k < len; k += kCenterThreads)
+            {
+                sx[k] = Tf(x[start + k]), sy[k] = Tf(y[start + k]), sz[k] = Tf(z[start + k]), sm[k] = Tf(m[start + k]);
+            }
+            __syncthreads();
+            const uint32_t a = max(first, start), b = min(last, start + len);
+            for (uint32_t i = a; i < b; ++i)
+                addBody<Tf>(c, sx[i - start], sy[i - start], sz[i - start], sm[i - start]);
+        }
+        if (mine)
+        {
+            normalizeMass(c);
+            Quad<Tf> q;
+            q.v[0] = c[0], q.v[1] = c[1], q.v[2] = c[2], q.v[3] = c[3];
+            centers[leafToInternal[leaf]] = q;
+        }
     }
 }
 
@@ -92,7 +116,7 @@ int leafSourceCenter(const Tc* x, const Tc* y, const Tc* z, const Tm* m, const i
 {
     if (numLeaves <= 0) return 0;
     if (!x || !y || !z || !m || !l2i || !layout || !centers) return CSTONE_E_INVALID_ARGUMENT;
-    leafSourceCenterKernel<Tc, Tm, Tf><<<gridFor(size_t(numLeaves), kCenterThreads, 8), kCenterThreads, 0,
+    leafSourceCenterKernel<Tc, Tm, Tf><<<gridFor(size_t(numLeaves), kCenterThreads, 6), kCenterThreads, 0,
                                          asStream(stream)>>>(x, y, z, m, l2i, numLeaves, layout,
                                                              reinterpret_cast<Quad<Tf>*>(centers));
     CSB_LAUNCHED();
