@@ -44,42 +44,52 @@ struct alignas(16) Quad
     T v[4];
 };
 
+constexpr int kLeafThreads = 256;  // leaves per block
 constexpr int kCenterChunk = 1024; // particles staged per round: 4 x 1024 x sizeof(Tf) = 32 KB for double
 
 /* One thread per leaf, 256 consecutive leaves per block.  The particles of those leaves are one contiguous run: the
- * block streams it through shared memory in chunks (coalesced loads, converted to Tf), and every thread adds the part
- * of its leaf that lies in the chunk, in particle order — the running sums live in registers across chunks, so the
- * summation order is exactly the sequential one of massCenter(). */
+ * block streams it through shared memory in chunks (coalesced loads; the products |m| x, |m| y, |m| z are formed
+ * there, by all threads), and every thread adds the part of its leaf that lies in the chunk, in particle order — the
+ * running sums live in registers across chunks, so the summation order is exactly the sequential one of massCenter()
+ * and every product / sum is the same IEEE operation (no contraction). */
 template<class Tc, class Tm, class Tf>
-__global__ void __launch_bounds__(kCenterThreads)
+__global__ void __launch_bounds__(kLeafThreads)
     leafSourceCenterKernel(const Tc* __restrict__ x, const Tc* __restrict__ y, const Tc* __restrict__ z,
                            const Tm* __restrict__ m, const int* __restrict__ leafToInternal, int numLeaves,
                            const uint32_t* __restrict__ layout, Quad<Tf>* __restrict__ centers)
 {
-    __shared__ Tf sx[kCenterChunk], sy[kCenterChunk], sz[kCenterChunk], sm[kCenterChunk];
-    for (int leafBase = blockIdx.x * kCenterThreads; leafBase < numLeaves; leafBase += gridDim.x * kCenterThreads)
+    extern __shared__ __align__(16) unsigned char sRaw[];
+    Tf* sx = reinterpret_cast<Tf*>(sRaw);
+    Tf* sy = sx + kCenterChunk;
+    Tf* sz = sy + kCenterChunk;
+    Tf* sw = sz + kCenterChunk;
+    for (int leafBase = blockIdx.x * kLeafThreads; leafBase < numLeaves; leafBase += gridDim.x * kLeafThreads)
     {
-        const int nb        = min(kCenterThreads, numLeaves - leafBase);
-        const int leaf      = leafBase + int(threadIdx.x);
-        const bool mine     = int(threadIdx.x) < nb;
-        const uint32_t p0   = layout[leafBase], p1 = layout[leafBase + nb];
+        const int nb         = min(kLeafThreads, numLeaves - leafBase);
+        const int leaf       = leafBase + int(threadIdx.x);
+        const bool mine      = int(threadIdx.x) < nb;
+        const uint32_t p0    = layout[leafBase], p1 = layout[leafBase + nb];
         const uint32_t first = mine ? layout[leaf] : p1, last = mine ? layout[leaf + 1] : p1;
-        Tf c[4] = {0, 0, 0, 0};
+        Tf c0 = 0, c1 = 0, c2 = 0, c3 = 0;
         for (uint32_t start = p0; start < p1; start += kCenterChunk)
         {
             const uint32_t len = min(uint32_t(kCenterChunk), p1 - start);
             __syncthreads();
-            for (uint32_t k = threadIdx.x; k < len; k += kCenterThreads)
+            for (uint32_t k = threadIdx.x; k < len; k += kLeafThreads)
             {
-                sx[k] = Tf(x[start + k]), sy[k] = Tf(y[start + k]), sz[k] = Tf(z[start + k]), sm[k] = Tf(m[start + k]);
+                const Tf w = fabs(Tf(m[start + k]));
+                sx[k] = w * Tf(x[start + k]), sy[k] = w * Tf(y[start + k]), sz[k] = w * Tf(z[start + k]), sw[k] = w;
             }
             __syncthreads();
             const uint32_t a = max(first, start), b = min(last, start + len);
             for (uint32_t i = a; i < b; ++i)
-                addBody<Tf>(c, sx[i - start], sy[i - start], sz[i - start], sm[i - start]);
+            {
+                c0 += sx[i - start], c1 += sy[i - start], c2 += sz[i - start], c3 += sw[i - start];
+            }
         }
         if (mine)
         {
+            Tf c[4] = {c0, c1, c2, c3};
             normalizeMass(c);
             Quad<Tf> q;
             q.v[0] = c[0], q.v[1] = c[1], q.v[2] = c[2], q.v[3] = c[3];
@@ -116,7 +126,13 @@ int leafSourceCenter(const Tc* x, const Tc* y, const Tc* z, const Tm* m, const i
 {
     if (numLeaves <= 0) return 0;
     if (!x || !y || !z || !m || !l2i || !layout || !centers) return CSTONE_E_INVALID_ARGUMENT;
-    leafSourceCenterKernel<Tc, Tm, Tf><<<gridFor(size_t(numLeaves), kCenterThreads, 6), kCenterThreads, 0,
+    constexpr int smem = 4 * kCenterChunk * int(sizeof(Tf));
+    static bool attr   = [] {
+        return cudaFuncSetAttribute(leafSourceCenterKernel<Tc, Tm, Tf>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    smem) == cudaSuccess;
+    }();
+    if (!attr) return int(cudaErrorInvalidValue);
+    leafSourceCenterKernel<Tc, Tm, Tf><<<gridFor(size_t(numLeaves), kLeafThreads, 6), kLeafThreads, smem,
                                          asStream(stream)>>>(x, y, z, m, l2i, numLeaves, layout,
                                                              reinterpret_cast<Quad<Tf>*>(centers));
     CSB_LAUNCHED();
