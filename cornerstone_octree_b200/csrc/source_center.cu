@@ -50,7 +50,8 @@ constexpr int kCenterChunk = 1024; // particles staged per round: 4 x 1024 x siz
 /* One thread per leaf, 256 consecutive leaves per block.  The particles of those leaves are one contiguous run: the
  * block streams it through shared memory in chunks (coalesced loads; the products |m| x, |m| y, |m| z are formed
  * there, by all threads), and every thread adds the part of its leaf that lies in the chunk, in particle order — the
- * running sums live in registers across chunks, so the summation order is exactly the sequential one of massCenter()
+ * running sums live in registers across chunks (and the next chunk is already in flight to registers while this one
+ * is summed), so the summation order is exactly the sequential one of massCenter()
  * and every product / sum is the same IEEE operation (no contraction). */
 template<class Tc, class Tm, class Tf>
 __global__ void __launch_bounds__(kLeafThreads)
@@ -71,16 +72,36 @@ __global__ void __launch_bounds__(kLeafThreads)
         const uint32_t p0    = layout[leafBase], p1 = layout[leafBase + nb];
         const uint32_t first = mine ? layout[leaf] : p1, last = mine ? layout[leaf + 1] : p1;
         Tf c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+        // register-staged pipeline: the loads of chunk k+1 are in flight while the leaves of chunk k are summed
+        constexpr int kPer = kCenterChunk / kLeafThreads;
+        Tc rx[kPer], ry[kPer], rz[kPer];
+        Tm rm[kPer];
+        auto fetch = [&](uint32_t start)
+        {
+#pragma unroll
+            for (int j = 0; j < kPer; ++j)
+            {
+                const uint32_t k = start + threadIdx.x + uint32_t(j) * kLeafThreads;
+                if (k < p1) { rx[j] = x[k], ry[j] = y[k], rz[j] = z[k], rm[j] = m[k]; }
+            }
+        };
+        if (p0 < p1) fetch(p0);
         for (uint32_t start = p0; start < p1; start += kCenterChunk)
         {
             const uint32_t len = min(uint32_t(kCenterChunk), p1 - start);
             __syncthreads();
-            for (uint32_t k = threadIdx.x; k < len; k += kLeafThreads)
+#pragma unroll
+            for (int j = 0; j < kPer; ++j)
             {
-                const Tf w = fabs(Tf(m[start + k]));
-                sx[k] = w * Tf(x[start + k]), sy[k] = w * Tf(y[start + k]), sz[k] = w * Tf(z[start + k]), sw[k] = w;
+                const uint32_t k = threadIdx.x + uint32_t(j) * kLeafThreads;
+                if (k < len)
+                {
+                    const Tf w = fabs(Tf(rm[j]));
+                    sx[k] = w * Tf(rx[j]), sy[k] = w * Tf(ry[j]), sz[k] = w * Tf(rz[j]), sw[k] = w;
+                }
             }
             __syncthreads();
+            if (start + kCenterChunk < p1) fetch(start + kCenterChunk);
             const uint32_t a = max(first, start), b = min(last, start + len);
             for (uint32_t i = a; i < b; ++i)
             {
