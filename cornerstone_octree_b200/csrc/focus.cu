@@ -283,7 +283,8 @@ __global__ void __launch_bounds__(kFocusThreads) moveCentersKernel(const T* __re
  * one round trip per opened node: prefixes, centres and child offsets of the eight siblings; the child offset rides on
  * the stack).  Nodes fully inside the focus end the descent; every node that fails the MAC w.r.t. a leaf
  * (evaluateMacPbc, exact expression, no contraction) is marked and opened.  Stack depth <= 7 per level + 8.
- * Measured alternatives (profiles/r01h): thread per leaf 1.34 ms, union walk without the batched loads 2.10 ms,
+ * Measured alternatives (profiles/r01h): eight warps sharing one group of 32 leaves (subtrees of level 3 dealt to the
+ * warps) 1.31 ms, thread per leaf 1.34 ms, union walk without the batched loads 2.10 ms,
  * leaves with work packed densely per block first 2.02 ms (fewer, longer walks: the critical path grows). */
 constexpr int kMarkThreads = 128;
 constexpr int kMarkStack   = 160;
@@ -341,7 +342,7 @@ __global__ void __launch_bounds__(kMarkThreads)
             for (int d = 0; d < 3; ++d)
             {
                 T dx = tc[d] - c[d];
-                dx -= T(box.pbc[d]) * box.len[d] * rint(dx * box.ilen[d]);
+                if (box.pbc[d]) dx -= box.len[d] * rint(dx * box.ilen[d]); // open axis: the fold term is an exact 0
                 dx = fabs(dx);
                 dx -= ts[d];
                 dx += fabs(dx);
