@@ -275,19 +275,48 @@ __global__ void __launch_bounds__(kFocusThreads) moveCentersKernel(const T* __re
 }
 
 // ------------------------------------------------------------------------------------------------ markMacs
-/* One WARP per 32 consecutive focus leaves, one lane per leaf.  The reference walks the tree once per focus leaf
- * [traversal/macs.hpp:196-269]; neighbouring leaves open almost the same nodes, so here the warp walks the UNION of the
- * 32 walks once, with a shared stack of (first child, lane mask) entries: a lane takes part in the test of a node only
- * if it failed the MAC at every ancestor, exactly as in its own walk, so the set of marked nodes is the reference's.
- * The walk is a chain of dependent loads, so the eight children of a node are fetched together (uniform addresses,
- * one round trip per opened node: prefixes, centres and child offsets of the eight siblings; the child offset rides on
- * the stack).  Nodes fully inside the focus end the descent; every node that fails the MAC w.r.t. a leaf
- * (evaluateMacPbc, exact expression, no contraction) is marked and opened.  Stack depth <= 7 per level + 8.
- * Measured alternatives (profiles/r01h): eight warps sharing one group of 32 leaves (subtrees of level 3 dealt to the
- * warps) 1.31 ms, thread per leaf 1.34 ms, union walk without the batched loads 2.10 ms,
- * leaves with work packed densely per block first 2.02 ms (fewer, longer walks: the critical path grows). */
-constexpr int kMarkThreads = 128;
+/* One BLOCK (8 warps) per 32 consecutive focus leaves, one lane per leaf.  The reference walks the tree once per focus
+ * leaf [traversal/macs.hpp:196-269]; neighbouring leaves open almost the same nodes, so here the UNION of the 32 walks
+ * is walked once, with stack entries (first child, lane mask): a lane takes part in the test of a node only if it
+ * failed the MAC at every ancestor, exactly as in its own walk, so the set of marked nodes is the reference's.
+ * A leaf near the focus surface opens ~2000 nodes, a long serial chain (ncu of the one-warp version: 10 % of the warp
+ * slots active, SMs idle 42 % of the time): the eight warps of the block share the walk through a small pool in shared
+ * memory — a busy warp hands surplus stack entries to the pool while it is low, an idle warp takes one, the round ends
+ * when the pool is empty and no warp is busy (counter under a shared-memory lock).
+ * The eight children of a node are fetched together (uniform addresses, one round trip per opened node: prefixes,
+ * centres and child offsets of the eight siblings; the child offset rides on the stack).  Nodes fully inside the focus
+ * end the descent; every node that fails the MAC w.r.t. a leaf (evaluateMacPbc, exact expression, no contraction) is
+ * marked and opened.  Private stack depth <= 7 per level + 8.
+ * Measured (32 M particles, focus = 262144 leaves, profiles/r01h): thread per leaf (the reference's scheme) 1.34 ms,
+ * one warp per 32 leaves 0.99 ms (without the batched loads 2.10), leaves with work packed densely per block first
+ * 2.02 ms, subtrees of level 3 dealt statically to 8 warps 1.31 ms, this version 0.63 ms. */
+constexpr int kMarkThreads = 256; // 8 warps share the walk of one group of 32 focus leaves
+constexpr int kMarkWarps   = kMarkThreads / 32;
 constexpr int kMarkStack   = 160;
+constexpr int kMarkPool    = 64;  // shared pool of open nodes, filled by busy warps, drained by idle ones
+
+template<class T>
+struct MarkShared
+{
+    int2 stack[kMarkWarps][kMarkStack];
+    int2 pool[kMarkPool];
+    T tc[3][32], ts[3][32];
+    unsigned maxLevel[32];
+    unsigned aliveMask;
+    int lock, poolCount, active;
+};
+
+__device__ inline void markLock(int* lock)
+{
+    while (atomicCAS(lock, 0, 1) != 0)
+        __nanosleep(64);
+    __threadfence_block();
+}
+__device__ inline void markUnlock(int* lock)
+{
+    __threadfence_block();
+    atomicExch(lock, 0);
+}
 
 template<class K, class T>
 __global__ void __launch_bounds__(kMarkThreads)
@@ -295,39 +324,56 @@ __global__ void __launch_bounds__(kMarkThreads)
                    const K* __restrict__ prefixes, const int* __restrict__ childOffsets, const T* __restrict__ centers,
                    DBox<T> box, const K* __restrict__ focusNodes, int numFocusNodes, int limitSource, char* markings)
 {
-    __shared__ int2 sStack[kMarkThreads / 32][kMarkStack];
-    int2* stack = sStack[threadIdx.x >> 5];
+    __shared__ MarkShared<T> sh;
+    const int warp      = int(threadIdx.x >> 5);
+    const unsigned lane = laneId();
+    int2* stack         = sh.stack[warp];
 
     constexpr int maxCoord = 1 << KeyTraits<K>::maxLevel;
     const T uL             = T(1.) / T(maxCoord);
     const K focusStart = focusNodes[0], focusEnd = focusNodes[numFocusNodes];
-    const unsigned lane = laneId();
-    for (int base = int((blockIdx.x * blockDim.x + threadIdx.x) & ~31u); base < numFocusNodes;
-         base += int(gridDim.x * blockDim.x))
+    for (int base = int(blockIdx.x) * 32; base < numFocusNodes; base += int(gridDim.x) * 32)
     {
-        const int i = base + int(lane);
-        bool alive  = i < numFocusNodes;
-        T tc[3] = {0, 0, 0}, ts[3] = {0, 0, 0};
-        unsigned maxLevel = KeyTraits<K>::maxLevel;
-        if (alive)
+        // ---- warp 0: the 32 targets of this block round (centre, size, deepest source level, has work at all)
+        __syncthreads();
+        if (warp == 0)
         {
-            const K a = focusNodes[i], b = focusNodes[i + 1];
-            const unsigned tl = treeLevel<K>(K(b - a));
-            const IBox target = sfcIBox<K>(kind, dec, a, tl);
-            IBox ext;
-#pragma unroll
-            for (int d = 0; d < 3; ++d)
-                ext.lo[d] = target.lo[d] - 1, ext.hi[d] = target.hi[d] + 1;
-            alive = !containedIn<K>(kind, enc, focusStart, focusEnd, ext);
-#pragma unroll
-            for (int d = 0; d < 3; ++d)
+            const int i = base + int(lane);
+            bool alive  = i < numFocusNodes;
+            T c[3] = {0, 0, 0}, sz[3] = {0, 0, 0};
+            unsigned ml = KeyTraits<K>::maxLevel;
+            if (alive)
             {
-                const T halfUnit = T(0.5) * uL * box.len[d];
-                tc[d]            = box.lo[d] + T(target.hi[d] + target.lo[d]) * halfUnit;
-                ts[d]            = T(target.hi[d] - target.lo[d]) * halfUnit;
+                const K a = focusNodes[i], b = focusNodes[i + 1];
+                const unsigned tl = treeLevel<K>(K(b - a));
+                const IBox target = sfcIBox<K>(kind, dec, a, tl);
+                IBox ext;
+#pragma unroll
+                for (int d = 0; d < 3; ++d)
+                    ext.lo[d] = target.lo[d] - 1, ext.hi[d] = target.hi[d] + 1;
+                alive = !containedIn<K>(kind, enc, focusStart, focusEnd, ext);
+#pragma unroll
+                for (int d = 0; d < 3; ++d)
+                {
+                    const T halfUnit = T(0.5) * uL * box.len[d];
+                    c[d]             = box.lo[d] + T(target.hi[d] + target.lo[d]) * halfUnit;
+                    sz[d]            = T(target.hi[d] - target.lo[d]) * halfUnit;
+                }
+                if (limitSource) ml = unsigned(max(int(tl) - 1, 0));
             }
-            if (limitSource) maxLevel = unsigned(max(int(tl) - 1, 0));
+#pragma unroll
+            for (int d = 0; d < 3; ++d)
+                sh.tc[d][lane] = c[d], sh.ts[d][lane] = sz[d];
+            sh.maxLevel[lane]    = ml;
+            const unsigned amask = __ballot_sync(0xffffffffu, alive);
+            if (lane == 0) sh.aliveMask = amask, sh.lock = 0, sh.poolCount = 0, sh.active = 1;
         }
+        __syncthreads();
+        const unsigned aliveMask = sh.aliveMask;
+        if (aliveMask == 0) continue; // block-uniform
+        const T tc[3] = {sh.tc[0][lane], sh.tc[1][lane], sh.tc[2][lane]};
+        const T ts[3] = {sh.ts[0][lane], sh.ts[1][lane], sh.ts[2][lane]};
+        const unsigned maxLevel = sh.maxLevel[lane];
 
         // lanes of `mask` test a node given by its prefix, centre and MAC; returns the lanes that fail the MAC
         auto check = [&](K prefix, T cx, T cy, T cz, T mac, unsigned mask) -> unsigned
@@ -354,16 +400,76 @@ __global__ void __launch_bounds__(kMarkThreads)
             return __ballot_sync(0xffffffffu, violates);
         };
 
-        const unsigned rootFail =
-            check(prefixes[0], centers[0], centers[1], centers[2], centers[3], __ballot_sync(0xffffffffu, alive));
-        if (!rootFail) continue;
-        if (lane == 0 && !markings[0]) markings[0] = 1;
-        int first = childOffsets[0];
-        if (first == 0) continue;
+        // ---- warp 0 opens the root; the other warps start idle and take work from the pool
         int sp        = 0;
-        unsigned mask = rootFail;
+        bool busy     = false;
+        if (warp == 0)
+        {
+            const unsigned rootFail = check(prefixes[0], centers[0], centers[1], centers[2], centers[3], aliveMask);
+            const int first         = childOffsets[0];
+            if (rootFail && lane == 0 && !markings[0]) markings[0] = 1;
+            if (rootFail && first != 0)
+            {
+                if (lane == 0) stack[0] = make_int2(first, int(rootFail));
+                sp   = 1;
+                busy = true;
+            }
+            if (!busy)
+            {
+                if (lane == 0)
+                {
+                    markLock(&sh.lock);
+                    sh.active = 0;
+                    markUnlock(&sh.lock);
+                }
+            }
+        }
+        __syncwarp();
         while (true)
         {
+            if (sp == 0)
+            {
+                // out of private work: take an entry from the pool, or leave when nobody can produce any more
+                int2 e   = make_int2(0, 0);
+                int state = 0; // 0 retry, 1 got work, 2 done
+                if (lane == 0)
+                {
+                    markLock(&sh.lock);
+                    if (busy) sh.active -= 1;
+                    if (sh.poolCount > 0)
+                    {
+                        e = sh.pool[--sh.poolCount];
+                        sh.active += 1;
+                        state = 1;
+                    }
+                    else if (sh.active == 0) { state = 2; }
+                    markUnlock(&sh.lock);
+                }
+                busy  = false;
+                state = __shfl_sync(0xffffffffu, state, 0);
+                if (state == 2) break;
+                if (state == 0)
+                {
+                    __nanosleep(200);
+                    continue;
+                }
+                e.x = __shfl_sync(0xffffffffu, e.x, 0), e.y = __shfl_sync(0xffffffffu, e.y, 0);
+                if (lane == 0) stack[0] = e;
+                sp   = 1;
+                busy = true;
+                __syncwarp();
+            }
+            const int2 e        = stack[--sp];
+            __syncwarp();
+            const int first     = e.x;
+            const unsigned mask = unsigned(e.y);
+#ifdef CSB_MARK_DEBUG
+            if (first <= 0 || first > (1 << 26))
+            {
+                if (lane == 0) printf("markMacs bad entry: block %d warp %d sp %d first %d mask %08x pool %d active %d\n", blockIdx.x, warp, sp, first, mask, sh.poolCount, sh.active);
+                break;
+            }
+#endif
             // the eight children: all loads first (uniform addresses, independent), then the tests
             K cp[8];
             T cc[8][4];
@@ -391,11 +497,27 @@ __global__ void __launch_bounds__(kMarkThreads)
                     }
                 }
             }
-            if (sp == 0) break;
             __syncwarp();
-            const int2 e = stack[--sp];
-            __syncwarp();
-            first = e.x, mask = unsigned(e.y);
+            // share: keep one entry, hand the rest of the surplus to idle warps while the pool is low
+            // (the pool level is read by lane 0 and broadcast: the lanes must agree on the branch)
+            const int poolNow = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile int*>(&sh.poolCount), 0);
+            if (sp >= 2 && poolNow < kMarkWarps)
+            {
+                int give = 0;
+                if (lane == 0)
+                {
+                    markLock(&sh.lock);
+                    give = min(sp - 1, kMarkPool - sh.poolCount);
+                    give = min(give, 2 * kMarkWarps - sh.poolCount);
+                    give = max(give, 0);
+                    for (int k = 0; k < give; ++k)
+                        sh.pool[sh.poolCount++] = stack[sp - 1 - k]; // from the top: only lane 0 touches the stack
+                    markUnlock(&sh.lock);
+                }
+                give = __shfl_sync(0xffffffffu, give, 0);
+                sp -= give;
+                __syncwarp();
+            }
         }
     }
 }
@@ -525,7 +647,7 @@ CSB_FOCUS_API(k64, uint64_t)
         SfcTables tabs;                                                                                                \
         int st = getSfcTables(&tabs);                                                                                  \
         if (st) return st;                                                                                             \
-        markMacsKernel<K, T><<<gridFor(size_t(numFocusNodes), kMarkThreads, 8), kMarkThreads, 0, asStream(stream)>>>(                    \
+        markMacsKernel<K, T><<<gridFor(size_t(numFocusNodes) * kMarkWarps, kMarkThreads, 8), kMarkThreads, 0, asStream(stream)>>>(                    \
             kind, tabs.enc, tabs.dec, prefixes, childOffsets, centers4, makeDBox<T>(box), focusNodes, numFocusNodes,   \
             limitSource, markings);                                                                                    \
         CSB_LAUNCHED();                                                                                                \
