@@ -4,6 +4,7 @@ travel with their particles, neighbour lists equal the oracle's.  The multi-rank
 tools/domain_ranks.py under torchrun (2 GPUs) and, for the host logic, by tests/test_domain_host.py on the CPU."""
 import numpy as np
 import pytest
+import torch
 
 import gen
 from oracle import loader
@@ -85,3 +86,20 @@ def test_bucket_precondition():
     from cornerstone_octree_b200.domain import Domain
     with pytest.raises(RuntimeError):
         Domain(0, 1, 8, 16)
+
+
+def test_two_rank_domain_matches_global_search():
+    """tools/domain_ranks.py under torchrun on 2 GPUs: conservation, SFC order and ranges, neighbour lists of every
+    assigned particle equal to a single global search by the CPU oracle (halos sufficient), exchange_halos values,
+    a second sync after a displacement.  Skipped on a 1-GPU box."""
+    import os
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29533", os.path.join(root, "tools", "domain_ranks.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=root)
+    print(r.stdout[-3000:], r.stderr[-3000:])
+    assert r.returncode == 0

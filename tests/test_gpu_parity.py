@@ -184,3 +184,53 @@ def test_neighbors_merged_leaf_runs(bucket, genname, bnd, gpu, port):
     a = pipeline.run(port, 1, x, y, z, h, box, np.uint64, bucket, 150)
     b = pipeline.run(gpu, 1, x, y, z, h, box, np.uint64, bucket, 150)
     assert pipeline.compare(a, b, 150) == []
+
+
+def test_neighbors_count_only_and_plain_entry(gpu, port):
+    """ngmax = 0 (no list, counts only, NULL neighbour pointer) and the entry point without workspace give the same
+    counts / lists as the workspace path"""
+    import torch
+    from cornerstone_octree_b200 import ops
+    import gpu_adapter as ga
+    x, y, z, h, box = make_case("gaussian", 30000, np.float64, (0, 1, 0))
+    a = pipeline.run(port, 1, x, y, z, h, box, np.uint64, 32, 64)
+    oct_ = {k: a[k] for k in ("prefixes", "parents", "level_range", "internal_to_leaf", "leaf_to_internal")}
+    oct_["child_offsets"] = np.concatenate((a["child_offsets"], np.zeros(1, np.int32)))
+    L = a["tree"].size - 1
+    oct_.update(num_leaf_nodes=L, num_internal_nodes=(L - 1) // 7, num_nodes=L + (L - 1) // 7)
+    layout = np.zeros(L + 1, dtype=np.uint32)
+    np.cumsum(a["counts"], out=layout[1:])
+    d = ga.oct_to_dev(oct_)
+    args = [ga.to_dev(a[k]) for k in ("x", "y", "z", "h")]
+    n = x.size
+    common = (0, n, ga.conv_box(box), d, ga.to_dev(layout), ga.to_dev(a["centers"]), ga.to_dev(a["sizes"]))
+    # counts only
+    nc0 = torch.full((n,), -1, dtype=torch.int32, device="cuda")
+    dummy = torch.empty((n, 0), dtype=torch.int32, device="cuda")
+    ops.find_neighbors(*args, *common, 0, neighbors=dummy, neighbors_count=nc0)
+    np.testing.assert_array_equal(nc0.cpu().numpy().view(np.uint32), a["neighbors_count"])
+    # plain entry point (no workspace)
+    nb1, nc1 = ops.find_neighbors(*args, *common, 64, use_workspace=False)
+    nb1, nc1 = nb1.cpu().numpy().view(np.uint32), nc1.cpu().numpy().view(np.uint32)
+    np.testing.assert_array_equal(nc1, a["neighbors_count"])
+    for i in range(0, n, 97):
+        k = min(int(nc1[i]), 64)
+        np.testing.assert_array_equal(nb1[i, :k], a["neighbors"][i, :k])
+
+
+@pytest.mark.parametrize("kd", [np.uint32, np.uint64])
+def test_node_counts_unaligned_keys(kd, gpu, port):
+    """particle keys that do not start on a 16-byte boundary take the plain-load kernel; same counts"""
+    import torch
+    from cornerstone_octree_b200 import ops
+    import gpu_adapter as ga
+    keys = np.sort(gen.gaussian_keys(100001, kd))
+    tree, counts = port.compute_octree(keys[1:], 16)
+    dk = ga.to_dev(keys)
+    view = dk[1:]  # 4 or 8 bytes past a 256-byte aligned allocation
+    assert view.data_ptr() % 16 != 0
+    got = ops.compute_node_counts(ga.to_dev(tree), view)
+    np.testing.assert_array_equal(got.cpu().numpy().view(np.uint32), counts)
+    got = ops.compute_node_counts(ga.to_dev(tree), dk[2:] if kd == np.uint64 else dk[4:])
+    want = port.compute_node_counts(tree, keys[2:] if kd == np.uint64 else keys[4:])
+    np.testing.assert_array_equal(got.cpu().numpy().view(np.uint32), want)
