@@ -275,12 +275,12 @@ __global__ void __launch_bounds__(kFocusThreads) moveCentersKernel(const T* __re
 }
 
 // ------------------------------------------------------------------------------------------------ markMacs
-/* One BLOCK (8 warps) per 32 consecutive focus leaves, one lane per leaf.  The reference walks the tree once per focus
+/* One BLOCK (4 warps) per 32 consecutive focus leaves, one lane per leaf.  The reference walks the tree once per focus
  * leaf [traversal/macs.hpp:196-269]; neighbouring leaves open almost the same nodes, so here the UNION of the 32 walks
  * is walked once, with stack entries (first child, lane mask): a lane takes part in the test of a node only if it
  * failed the MAC at every ancestor, exactly as in its own walk, so the set of marked nodes is the reference's.
  * A leaf near the focus surface opens ~2000 nodes, a long serial chain (ncu of the one-warp version: 10 % of the warp
- * slots active, SMs idle 42 % of the time): the eight warps of the block share the walk through a small pool in shared
+ * slots active, SMs idle 42 % of the time): the warps of the block share the walk through a small pool in shared
  * memory — a busy warp hands surplus stack entries to the pool while it is low, an idle warp takes one, the round ends
  * when the pool is empty and no warp is busy (counter under a shared-memory lock).
  * The eight children of a node are fetched together (uniform addresses, one round trip per opened node: prefixes,
@@ -289,8 +289,9 @@ __global__ void __launch_bounds__(kFocusThreads) moveCentersKernel(const T* __re
  * marked and opened.  Private stack depth <= 7 per level + 8.
  * Measured (32 M particles, focus = 262144 leaves, profiles/r01h): thread per leaf (the reference's scheme) 1.34 ms,
  * one warp per 32 leaves 0.99 ms (without the batched loads 2.10), leaves with work packed densely per block first
- * 2.02 ms, subtrees of level 3 dealt statically to 8 warps 1.31 ms, this version 0.63 ms. */
-constexpr int kMarkThreads = 256; // 8 warps share the walk of one group of 32 focus leaves
+ * 2.02 ms, subtrees of level 3 dealt statically to 8 warps 1.31 ms, this version 0.63 ms with 8 warps per block and
+ * 0.58 ms with 4. */
+constexpr int kMarkThreads = 128; // the warps of a block share the walk of one group of 32 focus leaves
 constexpr int kMarkWarps   = kMarkThreads / 32;
 constexpr int kMarkStack   = 160;
 constexpr int kMarkPool    = 64;  // shared pool of open nodes, filled by busy warps, drained by idle ones
