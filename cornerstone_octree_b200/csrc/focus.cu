@@ -290,7 +290,8 @@ __global__ void __launch_bounds__(kFocusThreads) moveCentersKernel(const T* __re
  * Measured (32 M particles, focus = 262144 leaves, profiles/r01h): thread per leaf (the reference's scheme) 1.34 ms,
  * one warp per 32 leaves 0.99 ms (without the batched loads 2.10), leaves with work packed densely per block first
  * 2.02 ms, subtrees of level 3 dealt statically to 8 warps 1.31 ms, this version 0.63 ms with 8 warps per block and
- * 0.58 ms with 4. */
+ * 0.58 ms with 4; 0.50 ms with one block per group for the hardware scheduler instead of a grid-stride loop over a
+ * capped grid (the groups with long walks are spread unevenly). */
 constexpr int kMarkThreads = 128; // the warps of a block share the walk of one group of 32 focus leaves
 constexpr int kMarkWarps   = kMarkThreads / 32;
 constexpr int kMarkStack   = 160;
@@ -648,7 +649,8 @@ CSB_FOCUS_API(k64, uint64_t)
         SfcTables tabs;                                                                                                \
         int st = getSfcTables(&tabs);                                                                                  \
         if (st) return st;                                                                                             \
-        markMacsKernel<K, T><<<gridFor(size_t(numFocusNodes) * kMarkWarps, kMarkThreads, 8), kMarkThreads, 0, asStream(stream)>>>(                    \
+        /* one block per 32 focus leaves, uncapped: groups without work end at once, the hardware scheduler balances */ \
+        markMacsKernel<K, T><<<unsigned((numFocusNodes + 31) / 32), kMarkThreads, 0, asStream(stream)>>>(              \
             kind, tabs.enc, tabs.dec, prefixes, childOffsets, centers4, makeDBox<T>(box), focusNodes, numFocusNodes,   \
             limitSource, markings);                                                                                    \
         CSB_LAUNCHED();                                                                                                \
