@@ -116,7 +116,8 @@ int findHalos(int kind, const K* prefixes, const int* childOffsets, const int* i
     SfcTables tabs;
     int st = getSfcTables(&tabs);
     if (st) return st;
-    unsigned grid = gridFor(size_t(lastNode - firstNode), kHaloThreads, 8);
+    // one thread per leaf, uncapped: most leaves end at the containedIn test, the hardware scheduler balances the rest
+    unsigned grid = unsigned((size_t(lastNode - firstNode) + kHaloThreads - 1) / kHaloThreads);
     findHalosKernel<K, T><<<grid, kHaloThreads, 0, asStream(stream)>>>(kind, tabs.enc, tabs.dec, prefixes,
                                                                          childOffsets, internalToLeaf, leaves, radii,
                                                                          makeDBox<T>(box), firstNode, lastNode, flags);
