@@ -178,6 +178,30 @@ static void macRefinementFullSurface()
     EXPECT(int(tree.treeLeaves().size()) - 1 == 64 + 7 + 3 * numNodesFace + 3 * numNodesEdge + numNodesVertex);
 }
 
+// never called: instantiates every type combination of the facade templates so that the host-compiler check covers them
+[[maybe_unused]] static void instantiateAll()
+{
+    DeviceVector<LocalIndex> temp, groups, layout;
+    DeviceVector<float> xf, hf;
+    DeviceVector<double> xd, hd;
+    DeviceVector<uint32_t> l32;
+    DeviceVector<uint64_t> l64;
+    Box<float> bf(0, 1);
+    Box<double> bd(0, 1);
+    computeGroupSplits(0u, 0u, xf.data(), xf.data(), xf.data(), hf.data(), l32.data(), 0, layout.data(), bf, 32, 1.0f, temp, groups);
+    computeGroupSplits(0u, 0u, xf.data(), xf.data(), xf.data(), hf.data(), l64.data(), 0, layout.data(), bf, 32, 1.0f, temp, groups);
+    computeGroupSplits(0u, 0u, xd.data(), xd.data(), xd.data(), hf.data(), l32.data(), 0, layout.data(), bd, 64, 1.0f, temp, groups);
+    computeGroupSplits(0u, 0u, xd.data(), xd.data(), xd.data(), hf.data(), l64.data(), 0, layout.data(), bd, 64, 1.0f, temp, groups);
+    computeGroupSplits(0u, 0u, xd.data(), xd.data(), xd.data(), hd.data(), l32.data(), 0, layout.data(), bd, 64, 1.0f, temp, groups);
+    FocusedOctreeSingleNode<unsigned> t32(8, 0.5f);
+    FocusedOctreeSingleNode<uint64_t> t64(8, 0.5f);
+    t32.update(bf, l32, 0u, 1u);
+    t32.update(bd, l32, 0u, 1u);
+    t64.update(bf, l64, uint64_t(0), uint64_t(1));
+    t32.macRefine(bf, 0u, 1u, 0u, 2u, 1.0f);
+    t64.macRefine(bd, uint64_t(0), uint64_t(1), uint64_t(0), uint64_t(2), 1.0f);
+}
+
 int main(int argc, char** argv)
 {
     if (argc < 2 || std::strcmp(argv[1], "run") != 0)
