@@ -198,3 +198,26 @@ def test_source_centers(ref, kd, types):
     # the root holds the total |mass| up to summation order and a centre inside the cloud
     assert abs(want[0, 3] - np.abs(m.astype(np.float64)).sum()) < 1e-3 * n
     assert np.all(np.abs(want[0, :3]) < 0.1)
+
+
+class _GpuFocusImpl:
+    """focus_kat interface over the C ABI"""
+
+    def enforce(self, keys, oc, node_ops):
+        d = ga.oct_to_dev(oc)
+        got = ga.to_dev(node_ops)
+        status = ops.enforce_keys(ga.to_dev(keys), d, got)
+        return got.cpu().numpy(), status
+
+    def protect(self, oc, node_ops):
+        d = ga.oct_to_dev(oc)
+        got = ga.to_dev(node_ops)
+        conv = ops.protect_ancestors(d, got)
+        return got.cpu().numpy(), conv
+
+
+def test_reference_known_answers(port):
+    """the reference unit tests' vectors for enforceKeys / protectAncestors, through the CUDA library"""
+    import focus_kat
+    focus_kat.check_key_enforcement(_GpuFocusImpl(), port.build_octree)
+    focus_kat.check_protect_ancestors(_GpuFocusImpl(), port.build_octree)
