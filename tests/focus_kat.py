@@ -67,3 +67,40 @@ def check_protect_ancestors(impl, build_octree):
         want = [0] * 25
         want[0] = want[1] = want[9] = 1
         assert out.tolist() == want and not conv
+
+
+def check_rebalance_decision(impl, build_octree, upsweep_sum):
+    """TEST(FocusedOctree, rebalanceDecision), first two cases [ref: test/unit/focus/octree_focus.cpp:80-130]:
+    impl.decision(octree, counts, macs, focus_start, focus_end, bucket) -> node ops; leaf ops after protectAncestors"""
+    for kd in (np.uint32, np.uint64):
+        ml = 10 if kd == np.uint32 else 21
+        r1, r2 = 1 << (3 * (ml - 1)), 1 << (3 * (ml - 2))
+        keys = set(i * r1 for i in range(9)) | set(i * r2 for i in range(8)) | set(7 * r1 + i * r2 for i in range(8))
+        tree = np.array(sorted(keys), dtype=kd)  # OctreeMaker{}.divide().divide(0).divide(7): 22 leaves
+        oc = build_octree(tree)
+        L, I = oc["num_leaf_nodes"], oc["num_internal_nodes"]
+        assert L == 22
+        l2i = oc["leaf_to_internal"][I:]
+        cases = [
+            # counts win: the leaves 14-21 are fused although the MAC asks for a split of 14
+            ([1, 1, 1, 2, 1, 1, 1, 1, 1, 1, 2, 1, 1, 1, 0, 0, 0, 0, 0, 0, 0, 0],
+             [0, 0, 1, 0, 1, 1, 1, 1, 1, 0, 1, 1, 1, 1, 1, 0, 0, 0, 0, 0, 0, 0],
+             [1, 1, 1, 8, 1, 1, 1, 1, 1, 1, 8, 1, 1, 1, 1, 0, 0, 0, 0, 0, 0, 0], False),
+            # the MAC wins: the leaves 14-21 stay, but are not split
+            ([1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 0, 0, 2, 1, 0, 0, 0, 0],
+             [0, 0, 1, 1, 1, 1, 1, 1, 1, 0, 1, 1, 1, 1, 0, 0, 0, 0, 0, 0, 0, 0],
+             [1] * 22, True),
+        ]
+        for leaf_counts, leaf_macs, want, want_conv in cases:
+            counts = np.zeros(oc["num_nodes"], dtype=np.uint32)
+            counts[l2i] = leaf_counts
+            counts = upsweep_sum(oc["level_range"], oc["child_offsets"], counts)
+            macs = np.zeros(oc["num_nodes"], dtype=np.int8)
+            macs[l2i] = leaf_macs
+            for prefix in (0o1, 0o10, 0o17):  # internal cell macs in placeholder-bit format
+                (idx,) = np.nonzero(oc["prefixes"][:oc["num_nodes"]] == prefix)
+                macs[idx[0]] = 1
+            node_ops = impl.decision(oc, counts, macs, int(tree[0]), int(tree[8]), 1)
+            node_ops, conv = impl.protect(oc, node_ops)
+            assert node_ops[l2i].tolist() == want
+            assert bool(conv) == want_conv

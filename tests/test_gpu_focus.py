@@ -215,9 +215,14 @@ class _GpuFocusImpl:
         conv = ops.protect_ancestors(d, got)
         return got.cpu().numpy(), conv
 
+    def decision(self, oc, counts, macs, fs, fe, bucket):
+        d = ga.oct_to_dev(oc)
+        return ops.rebalance_decision_essential(d, ga.to_dev(counts), ga.to_dev(macs), fs, fe, bucket).cpu().numpy()
+
 
 def test_reference_known_answers(port):
     """the reference unit tests' vectors for enforceKeys / protectAncestors, through the CUDA library"""
     import focus_kat
     focus_kat.check_key_enforcement(_GpuFocusImpl(), port.build_octree)
     focus_kat.check_protect_ancestors(_GpuFocusImpl(), port.build_octree)
+    focus_kat.check_rebalance_decision(_GpuFocusImpl(), port.build_octree, port.upsweep_sum)

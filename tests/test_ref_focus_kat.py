@@ -13,6 +13,9 @@ class RefImpl:
     def protect(self, oc, ops):
         return self.ref.protect_ancestors(oc, ops)
 
+    def decision(self, oc, counts, macs, fs, fe, bucket):
+        return self.ref.rebalance_decision_essential(oc, counts, macs, fs, fe, bucket)
+
 
 def test_key_enforcement(ref):
     focus_kat.check_key_enforcement(RefImpl(ref), ref.build_octree)
@@ -20,3 +23,7 @@ def test_key_enforcement(ref):
 
 def test_protect_ancestors(ref):
     focus_kat.check_protect_ancestors(RefImpl(ref), ref.build_octree)
+
+
+def test_rebalance_decision(ref):
+    focus_kat.check_rebalance_decision(RefImpl(ref), ref.build_octree, ref.upsweep_sum)
