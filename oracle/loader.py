@@ -406,3 +406,108 @@ class RefFocusTree:
         counts = np.zeros(n, dtype=np.uint32)
         self.o._f("focus_tree_get_" + self.ks)(self.h, _ptr(leaves), _ptr(counts))
         return leaves, counts
+
+
+# ------------------------------------------------------------------------------------------------
+# multi-rank oracle: the reference's Domain<KeyType,T,CpuTag> on P thread-ranks (oracle/ref_domain.cpp)
+# ------------------------------------------------------------------------------------------------
+_REFDOM_PATH = os.path.join(_HERE, "_ref", "liboracle_refdom.so")
+
+
+def refdom_available():
+    return os.path.exists(_REFDOM_PATH)
+
+
+class RefDomain:
+    """P ranks of the UNMODIFIED reference Domain (domain/domain.hpp:66-699) in this process, one thread per rank over
+    the mpi.h shim.  Drives them as test/integration_mpi/domain_nranks.cpp:103-149 does."""
+
+    def __init__(self, nranks, bucket, bucket_focus, theta, limits, pbc=(0, 0, 0), kdtype=np.uint64, fdtype=np.float64,
+                 nprops=0, omp_per_rank=None):
+        self.lib = C.CDLL(_REFDOM_PATH)
+        self.P, self.kd, self.fd, self.nprops = nranks, np.dtype(kdtype), np.dtype(fdtype), nprops
+        self.sfx = "_%s_%s" % (_ks(kdtype), _ts(fdtype))
+        lim = np.asarray(limits, dtype=self.fd)
+        if lim.size == 2:
+            lim = np.array([lim[0], lim[1]] * 3, dtype=self.fd)
+        p = np.asarray(pbc, dtype=np.int32)
+        if omp_per_rank is None:
+            omp_per_rank = max(1, (os.cpu_count() or 1) // nranks)
+        f = self._f("create", C.c_void_p)
+        self.h = C.c_void_p(f(nranks, C.c_uint(bucket), C.c_uint(bucket_focus), C.c_float(theta), _ptr(lim), _ptr(p),
+                              nprops, omp_per_rank))
+
+    def _f(self, name, restype=C.c_int):
+        fn = getattr(self.lib, "cstone_refdom_" + name + self.sfx)
+        fn.restype = restype
+        return fn
+
+    def close(self):
+        if self.h:
+            self._f("destroy", None)(self.h)
+            self.h = None
+
+    def set(self, rank, x, y, z, h, props=()):
+        a = [np.ascontiguousarray(v, dtype=self.fd) for v in (x, y, z, h)]
+        pr = [np.ascontiguousarray(v, dtype=self.fd) for v in props] + [None, None]
+        self._f("set")(self.h, rank, C.c_uint64(a[0].size), *[_ptr(v) for v in a], _ptr(pr[0]), _ptr(pr[1]))
+
+    def sync(self):
+        st = self._f("sync")(self.h)
+        assert st == 0, "reference Domain::sync failed"
+
+    def info(self, rank):
+        out = np.zeros(8, dtype=np.int64)
+        box = np.zeros(6, dtype=self.fd)
+        self._f("info", None)(self.h, rank, _ptr(out), _ptr(box))
+        return dict(start=int(out[0]), end=int(out[1]), size=int(out[2]), focus_leaves=int(out[3]),
+                    global_leaves=int(out[4]), start_cell=int(out[5]), end_cell=int(out[6]), n=int(out[7]), box=box)
+
+    def arrays(self, rank):
+        """keys, x, y, z, h (+ properties) of one rank after sync, halos included"""
+        n = self.info(rank)["n"]
+        out = [np.zeros(n, dtype=self.kd)] + [np.zeros(n, dtype=self.fd) for _ in range(4 + self.nprops)]
+        for which, a in enumerate(out[:5]):
+            self._f("get_array")(self.h, rank, which, _ptr(a))
+        for k in range(self.nprops):
+            self._f("get_array")(self.h, rank, 5 + k, _ptr(out[5 + k]))
+        return out
+
+    def trees(self, rank):
+        inf = self.info(rank)
+        gl = np.zeros(inf["global_leaves"] + 1, dtype=self.kd)
+        fl = np.zeros(inf["focus_leaves"] + 1, dtype=self.kd)
+        fc = np.zeros(inf["focus_leaves"], dtype=np.uint32)
+        lay = np.zeros(inf["focus_leaves"] + 1, dtype=np.uint32)
+        asg = np.zeros(2 * self.P, dtype=np.int32)
+        for which, a in enumerate((gl, fl, fc, lay, asg)):
+            self._f("get_tree")(self.h, rank, which, _ptr(a))
+        return dict(global_leaves=gl, focus_leaves=fl, focus_counts=fc, layout=lay, focus_assignment=asg.reshape(-1, 2))
+
+    def find_neighbors(self, ngmax):
+        """the reference's findNeighbors over every rank's assigned range: list of (neighbors[n, ngmax], counts[n])"""
+        res, nbp, ncp = [], (C.c_void_p * self.P)(), (C.c_void_p * self.P)()
+        for r in range(self.P):
+            inf = self.info(r)
+            n = inf["end"] - inf["start"]
+            nb = np.zeros((n, ngmax), dtype=np.uint32)
+            nc = np.zeros(n, dtype=np.uint32)
+            res.append((nb, nc))
+            nbp[r], ncp[r] = nb.ctypes.data, nc.ctypes.data
+        st = self._f("find_neighbors")(self.h, C.c_uint(ngmax), nbp, ncp)
+        assert st == 0
+        return res
+
+    def exchange_halos(self, arrays):
+        """arrays[rank]: fdtype[nParticlesWithHalos(rank)] with the assigned range filled; halos are filled in place"""
+        ptrs = (C.c_void_p * self.P)()
+        for r in range(self.P):
+            assert arrays[r].dtype == self.fd and arrays[r].size == self.info(r)["size"]
+            ptrs[r] = arrays[r].ctypes.data
+        st = self._f("exchange_halos")(self.h, ptrs)
+        assert st == 0
+
+    def seconds(self):
+        a, b = C.c_double(0), C.c_double(0)
+        self._f("seconds", None)(self.h, C.byref(a), C.byref(b))
+        return a.value, b.value
