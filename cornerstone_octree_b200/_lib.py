@@ -62,6 +62,7 @@ _PROTOS = {
     "gather_multi": (_i, [_vp, _sz, _i, _vp, _vp, _vp, _vp]),
     "exclusive_scan_u32": (_i, [_vp, _vp, _sz, _u32, _vp, _vp]),
     "inclusive_scan_u32": (_i, [_vp, _vp, _sz, _vp, _vp]),
+    "exclusive_scan_u32_noalloc": (_i, [_vp, _vp, _sz, _u32, _vp]),
     "upsweep_sum": (_i, [_i32, _vp, _vp, _vp, _vp]),
     "compute_node_layout": (_i, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
 }

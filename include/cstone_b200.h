@@ -173,6 +173,17 @@ int cstone_b200_exclusive_scan_u32(const uint32_t* in, uint32_t* out, size_t n, 
                                    void* stream);
 int cstone_b200_inclusive_scan_u32(const uint32_t* in, uint32_t* out, size_t n, void* temp, void* stream);
 
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as cstone_b200_exclusive_scan_u32, but the scratch lives in a file-scope device array inside the
+ * library (65 792 bytes, held by every GPU that loads the library until the process exits), so the call allocates
+ * nothing: no cudaMalloc / cudaFree / allocating library routine.
+ * Limit: n <= CSTONE_B200_SCAN_NOALLOC_MAX_N, CSTONE_E_TOO_LARGE otherwise (nothing is launched).
+ * All calls on one GPU share the array; each call clears the part it uses on `stream` first.  Calls that overlap on
+ * the GPU (streams without an ordering between them) race on it: order them. */
+#define CSTONE_B200_SCAN_NOALLOC_MAX_N 16777216u
+int cstone_b200_exclusive_scan_u32_noalloc(const uint32_t* in, uint32_t* out, size_t n, uint32_t init, void* stream);
+
 /* ------------------------------------------------------------------------
  * a6  leaf particle counts
  * [ref: tree/csarray_gpu.h:55-62 computeNodeCountsGpu<KeyType>]
