@@ -199,8 +199,14 @@ _DOMAIN_PROTOS = {
     "tree_view": (_i, [_vp, _vp]),
     "global_tree": (_i, [_vp, _vp, _vp, _vp]),
     "find_neighbors": (_i, [_vp, _vp, _vp, _vp, _vp, _u32, _vp, _vp]),
+    "set_local_world": (_i, [_vp, _vp]),
 }
-DOMAIN_EXPORTED = ["nccl_unique_id", "nccl_comm_init", "nccl_comm_destroy", "host_assignment_k32",
+lib.cstone_b200_local_world_create.restype = _vp
+lib.cstone_b200_local_world_create.argtypes = [_i]
+lib.cstone_b200_local_world_destroy.restype = None
+lib.cstone_b200_local_world_destroy.argtypes = [_vp]
+DOMAIN_EXPORTED = ["nccl_unique_id", "nccl_comm_init", "nccl_comm_destroy", "local_world_create", "local_world_destroy",
+                   "host_assignment_k32",
                    "host_assignment_k64", "host_limit_box_shrinking_f32", "host_limit_box_shrinking_f64",
                    "host_uniform_bins", "host_limit_boundary_shifts_k32", "host_limit_boundary_shifts_k64"]
 for ks in ("k32", "k64"):

@@ -22,11 +22,13 @@
 #include <nccl.h>
 
 #include <cstdio>
+#include <memory>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
 
 #include "../../include/cstone_b200_domain.h"
+#include "comm.hpp"
 #include "halo_box.cuh"
 #include "scan.cuh"
 #include "domain_host.hpp"
@@ -326,8 +328,9 @@ __global__ void __launch_bounds__(128) surfaceBoxesKernel(int kind,
     for (int leaf = blockIdx.x * blockDim.x + threadIdx.x; leaf < numLeaves; leaf += gridDim.x * blockDim.x)
     {
         if (counts[leaf] == 0) continue;
+        // every non-empty leaf of this tree holds particles of this rank, also one that straddles a rank boundary
+        // (sparse regions, ranks with fewer particles than the bucket size): containedIn rejects interior leaves
         K start = leaves[leaf], end = leaves[leaf + 1];
-        if (start < lowest || end > highest) continue; // not one of my leaves
         IBox nodeBox = sfcIBox<K>(kind, dec, start, treeLevel<K>(K(end - start)));
         IBox halo    = makeHaloBox<K, T>(nodeBox, radii[leaf], box);
         if (containedIn<K>(kind, enc, lowest, highest, halo)) continue;
@@ -473,7 +476,14 @@ public:
     }
     //! one-shot: the stream waits for `e` before h and the properties are first read (their upload may still run)
     void setFieldsReadyEvent(void* e) { fieldsReady_ = reinterpret_cast<cudaEvent_t>(e); }
-    void setComm(void* c) { comm_ = reinterpret_cast<ncclComm_t>(c); }
+    void setComm(void* c) { comm_.reset(new NcclComm(reinterpret_cast<ncclComm_t>(c), rank_, nRanks_)); }
+    //! P ranks as P host threads of this process on one GPU (comm.hpp LocalComm): test transport
+    void setLocalWorld(LocalWorld* w) { comm_.reset(new LocalComm(w, rank_)); }
+    ~Engine()
+    {
+        for (cudaEvent_t e : ev_)
+            if (e) cudaEventDestroy(e);
+    }
     //! space-filling curve of the keys (the reference's Domain hard-wires Hilbert, sfc/sfc.hpp:54-55); before the first sync
     int setSfcKind(int kind)
     {
@@ -545,7 +555,7 @@ private:
     float theta_;
     CBox box_;
     bool firstCall_   = true;
-    ncclComm_t comm_  = nullptr;
+    std::unique_ptr<Comm> comm_;
     cudaEvent_t fieldsReady_ = nullptr;
     int sfcKind_      = CSTONE_SFC_HILBERT;
     cudaStream_t s_   = nullptr; // legacy default stream: ordered with the caller's default-stream work
@@ -596,7 +606,7 @@ int Engine<K, T>::updateBox(const T* x, const T* y, const T* z, size_t n)
         T v[6] = {mm[0], -mm[1], mm[2], -mm[3], mm[4], -mm[5]};
         CSB_TRY(small_.reserve(4096));
         CSB_CUDA(cudaMemcpyAsync(small_.p, v, sizeof(v), cudaMemcpyHostToDevice, s_));
-        CSB_NCCL(ncclAllReduce(small_.p, small_.p, 6, sizeof(T) == 8 ? ncclDouble : ncclFloat, ncclMin, comm_, s_));
+        CSB_TRY(comm_->allReduce(small_.p, 6, sizeof(T) == 8 ? CommType::f64 : CommType::f32, CommOp::min, s_));
         CSB_CUDA(cudaMemcpyAsync(v, small_.p, sizeof(v), cudaMemcpyDeviceToHost, s_));
         CSB_CUDA(cudaStreamSynchronize(s_));
         for (int d = 0; d < 3; ++d)
@@ -624,7 +634,8 @@ int Engine<K, T>::allreduceCounts()
     // [ref: tree/update_mpi.hpp:58-66] counts = max(local, Allreduce(SUM)(local))
     int n = global_.numNodes;
     CSB_TRY(small_.reserve(size_t(n) * 4 + 4096));
-    CSB_NCCL(ncclAllReduce(global_.counts.p, small_.p, n, ncclUint32, ncclSum, comm_, s_));
+    CSB_CUDA(cudaMemcpyAsync(small_.p, global_.counts.p, size_t(n) * 4, cudaMemcpyDeviceToDevice, s_));
+    CSB_TRY(comm_->allReduce(small_.p, size_t(n), CommType::u32, CommOp::sum, s_));
     maxMergeKernel<<<gridFor(size_t(n), 256), 256, 0, s_>>>(global_.counts.template as<uint32_t>(),
                                                           small_.template as<uint32_t>(), n);
     CSB_LAUNCHED();
@@ -721,7 +732,7 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
                                 const void* const* props, const int* propBytes)
 {
     if (nprops < 0 || nprops > kMaxProps || (nIn && (!x || !y || !z || !h))) return CSTONE_E_INVALID_ARGUMENT;
-    if (nRanks_ > 1 && !comm_) return CSTONE_E_INVALID_ARGUMENT;
+    if (nRanks_ > 1 && !comm_) return CSTONE_E_INVALID_ARGUMENT; // set_comm or set_local_world first
     if (nIn >= (uint64_t(1) << 30)) return CSTONE_E_TOO_LARGE;
     uint64_t inStart = 0, inEnd = nIn;
     if (!firstCall_)
@@ -834,7 +845,7 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         uint32_t* dMine = dPos + P + 1;
         uint32_t* dAll  = dMine + P;
         CSB_CUDA(cudaMemcpyAsync(dMine, sendCount.data(), 4 * P, cudaMemcpyHostToDevice, s_));
-        CSB_NCCL(ncclAllGather(dMine, dAll, P, ncclUint32, comm_, s_));
+        CSB_TRY(comm_->allGather(dMine, dAll, 4 * size_t(P), s_));
         std::vector<uint32_t> matrix(size_t(P) * P);
         CSB_CUDA(cudaMemcpyAsync(matrix.data(), dAll, 4 * size_t(P) * P, cudaMemcpyDeviceToHost, s_));
         CSB_CUDA(cudaStreamSynchronize(s_));
@@ -850,21 +861,21 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         // 7. exchange: grouped NCCL send/recv, received straight into place [ref: domaindecomp_mpi_gpu.cuh:85-185]
         for (int a = 0; a < na; ++a)
             CSB_TRY(recv_[a].reserve(size_t(eb[a]) * nAssigned_ + 256));
-        CSB_NCCL(ncclGroupStart());
-        for (int q = 0; q < P; ++q)
         {
-            if (q == rank_) continue;
-            for (int a = 0; a < na; ++a)
+            std::vector<CommMsg> sends, recvs;
+            for (int q = 0; q < P; ++q)
             {
-                if (sendCount[q])
-                    CSB_NCCL(ncclSend(pack_[a].template as<char>() + size_t(sendStart[q]) * eb[a], size_t(sendCount[q]) * eb[a],
-                                      ncclInt8, q, comm_, s_));
-                if (recvCount[q])
-                    CSB_NCCL(ncclRecv(recv_[a].template as<char>() + size_t(recvOff[q]) * eb[a], size_t(recvCount[q]) * eb[a],
-                                      ncclInt8, q, comm_, s_));
+                if (q == rank_) continue;
+                for (int a = 0; a < na; ++a)
+                {
+                    if (sendCount[q])
+                        sends.push_back({q, pack_[a].template as<char>() + size_t(sendStart[q]) * eb[a], size_t(sendCount[q]) * eb[a]});
+                    if (recvCount[q])
+                        recvs.push_back({q, recv_[a].template as<char>() + size_t(recvOff[q]) * eb[a], size_t(recvCount[q]) * eb[a]});
+                }
             }
+            CSB_TRY(comm_->exchange(sends, recvs, s_));
         }
-        CSB_NCCL(ncclGroupEnd());
         for (int a = 0; a < na; ++a)
             if (sendCount[rank_])
                 CSB_CUDA(cudaMemcpyAsync(recv_[a].template as<char>() + size_t(recvOff[rank_]) * eb[a],
@@ -996,7 +1007,7 @@ int Engine<K, T>::discoverHalos()
         sfcKind_,         tabs.enc, tabs.dec, focus_.treeA.template as<K>(), focus_.counts.template as<uint32_t>(), radii_.template as<float>(), L, lowest,
         highest, makeDBox<T>(&box_), surf_.template as<IBox6>(), uint32_t(L), dCount);
     CSB_LAUNCHED();
-    CSB_NCCL(ncclAllGather(dCount, dCount + 1, 1, ncclUint32, comm_, s_));
+    CSB_TRY(comm_->allGather(dCount, dCount + 1, 4, s_));
     std::vector<uint32_t> nS(P);
     CSB_CUDA(cudaMemcpyAsync(nS.data(), dCount + 1, 4 * P, cudaMemcpyDeviceToHost, s_));
     CSB_CUDA(cudaStreamSynchronize(s_));
@@ -1008,7 +1019,7 @@ int Engine<K, T>::discoverHalos()
     // d. everybody gets everybody's surface boxes (tens of MB at most: surface ~ N^(2/3))
     CSB_TRY(surf_.reserve(sizeof(IBox6) * size_t(maxS) + 256, true, s_));
     CSB_TRY(allSurf_.reserve(sizeof(IBox6) * size_t(maxS) * P + 256));
-    CSB_NCCL(ncclAllGather(surf_.p, allSurf_.p, sizeof(IBox6) * size_t(maxS), ncclInt8, comm_, s_));
+    CSB_TRY(comm_->allGather(surf_.p, allSurf_.p, sizeof(IBox6) * size_t(maxS), s_));
 
     lap();
     // e. reverse collision against my own leaves
@@ -1054,7 +1065,7 @@ int Engine<K, T>::discoverHalos()
     uint32_t* dMine = dCount + 1 + P;
     uint32_t* dAll  = dMine + P;
     CSB_CUDA(cudaMemcpyAsync(dMine, haloSendCount_.data(), 4 * P, cudaMemcpyHostToDevice, s_));
-    CSB_NCCL(ncclAllGather(dMine, dAll, P, ncclUint32, comm_, s_));
+    CSB_TRY(comm_->allGather(dMine, dAll, 4 * size_t(P), s_));
     std::vector<uint32_t> matrix(size_t(P) * P);
     CSB_CUDA(cudaMemcpyAsync(matrix.data(), dAll, 4 * size_t(P) * P, cudaMemcpyDeviceToHost, s_));
     CSB_CUDA(cudaStreamSynchronize(s_));
@@ -1080,6 +1091,9 @@ int Engine<K, T>::discoverHalos()
     }
 
     lap();
+    if (lapOn && nLap != 7)
+        for (int k = 0; k < nLap; ++k)
+            cudaEventDestroy(lapEv[k]);
     if (lapOn && nLap == 7)
     {
         cudaEventSynchronize(lapEv[6]);
@@ -1148,22 +1162,21 @@ int Engine<K, T>::exchangeHalos(int narrays, void* const* arrays, const int* ele
             CSB_LAUNCHED();
         }
     // one NCCL group; every message is received directly in its halo range [ref: halos/exchange_halos_gpu.cuh:34-119]
-    CSB_NCCL(ncclGroupStart());
+    std::vector<CommMsg> sends, recvs;
     for (int q = 0; q < P; ++q)
     {
         if (q == rank_) continue;
         for (int a = 0; a < narrays; ++a)
         {
             if (haloSendCount_[q])
-                CSB_NCCL(ncclSend(haloPack_.template as<char>() + off[a] + size_t(haloSendOffset_[q]) * elemBytes[a],
-                                  size_t(haloSendCount_[q]) * elemBytes[a], ncclInt8, q, comm_, s_));
+                sends.push_back({q, haloPack_.template as<char>() + off[a] + size_t(haloSendOffset_[q]) * elemBytes[a],
+                                 size_t(haloSendCount_[q]) * elemBytes[a]});
             if (haloRecvCount_[q])
-                CSB_NCCL(ncclRecv(reinterpret_cast<char*>(arrays[a]) + size_t(haloRecvOffset_[q]) * elemBytes[a],
-                                  size_t(haloRecvCount_[q]) * elemBytes[a], ncclInt8, q, comm_, s_));
+                recvs.push_back({q, reinterpret_cast<char*>(arrays[a]) + size_t(haloRecvOffset_[q]) * elemBytes[a],
+                                 size_t(haloRecvCount_[q]) * elemBytes[a]});
         }
     }
-    CSB_NCCL(ncclGroupEnd());
-    return 0;
+    return comm_->exchange(sends, recvs, s_);
 }
 
 template<class K, class T>
@@ -1230,18 +1243,100 @@ int cstone_b200_nccl_comm_destroy(void* comm)
     return ncclCommDestroy(reinterpret_cast<ncclComm_t>(comm)) == ncclSuccess ? 0 : CSTONE_E_NCCL;
 }
 
-#define CSB_DOMAIN_DEF(KS, K, TS, T)                                                                                       cstone_b200_domain* cstone_b200_domain_create_##KS##_##TS(int rank, int nranks, unsigned bucket,                                                                                 unsigned bucketFocus, float theta,                                                                                     const cstone_box_##TS* box)                                  {                                                                                                                          if (!box || nranks < 1 || rank < 0 || rank >= nranks || bucket < bucketFocus || bucketFocus == 0) return nullptr;         return reinterpret_cast<cstone_b200_domain*>(new csb::Engine<K, T>(rank, nranks, bucket, bucketFocus, theta, *box));     }                                                                                                                      void cstone_b200_domain_destroy_##KS##_##TS(cstone_b200_domain* d) { delete reinterpret_cast<csb::Engine<K, T>*>(d); }     int cstone_b200_domain_set_comm_##KS##_##TS(cstone_b200_domain* d, void* comm)                                         {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              reinterpret_cast<csb::Engine<K, T>*>(d)->setComm(comm);                                                                return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_set_sfc_kind_##KS##_##TS(cstone_b200_domain* d, int kind)                                   \
+/* in-process transport (comm.hpp LocalComm): one world per group of thread-ranks that share a GPU */
+void* cstone_b200_local_world_create(int nranks) { return nranks >= 1 ? new (std::nothrow) csb::LocalWorld(nranks) : nullptr; }
+void cstone_b200_local_world_destroy(void* world) { delete static_cast<csb::LocalWorld*>(world); }
+
+#define CSB_ENGINE(K, T, d) reinterpret_cast<csb::Engine<K, T>*>(d)
+#define CSB_CENGINE(K, T, d) reinterpret_cast<const csb::Engine<K, T>*>(d)
+
+#define CSB_DOMAIN_DEF(KS, K, TS, T)                                                                                   \
+    cstone_b200_domain* cstone_b200_domain_create_##KS##_##TS(int rank, int nranks, unsigned bucket, unsigned bucketFocus,\
+                                                              float theta, const cstone_box_##TS* box)                 \
     {                                                                                                                  \
-        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
-        return reinterpret_cast<csb::Engine<K, T>*>(d)->setSfcKind(kind);                                              \
+        if (!box || nranks < 1 || rank < 0 || rank >= nranks || bucket < bucketFocus || bucketFocus == 0) return nullptr;\
+        return reinterpret_cast<cstone_b200_domain*>(new csb::Engine<K, T>(rank, nranks, bucket, bucketFocus, theta, *box));\
     }                                                                                                                  \
-    int cstone_b200_domain_set_fields_ready_event_##KS##_##TS(cstone_b200_domain* d, void* event)                                         {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              reinterpret_cast<csb::Engine<K, T>*>(d)->setFieldsReadyEvent(event);                                                                return 0;                                                                                                          }                                                                                                                      int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n, const T* x, const T* y,                                                             const T* z, const T* h, int nprops, const void* const* props,                                                          const int* pb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncBegin(n, x, y, z, h, nprops, props, pb);                       }                                                                                                                      int cstone_b200_domain_sync_finish_##KS##_##TS(cstone_b200_domain* d, K* keys, T* x, T* y, T* z, T* h,                                                                void* const* props)                                                     {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<csb::Engine<K, T>*>(d)->syncFinish(keys, x, y, z, h, props);                               }                                                                                                                      int cstone_b200_domain_exchange_halos_##KS##_##TS(cstone_b200_domain* d, int na, void* const* arrays,                                                                    const int* eb)                                                       {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              int st = reinterpret_cast<csb::Engine<K, T>*>(d)->exchangeHalos(na, arrays, eb);                                       if (st) return st;                                                                                                     cudaError_t e = cudaStreamSynchronize(nullptr);                                                                        return int(e);                                                                                                     }                                                                                                                      int cstone_b200_domain_info_##KS##_##TS(const cstone_b200_domain* d, int64_t* info8)                                   {                                                                                                                          if (!d || !info8) return CSTONE_E_INVALID_ARGUMENT;                                                                    reinterpret_cast<const csb::Engine<K, T>*>(d)->info(info8);                                                            return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_stage_ms_##KS##_##TS(const cstone_b200_domain* d, float* ms10)                              \
+    void cstone_b200_domain_destroy_##KS##_##TS(cstone_b200_domain* d) { delete CSB_ENGINE(K, T, d); }                 \
+    int cstone_b200_domain_set_comm_##KS##_##TS(cstone_b200_domain* d, void* comm)                                     \
     {                                                                                                                  \
-        if (!d || !ms10) return CSTONE_E_INVALID_ARGUMENT;                                                             \
-        reinterpret_cast<const csb::Engine<K, T>*>(d)->stageMs(ms10);                                                  \
+        if (!d || !comm) return CSTONE_E_INVALID_ARGUMENT;                                                             \
+        CSB_ENGINE(K, T, d)->setComm(comm);                                                                            \
         return 0;                                                                                                      \
     }                                                                                                                  \
-    int cstone_b200_domain_box_##KS##_##TS(const cstone_b200_domain* d, cstone_box_##TS* out)                              {                                                                                                                          if (!d || !out) return CSTONE_E_INVALID_ARGUMENT;                                                                      *out = reinterpret_cast<const csb::Engine<K, T>*>(d)->box();                                                           return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_tree_view_##KS##_##TS(const cstone_b200_domain* d, const void** ptrs10)                         {                                                                                                                          if (!d || !ptrs10) return CSTONE_E_INVALID_ARGUMENT;                                                                   reinterpret_cast<const csb::Engine<K, T>*>(d)->treeView(ptrs10);                                                       return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_global_tree_##KS##_##TS(const cstone_b200_domain* d, const K** leaves,                                                                         const uint32_t** counts, const K** assignment)                          {                                                                                                                          if (!d || !leaves || !counts || !assignment) return CSTONE_E_INVALID_ARGUMENT;                                         reinterpret_cast<const csb::Engine<K, T>*>(d)->globalTree(leaves, counts, assignment);                                 return 0;                                                                                                          }                                                                                                                      int cstone_b200_domain_find_neighbors_##KS##_##TS(const cstone_b200_domain* d, const T* x, const T* y,                                                                   const T* z, const T* h, uint32_t ngmax, uint32_t* nb,                                                                  uint32_t* nc)                                                        {                                                                                                                          if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                              return reinterpret_cast<const csb::Engine<K, T>*>(d)->findNeighbors(x, y, z, h, ngmax, nb, nc);                    }
+    int cstone_b200_domain_set_local_world_##KS##_##TS(cstone_b200_domain* d, void* world)                             \
+    {                                                                                                                  \
+        if (!d || !world) return CSTONE_E_INVALID_ARGUMENT;                                                            \
+        CSB_ENGINE(K, T, d)->setLocalWorld(static_cast<csb::LocalWorld*>(world));                                      \
+        return 0;                                                                                                      \
+    }                                                                                                                  \
+    int cstone_b200_domain_set_sfc_kind_##KS##_##TS(cstone_b200_domain* d, int kind)                                   \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return CSB_ENGINE(K, T, d)->setSfcKind(kind);                                                                  \
+    }                                                                                                                  \
+    int cstone_b200_domain_set_fields_ready_event_##KS##_##TS(cstone_b200_domain* d, void* event)                      \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        CSB_ENGINE(K, T, d)->setFieldsReadyEvent(event);                                                               \
+        return 0;                                                                                                      \
+    }                                                                                                                  \
+    int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n, const T* x, const T* y, const T* z,\
+                                                      const T* h, int nprops, const void* const* props, const int* pb) \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return CSB_ENGINE(K, T, d)->syncBegin(n, x, y, z, h, nprops, props, pb);                                       \
+    }                                                                                                                  \
+    int cstone_b200_domain_sync_finish_##KS##_##TS(cstone_b200_domain* d, K* keys, T* x, T* y, T* z, T* h,             \
+                                                   void* const* props)                                                 \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return CSB_ENGINE(K, T, d)->syncFinish(keys, x, y, z, h, props);                                               \
+    }                                                                                                                  \
+    int cstone_b200_domain_exchange_halos_##KS##_##TS(cstone_b200_domain* d, int na, void* const* arrays, const int* eb)\
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        int st = CSB_ENGINE(K, T, d)->exchangeHalos(na, arrays, eb);                                                   \
+        if (st) return st;                                                                                             \
+        return int(cudaStreamSynchronize(nullptr));                                                                    \
+    }                                                                                                                  \
+    int cstone_b200_domain_info_##KS##_##TS(const cstone_b200_domain* d, int64_t* info8)                               \
+    {                                                                                                                  \
+        if (!d || !info8) return CSTONE_E_INVALID_ARGUMENT;                                                            \
+        CSB_CENGINE(K, T, d)->info(info8);                                                                             \
+        return 0;                                                                                                      \
+    }                                                                                                                  \
+    int cstone_b200_domain_stage_ms_##KS##_##TS(const cstone_b200_domain* d, float* ms10)                              \
+    {                                                                                                                  \
+        if (!d || !ms10) return CSTONE_E_INVALID_ARGUMENT;                                                             \
+        CSB_CENGINE(K, T, d)->stageMs(ms10);                                                                           \
+        return 0;                                                                                                      \
+    }                                                                                                                  \
+    int cstone_b200_domain_box_##KS##_##TS(const cstone_b200_domain* d, cstone_box_##TS* out)                          \
+    {                                                                                                                  \
+        if (!d || !out) return CSTONE_E_INVALID_ARGUMENT;                                                              \
+        *out = CSB_CENGINE(K, T, d)->box();                                                                            \
+        return 0;                                                                                                      \
+    }                                                                                                                  \
+    int cstone_b200_domain_tree_view_##KS##_##TS(const cstone_b200_domain* d, const void** ptrs10)                     \
+    {                                                                                                                  \
+        if (!d || !ptrs10) return CSTONE_E_INVALID_ARGUMENT;                                                           \
+        CSB_CENGINE(K, T, d)->treeView(ptrs10);                                                                        \
+        return 0;                                                                                                      \
+    }                                                                                                                  \
+    int cstone_b200_domain_global_tree_##KS##_##TS(const cstone_b200_domain* d, const K** leaves, const uint32_t** counts,\
+                                                   const K** assignment)                                               \
+    {                                                                                                                  \
+        if (!d || !leaves || !counts || !assignment) return CSTONE_E_INVALID_ARGUMENT;                                 \
+        CSB_CENGINE(K, T, d)->globalTree(leaves, counts, assignment);                                                  \
+        return 0;                                                                                                      \
+    }                                                                                                                  \
+    int cstone_b200_domain_find_neighbors_##KS##_##TS(const cstone_b200_domain* d, const T* x, const T* y, const T* z, \
+                                                      const T* h, uint32_t ngmax, uint32_t* nb, uint32_t* nc)          \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return CSB_CENGINE(K, T, d)->findNeighbors(x, y, z, h, ngmax, nb, nc);                                         \
+    }
 
 CSB_DOMAIN_DEF(k64, uint64_t, f64, double)
 CSB_DOMAIN_DEF(k64, uint64_t, f32, float)

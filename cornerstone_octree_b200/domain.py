@@ -75,6 +75,11 @@ class Domain:
         self._comm = comm
         _check(_fn("set_comm", self.bits, self.fd)(self._h, comm), "set_comm")
 
+    def set_local_world(self, world):
+        """in-process transport: this Domain is one of `world.num_ranks` thread-ranks sharing the GPU (see LocalWorld)"""
+        self._world = world  # keep it alive
+        _check(_fn("set_local_world", self.bits, self.fd)(self._h, world.handle), "set_local_world")
+
     # ---- sync
     def sync(self, x, y, z, h, props=(), fields_ready=None):
         """[ref: domain/domain.hpp:196-243] returns (keys, x, y, z, h, props) as NEW tensors of the new local size:
@@ -200,3 +205,45 @@ def _alias(ptr, n, dtype):
         if st != 0:
             raise RuntimeError("cudaMemcpy failed: %d" % st)
     return out
+
+
+class LocalWorld:
+    """P ranks as P host threads of this process on ONE GPU (include/cstone_b200_domain.h, in-process transport): a
+    checking tool for the multi-rank path on single-GPU machines.  Usage:
+        world = LocalWorld(P); doms = [Domain(r, P, ...) for r in range(P)]; [d.set_local_world(world) for d in doms]
+        results = world.run(lambda r: doms[r].sync(...))      # one thread per rank, collectives meet inside"""
+
+    def __init__(self, num_ranks):
+        self.num_ranks = num_ranks
+        self.handle = C.c_void_p(lib.cstone_b200_local_world_create(num_ranks))
+        if not self.handle:
+            raise RuntimeError("cstone_b200_local_world_create failed")
+
+    def run(self, fn):
+        """fn(rank) on one thread per rank (ctypes releases the GIL inside the library); returns the results in rank
+        order and re-raises the first exception"""
+        import threading
+        out, err = [None] * self.num_ranks, [None] * self.num_ranks
+        dev = torch.cuda.current_device()
+
+        def body(r):
+            try:
+                torch.cuda.set_device(dev)
+                out[r] = fn(r)
+            except BaseException as e:  # noqa: BLE001  (reported to the caller below)
+                err[r] = e
+
+        threads = [threading.Thread(target=body, args=(r,)) for r in range(self.num_ranks)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        for e in err:
+            if e is not None:
+                raise e
+        return out
+
+    def close(self):
+        if self.handle:
+            lib.cstone_b200_local_world_destroy(self.handle)
+            self.handle = None

@@ -38,6 +38,14 @@ int cstone_b200_nccl_unique_id(void* id128 /* 128 bytes, HOST */);
 int cstone_b200_nccl_comm_init(const void* id128, int nranks, int rank, void** comm_out);
 int cstone_b200_nccl_comm_destroy(void* comm);
 
+/* In-process transport for single-GPU checks of the multi-rank path (no counterpart in the reference, whose ranks are
+ * MPI processes): P ranks = P engine instances of ONE process, each driven by its own host thread on the same GPU;
+ * messages are device-to-device copies, collectives meet at a host barrier.  Create one world, hand it to all P
+ * engines with ..._set_local_world instead of ..._set_comm, then call sync_begin / exchange_halos of the P engines
+ * concurrently from P threads.  Host-synchronous: a checking tool, not a fast path. */
+void* cstone_b200_local_world_create(int nranks);
+void cstone_b200_local_world_destroy(void* world);
+
 #define CSB_DOMAIN_DECL(KS, K, TS, T)                                                                                  \
     /* [ref: domain/domain.hpp:95-113 Domain(rank, nRanks, bucketSize, bucketSizeFocus, theta, box)] */               \
     cstone_b200_domain* cstone_b200_domain_create_##KS##_##TS(int rank, int nranks, unsigned bucket_size,              \
@@ -45,6 +53,7 @@ int cstone_b200_nccl_comm_destroy(void* comm);
                                                               const cstone_box_##TS* box);                             \
     void cstone_b200_domain_destroy_##KS##_##TS(cstone_b200_domain* d);                                                \
     int cstone_b200_domain_set_comm_##KS##_##TS(cstone_b200_domain* d, void* nccl_comm);                               \
+    int cstone_b200_domain_set_local_world_##KS##_##TS(cstone_b200_domain* d, void* local_world);                      \
     int cstone_b200_domain_set_fields_ready_event_##KS##_##TS(cstone_b200_domain* d, void* cuda_event);                \
     /* CSTONE_SFC_HILBERT (default, what the reference's Domain hard-wires: sfc/sfc.hpp:54-55) or CSTONE_SFC_MORTON;  \
      * call before the first sync */                                                                                   \

@@ -1,0 +1,210 @@
+"""Multi-rank Domain on ONE GPU against the reference's multi-rank Domain.
+
+P engine instances run as P host threads of this process over the in-process transport (cornerstone_octree_b200.domain
+LocalWorld; include/cstone_b200_domain.h), so the particle exchange, the merge re-sort, halo discovery, halo exchange and
+exchangeHalos run on the single-GPU test box.  The checker is the reference's own Domain<KeyType,T,CpuTag> on P
+thread-ranks (oracle/ref_domain.cpp, pinned by tests/test_ref_domain.py), driven with the same inputs as
+test/integration_mpi/domain_nranks.cpp:103-149 drives it.  Per rank and per sync, bit-exact:
+  box, replicated global leaf array, the assigned particle set (keys, x, y, z, h and a conserved property, in SFC order),
+  neighbour counts of every assigned particle and neighbour lists as sets of global particle ids, and the values
+  exchangeHalos delivers."""
+import numpy as np
+import pytest
+
+import gen
+from oracle import loader
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def make_cloud(name, n):
+    rng = np.random.default_rng(17)
+    if name == "gaussian":  # domain_nranks.cpp:57-101
+        lim, pbc = (-1.0, 1.0), (0, 0, 0)
+        x, y, z = gen.gaussian(n, lim, np.float64)
+        h = 0.6 * (0.05 + 0.2 * (x * x + y * y + z * z)) * np.cbrt(1000.0 / n)
+    elif name == "uniform-pbc":
+        lim, pbc = (0.0, 1.0), (1, 1, 1)
+        x, y, z = gen.uniform(n, lim, np.float64)
+        h = 0.5 * np.cbrt(3 * 40 / (4 * np.pi * n)) * (0.8 + 0.4 * rng.random(n))
+    elif name == "two-clusters":  # sparse space between dense clumps: leaves straddling rank boundaries
+        lim, pbc = (-1.0, 1.0), (0, 0, 0)
+        c = np.where(rng.random(n) < 0.5, -0.55, 0.55)
+        x, y, z = (np.clip(c + 0.08 * rng.standard_normal(n), -1, 1) for _ in range(3))
+        x[: n // 50] = rng.uniform(-1, 1, n // 50)  # a thin background
+        y[: n // 50] = rng.uniform(-1, 1, n // 50)
+        z[: n // 50] = rng.uniform(-1, 1, n // 50)
+        h = np.full(n, 0.5 * 0.16 * np.cbrt(3 * 40 / (4 * np.pi * n)))
+        h[: n // 50] = 0.08
+    else:
+        raise ValueError(name)
+    return x, y, z, h, lim, pbc
+
+
+class Ranks:
+    """P CUDA engines over the in-process transport + the reference Domain on P thread-ranks, fed the same slabs"""
+
+    def __init__(self, P, bucket, bucket_focus, lim, pbc, x, y, z, h):
+        import torch
+        from cornerstone_octree_b200 import ops
+        from cornerstone_octree_b200.domain import Domain, LocalWorld
+        self.P, self.n, self.lim, self.pbc = P, x.size, lim, pbc
+        bnd = tuple(loader.PERIODIC if p else loader.OPEN for p in pbc)
+        self.world = LocalWorld(P)
+        self.doms = [Domain(r, P, bucket, bucket_focus, 0.5, ops.make_box(lim, bnd)) for r in range(P)]
+        for d in self.doms:
+            d.set_local_world(self.world)
+        self.ref = loader.RefDomain(P, bucket, bucket_focus, 0.5, list(lim), pbc=pbc, nprops=1)
+        gid = np.arange(self.n, dtype=np.float64)
+        self.state = []
+        for r in range(P):
+            s = slice(r * self.n // P, (r + 1) * self.n // P)
+            self.ref.set(r, x[s], y[s], z[s], h[s], props=[gid[s]])
+            self.state.append([_dev(a[s]) for a in (x, y, z, h, gid)])
+        self.torch = torch
+
+    def sync(self):
+        def one(r):
+            x, y, z, h, g = self.state[r]
+            keys, sx, sy, sz, sh, (sg,) = self.doms[r].sync(x, y, z, h, [g])
+            self.state[r] = [sx, sy, sz, sh, sg]
+            return keys
+        self.keys = self.world.run(one)
+        self.ref.sync()
+
+    def displace(self, amp):
+        """the same displacement field, addressed by global particle id, on both sides (assigned particles only matter);
+        periodic dimensions are wrapped back into the box, as a client integrating particle motion does"""
+        rng = np.random.default_rng(23)
+        d = amp * rng.standard_normal((3, self.n))
+
+        def moved(c, k):
+            if self.pbc[k]:
+                lo, hi = self.lim
+                c = lo + np.mod(c - lo, hi - lo)
+                c = np.where(c >= hi, lo, c)
+            return c
+        for r in range(self.P):
+            dom = self.doms[r]
+            s, e = dom.start_index, dom.end_index
+            g = self.state[r][4][s:e].cpu().numpy().astype(np.int64)
+            inf = self.ref.info(r)
+            arr = self.ref.arrays(r)
+            gi = arr[5][inf["start"]:inf["end"]].astype(np.int64)
+            new = [a.copy() for a in arr[1:6]]
+            for k in range(3):
+                cur = self.state[r][k][s:e].cpu().numpy()
+                self.state[r][k][s:e] = _dev(moved(cur + d[k][g], k))
+                new[k][inf["start"]:inf["end"]] = moved(new[k][inf["start"]:inf["end"]] + d[k][gi], k)
+            self.ref.set(r, new[0], new[1], new[2], new[3], props=[new[4]])
+
+    def check(self, ngmax=200):
+        """compare every rank with the reference rank; returns the summed neighbour count (for an all-to-all check)"""
+        torch = self.torch
+        nref = self.ref.find_neighbors(ngmax)
+
+        def nb(r):
+            sx, sy, sz, sh, sg = self.state[r]
+            self.doms[r].exchange_halos([sg])
+            return self.doms[r].find_neighbors(sx, sy, sz, sh, ngmax)
+        nmine = self.world.run(nb)
+        # the reference leaves property halos undefined until exchangeHalos (domain/domain.hpp:158-165)
+        ref_g = []
+        for r in range(self.P):
+            inf, arr = self.ref.info(r), self.ref.arrays(r)
+            buf = np.full(inf["size"], -1.0)
+            buf[inf["start"]:inf["end"]] = arr[5][inf["start"]:inf["end"]]
+            ref_g.append(buf)
+        self.ref.exchange_halos(ref_g)
+        total = 0
+        for r in range(self.P):
+            dom, inf = self.doms[r], self.ref.info(r)
+            rk, rx, ry, rz, rh, rg = self.ref.arrays(r)
+            rg = ref_g[r]
+            s, e = dom.start_index, dom.end_index
+            a, b = inf["start"], inf["end"]
+            # box and replicated global tree
+            box = dom.box()
+            assert [box.limits[i] for i in range(6)] == list(inf["box"]), "box of rank %d" % r
+            leaves, counts, bounds = dom.global_tree()
+            assert np.array_equal(leaves, self.ref.trees(r)["global_leaves"]), "global tree of rank %d" % r
+            # assigned set, SFC order
+            assert e - s == b - a, "rank %d owns %d particles, reference %d" % (r, e - s, b - a)
+            k = self.keys[r].cpu().numpy().view(np.uint64)
+            assert np.array_equal(k[s:e], rk[a:b]), "assigned keys of rank %d" % r
+            mine = [t.cpu().numpy() for t in self.state[r]]
+            for name, m, f in zip("xyzhg", mine, (rx, ry, rz, rh, rg)):
+                assert np.array_equal(m[s:e], f[a:b]), "assigned %s of rank %d" % (name, r)
+            # all keys (halos included) sorted and consistent with the coordinates
+            assert np.all(k[1:] >= k[:-1])
+            # halo values delivered by exchangeHalos belong to the halo coordinates
+            g = mine[4].astype(np.int64)
+            assert g.min() >= 0 and g.max() < self.n
+            # neighbours: counts equal, lists equal as sets of global ids
+            nb_m, nc_m = (t.cpu().numpy().view(np.uint32) for t in nmine[r])
+            nb_r, nc_r = nref[r]
+            assert np.array_equal(nc_m, nc_r), "neighbour counts of rank %d" % r
+            gm = np.where(np.arange(ngmax)[None, :] < nc_m[:, None], g[nb_m.astype(np.int64) % g.size], -1)
+            gr_all = rg.astype(np.int64)
+            gr = np.where(np.arange(ngmax)[None, :] < nc_r[:, None], gr_all[nb_r.astype(np.int64) % gr_all.size], -1)
+            full = nc_m <= ngmax
+            assert np.array_equal(np.sort(gm[full], axis=1), np.sort(gr[full], axis=1)), "neighbour sets of rank %d" % r
+            total += int(nc_m.sum())
+        return total
+
+    def halo_coordinates_match_ids(self, x, y, z):
+        for r in range(self.P):
+            sx, sy, sz, sh, sg = [t.cpu().numpy() for t in self.state[r]]
+            g = sg.astype(np.int64)
+            assert np.array_equal(sx, x[g]) and np.array_equal(sy, y[g]) and np.array_equal(sz, z[g])
+
+    def close(self):
+        for d in self.doms:
+            d.close()
+        self.world.close()
+        self.ref.close()
+
+
+CASES = [("gaussian", 2, 20000, 64, 8), ("gaussian", 4, 20000, 50, 10), ("uniform-pbc", 4, 30000, 64, 16),
+         ("two-clusters", 3, 24000, 64, 8), ("gaussian", 8, 40000, 128, 16)]
+
+
+@pytest.mark.parametrize("cloud,P,n,bucket,bucket_focus", CASES, ids=["%s-P%d" % (c[0], c[1]) for c in CASES])
+def test_ranks_match_reference_domain(cloud, P, n, bucket, bucket_focus):
+    if not loader.refdom_available():
+        pytest.skip("oracle/_ref/liboracle_refdom.so did not travel")
+    x, y, z, h, lim, pbc = make_cloud(cloud, n)
+    rk = Ranks(P, bucket, bucket_focus, lim, pbc, x, y, z, h)
+    try:
+        rk.sync()  # first sync: unsorted slabs, everything moves (full-sort path)
+        rk.check()
+        rk.halo_coordinates_match_ids(x, y, z)
+        for amp in (0.002, 0.01):  # steady state: few particles change rank (merge path)
+            rk.displace(amp)
+            rk.sync()
+            rk.check()
+    finally:
+        rk.close()
+
+
+def test_ranks_with_fewer_particles_than_the_bucket():
+    """every rank holds fewer particles than bucketSizeFocus: the only focus leaf is the root and straddles every rank
+    boundary (such leaves used to publish no halo box, neighbour lists came out truncated)"""
+    if not loader.refdom_available():
+        pytest.skip("oracle/_ref/liboracle_refdom.so did not travel")
+    P, n = 4, 24
+    x, y, z = gen.uniform(n, (0.0, 1.0), np.float64)
+    h = np.full(n, 0.3)
+    rk = Ranks(P, 16, 8, (0.0, 1.0), (0, 0, 0), x, y, z, h)
+    try:
+        rk.sync()
+        total = rk.check(ngmax=64)
+        d2 = sum((c[None, :] - c[:, None]) ** 2 for c in (x, y, z))
+        assert total == int((d2 < (2 * h[:, None]) ** 2).sum() - n)
+    finally:
+        rk.close()
