@@ -132,7 +132,7 @@ class HotPath:
         self._mark("find_halos")
         # a15 neighbours
         if self.with_neighbors:
-            ops.find_neighbors(xs, ys, zs, hs, 0, n, box, v, self._layout, self._centers, self._sizes, self.ngmax,
+            ops.find_neighbors(xs, ys, zs, hs, 0, n, box, v, self._layout[:L + 1], self._centers, self._sizes, self.ngmax,
                                self.neighbors, self.neighbors_count)
         self._mark("find_neighbors")
         return L
