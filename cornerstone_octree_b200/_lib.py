@@ -190,6 +190,9 @@ _DOMAIN_PROTOS = {
     "set_comm": (_i, [_vp, _vp]),
     "set_fields_ready_event": (_i, [_vp, _vp]),
     "set_sfc_kind": (_i, [_vp, _i]),
+    "set_end_index": (_i, [_vp, _u64]),
+    "set_halo_factor": (_i, [_vp, _f]),
+    "cells": (_i, [_vp, _vp]),
     "sync_begin": (_i64, [_vp, _u64, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "sync_finish": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "exchange_halos": (_i, [_vp, _i, _vp, _vp]),

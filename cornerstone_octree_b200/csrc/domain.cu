@@ -449,7 +449,11 @@ __global__ void __launch_bounds__(256) expandSendListKernel(const unsigned char*
     }
 }
 
-//! dst[i] = src[idx[i] + offset] for 4- or 8-byte elements (pack of halo messages)
+struct Elem12
+{
+    uint32_t v[3];
+};
+//! dst[i] = src[idx[i] + offset] for 4-, 8-, 12- or 16-byte elements (pack of halo messages)
 template<class E>
 __global__ void __launch_bounds__(256)
     packKernel(const uint32_t* __restrict__ idx, uint32_t n, uint32_t offset, const E* __restrict__ src, E* __restrict__ dst)
@@ -489,6 +493,37 @@ public:
     {
         if (kind != CSTONE_SFC_MORTON && kind != CSTONE_SFC_HILBERT) return CSTONE_E_INVALID_ARGUMENT;
         sfcKind_ = kind;
+        return 0;
+    }
+    //! [ref: domain/domain.hpp:396 setEndIndex] particles appended behind the assigned range join it at the next sync
+    int setEndIndex(uint64_t i)
+    {
+        if (i < start_ || i > nTotal_) return CSTONE_E_INVALID_ARGUMENT;
+        end_ = i;
+        return 0;
+    }
+    //! [ref: domain/domain.hpp:412 setHaloFactor, halos/halos.hpp:162] halo search radius = 2 * factor * max h of the leaf
+    int setHaloFactor(float f)
+    {
+        if (!(f > 0.f)) return CSTONE_E_INVALID_ARGUMENT;
+        haloFactor_ = f;
+        return 0;
+    }
+    //! [ref: domain/domain.hpp:404-406 startCell / endCell] leaves of the search tree that hold the assigned particles
+    int cells(int32_t* out2)
+    {
+        if (!search_.numNodes || boundaries_.empty()) return CSTONE_E_INVALID_ARGUMENT;
+        CSB_TRY(small_.reserve(cstone_b200_reduce_temp_bytes() + 256));
+        uint64_t r[2];
+        const K b[2] = {boundaries_[rank_], boundaries_[rank_ + 1]};
+        for (int k = 0; k < 2; ++k)
+        {
+            if constexpr (sizeof(K) == 8)
+                CSB_TRY(cstone_b200_lower_bound_u64(search_.treeA.template as<uint64_t>(), size_t(search_.numNodes) + 1, b[k], &r[k], small_.p, s_));
+            else
+                CSB_TRY(cstone_b200_lower_bound_u32(search_.treeA.template as<uint32_t>(), size_t(search_.numNodes) + 1, b[k], &r[k], small_.p, s_));
+        }
+        out2[0] = int32_t(r[0]), out2[1] = int32_t(r[1]);
         return 0;
     }
     //! device time between the stage markers of the last sync (ms); kNumMarks - 1 values
@@ -558,6 +593,7 @@ private:
     std::unique_ptr<Comm> comm_;
     cudaEvent_t fieldsReady_ = nullptr;
     int sfcKind_      = CSTONE_SFC_HILBERT;
+    float haloFactor_ = 1.0f;
     cudaStream_t s_   = nullptr; // legacy default stream: ordered with the caller's default-stream work
 
     // particle state
@@ -741,7 +777,8 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         inStart = start_, inEnd = end_;
     }
     for (int a = 0; a < nprops; ++a)
-        if ((propBytes[a] != 4 && propBytes[a] != 8) || !props[a]) return CSTONE_E_INVALID_ARGUMENT;
+        if ((propBytes[a] != 4 && propBytes[a] != 8 && propBytes[a] != 12 && propBytes[a] != 16) || !props[a])
+            return CSTONE_E_INVALID_ARGUMENT; // [ref: domain/buffer_description.hpp:98-110: elements up to 16 bytes]
     const size_t np = size_t(inEnd - inStart);
     const int na    = 4 + nprops;
     int eb[4 + kMaxProps];
@@ -993,7 +1030,7 @@ int Engine<K, T>::discoverHalos()
     lap();
     // b. search radius per leaf [ref: halos/halos.hpp:148-160]
     CSB_TRY(radii_.reserve(4 * size_t(L) + 256));
-    CSB_TRY((Api<K, T>::haloRadii(shAssigned_.template as<T>(), layout_.template as<uint32_t>(), size_t(L), 2.0f,
+    CSB_TRY((Api<K, T>::haloRadii(shAssigned_.template as<T>(), layout_.template as<uint32_t>(), size_t(L), 2.0f * haloFactor_,
                                   radii_.template as<float>(), s_)));
 
     // c. halo boxes of my surface leaves
@@ -1141,7 +1178,8 @@ int Engine<K, T>::exchangeHalos(int narrays, void* const* arrays, const int* ele
     std::vector<size_t> off(narrays);
     for (int a = 0; a < narrays; ++a)
     {
-        if ((elemBytes[a] != 4 && elemBytes[a] != 8) || !arrays[a]) return CSTONE_E_INVALID_ARGUMENT;
+        if ((elemBytes[a] != 4 && elemBytes[a] != 8 && elemBytes[a] != 12 && elemBytes[a] != 16) || !arrays[a])
+            return CSTONE_E_INVALID_ARGUMENT;
         off[a] = total;
         total += (size_t(nHaloSend_) * elemBytes[a] + 255) / 256 * 256;
     }
@@ -1151,7 +1189,15 @@ int Engine<K, T>::exchangeHalos(int narrays, void* const* arrays, const int* ele
         for (int a = 0; a < narrays; ++a)
         {
             unsigned grid = gridFor(size_t(nHaloSend_), 256);
-            if (elemBytes[a] == 8)
+            if (elemBytes[a] == 16)
+                packKernel<uint4><<<grid, 256, 0, s_>>>(sendIdx_.template as<uint32_t>(), uint32_t(nHaloSend_), uint32_t(start_),
+                                                       reinterpret_cast<const uint4*>(arrays[a]),
+                                                       reinterpret_cast<uint4*>(haloPack_.template as<char>() + off[a]));
+            else if (elemBytes[a] == 12)
+                packKernel<Elem12><<<grid, 256, 0, s_>>>(sendIdx_.template as<uint32_t>(), uint32_t(nHaloSend_), uint32_t(start_),
+                                                        reinterpret_cast<const Elem12*>(arrays[a]),
+                                                        reinterpret_cast<Elem12*>(haloPack_.template as<char>() + off[a]));
+            else if (elemBytes[a] == 8)
                 packKernel<uint64_t><<<grid, 256, 0, s_>>>(sendIdx_.template as<uint32_t>(), uint32_t(nHaloSend_), uint32_t(start_),
                                                           reinterpret_cast<const uint64_t*>(arrays[a]),
                                                           reinterpret_cast<uint64_t*>(haloPack_.template as<char>() + off[a]));
@@ -1274,6 +1320,21 @@ void cstone_b200_local_world_destroy(void* world) { delete static_cast<csb::Loca
     {                                                                                                                  \
         if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
         return CSB_ENGINE(K, T, d)->setSfcKind(kind);                                                                  \
+    }                                                                                                                  \
+    int cstone_b200_domain_set_end_index_##KS##_##TS(cstone_b200_domain* d, uint64_t end)                              \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return CSB_ENGINE(K, T, d)->setEndIndex(end);                                                                  \
+    }                                                                                                                  \
+    int cstone_b200_domain_set_halo_factor_##KS##_##TS(cstone_b200_domain* d, float factor)                            \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return CSB_ENGINE(K, T, d)->setHaloFactor(factor);                                                             \
+    }                                                                                                                  \
+    int cstone_b200_domain_cells_##KS##_##TS(cstone_b200_domain* d, int32_t* startEnd2)                                \
+    {                                                                                                                  \
+        if (!d || !startEnd2) return CSTONE_E_INVALID_ARGUMENT;                                                        \
+        return CSB_ENGINE(K, T, d)->cells(startEnd2);                                                                  \
     }                                                                                                                  \
     int cstone_b200_domain_set_fields_ready_event_##KS##_##TS(cstone_b200_domain* d, void* event)                      \
     {                                                                                                                  \

@@ -277,7 +277,17 @@ int cstone_b200_gather_multi(const uint32_t* map, size_t n, int numArrays, const
         int want = pass == 0 ? 4 : 8;
         for (int k = 0; k < numArrays; ++k)
         {
-            if (elemBytes[k] != 4 && elemBytes[k] != 8) return CSTONE_E_INVALID_ARGUMENT;
+            if (elemBytes[k] != 4 && elemBytes[k] != 8)
+            {
+                // wider rows (12 - 32 bytes, util::array properties): one single-array gather each, in the first pass
+                if (pass == 0)
+                {
+                    if (!src[k] || !dst[k]) return CSTONE_E_INVALID_ARGUMENT;
+                    int st = csb::permute<false>(map, n, src[k], dst[k], elemBytes[k], csb::asStream(stream));
+                    if (st) return st;
+                }
+                continue;
+            }
             if (elemBytes[k] != want) continue;
             if (!src[k] || !dst[k]) return CSTONE_E_INVALID_ARGUMENT;
             a.src[pos] = src[k];
@@ -286,6 +296,7 @@ int cstone_b200_gather_multi(const uint32_t* map, size_t n, int numArrays, const
             (pass == 0 ? a.n4 : a.n8)++;
         }
     }
+    if (pos == 0) return 0;
     bool aligned = (reinterpret_cast<uintptr_t>(map) & 15u) == 0;
     for (int k = 0; k < a.n8; ++k)
         aligned = aligned && (reinterpret_cast<uintptr_t>(a.dst[k]) & 15u) == 0;

@@ -22,6 +22,14 @@ def _check(st, where):
         raise CstoneError(int(st), "cstone_b200_domain_" + where)
 
 
+def _row_bytes(t):
+    """bytes per particle of a 1-D or row-per-particle tensor"""
+    n = 1
+    for d in t.shape[1:]:
+        n *= int(d)
+    return t.element_size() * n
+
+
 class Domain:
     """Domain(rank, num_ranks, bucket_size, bucket_size_focus, theta, box)  — same arguments as the reference"""
 
@@ -93,7 +101,9 @@ class Domain:
         n_in = x.numel()
         k = len(props)
         parr = (C.c_void_p * max(k, 1))(*[p.data_ptr() for p in props])
-        pbytes = (C.c_int * max(k, 1))(*[p.element_size() for p in props])
+        # a property is one value per particle or one ROW per particle (2-D tensor): 4, 8, 12 or 16 bytes per particle
+        # [ref: domain/buffer_description.hpp:98-110: util::array elements travel like scalars]
+        pbytes = (C.c_int * max(k, 1))(*[_row_bytes(p) for p in props])
         if fields_ready is not None:
             _check(_fn("set_fields_ready_event", self.bits, self.fd)(self._h, C.c_void_p(fields_ready.cuda_event)),
                    "set_fields_ready_event")
@@ -104,7 +114,7 @@ class Domain:
         dev = x.device
         keys = torch.empty(n_new, dtype=ops.KEY_TORCH[self.bits], device=dev)
         out = [torch.empty(n_new, dtype=x.dtype, device=dev) for _ in range(4)]
-        pout = [torch.empty(n_new, dtype=p.dtype, device=dev) for p in props]
+        pout = [torch.empty((n_new,) + tuple(p.shape[1:]), dtype=p.dtype, device=dev) for p in props]
         oarr = (C.c_void_p * max(k, 1))(*[p.data_ptr() for p in pout])
         _check(_fn("sync_finish", self.bits, self.fd)(self._h, ops._p(keys), ops._p(out[0]), ops._p(out[1]), ops._p(out[2]),
                                                     ops._p(out[3]), oarr), "sync_finish")
@@ -116,7 +126,7 @@ class Domain:
         if k == 0:
             return
         arr = (C.c_void_p * k)(*[a.data_ptr() for a in arrays])
-        eb = (C.c_int * k)(*[a.element_size() for a in arrays])
+        eb = (C.c_int * k)(*[_row_bytes(a) for a in arrays])
         _check(_fn("exchange_halos", self.bits, self.fd)(self._h, k, arr, eb), "exchange_halos")
 
     # ---- accessors [ref: domain/domain.hpp:389-437]
@@ -132,6 +142,20 @@ class Domain:
     @property
     def end_index(self):
         return self._info()[1]
+
+    def set_end_index(self, i):
+        """[ref: domain/domain.hpp:396 setEndIndex] particles written behind the assigned range join it at the next sync"""
+        _check(_fn("set_end_index", self.bits, self.fd)(self._h, int(i)), "set_end_index")
+
+    def set_halo_factor(self, factor):
+        """[ref: domain/domain.hpp:412 setHaloFactor] halo search radius = 2 * factor * max h of a leaf"""
+        _check(_fn("set_halo_factor", self.bits, self.fd)(self._h, float(factor)), "set_halo_factor")
+
+    def cells(self):
+        """[ref: domain/domain.hpp:404-406 startCell / endCell] leaves of the search tree inside the assigned SFC range"""
+        c = (C.c_int32 * 2)()
+        _check(_fn("cells", self.bits, self.fd)(self._h, c), "cells")
+        return int(c[0]), int(c[1])
 
     @property
     def n_particles(self):

@@ -7,6 +7,7 @@
 
 #include <cstddef>
 #include <utility>
+#include <type_traits>
 #include <vector>
 
 #include "box.hpp"
@@ -93,6 +94,23 @@ public:
 private:
     T* p_             = nullptr;
     std::size_t size_ = 0, cap_ = 0;
+};
+
+//! @brief pointer + length of a device array owned by a tree or a Domain, valid until its next update / sync
+template<class T>
+struct DeviceSpan
+{
+    const T* ptr;
+    std::size_t n;
+    const T* data() const { return ptr; }
+    std::size_t size() const { return n; }
+    //! copy to the host
+    std::vector<std::remove_const_t<T>> toHost() const
+    {
+        std::vector<std::remove_const_t<T>> h(n);
+        if (n) detail::check(cstone_b200_device_memcpy(h.data(), ptr, n * sizeof(T), 1), "DeviceSpan download");
+        return h;
+    }
 };
 
 template<class T>

@@ -39,16 +39,18 @@ template<class T, class KeyType>
 struct OctreeNsView
 {
     TreeNodeIndex numLeafNodes;
-    TreeNodeIndex numInternalNodes;
-    TreeNodeIndex numNodes;
     const KeyType* prefixes;
     const TreeNodeIndex* childOffsets;
     const TreeNodeIndex* internalToLeaf;
     const TreeNodeIndex* levelRange;
     const KeyType* leaves;
+    //! index of the first particle of each leaf
     const LocalIndex* layout;
+    //! geometrical node centres and half sizes
     const Vec3<T>* centers;
     const Vec3<T>* sizes;
+    //! enlarges the target boxes for slightly outdated trees; 1.0 for converged trees (the Domain's are)
+    float searchExtFactor{1.0};
 };
 
 namespace detail
@@ -64,6 +66,9 @@ struct DomainApi;
         static constexpr auto destroy       = cstone_b200_domain_destroy_##KS##_##TS;                                  \
         static constexpr auto setComm       = cstone_b200_domain_set_comm_##KS##_##TS;                                 \
         static constexpr auto setSfcKind    = cstone_b200_domain_set_sfc_kind_##KS##_##TS;                             \
+        static constexpr auto setEndIndex   = cstone_b200_domain_set_end_index_##KS##_##TS;                            \
+        static constexpr auto setHaloFactor = cstone_b200_domain_set_halo_factor_##KS##_##TS;                          \
+        static constexpr auto cells         = cstone_b200_domain_cells_##KS##_##TS;                                    \
         static constexpr auto syncBegin     = cstone_b200_domain_sync_begin_##KS##_##TS;                               \
         static constexpr auto syncFinish    = cstone_b200_domain_sync_finish_##KS##_##TS;                              \
         static constexpr auto exchangeHalos = cstone_b200_domain_exchange_halos_##KS##_##TS;                           \
@@ -153,8 +158,8 @@ public:
         static_assert(sizeof(typename KeyVec::value_type) == sizeof(K), "key vector does not match KeyType");
         static_assert(std::is_same_v<typename VectorX::value_type, T>, "coordinate vectors must hold T");
         static_assert(std::is_same_v<typename VectorH::value_type, T>, "h must hold T");
-        static_assert(((sizeof(typename Vectors1::value_type) == 4 || sizeof(typename Vectors1::value_type) == 8) && ...),
-                      "property element size must be 4 or 8 bytes");
+        static_assert(((sizeof(typename Vectors1::value_type) % 4 == 0 && sizeof(typename Vectors1::value_type) <= 16) && ...),
+                      "property elements: 4, 8, 12 or 16 bytes (domain/buffer_description.hpp:98-110)");
 
         const std::size_t n = x.size();
         std::apply([&](auto&... p) { checkSizesEqual(n, y, z, h, p...); }, particleProperties);
@@ -171,9 +176,15 @@ public:
         if (nNew == CSTONE_E_SIZE_MISMATCH) throw std::runtime_error("Domain sync: input array sizes are inconsistent\n");
         detail::check(nNew < 0 ? nNew : 0, "Domain::sync");
 
-        // contents are rewritten by syncFinish; only capacity matters
-        particleKeys.resize(nNew), x.resize(nNew), y.resize(nNew), z.resize(nNew), h.resize(nNew);
-        std::apply([&](auto&... p) { (p.resize(nNew), ...); }, particleProperties);
+        // contents are rewritten by syncFinish; only capacity matters.  Growth policy of the reference's reallocate
+        // (util/reallocate.hpp): a vector that has to grow reserves allocGrowthRate_ times the new size
+        auto grow = [&](auto& v)
+        {
+            if (v.capacity() < std::size_t(nNew)) v.reserve(std::size_t(double(nNew) * allocGrowthRate_));
+            v.resize(nNew);
+        };
+        grow(particleKeys), grow(x), grow(y), grow(z), grow(h);
+        std::apply([&](auto&... p) { (grow(p), ...); }, particleProperties);
         i = 0;
         std::apply([&](auto&... p) { ((out[i++] = p.data()), ...); }, particleProperties);
         detail::check(Api::syncFinish(d_, reinterpret_cast<K*>(particleKeys.data()), x.data(), y.data(), z.data(),
@@ -197,19 +208,39 @@ public:
 
     [[nodiscard]] LocalIndex startIndex() const { return LocalIndex(info_[0]); }
     [[nodiscard]] LocalIndex endIndex() const { return LocalIndex(info_[1]); }
+    //! [ref: domain/domain.hpp:396] set the index of the last particle (used to increase the number of particles)
+    void setEndIndex(const std::size_t i)
+    {
+        detail::check(Api::setEndIndex(d_, i), "Domain::setEndIndex");
+        info_[1] = int64_t(i);
+    }
     [[nodiscard]] LocalIndex nParticles() const { return endIndex() - startIndex(); }
     [[nodiscard]] LocalIndex nParticlesWithHalos() const { return LocalIndex(info_[2]); }
     const Box<T>& box() const { return box_; }
+    //! [ref: domain/domain.hpp:404-406] first / one-past-last leaf of the search tree inside the assigned SFC range
+    TreeNodeIndex startCell() const { return cellRange()[0]; }
+    TreeNodeIndex endCell() const { return cellRange()[1]; }
+    //! [ref: domain/domain.hpp:408] particle offsets of each leaf of the search tree (device memory, numLeafNodes + 1)
+    DeviceSpan<const LocalIndex> layout() const
+    {
+        const void* p[10];
+        detail::check(Api::treeView(d_, p), "Domain::layout");
+        return {static_cast<const LocalIndex*>(p[2]), std::size_t(info_[3]) + 1};
+    }
+    //! [ref: domain/domain.hpp:411] accepted for source compatibility: this engine converges both trees in every sync
+    void setTreeConv(bool flag) { convergeTrees_ = flag; }
+    //! [ref: domain/domain.hpp:412] halo search radius = 2 * factor * max h of a leaf
+    void setHaloFactor(float factor) { detail::check(Api::setHaloFactor(d_, factor), "Domain::setHaloFactor"); }
+    //! [ref: domain/domain.hpp:413] over-allocation of the particle arrays when they have to grow
+    void setGrowthAllocRate(float factor) { allocGrowthRate_ = factor; }
 
     //! [ref: domain/domain.hpp:424-437] search tree over assigned + halo particles (device pointers)
     OctreeNsView<T, KeyType> octreeProperties() const
     {
         const void* p[10];
         detail::check(Api::treeView(d_, p), "Domain::octreeProperties");
-        TreeNodeIndex L = TreeNodeIndex(info_[3]), M = TreeNodeIndex(info_[4]);
+        TreeNodeIndex L = TreeNodeIndex(info_[3]);
         return {L,
-                M - L,
-                M,
                 static_cast<const KeyType*>(p[3]),
                 static_cast<const TreeNodeIndex*>(p[4]),
                 static_cast<const TreeNodeIndex*>(p[5]),
@@ -271,6 +302,13 @@ private:
             if (s != value) throw std::runtime_error("Domain sync: input array sizes are inconsistent\n");
     }
 
+    std::array<TreeNodeIndex, 2> cellRange() const
+    {
+        int32_t c[2];
+        detail::check(Api::cells(d_, c), "Domain::startCell");
+        return {c[0], c[1]};
+    }
+
     void refresh()
     {
         detail::check(Api::info(d_, info_), "Domain::info");
@@ -283,6 +321,8 @@ private:
     Box<T> box_;
     cstone_b200_domain* d_ = nullptr;
     void* ownedComm_       = nullptr;
+    bool convergeTrees_    = false;
+    float allocGrowthRate_ = 1.05f;
     int64_t info_[8]       = {0, 0, 0, 0, 0, 0, 0, 0};
 };
 

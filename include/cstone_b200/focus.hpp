@@ -165,23 +165,6 @@ CSB_FOCUS_TREE_FACADE(k64, uint64_t)
 #undef CSB_FOCUS_TREE_FACADE
 } // namespace detail
 
-//! @brief pointer + length of a device array owned by the tree, valid until its next update
-template<class T>
-struct DeviceSpan
-{
-    const T* ptr;
-    std::size_t n;
-    const T* data() const { return ptr; }
-    std::size_t size() const { return n; }
-    //! copy to the host
-    std::vector<T> toHost() const
-    {
-        std::vector<T> h(n);
-        if (n) detail::check(cstone_b200_device_memcpy(h.data(), ptr, n * sizeof(T), 1), "DeviceSpan download");
-        return h;
-    }
-};
-
 /*! @brief A fully traversable octree, locally focused w.r.t. a MinMac criterion (single rank), device resident
  *
  * update() = one step of the reference class: rebalance by particle counts inside [focusStart, focusEnd) and by the

@@ -58,7 +58,16 @@ void cstone_b200_local_world_destroy(void* world);
     /* CSTONE_SFC_HILBERT (default, what the reference's Domain hard-wires: sfc/sfc.hpp:54-55) or CSTONE_SFC_MORTON;  \
      * call before the first sync */                                                                                   \
     int cstone_b200_domain_set_sfc_kind_##KS##_##TS(cstone_b200_domain* d, int sfc_kind);                              \
-    /* [ref: domain/domain.hpp:196-243 sync]; props: HOST array of nprops device pointers, element sizes 4 or 8 */    \
+    /* [ref: domain/domain.hpp:396 setEndIndex] particles the caller appended behind the assigned range            \
+     * (start <= end <= n_total) take part in the next sync */                                                         \
+    int cstone_b200_domain_set_end_index_##KS##_##TS(cstone_b200_domain* d, uint64_t end);                             \
+    /* [ref: domain/domain.hpp:412 setHaloFactor; halos/halos.hpp:162] halo radius = 2 * factor * max h per leaf */   \
+    int cstone_b200_domain_set_halo_factor_##KS##_##TS(cstone_b200_domain* d, float factor);                           \
+    /* [ref: domain/domain.hpp:404-406 startCell / endCell] first and one-past-last search-tree leaf of the assigned  \
+     * SFC range; start_end2 is a HOST array; synchronises the stream */                                               \
+    int cstone_b200_domain_cells_##KS##_##TS(cstone_b200_domain* d, int32_t* start_end2);                              \
+    /* [ref: domain/domain.hpp:196-243 sync]; props: HOST array of nprops device pointers, element sizes 4, 8, 12 or  \
+     * 16 bytes [ref: domain/buffer_description.hpp:98-110] */                                                          \
     int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n_in, const T* x, const T* y,    \
                                                       const T* z, const T* h, int nprops, const void* const* props,    \
                                                       const int* prop_bytes);                                          \

@@ -162,7 +162,15 @@ static void run(int rank, int nRanks, const std::array<char, 128>& id, LocalInde
         EXPECT(badCount == 0);
         EXPECT(badList == 0);
         auto view = domain.octreeProperties();
-        EXPECT(view.numLeafNodes > 0 && view.numNodes == view.numLeafNodes + view.numInternalNodes);
+        EXPECT(view.numLeafNodes > 0 && view.searchExtFactor == 1.0f);
+        // the reference's accessors: layout(), startCell(), endCell() [ref: domain/domain.hpp:404-408]
+        {
+            auto lay = domain.layout().toHost();
+            EXPECT(lay.size() == std::size_t(view.numLeafNodes) + 1 && lay.front() == 0 && lay.back() == n);
+            TreeNodeIndex c0 = domain.startCell(), c1 = domain.endCell();
+            EXPECT(0 <= c0 && c0 < c1 && c1 <= view.numLeafNodes);
+            EXPECT(lay[c0] == a && lay[c1] == b);
+        }
         std::printf("RANK %d step %d assigned %u total %u halosend %zu halorecv %zu leaves %d ncsum %llu\n", rank, step,
                     b - a, n, domain.numHaloSend(), domain.numHaloRecv(), view.numLeafNodes,
                     (unsigned long long)ncSum);

@@ -208,3 +208,75 @@ def test_ranks_with_fewer_particles_than_the_bucket():
         assert total == int((d2 < (2 * h[:, None]) ** 2).sum() - n)
     finally:
         rk.close()
+
+
+def test_wide_properties_accessors_and_growth():
+    """element sizes of 12 and 16 bytes through sync and exchangeHalos [ref: domain/buffer_description.hpp:98-110],
+    startCell / endCell / layout, setHaloFactor and setEndIndex [ref: domain/domain.hpp:396-413] on 3 thread-ranks"""
+    import torch
+    from cornerstone_octree_b200 import ops
+    from cornerstone_octree_b200.domain import Domain, LocalWorld
+    P, n = 3, 18000
+    x, y, z = gen.uniform(n, (0.0, 1.0), np.float64)
+    h = np.full(n, 0.5 * np.cbrt(3 * 40 / (4 * np.pi * n)))
+    gid = np.arange(n, dtype=np.float64)
+    world = LocalWorld(P)
+    doms = [Domain(r, P, 64, 16, 0.5, ops.make_box((0.0, 1.0))) for r in range(P)]
+    for d in doms:
+        d.set_local_world(world)
+
+    def rows(g):  # 16- and 12-byte rows that are functions of the particle id
+        g = g.to(torch.float32)
+        return torch.stack([g, g + 0.5, -g, torch.full_like(g, 7.0)], 1).contiguous(), torch.stack([2 * g, g - 1, g * g % 97], 1).contiguous()
+
+    state = []
+    for r in range(P):
+        s = slice(r * n // P, (r + 1) * n // P)
+        g = _dev(gid[s])
+        w4, w3 = rows(g)
+        state.append([_dev(x[s]), _dev(y[s]), _dev(z[s]), _dev(h[s]), g, w4, w3])
+
+    def one(r):
+        sx, sy, sz, sh, g, w4, w3 = state[r]
+        keys, sx, sy, sz, sh, (g, w4, w3) = doms[r].sync(sx, sy, sz, sh, [g, w4, w3])
+        state[r] = [sx, sy, sz, sh, g, w4, w3]
+        doms[r].exchange_halos([g, w4, w3])
+        return keys
+    try:
+        world.run(one)
+        halos0 = []
+        for r in range(P):
+            d = doms[r]
+            sx, sy, sz, sh, g, w4, w3 = state[r]
+            e4, e3 = rows(g)
+            assert torch.equal(w4, e4) and torch.equal(w3, e3), "wide rows of rank %d do not follow their particles" % r
+            assert np.array_equal(sx.cpu().numpy(), x[g.cpu().numpy().astype(np.int64)])
+            c0, c1 = d.cells()
+            layout = d.tree_arrays()["layout"].cpu().numpy()
+            assert 0 <= c0 < c1 < layout.size and layout[c0] == d.start_index and layout[c1] == d.end_index
+            halos0.append(d.n_particles_with_halos - d.n_particles)
+        # wider halo search: no rank receives fewer halos
+        for d in doms:
+            d.set_halo_factor(1.6)
+        world.run(one)
+        for r in range(P):
+            assert doms[r].n_particles_with_halos - doms[r].n_particles >= halos0[r]
+            g = state[r][4]
+            assert torch.equal(state[r][5], rows(g)[0])
+        assert sum(halos0) < sum(d.n_particles_with_halos - d.n_particles for d in doms)
+        # rank 0 creates k particles in the slots behind its assigned range and raises its end index
+        d0, k = doms[0], 5
+        e = d0.end_index
+        assert d0.n_particles_with_halos - e >= k
+        for a, v in zip(state[0][:4], (0.111, 0.222, 0.333, float(h[0]))):
+            a[e:e + k] = v + 1e-3 * torch.arange(k, device="cuda", dtype=a.dtype) * (0 if a is state[0][3] else 1)
+        state[0][4][e:e + k] = torch.arange(n, n + k, device="cuda", dtype=torch.float64)
+        state[0][5], state[0][6] = rows(state[0][4])
+        d0.set_end_index(e + k)
+        world.run(one)
+        ids = np.concatenate([state[r][4][doms[r].start_index:doms[r].end_index].cpu().numpy() for r in range(P)])
+        assert ids.size == n + k and np.array_equal(np.sort(ids), np.arange(n + k))
+    finally:
+        for d in doms:
+            d.close()
+        world.close()
