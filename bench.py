@@ -4,17 +4,21 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-One "step" = one pass of the whole hot path over one rank's particles:
-  computeSfcKeys -> sort (key + permutation) -> gather x,y,z,h -> cornerstone leaf array (built from the root)
-  -> internal-tree linking -> node centres -> layout -> halo radii -> findHalos (8 virtual ranks, every leaf searched
-  once as a local leaf) -> findNeighbors(ngmax) over all particles.
+One "step" = one steady-state pass of the hot path over every rank's particles: a small deterministic drift, then
+  Domain::sync (box, keys, sort, global tree + assignment, particle exchange, halo discovery + exchange, tree update
+  from the previous step's tree, linking, centres) and findNeighbors(ngmax) over the assigned particles
+  (+ findHalos for 8 virtual ranks at N = 1, BASELINE configs[1]).
 Workload at N=1: BASELINE.json configs[1] — 32 M uniform particles, u64 Hilbert keys, double, bucket 64 — with the
-metric's findNeighbors (ngmax 150, ~100 neighbours per particle) appended.
+metric's findNeighbors (ngmax 150, ~100 neighbours per particle) appended.  --fields 4 adds the four conserved
+double fields of configs[3]; --dist plummer is configs[2].
 
 The JSON line follows the contract in the task text: `value` is device-resident throughput, `e2e` goes through the
 C ABI from pinned HOST buffers (H2D of x,y,z,h and D2H of the results inside the timed region), `roofline` is the
-dominant kernel against MEASURED_PEAKS.json, `cpu_baseline` is the reference CPU code (oracle/_ref) timed on the
-host cores on a bounded sample.  `--impl reference` times only that CPU code (rank 0).
+dominant kernel against MEASURED_PEAKS.json, `check` is correctness evidence gathered inside this run.
+Reference arm (`--impl reference`, and the `cpu_baseline` leg of the default run at N = 1): the UNMODIFIED reference
+class Domain<KeyType,T,CpuTag>::sync + findNeighbors (oracle/_ref/liboracle_refdom.so: reference headers over a
+thread-rank mpi.h) on the host cores, one thread-rank per GPU of the run, the same generator, drift and steady-state
+stepping; at most --ref-total particles in total (32 M: the whole N = 1 workload).
 """
 import argparse
 import json
@@ -43,11 +47,22 @@ NEIGHBOR_TRAFFIC_BYTES = 23_385_864_000  # dram read (8.688 GB) + write (14.698 
 
 
 # ------------------------------------------------------------------------------------------------ inputs
+def mt19937_uniform(n, lo, hi, bg):
+    """n draws of std::uniform_real_distribution<double>(lo, hi) from a std::mt19937 (libstdc++): generate_canonical
+    takes two 32-bit outputs g1, g2 and returns (g1 + g2 * 2^32) / 2^64 in double arithmetic"""
+    raw = bg.random_raw(2 * n).astype(np.float64)
+    u = (raw[0::2] + raw[1::2] * 4294967296.0) / 18446744073709551616.0
+    u = np.where(u >= 1.0, np.nextafter(1.0, 0.0), u)
+    return u * (hi - lo) + lo
+
+
 def make_particles(n, dist, seed):
     """seeded synthetic cloud on the host: x,y,z,h (float64) and the box limits"""
-    rng = np.random.default_rng(seed)
     if dist == "uniform":
-        x, y, z = rng.random(n), rng.random(n), rng.random(n)  # all x, then all y, then all z
+        # SURVEY 8d / test/coord_samples/random.hpp:102-113: std::mt19937 gen(seed), all x, then all y, then all z
+        bg = np.random.MT19937()
+        bg._legacy_seeding(seed)
+        x, y, z = (mt19937_uniform(n, 0.0, 1.0, bg) for _ in range(3))
         lim = [0.0, 1.0] * 3
         h = np.full(n, 0.5 * (3.0 * NG0 / (4.0 * math.pi * n)) ** (1.0 / 3.0))
     elif dist == "plummer":
@@ -66,48 +81,95 @@ def make_particles(n, dist, seed):
 
 
 # ------------------------------------------------------------------------------------------------ CPU reference
-def cpu_pipeline(orc, x, y, z, h, box, bucket, ngmax, vranks=8):
-    """the same pass through the reference's CPU code (oracle/_ref) or our CPU port of it; returns mean neighbours"""
-    kind = 1
-    keys = orc.compute_sfc_keys(kind, x, y, z, box, np.uint64)
-    skeys, order = orc.sort_by_key(keys)
-    xs, ys, zs, hs = (orc.gather(order, a) for a in (x, y, z, h))
-    tree, counts = orc.compute_octree(skeys, bucket)
-    oc = orc.build_octree(tree)
-    centers, sizes = orc.geo_centers(kind, oc["prefixes"], box, np.float64)
-    L = tree.size - 1
-    layout = np.zeros(L + 1, dtype=np.uint32)
-    np.cumsum(counts, out=layout[1:])
-    radii = orc.halo_radii(hs, layout, 2.0)
-    for r in range(vranks):
-        first, last = r * L // vranks, (r + 1) * L // vranks
-        rr = np.zeros_like(radii)
-        rr[first:last] = radii[first:last]
-        orc.find_halos(kind, oc, tree, rr, box, first, last, np.float64)
-    nb, nc = orc.find_neighbors(xs, ys, zs, hs, 0, x.size, box, oc, layout, centers, sizes, ngmax)
-    return float(nc.mean())
+def drift_amplitude(h0):
+    return float(0.1 * h0)
 
 
-def time_cpu(n, dist, bucket, ngmax, steps, warmup):
+def time_reference(args, world, steps, warmup, total_cap, full_n=None):
+    """the reference's Domain<uint64_t,double,CpuTag>::sync + findNeighbors on `world` thread-ranks of this process
+    (oracle/_ref/liboracle_refdom.so), stepped exactly like the GPU arm: cold first sync, `warmup` steady steps, then
+    `steps` timed ones.  Returns (cpu_baseline dict, seconds per step, RefDomain or None)"""
     from oracle import loader
-    which = "ref" if loader.available("ref") else "port"
-    if which == "port" and not loader.available("port"):
-        loader.build("port")
-    orc = loader.load(which)
+    if not loader.refdom_available():
+        raise SystemExit("bench.py: oracle/_ref/liboracle_refdom.so is missing (run __graft_entry__.build() where the "
+                         "reference tree is present)")
     cores = os.cpu_count() or 1
-    orc.set_num_threads(cores)
-    x, y, z, h, lim = make_particles(n, dist, 42)
-    box = loader.make_box(lim)
+    full_n = full_n or args.n
+    n_rank = min(args.n, max(total_cap // world, 1))
+    lim_all, slabs = None, []
+    for r in range(world):
+        x, y, z, h, lim = make_particles(n_rank, args.dist, 42 + r)
+        if args.dist == "uniform" and world > 1:
+            h = h / world ** (1.0 / 3.0)  # same ~100 neighbours at the global density (as the GPU arm)
+        slabs.append((x, y, z, h))
+        lim_all = list(lim) if lim_all is None else [f(a, b) for f, a, b in zip([min, max] * 3, lim_all, lim)]
+    nprops = args.fields if args.fields in (0, 1, 2, 4) else 0
+    rd = loader.RefDomain(world, args.global_bucket, args.bucket, 0.5, lim_all, nprops=nprops,
+                          omp_per_rank=max(1, cores // world))
+    for r, (x, y, z, h) in enumerate(slabs):
+        gid = np.arange(r * n_rank, (r + 1) * n_rank, dtype=np.float64)
+        rd.set(r, x, y, z, h, props=[gid, 2 * gid][: min(nprops, 2)])  # 4 fields: id * {1,2,3,4}, derived inside
+    amp = drift_amplitude(slabs[0][3][0])
+    del slabs
+    sign = 1.0
+    t_first = time.perf_counter()
+    rd.bench_step(amp * sign, args.ngmax)  # cold: distributes the unsorted slabs, builds the trees from the root
+    first_s = time.perf_counter() - t_first
+    sign = -sign
     for _ in range(warmup):
-        cpu_pipeline(orc, x, y, z, h, box, bucket, ngmax)
+        rd.bench_step(amp * sign, args.ngmax)
+        sign = -sign
     t0 = time.perf_counter()
+    tot = (0, 0.0, 0)
     for _ in range(steps):
-        cpu_pipeline(orc, x, y, z, h, box, bucket, ngmax)
+        tot = rd.bench_step(amp * sign, args.ngmax)
+        sign = -sign
     dt = (time.perf_counter() - t0) / max(steps, 1)
-    kind = "reference" if which == "ref" else "port"
-    return dict(value=n / dt / 1e6, unit=UNIT, cores=cores, kind=kind,
-                sample="%d %s particles, same pipeline, oracle/%s, OpenMP %d threads, %.2f s/step" %
-                       (n, dist, "_ref" if which == "ref" else "port", cores, dt)), dt
+    assigned, nc_sum, halos = tot
+    sync_s, nb_s = rd.seconds()
+    base = dict(value=assigned / dt / 1e6, unit=UNIT, cores=cores, kind="reference",
+                sample="%d thread-rank(s) x %d %s particles = %d in total%s: reference Domain<u64,double,CpuTag>::sync + "
+                       "findNeighbors(ngmax %d), steady state, OpenMP %d thread(s) per rank; %.2f s/step (sync %.2f, "
+                       "findNeighbors %.2f), first sync %.1f s, %.1f neighbours / particle" %
+                       (world, n_rank, args.dist, assigned,
+                        "" if n_rank == full_n else " (bounded: the GPU arm runs %d per rank)" % full_n, args.ngmax,
+                        max(1, cores // world), dt, sync_s, nb_s, first_s, nc_sum / max(assigned, 1)),
+                particles=assigned, same_size=bool(n_rank == full_n))
+    return base, dt, rd
+
+
+def parity_in_run(args, n_check=1_000_000):
+    """correctness inside the run (N = 1): a fresh GPU Domain and the reference Domain on the same n_check-particle
+    cloud, one cold sync + findNeighbors each; keys, coordinates, tree leaves, neighbour counts and the raw neighbour
+    lists must be identical"""
+    import torch
+    from oracle import loader
+    from cornerstone_octree_b200 import ops
+    from cornerstone_octree_b200.domain import Domain
+    n = min(n_check, args.n)
+    x, y, z, h, lim = make_particles(n, args.dist, 4242)
+    rd = loader.RefDomain(1, args.global_bucket, args.bucket, 0.5, lim)
+    rd.set(0, x, y, z, h)
+    rd.bench_step(0.0, args.ngmax)
+    rk, rx, ry, rz, rh = rd.arrays(0)[:5]
+    rnb, rnc = rd.bench_neighbors(0, args.ngmax)
+    rleaves = rd.trees(0)["focus_leaves"]
+    rd.close()
+    dom = Domain(0, 1, args.global_bucket, args.bucket, 0.5, ops.make_box(lim))
+    keys, sx, sy, sz, sh, _ = dom.sync(*[torch.from_numpy(a).cuda() for a in (x, y, z, h)])
+    nb, nc = dom.find_neighbors(sx, sy, sz, sh, args.ngmax)
+    leaves = dom.tree_arrays()["leaves"].cpu().numpy().view(np.uint64)
+    nb, nc = nb.cpu().numpy().view(np.uint32), nc.cpu().numpy().view(np.uint32)
+    stored = np.arange(args.ngmax)[None, :] < np.minimum(nc, args.ngmax)[:, None]
+    res = dict(particles=int(n),
+               keys=bool(np.array_equal(keys.cpu().numpy().view(np.uint64), rk)),
+               coordinates=bool(all(np.array_equal(a.cpu().numpy(), b) for a, b in zip((sx, sy, sz, sh), (rx, ry, rz, rh)))),
+               leaves=bool(np.array_equal(leaves, rleaves)),
+               neighbour_counts=bool(np.array_equal(nc, rnc)),
+               neighbour_lists=bool(np.array_equal(np.where(stored, nb, 0), np.where(stored, rnb, 0))))
+    dom.close()
+    res["ok"] = all(v for k, v in res.items() if k != "particles")
+    return res
 
 
 # ------------------------------------------------------------------------------------------------ clocks
@@ -199,7 +261,11 @@ def main():
     ap.add_argument("--dist", default="uniform", choices=["uniform", "plummer"])
     ap.add_argument("--bucket", type=int, default=64)
     ap.add_argument("--ngmax", type=int, default=150)
-    ap.add_argument("--cpu-n", type=int, default=2_000_000, help="particles of the bounded CPU sample")
+    ap.add_argument("--fields", type=int, default=0, help="conserved double fields carried through sync (configs[3]: 4)")
+    ap.add_argument("--ref-total", type=int, default=32_000_000,
+                    help="upper bound of the particles (all thread-ranks together) of the reference arm")
+    ap.add_argument("--cpu-n", type=int, default=8_000_000, help="particles of the bounded cpu_baseline leg (N = 1)")
+    ap.add_argument("--no-check", action="store_true", help="skip the correctness checks inside the run")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--global-bucket", type=int, default=65536, help="bucketSize of the replicated global tree")
@@ -208,20 +274,35 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    workload = ("%dM %s particles per GPU, u64 Hilbert keys, double x/y/z/h, bucketSizeFocus=%d: steady-state "
+    nranks = args.gpus if args.impl == "reference" else world
+    workload = ("%dM %s particles per GPU, u64 Hilbert keys, double x/y/z/h%s, bucketSizeFocus=%d: steady-state "
                 "Domain::sync (box, keys, sort, global tree + assignment, particle exchange, halo discovery + exchange, "
                 "tree update, linking, centres) + findNeighbors(ngmax=%d) over the assigned particles%s" %
-                (args.n // 1_000_000, args.dist, args.bucket, args.ngmax,
-                 "; + findHalos for 8 virtual ranks (configs[1])" if int(os.environ.get("WORLD_SIZE", "1")) == 1 else ""))
+                (args.n // 1_000_000, args.dist, " + %d double fields" % args.fields if args.fields else "", args.bucket,
+                 args.ngmax, "; + findHalos for 8 virtual ranks (configs[1])" if nranks == 1 else ""))
+    # the same dictionary in both arms: what is computed, on what
+    config = dict(workload=workload, particles_per_gpu=args.n, ranks=nranks, dist=args.dist, keys="u64 Hilbert",
+                  real="f64", bucket_focus=args.bucket, bucket_global=args.global_bucket, ngmax=args.ngmax,
+                  fields=args.fields,
+                  generator="std::mt19937(42 + rank) + uniform_real_distribution, all x then y then z (SURVEY 8d); "
+                            "h = 0.5 cbrt(3 * 100 / (4 pi n_global))" if args.dist == "uniform" else
+                            "tests/gen.py plummer(seed 42 + rank), h from the local Plummer density",
+                  drift="0.1 h deterministic displacement before every sync, inside the timed region",
+                  l2="inputs (>= 1 GB per stage) exceed the 126 MB L2; no explicit flush")
 
     if args.impl == "reference":
+        # rank 0 alone runs the reference on the host cores, one thread-rank per GPU of the run; the other ranks leave
         if rank != 0:
             return 0
-        base, dt = time_cpu(args.cpu_n, args.dist, args.bucket, args.ngmax, args.steps, args.warmup)
+        base, dt, rd = time_reference(args, args.gpus, args.steps, args.warmup, args.ref_total)
+        rd.close()
+        if not base["same_size"]:
+            config = dict(config, reference_sample="%d particles per thread-rank instead of %d (bounded run time)" %
+                          (base["particles"] // args.gpus, args.n))
         line = dict(metric=METRIC, value=base["value"], unit=UNIT, n_gpus=args.gpus, steps=args.steps,
                     warmup=args.warmup, ms_per_step=dt * 1e3, higher_is_better=True, scaling="weak",
-                    vs_baseline=None, dtype="f64", data="synthetic", impl="reference",
-                    config=dict(workload=workload, sample=base["sample"]), cpu_baseline=base,
+                    vs_baseline=None, dtype="f64", data="synthetic", impl="reference", config=config,
+                    cpu_baseline=base,
                     e2e=dict(value=base["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                     gpu_launches=0)
         print(json.dumps(line))
@@ -250,8 +331,12 @@ def main():
     dom.init_comm_from_torch()
     dev = [torch.from_numpy(a).cuda() for a in (x, y, z, h)]
     del x, y, z
-    amp = float(0.1 * h[0])
-    state = {"a": dev, "sign": 1.0, "nb": None, "nc": None, "flags": None}
+    amp = drift_amplitude(h[0])
+    # conserved fields (configs[3]): double(global id) * {1, 2, ...}, so that what arrives can be checked
+    gid = torch.arange(rank * n, (rank + 1) * n, dtype=torch.float64, device="cuda")
+    fields = [gid * float(k + 1) for k in range(args.fields)]
+    del gid
+    state = {"a": dev, "f": fields, "sign": 1.0, "nb": None, "nc": None, "flags": None}
     vranks = 8
 
     def barrier():
@@ -308,8 +393,9 @@ def main():
         mark("start")
         drift(state["a"])
         mark("drift")
-        keys, sx, sy, sz, sh, _ = dom.sync(*state["a"], fields_ready=state.pop("h_ready", None))
+        keys, sx, sy, sz, sh, fl = dom.sync(*state["a"], props=state["f"], fields_ready=state.pop("h_ready", None))
         state["a"] = [sx, sy, sz, sh]
+        state["f"] = fl
         state["keys"] = keys
         mark("sync")
         if after_sync is not None:
@@ -335,6 +421,55 @@ def main():
     first_sync_s = time.perf_counter() - t0
     for _ in range(max(args.warmup, 3) - 1):
         run_step()
+    barrier()
+
+    def check_run(samples=64):
+        """correctness evidence inside the run (after a steady warm-up step): particle conservation, SFC order, the
+        fields still belong to their particles, and the neighbour counts of `samples` targets per rank against an
+        all-pairs count over the assigned particles of ALL ranks"""
+        sx, sy, sz, sh = state["a"]
+        s_, e_ = dom.start_index, dom.end_index
+        nw = e_ - s_
+        k = state["keys"]
+        out = dict(sorted_keys=bool((k[1:] >= k[:-1]).all().item()) if k.numel() > 1 else True)
+        tot = torch.tensor([float(nw)], dtype=torch.float64, device="cuda")
+        if args.fields:
+            f0 = state["f"][0][s_:e_]
+            out["fields_follow_particles"] = bool(all(torch.equal(state["f"][q][s_:e_], f0 * float(q + 1))
+                                                      for q in range(1, args.fields)))
+            tot = torch.cat([tot, f0.sum().reshape(1)])
+        idx = torch.arange(samples, device="cuda", dtype=torch.int64) * (nw - 1) // max(samples - 1, 1) + s_
+        tg = torch.stack([sx[idx], sy[idx], sz[idx], sh[idx]], 1)  # [samples, 4]
+        mine = state["nc"][idx - s_].to(torch.float64)
+        if world > 1:
+            dist.all_reduce(tot)
+            allt = [torch.empty_like(tg) for _ in range(world)]
+            dist.all_gather(allt, tg)
+            tg_all = torch.cat(allt, 0)
+        else:
+            tg_all = tg
+        ax, ay, az = sx[s_:e_], sy[s_:e_], sz[s_:e_]
+        cnt = torch.zeros(tg_all.shape[0], dtype=torch.float64, device="cuda")
+        for q in range(tg_all.shape[0]):
+            tx, ty, tz, th = (tg_all[q, c] for c in range(4))
+            d2 = (ax - tx) ** 2 + (ay - ty) ** 2 + (az - tz) ** 2  # the reference's expression: plain squares, x + y + z
+            cnt[q] = (d2 < 4.0 * th * th).sum()
+        if world > 1:
+            dist.all_reduce(cnt)
+        expect = cnt[rank * samples:(rank + 1) * samples] - 1.0  # the target itself
+        ok_nb = torch.tensor([float(torch.equal(expect, mine))], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(ok_nb, op=dist.ReduceOp.MIN)
+        out["particles_conserved"] = bool(int(tot[0].item()) == world * n)
+        if args.fields:
+            ng = world * n
+            out["id_sum_conserved"] = bool(tot[1].item() == ng * (ng - 1) / 2.0)
+        out["neighbour_counts_vs_all_pairs"] = bool(ok_nb.item() == 1.0)
+        out["sampled_targets"] = samples * world
+        out["ok"] = all(v for k_, v in out.items() if isinstance(v, bool))
+        return out
+
+    check = None if args.no_check else check_run()
     barrier()
 
     # ---- device-resident timing: EXACTLY K steps between two events
@@ -475,21 +610,28 @@ def main():
 
     cpu = None
     if not args.no_cpu and world == 1:
-        cpu, _ = time_cpu(args.cpu_n, args.dist, args.bucket, args.ngmax, 1, 0)
+        # bounded sample of the same workload through the reference's own Domain (the full-size run is --impl reference)
+        saved = args.n
+        args.n = min(args.n, args.cpu_n)
+        cpu, _, rd = time_reference(args, 1, 2, 1, args.cpu_n, full_n=saved)
+        rd.close()
+        args.n = saved
+        if not args.no_check:
+            check = dict(check or {}, parity_in_run=parity_in_run(args))
+            check["ok"] = bool(check.get("ok", True) and check["parity_in_run"]["ok"])
 
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
                 ms_per_step=ms_step, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64",
                 data="synthetic", impl="b200",
-                config=dict(workload=workload, particles_per_gpu=n, particles_global=n_global,
-                            halos_global=int(cnt[1].item()), leaves_rank0=int(info[3]), global_leaves=int(info[5]),
-                            neighbours_mean=round(nc_mean, 2), first_sync_s=round(first_sync_s, 3),
-                            drift="0.1 h deterministic displacement before every sync (3 torch kernels, inside the "
-                                  "timed region)",
-                            l2="inputs (>=1 GB per stage) exceed the 126 MB L2; no explicit flush",
-                            parallelism="1 rank" if world == 1 else
-                            "%d ranks, SFC-range sharding, NCCL all-reduce of global leaf counts, grouped NCCL "
-                            "send/recv for particle and halo exchange" % world),
-                clocks=clocks, e2e=e2e, gpu_launches=int(launches), roofline=roofline, stages=stages,
+                config=config,
+                observed=dict(particles_global=n_global, halos_global=int(cnt[1].item()), leaves_rank0=int(info[3]),
+                              global_leaves=int(info[5]), neighbours_mean=round(nc_mean, 2),
+                              particles_per_leaf=round(n_assigned / max(int(info[3]), 1), 1),
+                              first_sync_s=round(first_sync_s, 3),
+                              parallelism="1 rank" if world == 1 else
+                              "%d ranks, SFC-range sharding, NCCL all-reduce of global leaf counts, grouped NCCL "
+                              "send/recv for particle and halo exchange" % world),
+                check=check, clocks=clocks, e2e=e2e, gpu_launches=int(launches), roofline=roofline, stages=stages,
                 cpu_baseline=cpu)
     print(json.dumps(line))
     dom.close()

@@ -507,6 +507,22 @@ class RefDomain:
         st = self._f("exchange_halos")(self.h, ptrs)
         assert st == 0
 
+    def bench_step(self, amp, ngmax):
+        """bench.py's reference arm: drift (signed amplitude) + Domain::sync + findNeighbors on every rank;
+        returns (assigned particles, sum of neighbour counts, halos), each summed over the ranks"""
+        out = np.zeros(3, dtype=np.float64)
+        st = self._f("bench_step")(self.h, C.c_double(amp), C.c_uint(ngmax), _ptr(out))
+        assert st == 0, "reference bench step failed"
+        return int(out[0]), float(out[1]), int(out[2])
+
+    def bench_neighbors(self, rank, ngmax):
+        """neighbour lists and counts of the last bench_step of one rank (copies)"""
+        inf = self.info(rank)
+        n = inf["end"] - inf["start"]
+        nb, nc = C.POINTER(C.c_uint)(), C.POINTER(C.c_uint)()
+        self._f("bench_neighbors", None)(self.h, rank, C.byref(nb), C.byref(nc))
+        return (np.ctypeslib.as_array(nb, (n, ngmax)).copy(), np.ctypeslib.as_array(nc, (n,)).copy())
+
     def seconds(self):
         a, b = C.c_double(0), C.c_double(0)
         self._f("seconds", None)(self.h, C.byref(a), C.byref(b))

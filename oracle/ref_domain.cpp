@@ -15,6 +15,7 @@
 #include <omp.h>
 
 #include <chrono>
+#include <cmath>
 #include <cstring>
 #include <memory>
 #include <tuple>
@@ -34,9 +35,11 @@ struct RankState
     std::unique_ptr<Domain<K, T, CpuTag>> domain;
     std::vector<K> keys;
     std::vector<T> x, y, z, h;
-    std::vector<T> p0, p1; // up to two conserved properties
+    std::vector<T> p0, p1, p2, p3; // up to four conserved properties (0, 1, 2 or 4 are wired)
     std::vector<T> s1, s2, s3;
     double syncSeconds = 0, nbSeconds = 0;
+    std::vector<unsigned> nb, nc; // neighbour lists / counts kept between bench steps
+    double ncSum = 0;
 };
 
 template<class K, class T>
@@ -102,6 +105,59 @@ void nbRank(int rank, void* arg)
     r.nbSeconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
+/* One step of bench.py's reference arm on one rank: the drift bench.py applies on the GPU (same expressions, same
+ * order), Domain::sync, findNeighbors over the assigned range into buffers that live across steps. */
+template<class K, class T>
+struct StepArg
+{
+    World<K, T>* w;
+    double amp; // signed amplitude of this step
+    unsigned ngmax;
+};
+
+template<class K, class T>
+void stepRank(int rank, void* arg)
+{
+    auto* a = static_cast<StepArg<K, T>*>(arg);
+    auto* w = a->w;
+    auto& r = w->ranks[rank];
+    omp_set_num_threads(w->ompPerRank);
+    MPI_Barrier(MPI_COMM_WORLD);
+    auto t0 = std::chrono::steady_clock::now();
+    const T wv  = T(2.0 * 3.14159265358979323846 * 37.0);
+    const T amp = T(a->amp);
+    const std::size_t n = r.x.size();
+#pragma omp parallel for
+    for (std::size_t i = 0; i < n; ++i)
+        r.x[i] += amp * std::sin(r.y[i] * wv);
+#pragma omp parallel for
+    for (std::size_t i = 0; i < n; ++i)
+        r.y[i] += amp * std::sin(r.z[i] * wv);
+#pragma omp parallel for
+    for (std::size_t i = 0; i < n; ++i)
+        r.z[i] += amp * std::sin(r.x[i] * wv);
+    r.keys.resize(r.x.size());
+    if (w->nprops == 0) r.domain->sync(r.keys, r.x, r.y, r.z, r.h, std::tuple{}, std::tie(r.s1, r.s2, r.s3));
+    else if (w->nprops == 1) r.domain->sync(r.keys, r.x, r.y, r.z, r.h, std::tie(r.p0), std::tie(r.s1, r.s2, r.s3));
+    else if (w->nprops == 2) r.domain->sync(r.keys, r.x, r.y, r.z, r.h, std::tie(r.p0, r.p1), std::tie(r.s1, r.s2, r.s3));
+    else r.domain->sync(r.keys, r.x, r.y, r.z, r.h, std::tie(r.p0, r.p1, r.p2, r.p3), std::tie(r.s1, r.s2, r.s3));
+    MPI_Barrier(MPI_COMM_WORLD);
+    r.syncSeconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    auto t1 = std::chrono::steady_clock::now();
+    const std::size_t nw = r.domain->nParticles();
+    if (r.nb.size() < nw * a->ngmax) r.nb.resize(std::size_t(double(nw) * 1.05) * a->ngmax);
+    if (r.nc.size() < nw) r.nc.resize(std::size_t(double(nw) * 1.05));
+    findNeighbors(r.x.data(), r.y.data(), r.z.data(), r.h.data(), r.domain->startIndex(), r.domain->endIndex(),
+                  r.domain->box(), r.domain->octreeProperties(), a->ngmax, r.nb.data(), r.nc.data());
+    MPI_Barrier(MPI_COMM_WORLD);
+    r.nbSeconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count();
+    double s    = 0;
+#pragma omp parallel for reduction(+ : s)
+    for (std::size_t i = 0; i < nw; ++i)
+        s += r.nc[i];
+    r.ncSum = s;
+}
+
 template<class T>
 Box<T> toBox(const T* lim, const int* pbc)
 {
@@ -132,6 +188,13 @@ int setRank(void* h, int rank, uint64_t n, const T* x, const T* y, const T* z, c
     r.x.assign(x, x + n), r.y.assign(y, y + n), r.z.assign(z, z + n), r.h.assign(hh, hh + n);
     if (w->nprops > 0) r.p0.assign(p0, p0 + n);
     if (w->nprops > 1) r.p1.assign(p1, p1 + n);
+    if (w->nprops > 2)
+    {
+        // bench.py's c4 fields: double(globalId) * {1,2,3,4}; p0 carries the id, the others are derived here
+        r.p1.resize(n), r.p2.resize(n), r.p3.resize(n);
+        for (uint64_t i = 0; i < n; ++i)
+            r.p1[i] = T(2) * p0[i], r.p2[i] = T(3) * p0[i], r.p3[i] = T(4) * p0[i];
+    }
     return 0;
 }
 
@@ -272,6 +335,28 @@ int getTree(void* h, int rank, int which, void* out)
         for (int r = 0; r < w->P; ++r)                                                                                 \
             std::memcpy(arrays[r], vecs[r].data(), vecs[r].size() * sizeof(T));                                        \
         return st;                                                                                                     \
+    }                                                                                                                  \
+    /* bench.py reference arm: drift + sync + findNeighbors on every rank; out3 = assigned particles (sum over ranks),  \
+     * sum of neighbour counts, halos (sum over ranks) */                                                              \
+    int cstone_refdom_bench_step_##KS##_##TS(void* h, double amp, unsigned ngmax, double* out3)                        \
+    {                                                                                                                  \
+        auto* w = static_cast<World<K, T>*>(h);                                                                        \
+        StepArg<K, T> a{w, amp, ngmax};                                                                                \
+        int st = mpi_shim_run(w->P, stepRank<K, T>, &a);                                                               \
+        out3[0] = out3[1] = out3[2] = 0;                                                                               \
+        for (auto& r : w->ranks)                                                                                       \
+        {                                                                                                              \
+            out3[0] += double(r.domain->nParticles());                                                                 \
+            out3[1] += r.ncSum;                                                                                        \
+            out3[2] += double(r.domain->nParticlesWithHalos() - r.domain->nParticles());                               \
+        }                                                                                                              \
+        return st;                                                                                                     \
+    }                                                                                                                  \
+    /* neighbour results of the last bench step of one rank (views into the oracle's buffers) */                       \
+    void cstone_refdom_bench_neighbors_##KS##_##TS(void* h, int rank, const unsigned** nb, const unsigned** nc)        \
+    {                                                                                                                  \
+        auto& r = static_cast<World<K, T>*>(h)->ranks[rank];                                                           \
+        *nb = r.nb.data(), *nc = r.nc.data();                                                                          \
     }                                                                                                                  \
     void cstone_refdom_seconds_##KS##_##TS(void* h, double* sync, double* nb)                                          \
     {                                                                                                                  \
