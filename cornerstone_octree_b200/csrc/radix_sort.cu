@@ -175,11 +175,17 @@ __global__ void __launch_bounds__(512) histogramKernel(const K* __restrict__ key
 }
 
 // 2. exclusive scan of each pass's 256 bins (one block of 256 threads per pass)
-__global__ void __launch_bounds__(kRadix) binOffsetsKernel(uint32_t* __restrict__ hist)
+/* Also notes in tickets[32 * pass + 1] whether every key carries the same digit in this pass (one bin holds all n keys):
+ * such a pass is the identity permutation.  A pair of passes (2q, 2q+1), q >= 1, that are both uniform is skipped
+ * altogether (the ping-pong buffers keep their roles); a single uniform pass copies its tile straight across.  The
+ * Warren-Salmon prefixes buildOctree sorts occupy 3 * depth + 1 low bits, so 4 - 5 of their 8 passes fall away. */
+__global__ void __launch_bounds__(kRadix) binOffsetsKernel(uint32_t* __restrict__ hist, uint32_t* __restrict__ tickets,
+                                                           uint32_t n)
 {
     __shared__ uint32_t sWarp[kRadix / 32];
     uint32_t* h   = hist + blockIdx.x * kRadix;
     uint32_t c    = h[threadIdx.x];
+    if (c == n) tickets[blockIdx.x * 32 + 1] = 1u;
     uint32_t incl = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1)
@@ -260,6 +266,21 @@ __global__ void __launch_bounds__(kSortThreads, RS_MINBLOCKS(K)) onesweepKernel(
     const unsigned tid  = threadIdx.x;
     const unsigned lane = tid & 31u;
     const unsigned warp = tid >> 5;
+
+    /* uniform digit (see binOffsetsKernel): `ticket` is tickets + 32 * pass, the flag of the partner pass of the pair
+     * sits 32 words before (odd pass) or after (even pass) */
+    if (ticket[1])
+    {
+        const int pass = shift / kRadixBits;
+        if (pass >= 2 && ((pass & 1) ? ticket[1 - 32] : ticket[1 + 32])) return; // both passes of the pair: nothing moves
+        const uint32_t base = blockIdx.x * uint32_t(kSortTile);
+        for (uint32_t i = base + tid; i < min(base + uint32_t(kSortTile), n); i += kSortThreads)
+        {
+            keysOut[i] = keysIn[i];
+            valsOut[i] = Iota ? i : valsIn[i];
+        }
+        return;
+    }
 
     if (tid == 0) sm.tile = atomicAdd(ticket, 1u);
 #pragma unroll
@@ -462,7 +483,7 @@ int sortByKey(K* keys, uint32_t* values, K* keyBuf, uint32_t* valueBuf, size_t n
 
     histogramKernel<K><<<gridFor(n, 512 * 8, 2), 512, 0, s>>>(keys, n, t.hist);
     CSB_LAUNCHED();
-    binOffsetsKernel<<<P, kRadix, 0, s>>>(t.hist);
+    binOffsetsKernel<<<P, kRadix, 0, s>>>(t.hist, t.tickets, uint32_t(n));
     CSB_LAUNCHED();
 
     static bool attrSet[2] = {false, false};

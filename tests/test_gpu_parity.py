@@ -96,6 +96,37 @@ def test_sort_sizes(kd, n, gpu):
         assert np.array_equal(sk2, keys[ref]) and np.array_equal(v2, vals[ref])
 
 
+@pytest.mark.parametrize("kd", [np.uint32, np.uint64])
+@pytest.mark.parametrize("pattern", ["low16", "low24", "high-only", "middle-constant", "all-equal", "placeholder-prefixes"])
+def test_sort_uniform_digit_passes(kd, pattern, gpu):
+    """passes whose digit is the same for every key are skipped in pairs or turned into a straight copy
+    (radix_sort.cu binOffsetsKernel): same permutation as numpy's stable sort, with and without a payload"""
+    n = 300007
+    rng = np.random.default_rng(5)
+    bits = 30 if kd == np.uint32 else 63
+    r = rng.integers(0, 2 ** 62, n, dtype=np.uint64)
+    if pattern == "low16":
+        keys = r & 0xffff
+    elif pattern == "low24":
+        keys = r & 0xffffff
+    elif pattern == "high-only":
+        keys = (r & 0xff) << (bits - 8)
+    elif pattern == "middle-constant":
+        keys = (r & ((1 << bits) - 1)) & ~np.uint64(0xff00) | np.uint64(0x5a00)
+    elif pattern == "all-equal":
+        keys = np.full(n, 12345, dtype=np.uint64)
+    else:  # Warren-Salmon keys of a depth-5 tree: 16 significant bits and the placeholder bit
+        lvl = rng.integers(0, 6, n).astype(np.uint64)
+        keys = (np.uint64(1) << (3 * lvl)) | (r & ((np.uint64(1) << (3 * lvl)) - np.uint64(1)))
+    keys = keys.astype(kd)
+    ref = np.argsort(keys, kind="stable").astype(np.uint32)
+    sk, order = gpu.sort_by_key(keys)
+    assert np.array_equal(order, ref) and np.array_equal(sk, keys[ref])
+    vals = rng.integers(0, 2 ** 31, n).astype(np.uint32)
+    sk2, v2 = gpu.sort_by_key(keys, vals)
+    assert np.array_equal(sk2, keys[ref]) and np.array_equal(v2, vals[ref])
+
+
 def test_scan_and_minmax(gpu):
     import torch
     from cornerstone_octree_b200 import ops
