@@ -181,8 +181,30 @@ __global__ void __launch_bounds__(256)
         lo[d] = arr[d] ? arr[d][0] : T(0);
         hi[d] = lo[d];
     }
-    size_t stride = size_t(gridDim.x) * blockDim.x;
-    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    const size_t stride = size_t(gridDim.x) * blockDim.x;
+    size_t i            = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    // four strided elements of each array per trip: 12 independent loads in flight per thread (a streaming reduction
+    // with one load per trip reached 55 % of the HBM peak)
+    for (; i + 3 * stride < n; i += 4 * stride)
+    {
+        T v[3][4];
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+            if (arr[d])
+            {
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    v[d][u] = arr[d][i + u * stride];
+            }
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+            if (arr[d])
+            {
+                lo[d] = min(min(lo[d], min(v[d][0], v[d][1])), min(v[d][2], v[d][3]));
+                hi[d] = max(max(hi[d], max(v[d][0], v[d][1])), max(v[d][2], v[d][3]));
+            }
+    }
+    for (; i < n; i += stride)
     {
 #pragma unroll
         for (int d = 0; d < 3; ++d)
