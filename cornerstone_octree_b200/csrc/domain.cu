@@ -130,8 +130,12 @@ __global__ void insertionPointsKernel(const K* __restrict__ own, uint32_t nOwn, 
     }
 }
 
+/* Two-source map of the steady-state merge: bit 31 clear = index into the caller's arrays (a particle that stayed on
+ * this rank, reached through the map of the first sort), bit 31 set = index into the receive buffers (an arrival). */
+constexpr uint32_t kFromRecv = 0x80000000u;
+
 template<class K>
-__global__ void mergeScatterKernel(const K* __restrict__ own, uint32_t nOwn, uint32_t ownOffset,
+__global__ void mergeScatterKernel(const K* __restrict__ own, uint32_t nOwn, const uint32_t* __restrict__ ownMap,
                                    const uint32_t* __restrict__ scanE, const K* __restrict__ f,
                                    const uint32_t* __restrict__ fv, const uint32_t* __restrict__ ip, uint32_t nF,
                                    K* __restrict__ outKeys, uint32_t* __restrict__ outOrder)
@@ -142,14 +146,43 @@ __global__ void mergeScatterKernel(const K* __restrict__ own, uint32_t nOwn, uin
         {
             uint32_t pos  = i + scanE[i + 1];
             outKeys[pos]  = own[i];
-            outOrder[pos] = ownOffset + i;
+            outOrder[pos] = ownMap[i];
         }
         else
         {
             uint32_t u    = i - nOwn;
             uint32_t pos  = ip[u] + u;
             outKeys[pos]  = f[u];
-            outOrder[pos] = fv[u];
+            outOrder[pos] = fv[u] | kFromRecv;
+        }
+    }
+}
+
+struct GatherTwoArgs
+{
+    const void* orig[16];
+    const void* recv[16];
+    void* dst[16];
+    int words[16]; // element size in 4-byte words
+    int na;
+};
+//! dst[k][i] = (map[i] & kFromRecv ? recv[k] : orig[k])[map[i] & ~kFromRecv] for every array k, one read of the map
+__global__ void __launch_bounds__(256) gatherTwoKernel(const uint32_t* __restrict__ map, size_t n, GatherTwoArgs a)
+{
+    const size_t stride = size_t(gridDim.x) * blockDim.x;
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        const uint32_t m = map[i];
+        const size_t j   = m & ~kFromRecv;
+        for (int k = 0; k < a.na; ++k)
+        {
+            const void* src = (m & kFromRecv) ? a.recv[k] : a.orig[k];
+            if (a.words[k] == 2)
+                reinterpret_cast<uint64_t*>(a.dst[k])[i] = reinterpret_cast<const uint64_t*>(src)[j];
+            else
+                for (int w = 0; w < a.words[k]; ++w)
+                    reinterpret_cast<uint32_t*>(a.dst[k])[i * a.words[k] + w] =
+                        reinterpret_cast<const uint32_t*>(src)[j * a.words[k] + w];
         }
     }
 }
@@ -571,7 +604,7 @@ private:
     int updateGlobalTree(const K* keys, size_t n);
     int allreduceCounts();
     int linkTree(LeafArrayDev<K, T>& tree, bool withCenters);
-    int convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n, bool& fresh);
+    int convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n, bool& fresh, int maxSteadyIter = 64);
     int discoverHalos();
     int hostCounts(const uint32_t* dev, int n, std::vector<uint32_t>& out)
     {
@@ -583,6 +616,29 @@ private:
     int gatherMulti(const uint32_t* map, size_t n, int na, const void* const* src, void* const* dst, const int* eb)
     {
         return cstone_b200_gather_multi(map, n, na, src, dst, eb, s_);
+    }
+    //! the assigned set in SFC order: from the receive buffers through order_, or from two sources through map2_
+    int gatherAssigned(size_t n, int na, const int* which, void* const* dst, const int* eb)
+    {
+        if (n == 0) return 0;
+        if (!map2_)
+        {
+            const void* src[4 + kMaxProps];
+            int ebs[4 + kMaxProps];
+            for (int k = 0; k < na; ++k)
+                src[k] = recv_[which[k]].p, ebs[k] = eb[which[k]];
+            return gatherMulti(order_.template as<uint32_t>(), n, na, src, dst, ebs);
+        }
+        GatherTwoArgs a{};
+        a.na = na;
+        for (int k = 0; k < na; ++k)
+        {
+            a.orig[k] = origSrc_[which[k]], a.recv[k] = recv_[which[k]].p, a.dst[k] = dst[k];
+            a.words[k] = eb[which[k]] / 4;
+        }
+        gatherTwoKernel<<<gridFor(n, 256, 8), 256, 0, s_>>>(map2_, n, a);
+        CSB_LAUNCHED();
+        return 0;
     }
 
     int rank_, nRanks_;
@@ -603,6 +659,9 @@ private:
 
     // scratch + SFC-ordered arrays
     DevBuf keys_, keyBuf_, order_, valBuf_, sortTemp_, mmTemp_, small_;
+    // steady-state merge: the assigned set is gathered from two sources through map2_ (see mergeScatterKernel)
+    const uint32_t* map2_ = nullptr;
+    const void* origSrc_[4 + 12] = {nullptr};
     DevBuf pack_[4 + kMaxProps], recv_[4 + kMaxProps], fin_[4 + kMaxProps];
     DevBuf skeys_, fkeys_, shAssigned_, merge_;
 
@@ -713,8 +772,9 @@ int Engine<K, T>::updateGlobalTree(const K* keys, size_t n)
 
 //! iterate a local tree to convergence on the given sorted keys (from the root on the first use)
 template<class K, class T>
-int Engine<K, T>::convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n, bool& fresh)
+int Engine<K, T>::convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n, bool& fresh, int maxSteadyIter)
 {
+    const bool wasFresh = fresh;
     if (fresh)
     {
         CSB_TRY(tree.reset(uint32_t(n), s_));
@@ -727,7 +787,8 @@ int Engine<K, T>::convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n
                                        keys + n, s_)));
     }
     bool conv = false;
-    for (int it = 0; it < 64 && !conv; ++it)
+    const int iters = wasFresh ? 64 : maxSteadyIter;
+    for (int it = 0; it < iters && !conv; ++it)
         CSB_TRY(tree.update(keys, keys + n, bucketFocus_, conv, s_));
     return 0;
 }
@@ -802,7 +863,7 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
     auto reserveSort = [&](size_t n) -> int
     {
         CSB_TRY(keyBuf_.reserve(sizeof(K) * n + 256));
-        CSB_TRY(order_.reserve(4 * n + 256));
+        CSB_TRY(order_.reserve(4 * n + 256, true, s_)); // (keeps the map of the first sort: the merge reads it)
         CSB_TRY(valBuf_.reserve(4 * n + 256));
         CSB_TRY(sortTemp_.reserve((Api<K, T>::sortTemp(n)) + 256));
         return 0;
@@ -865,20 +926,7 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         for (int q = 0; q < P; ++q)
             sendCount[q] = sendStart[q + 1] - sendStart[q];
 
-        // 5. ONE gather orders all outgoing messages (sorted by key = grouped by destination rank)
-        for (int a = 0; a < na; ++a)
-        {
-            CSB_TRY(pack_[a].reserve(size_t(eb[a]) * np + 256));
-            dst[a] = pack_[a].p;
-        }
-        if (fieldsReady_)
-        {
-            CSB_CUDA(cudaStreamWaitEvent(s_, fieldsReady_, 0));
-            fieldsReady_ = nullptr;
-        }
-        if (np) CSB_TRY(gatherMulti(order_.template as<uint32_t>(), np, na, src, dst, eb));
-
-        // 6. who sends how much to whom
+        // 5. who sends how much to whom
         uint32_t* dMine = dPos + P + 1;
         uint32_t* dAll  = dMine + P;
         CSB_CUDA(cudaMemcpyAsync(dMine, sendCount.data(), 4 * P, cudaMemcpyHostToDevice, s_));
@@ -894,6 +942,39 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         }
         nAssigned_ = recvOff[P];
         if (nAssigned_ >= (uint64_t(1) << 30)) return CSTONE_E_TOO_LARGE;
+        /* steady state = nearly everything stays here: the particles that stay are neither packed nor copied, the
+         * assigned set is later gathered from two sources (caller arrays through the sort map, receive buffers) */
+        const bool steady = nAssigned_ && size_t(uint32_t(nAssigned_) - sendCount[rank_]) * 4 <= size_t(nAssigned_);
+
+        // 6. ONE gather orders the outgoing messages (sorted by key = grouped by destination rank)
+        for (int a = 0; a < na; ++a)
+        {
+            CSB_TRY(pack_[a].reserve(size_t(eb[a]) * np + 256));
+            dst[a]      = pack_[a].p;
+            origSrc_[a] = src[a];
+        }
+        if (fieldsReady_)
+        {
+            CSB_CUDA(cudaStreamWaitEvent(s_, fieldsReady_, 0));
+            fieldsReady_ = nullptr;
+        }
+        if (!steady)
+        {
+            if (np) CSB_TRY(gatherMulti(order_.template as<uint32_t>(), np, na, src, dst, eb));
+        }
+        else
+        {
+            // only what leaves: the sorted ranges below and above the part that stays
+            const size_t lo = sendStart[rank_], hiStart = size_t(sendStart[rank_]) + sendCount[rank_];
+            void* d2[4 + kMaxProps];
+            if (lo) CSB_TRY(gatherMulti(order_.template as<uint32_t>(), lo, na, src, dst, eb));
+            if (np > hiStart)
+            {
+                for (int a = 0; a < na; ++a)
+                    d2[a] = pack_[a].template as<char>() + hiStart * size_t(eb[a]);
+                CSB_TRY(gatherMulti(order_.template as<uint32_t>() + hiStart, np - hiStart, na, src, d2, eb));
+            }
+        }
 
         // 7. exchange: grouped NCCL send/recv, received straight into place [ref: domaindecomp_mpi_gpu.cuh:85-185]
         for (int a = 0; a < na; ++a)
@@ -913,11 +994,12 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
             }
             CSB_TRY(comm_->exchange(sends, recvs, s_));
         }
-        for (int a = 0; a < na; ++a)
-            if (sendCount[rank_])
-                CSB_CUDA(cudaMemcpyAsync(recv_[a].template as<char>() + size_t(recvOff[rank_]) * eb[a],
-                                         pack_[a].template as<char>() + size_t(sendStart[rank_]) * eb[a],
-                                         size_t(sendCount[rank_]) * eb[a], cudaMemcpyDeviceToDevice, s_));
+        if (!steady)
+            for (int a = 0; a < na; ++a)
+                if (sendCount[rank_])
+                    CSB_CUDA(cudaMemcpyAsync(recv_[a].template as<char>() + size_t(recvOff[rank_]) * eb[a],
+                                             pack_[a].template as<char>() + size_t(sendStart[rank_]) * eb[a],
+                                             size_t(sendCount[rank_]) * eb[a], cudaMemcpyDeviceToDevice, s_));
 
         mark(5);
         // 8. keys + order of the assigned set (P sorted runs) [ref: domain/assignment.hpp:141-150]
@@ -926,17 +1008,19 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         CSB_TRY(reserveSort(n));
         K* skeys = skeys_.template as<K>();
         const uint32_t nOwn = sendCount[rank_], nLeft = recvOff[rank_], nF = uint32_t(n) - nOwn;
-        if (n && size_t(nF) * 4 <= n)
+        map2_ = nullptr;
+        if (steady)
         {
             /* steady state: nearly everything stayed here.  The own run is already sorted (keys are those of step 2),
              * so only the foreign arrivals are keyed and sorted, then merged in:  O(n) streaming instead of a second
              * 8-pass sort of all n keys. */
-            const K* ownKeys = keys + sendStart[rank_];
-            uint32_t* order  = order_.template as<uint32_t>();
+            const K* ownKeys       = keys + sendStart[rank_];
+            const uint32_t* ownMap = order_.template as<uint32_t>() + sendStart[rank_]; // caller index of own particle i
+            uint32_t* order        = valBuf_.template as<uint32_t>();                   // two-source map (see kFromRecv)
             if (nF == 0)
             {
                 CSB_CUDA(cudaMemcpyAsync(skeys, ownKeys, sizeof(K) * n, cudaMemcpyDeviceToDevice, s_));
-                CSB_TRY(cstone_b200_sequence_u32(order, n, 0u, s_));
+                map2_ = ownMap;
             }
             else
             {
@@ -966,8 +1050,9 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
                 insertionPointsKernel<K><<<gridFor(nF, 256), 256, 0, s_>>>(ownKeys, nOwn, fk, nF, ip, cnt);
                 CSB_LAUNCHED();
                 CSB_TRY(cstone_b200_exclusive_scan_u32(cnt, cnt, size_t(nOwn) + 1, 0u, scanTmp, s_));
-                mergeScatterKernel<K><<<gridFor(n, 256), 256, 0, s_>>>(ownKeys, nOwn, nLeft, cnt, fk, fv, ip, nF, skeys, order);
+                mergeScatterKernel<K><<<gridFor(n, 256), 256, 0, s_>>>(ownKeys, nOwn, ownMap, cnt, fk, fv, ip, nF, skeys, order);
                 CSB_LAUNCHED();
+                map2_ = order;
             }
         }
         else if (n)
@@ -979,7 +1064,11 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         }
         // h in SFC order for the halo search radii
         CSB_TRY(shAssigned_.reserve(sizeof(T) * n + 256));
-        if (n) CSB_TRY(cstone_b200_gather(order_.template as<uint32_t>(), n, recv_[3].p, shAssigned_.p, int(sizeof(T)), s_));
+        {
+            const int which[1] = {3};
+            void* d1[1]        = {shAssigned_.p};
+            CSB_TRY(gatherAssigned(n, 1, which, d1, eb));
+        }
 
         mark(6);
         // 9. halos
@@ -1022,8 +1111,11 @@ int Engine<K, T>::discoverHalos()
         cudaEventRecord(lapEv[nLap++], s_);
     };
     lap();
-    // a. tree over the assigned particles, linked (for the reverse collision) and with its particle layout
-    CSB_TRY(convergeTree(focus_, skeys, n, focusFresh_));
+    /* a. tree over the assigned particles, linked (for the reverse collision) and with its particle layout.  Halo
+     * discovery needs A valid leaf array with exact counts, not THE converged one: after the first sync the tree of the
+     * previous step gets one rebalance + recount step per sync (it follows the particles one step behind) instead of
+     * a convergence loop, which cost the ranks whose tree changed a second iteration and everybody else the wait. */
+    CSB_TRY(convergeTree(focus_, skeys, n, focusFresh_, 1));
     CSB_TRY(linkTree(focus_, false));
     const int L = focus_.numNodes;
 
@@ -1144,15 +1236,15 @@ int Engine<K, T>::discoverHalos()
     }
     // h. assigned particles straight to their final position, then the halos of x,y,z,h
     mark(7);
-    const void* src[4 + kMaxProps];
     void* dst[4 + kMaxProps];
+    int which[4 + kMaxProps];
     for (int a = 0; a < na; ++a)
     {
         CSB_TRY(fin_[a].reserve(size_t(eb[a]) * nTotal_ + 256));
-        src[a] = recv_[a].p;
-        dst[a] = fin_[a].template as<char>() + size_t(start_) * eb[a];
+        which[a] = a;
+        dst[a]   = fin_[a].template as<char>() + size_t(start_) * eb[a];
     }
-    if (n) CSB_TRY(gatherMulti(order_.template as<uint32_t>(), n, na, src, dst, eb));
+    CSB_TRY(gatherAssigned(n, na, which, dst, eb));
     void* xyzh[4] = {fin_[0].p, fin_[1].p, fin_[2].p, fin_[3].p};
     CSB_TRY(exchangeHalos(4, xyzh, eb));
 
