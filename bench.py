@@ -257,7 +257,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--n", type=int, default=32_000_000, help="particles per GPU")
+    ap.add_argument("--n", "--particles", dest="n", type=int, default=32_000_000, help="particles per GPU")
     ap.add_argument("--dist", default="uniform", choices=["uniform", "plummer"])
     ap.add_argument("--bucket", type=int, default=64)
     ap.add_argument("--ngmax", type=int, default=150)
