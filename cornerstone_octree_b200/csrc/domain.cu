@@ -603,8 +603,16 @@ private:
     int updateBox(const T* x, const T* y, const T* z, size_t n);
     int updateGlobalTree(const K* keys, size_t n);
     int allreduceCounts();
-    int linkTree(LeafArrayDev<K, T>& tree, bool withCenters);
-    int convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n, bool& fresh, int maxSteadyIter = 64);
+    //! internal tree + particle layout of a leaf array; one set per tree, so that a tree whose leaves did not change
+    //! between two syncs is not linked again (the leaf COUNTS change every step, the leaves rarely do)
+    struct Linked
+    {
+        DevBuf prefixes, childOffsets, parents, levelRange, internalToLeaf, leafToInternal, layout;
+        bool valid = false;
+    };
+    int linkTree(LeafArrayDev<K, T>& tree, Linked& ln, bool withCenters, bool leavesChanged);
+    int convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n, bool& fresh, int maxSteadyIter = 64,
+                     bool* leavesChanged = nullptr);
     int discoverHalos();
     int hostCounts(const uint32_t* dev, int n, std::vector<uint32_t>& out)
     {
@@ -670,7 +678,11 @@ private:
     bool globalFresh_ = true, focusFresh_ = true, searchFresh_ = true;
     std::vector<K> hGlobalLeaves_, boundaries_, oldBoundaries_;
     std::vector<uint32_t> hGlobalCounts_, rankCounts_;
-    DevBuf prefixes_, childOffsets_, parents_, levelRange_, internalToLeaf_, leafToInternal_, centers_, sizes_, layout_;
+    Linked lnS_, lnF_; // of search_ (assigned + halos) and of focus_ (assigned, halo discovery)
+    DevBuf &prefixes_ = lnS_.prefixes, &childOffsets_ = lnS_.childOffsets, &parents_ = lnS_.parents,
+           &levelRange_ = lnS_.levelRange, &internalToLeaf_ = lnS_.internalToLeaf, &leafToInternal_ = lnS_.leafToInternal,
+           &layout_ = lnS_.layout;
+    DevBuf centers_, sizes_;
     DevBuf octTemp_, scanTemp_, radii_;
     mutable DevBuf nbInfo_; // node records of findNeighbors
 
@@ -772,7 +784,8 @@ int Engine<K, T>::updateGlobalTree(const K* keys, size_t n)
 
 //! iterate a local tree to convergence on the given sorted keys (from the root on the first use)
 template<class K, class T>
-int Engine<K, T>::convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n, bool& fresh, int maxSteadyIter)
+int Engine<K, T>::convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n, bool& fresh, int maxSteadyIter,
+                               bool* leavesChanged)
 {
     const bool wasFresh = fresh;
     if (fresh)
@@ -788,37 +801,47 @@ int Engine<K, T>::convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n
     }
     bool conv = false;
     const int iters = wasFresh ? 64 : maxSteadyIter;
+    bool changed    = wasFresh;
     for (int it = 0; it < iters && !conv; ++it)
+    {
         CSB_TRY(tree.update(keys, keys + n, bucketFocus_, conv, s_));
+        changed = changed || !conv; // converged == every node op was "keep": the leaves are those of the call before
+    }
+    if (leavesChanged) *leavesChanged = changed;
     return 0;
 }
 
 template<class K, class T>
-int Engine<K, T>::linkTree(LeafArrayDev<K, T>& tree, bool withCenters)
+int Engine<K, T>::linkTree(LeafArrayDev<K, T>& tree, typename Engine<K, T>::Linked& ln, bool withCenters, bool leavesChanged)
 {
     int L = tree.numNodes, M = L + (L - 1) / 7;
-    CSB_TRY(prefixes_.reserve(sizeof(K) * size_t(M)));
-    CSB_TRY(childOffsets_.reserve(4 * (size_t(M) + 1)));
-    CSB_TRY(parents_.reserve(4 * size_t(std::max(1, (M - 1) / 8))));
-    CSB_TRY(levelRange_.reserve(4 * 32));
-    CSB_TRY(internalToLeaf_.reserve(4 * size_t(M)));
-    CSB_TRY(leafToInternal_.reserve(4 * size_t(M)));
-    uint64_t tb = Api<K, T>::octreeTemp(L);
-    CSB_TRY(octTemp_.reserve(tb + 512));
-    CSB_TRY((Api<K, T>::buildOctree(tree.treeA.template as<K>(), L, prefixes_.template as<K>(), childOffsets_.template as<int32_t>(),
-                                    parents_.template as<int32_t>(), levelRange_.template as<int32_t>(),
-                                    internalToLeaf_.template as<int32_t>(), leafToInternal_.template as<int32_t>(), octTemp_.p,
-                                    octTemp_.bytes, s_)));
+    if (leavesChanged || !ln.valid)
+    {
+        CSB_TRY(ln.prefixes.reserve(sizeof(K) * size_t(M)));
+        CSB_TRY(ln.childOffsets.reserve(4 * (size_t(M) + 1)));
+        CSB_TRY(ln.parents.reserve(4 * size_t(std::max(1, (M - 1) / 8))));
+        CSB_TRY(ln.levelRange.reserve(4 * 32));
+        CSB_TRY(ln.internalToLeaf.reserve(4 * size_t(M)));
+        CSB_TRY(ln.leafToInternal.reserve(4 * size_t(M)));
+        uint64_t tb = Api<K, T>::octreeTemp(L);
+        CSB_TRY(octTemp_.reserve(tb + 512));
+        CSB_TRY((Api<K, T>::buildOctree(tree.treeA.template as<K>(), L, ln.prefixes.template as<K>(), ln.childOffsets.template as<int32_t>(),
+                                        ln.parents.template as<int32_t>(), ln.levelRange.template as<int32_t>(),
+                                        ln.internalToLeaf.template as<int32_t>(), ln.leafToInternal.template as<int32_t>(), octTemp_.p,
+                                        octTemp_.bytes, s_)));
+        ln.valid = true;
+    }
     // layout = exclusive scan of the leaf counts (every leaf of this tree is present)
-    CSB_TRY(layout_.reserve(4 * (size_t(L) + 1)));
+    CSB_TRY(ln.layout.reserve(4 * (size_t(L) + 1)));
     CSB_TRY(scanTemp_.reserve(cstone_b200_scan_temp_bytes(uint64_t(L) + 1) + 512));
-    CSB_TRY(cstone_b200_compute_node_layout(tree.counts.template as<uint32_t>(), nullptr, 0, L, L, layout_.template as<uint32_t>(),
+    CSB_TRY(cstone_b200_compute_node_layout(tree.counts.template as<uint32_t>(), nullptr, 0, L, L, ln.layout.template as<uint32_t>(),
                                             scanTemp_.p, s_));
     if (withCenters)
     {
         CSB_TRY(centers_.reserve(sizeof(T) * 3 * size_t(M)));
         CSB_TRY(sizes_.reserve(sizeof(T) * 3 * size_t(M)));
-        CSB_TRY((Api<K, T>::geoCenters(sfcKind_, prefixes_.template as<K>(), M, centers_.template as<T>(), sizes_.template as<T>(), &box_, s_)));
+        // the box moves with the particles: centres and sizes are recomputed in every sync
+        CSB_TRY((Api<K, T>::geoCenters(sfcKind_, ln.prefixes.template as<K>(), M, centers_.template as<T>(), sizes_.template as<T>(), &box_, s_)));
     }
     return 0;
 }
@@ -1077,9 +1100,10 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
     }
 
     // 10. search tree over assigned + halo particles, linked, with node centres and layout
-    CSB_TRY(convergeTree(search_, fkeys_.template as<K>(), size_t(nTotal_), searchFresh_));
+    bool searchChanged = true;
+    CSB_TRY(convergeTree(search_, fkeys_.template as<K>(), size_t(nTotal_), searchFresh_, 64, &searchChanged));
     mark(9);
-    CSB_TRY(linkTree(search_, true));
+    CSB_TRY(linkTree(search_, lnS_, true, searchChanged));
     mark(10);
     CSB_CUDA(cudaStreamSynchronize(s_));
     firstCall_ = false;
@@ -1115,14 +1139,15 @@ int Engine<K, T>::discoverHalos()
      * discovery needs A valid leaf array with exact counts, not THE converged one: after the first sync the tree of the
      * previous step gets one rebalance + recount step per sync (it follows the particles one step behind) instead of
      * a convergence loop, which cost the ranks whose tree changed a second iteration and everybody else the wait. */
-    CSB_TRY(convergeTree(focus_, skeys, n, focusFresh_, 1));
-    CSB_TRY(linkTree(focus_, false));
+    bool focusChanged = true;
+    CSB_TRY(convergeTree(focus_, skeys, n, focusFresh_, 1, &focusChanged));
+    CSB_TRY(linkTree(focus_, lnF_, false, focusChanged));
     const int L = focus_.numNodes;
 
     lap();
     // b. search radius per leaf [ref: halos/halos.hpp:148-160]
     CSB_TRY(radii_.reserve(4 * size_t(L) + 256));
-    CSB_TRY((Api<K, T>::haloRadii(shAssigned_.template as<T>(), layout_.template as<uint32_t>(), size_t(L), 2.0f * haloFactor_,
+    CSB_TRY((Api<K, T>::haloRadii(shAssigned_.template as<T>(), lnF_.layout.template as<uint32_t>(), size_t(L), 2.0f * haloFactor_,
                                   radii_.template as<float>(), s_)));
 
     // c. halo boxes of my surface leaves
@@ -1156,8 +1181,8 @@ int Engine<K, T>::discoverHalos()
     CSB_CUDA(cudaMemsetAsync(flags_.p, 0, size_t(P) * L, s_));
     {
         dim3 grid(gridFor(size_t(maxS), 128, 4), P);
-        reverseCollisionKernel<K><<<grid, 128, 0, s_>>>(sfcKind_, tabs.dec, prefixes_.template as<K>(), childOffsets_.template as<int32_t>(),
-                                                       internalToLeaf_.template as<int32_t>(), focus_.counts.template as<uint32_t>(), L,
+        reverseCollisionKernel<K><<<grid, 128, 0, s_>>>(sfcKind_, tabs.dec, lnF_.prefixes.template as<K>(), lnF_.childOffsets.template as<int32_t>(),
+                                                       lnF_.internalToLeaf.template as<int32_t>(), focus_.counts.template as<uint32_t>(), L,
                                                        lowest, highest, allSurf_.template as<IBox6>(), dCount + 1, maxS, P, rank_,
                                                        flags_.template as<unsigned char>());
         CSB_LAUNCHED();
@@ -1183,7 +1208,7 @@ int Engine<K, T>::discoverHalos()
     CSB_TRY(sendIdx_.reserve(4 * size_t(nHaloSend_) + 256));
     if (nHaloSend_)
     {
-        expandSendListKernel<<<gridFor(PL, 256), 256, 0, s_>>>(flags_.template as<unsigned char>(), layout_.template as<uint32_t>(),
+        expandSendListKernel<<<gridFor(PL, 256), 256, 0, s_>>>(flags_.template as<unsigned char>(), lnF_.layout.template as<uint32_t>(),
                                                               sendScan_.template as<uint32_t>(), size_t(L), PL,
                                                               sendIdx_.template as<uint32_t>());
         CSB_LAUNCHED();
