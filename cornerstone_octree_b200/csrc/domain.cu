@@ -239,6 +239,13 @@ struct Api
         if constexpr (k64) return cstone_b200_update_octree_k64(f, l, bucket, 0xFFFFFFFFu, ta, tb, counts, ops, cap, n, conv, temp, s);
         else return cstone_b200_update_octree_k32(f, l, bucket, 0xFFFFFFFFu, ta, tb, counts, ops, cap, n, conv, temp, s);
     }
+    //! rebalance decision + scan only: new node count and "every op was keep" [ref: tree/csarray_gpu.h:75-77]
+    static int nodeOps(const K* tree, int32_t n, const uint32_t* counts, unsigned bucket, int32_t* ops, int32_t* newN,
+                       int32_t* conv, void* temp, void* s)
+    {
+        if constexpr (k64) return cstone_b200_compute_node_ops_k64(tree, n, counts, bucket, ops, newN, conv, temp, s);
+        else return cstone_b200_compute_node_ops_k32(tree, n, counts, bucket, ops, newN, conv, temp, s);
+    }
     static int nodeCounts(const K* tree, uint32_t* counts, int32_t n, const K* f, const K* l, void* s)
     {
         if constexpr (k64) return cstone_b200_compute_node_counts_k64(tree, counts, n, f, l, 0xFFFFFFFFu, 1, s);
@@ -316,9 +323,22 @@ struct LeafArrayDev
         numNodes = 1;
         return 0;
     }
-    //! one rebalance + recount step [ref: tree/csarray.hpp:429-448]; counts must hold the counts to decide on
-    int update(const K* first, const K* last, unsigned bucket, bool& converged, cudaStream_t s)
+    /*! one rebalance + recount step [ref: tree/csarray.hpp:429-448]; counts must hold the counts to decide on.
+     *  countsAreCurrent: the counts were computed on [first, last) for THIS tree — then a decision of "keep" for every
+     *  node leaves tree and counts as they are, and neither the tree is written again nor the keys are counted again */
+    int update(const K* first, const K* last, unsigned bucket, bool& converged, cudaStream_t s, bool countsAreCurrent = false)
     {
+        if (countsAreCurrent)
+        {
+            int32_t newN = 0, conv = 0;
+            CSB_TRY((Api<K, T>::nodeOps(treeA.as<K>(), numNodes, counts.as<uint32_t>(), bucket, nodeOps.as<int32_t>(), &newN, &conv,
+                                        temp.p, s)));
+            if (conv && newN == numNodes)
+            {
+                converged = true;
+                return 0;
+            }
+        }
         for (;;)
         {
             int32_t n = numNodes, conv = 0;
@@ -804,7 +824,8 @@ int Engine<K, T>::convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n
     bool changed    = wasFresh;
     for (int it = 0; it < iters && !conv; ++it)
     {
-        CSB_TRY(tree.update(keys, keys + n, bucketFocus_, conv, s_));
+        // steady state, first step: the counts were just taken on these keys with this tree
+        CSB_TRY(tree.update(keys, keys + n, bucketFocus_, conv, s_, !wasFresh && it == 0));
         changed = changed || !conv; // converged == every node op was "keep": the leaves are those of the call before
     }
     if (leavesChanged) *leavesChanged = changed;
