@@ -545,45 +545,62 @@ def main():
                     nc=torch.empty(int(n_assigned * 1.2) + 1024, dtype=torch.int32).pin_memory())
         moved = {"h2d": 0, "d2h": 0}
 
-        copy_stream = torch.cuda.Stream()
+        d2h_stream, h2d_stream = torch.cuda.Stream(), torch.cuda.Stream()
 
-        def e2e_step():
-            # x, y, z first (box and keys need all of them), h behind them on the copy stream: the engine waits for
-            # `h_ready` only where it first reads h, so box, keys and sort overlap the rest of the upload
-            with torch.cuda.stream(copy_stream):
-                up = [t_.cuda(non_blocking=True) for t_ in hin[:3]]
+        def upload(after=None):
+            """x, y, z, h of the NEXT step from the pinned host buffers (on the upload stream; `after[k]` = event behind
+            which host buffer k holds its data).  x, y, z first: box and keys need all of them; the engine waits for
+            `h_ready` only where it first reads h, so box, keys and sort overlap the rest of the upload."""
+            with torch.cuda.stream(h2d_stream):
+                up = []
+                for k in range(3):
+                    if after is not None:
+                        h2d_stream.wait_event(after[k])
+                    up.append(hin[k].cuda(non_blocking=True))
                 xyz_ready = torch.cuda.Event()
                 xyz_ready.record()
+                if after is not None:
+                    h2d_stream.wait_event(after[3])
                 up.append(hin[3].cuda(non_blocking=True))
                 h_ready = torch.cuda.Event()
                 h_ready.record()
-            torch.cuda.current_stream().wait_event(xyz_ready)
-            for t_ in up:
+            return dict(t=up, xyz_ready=xyz_ready, h_ready=h_ready, bytes=sum(t_.numel() * t_.element_size() for t_ in hin))
+
+        def e2e_step():
+            # the inputs of this step travel since the previous step's download delivered them to the host (double
+            # buffering: PCIe up and down run next to findNeighbors); the first step uploads in its own time
+            nxt = state.pop("next_up", None) or upload()
+            torch.cuda.current_stream().wait_event(nxt["xyz_ready"])
+            for t_ in nxt["t"]:
                 t_.record_stream(torch.cuda.current_stream())
-            state["a"] = up
-            state["h_ready"] = h_ready
-            moved["h2d"] = sum(t_.numel() * t_.element_size() for t_ in hin)
+            state["a"] = nxt["t"]
+            state["h_ready"] = nxt["h_ready"]
+            moved["h2d"] = nxt["bytes"]
 
             def download_synced():
                 # keys, x, y, z, h are final once sync returns: their download runs on a second stream while
-                # findNeighbors computes (what a host-side client of Domain would do)
+                # findNeighbors computes (what a host-side client of Domain would do), and every array goes back up
+                # for the next step as soon as it has arrived (the next step's input IS this step's output)
                 m_ = dom.n_particles_with_halos
                 ev = torch.cuda.Event()
                 ev.record()
-                copy_stream.wait_event(ev)
-                with torch.cuda.stream(copy_stream):
-                    hout["keys"][:m_].copy_(state["keys"], non_blocking=True)
-                    for o, s_ in zip(hout["arr"], state["a"]):
+                d2h_stream.wait_event(ev)
+                arrived = []
+                with torch.cuda.stream(d2h_stream):
+                    for k, (o, s_) in enumerate(zip(hout["arr"], state["a"])):
                         o[:m_].copy_(s_, non_blocking=True)
+                        e_ = torch.cuda.Event()
+                        e_.record()
+                        arrived.append(e_)
+                        hin[k] = o[:m_]
+                    hout["keys"][:m_].copy_(state["keys"], non_blocking=True)
+                state["next_up"] = upload(after=arrived)
 
             nw = run_step(after_sync=download_synced)
             m = dom.n_particles_with_halos
             hout["nc"][:nw].copy_(state["nc"][:nw], non_blocking=True)
             moved["d2h"] = m * (bits // 8) + 4 * m * 8 + nw * 4
-            torch.cuda.synchronize()
-            # the next step starts from what the host received (sizes must match the Domain's state)
-            for k in range(4):
-                hin[k] = hout["arr"][k][:m]
+            torch.cuda.synchronize()  # the host holds this step's results (and the next inputs are on the device)
 
         e2e_step()
         barrier()
@@ -596,11 +613,20 @@ def main():
         if world > 1:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         ms_e2e = float(te.item()) / args.steps
+        # what reached the host after the last step: sorted keys, the device's neighbour counts, the device's arrays
+        m_l, nw_l = dom.n_particles_with_halos, dom.n_particles
+        hk = hout["keys"][:m_l]
+        e2e_ok = bool((hk[1:] >= hk[:-1]).all().item()) and bool(torch.equal(hout["nc"][:nw_l], state["nc"][:nw_l].cpu())) and \
+            bool(torch.equal(hout["arr"][0][:m_l], state["a"][0].cpu()))
         e2e = dict(value=n_global / (ms_e2e * 1e-3) / 1e6, unit=UNIT, h2d_bytes_per_step=int(moved["h2d"]),
                    d2h_bytes_per_step=int(moved["d2h"]), ms_per_step=ms_e2e,
                    outputs="keys, x, y, z, h (assigned + halos, SFC order) and neighbour counts; the neighbour lists "
                            "(%d x %d x 4 B per rank) stay device-resident as for Domain<...,GpuTag> clients" %
-                           (n_assigned, args.ngmax))
+                           (n_assigned, args.ngmax),
+                   host_results_ok=e2e_ok,
+                   pipeline="double-buffered: the download of a step's arrays and their upload as the next step's "
+                            "inputs run on two copy streams next to findNeighbors; every step waits for its own "
+                            "inputs and ends with its neighbour counts on the host")
 
     if rank != 0:
         dom.close()
