@@ -196,6 +196,7 @@ _DOMAIN_PROTOS = {
     "sync_begin": (_i64, [_vp, _u64, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "sync_finish": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "exchange_halos": (_i, [_vp, _i, _vp, _vp]),
+    "reapply_sync": (_i, [_vp, _i, _vp, _vp, _vp]),
     "info": (_i, [_vp, _vp]),
     "box": (_i, [_vp, _vp]),
     "stage_ms": (_i, [_vp, _vp]),

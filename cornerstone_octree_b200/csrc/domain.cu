@@ -594,6 +594,7 @@ public:
                       const int* propBytes);
     int syncFinish(K* keys, T* x, T* y, T* z, T* h, void* const* props);
     int exchangeHalos(int narrays, void* const* arrays, const int* elemBytes);
+    int reapplySync(int narrays, const void* const* in, const int* elemBytes, void* const* out);
     int findNeighbors(const T* x, const T* y, const T* z, const T* h, uint32_t ngmax, uint32_t* nb, uint32_t* nc) const;
 
     void info(int64_t* o) const
@@ -690,6 +691,14 @@ private:
     // steady-state merge: the assigned set is gathered from two sources through map2_ (see mergeScatterKernel)
     const uint32_t* map2_ = nullptr;
     const void* origSrc_[4 + 12] = {nullptr};
+    // exchange pattern of the last sync, kept for reapplySync [ref: domain/domain.hpp:334-378]
+    struct Pattern
+    {
+        bool valid = false, steady = false;
+        uint64_t inStart = 0, np = 0, nAssigned = 0, start = 0;
+        std::vector<uint32_t> sendStart, sendCount, recvOff, recvCount;
+    } pat_;
+    DevBuf order1Keep_; // map of the first sort when the second sort overwrites order_ (first sync / large exchanges)
     DevBuf pack_[4 + kMaxProps], recv_[4 + kMaxProps], fin_[4 + kMaxProps];
     DevBuf skeys_, fkeys_, shAssigned_, merge_;
 
@@ -938,6 +947,7 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
     {
         // every particle stays: one gather into the final arrays, no halos
         nAssigned_ = np, start_ = 0, end_ = np, nTotal_ = np, nHaloSend_ = 0;
+        pat_.valid = true, pat_.steady = false, pat_.inStart = inStart, pat_.np = np, pat_.nAssigned = np, pat_.start = 0;
         for (int a = 0; a < na; ++a)
         {
             CSB_TRY(fin_[a].reserve(size_t(eb[a]) * np + 256));
@@ -989,6 +999,15 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         /* steady state = nearly everything stays here: the particles that stay are neither packed nor copied, the
          * assigned set is later gathered from two sources (caller arrays through the sort map, receive buffers) */
         const bool steady = nAssigned_ && size_t(uint32_t(nAssigned_) - sendCount[rank_]) * 4 <= size_t(nAssigned_);
+
+        pat_.valid = true, pat_.steady = steady, pat_.inStart = inStart, pat_.np = np, pat_.nAssigned = nAssigned_;
+        pat_.sendStart = sendStart, pat_.sendCount = sendCount, pat_.recvOff = recvOff, pat_.recvCount = recvCount;
+        if (!steady && np)
+        {
+            // the second sort below reuses order_: keep the map of the first one for reapplySync
+            CSB_TRY(order1Keep_.reserve(4 * np + 256));
+            CSB_CUDA(cudaMemcpyAsync(order1Keep_.p, order_.p, 4 * np, cudaMemcpyDeviceToDevice, s_));
+        }
 
         // 6. ONE gather orders the outgoing messages (sorted by key = grouped by destination rank)
         for (int a = 0; a < na; ++a)
@@ -1253,6 +1272,7 @@ int Engine<K, T>::discoverHalos()
         if (q > rank_) right += haloRecvCount_[q];
     }
     start_  = left;
+    pat_.start = left;
     end_    = left + n;
     nTotal_ = end_ + right;
     if (nTotal_ >= (uint64_t(1) << 30)) return CSTONE_E_TOO_LARGE;
@@ -1361,6 +1381,96 @@ int Engine<K, T>::exchangeHalos(int narrays, void* const* arrays, const int* ele
         }
     }
     return comm_->exchange(sends, recvs, s_);
+}
+
+/*! [ref: domain/domain.hpp:334-378 reapplySync] the particle exchange and re-ordering of the LAST sync applied to further
+ *  arrays.  in[a]: the array in the layout the caller's arrays had BEFORE that sync (device pointer, at least
+ *  inStart + np elements); out[a]: nParticlesWithHalos elements of the new layout, of which the assigned range
+ *  [startIndex, endIndex) is written (halos: exchangeHalos).  The reference does this for host arrays only. */
+template<class K, class T>
+int Engine<K, T>::reapplySync(int narrays, const void* const* in, const int* eb, void* const* out)
+{
+    if (!pat_.valid) return CSTONE_E_INVALID_ARGUMENT;
+    if (narrays == 0) return 0;
+    if (narrays < 0 || narrays > 4 + kMaxProps || !in || !eb || !out) return CSTONE_E_INVALID_ARGUMENT;
+    for (int a = 0; a < narrays; ++a)
+        if ((eb[a] != 4 && eb[a] != 8 && eb[a] != 12 && eb[a] != 16) || !in[a] || !out[a]) return CSTONE_E_INVALID_ARGUMENT;
+    const size_t np = size_t(pat_.np), n = size_t(pat_.nAssigned);
+    const void* src[4 + kMaxProps];
+    void* dst[4 + kMaxProps];
+    for (int a = 0; a < narrays; ++a)
+    {
+        src[a] = static_cast<const char*>(in[a]) + size_t(pat_.inStart) * eb[a];
+        dst[a] = static_cast<char*>(out[a]) + size_t(pat_.start) * eb[a];
+    }
+    if (nRanks_ == 1)
+    {
+        if (np) CSB_TRY(gatherMulti(order_.template as<uint32_t>(), np, narrays, src, dst, eb));
+        return int(cudaStreamSynchronize(s_));
+    }
+    const int P = nRanks_;
+    const auto &sendStart = pat_.sendStart, &sendCount = pat_.sendCount, &recvOff = pat_.recvOff, &recvCount = pat_.recvCount;
+    const uint32_t* order1 = pat_.steady ? order_.template as<uint32_t>() : order1Keep_.template as<uint32_t>();
+    void* pk[4 + kMaxProps];
+    for (int a = 0; a < narrays; ++a)
+    {
+        CSB_TRY(pack_[a].reserve(size_t(eb[a]) * np + 256));
+        CSB_TRY(recv_[a].reserve(size_t(eb[a]) * n + 256));
+        pk[a] = pack_[a].p;
+    }
+    if (!pat_.steady)
+    {
+        if (np) CSB_TRY(gatherMulti(order1, np, narrays, src, pk, eb));
+    }
+    else
+    {
+        const size_t lo = sendStart[rank_], hiStart = size_t(sendStart[rank_]) + sendCount[rank_];
+        void* d2[4 + kMaxProps];
+        if (lo) CSB_TRY(gatherMulti(order1, lo, narrays, src, pk, eb));
+        if (np > hiStart)
+        {
+            for (int a = 0; a < narrays; ++a)
+                d2[a] = pack_[a].template as<char>() + hiStart * size_t(eb[a]);
+            CSB_TRY(gatherMulti(order1 + hiStart, np - hiStart, narrays, src, d2, eb));
+        }
+    }
+    {
+        std::vector<CommMsg> sends, recvs;
+        for (int q = 0; q < P; ++q)
+        {
+            if (q == rank_) continue;
+            for (int a = 0; a < narrays; ++a)
+            {
+                if (sendCount[q])
+                    sends.push_back({q, pack_[a].template as<char>() + size_t(sendStart[q]) * eb[a], size_t(sendCount[q]) * eb[a]});
+                if (recvCount[q])
+                    recvs.push_back({q, recv_[a].template as<char>() + size_t(recvOff[q]) * eb[a], size_t(recvCount[q]) * eb[a]});
+            }
+        }
+        CSB_TRY(comm_->exchange(sends, recvs, s_));
+    }
+    if (!pat_.steady)
+    {
+        for (int a = 0; a < narrays; ++a)
+            if (sendCount[rank_])
+                CSB_CUDA(cudaMemcpyAsync(recv_[a].template as<char>() + size_t(recvOff[rank_]) * eb[a],
+                                         pack_[a].template as<char>() + size_t(sendStart[rank_]) * eb[a],
+                                         size_t(sendCount[rank_]) * eb[a], cudaMemcpyDeviceToDevice, s_));
+        const void* rsrc[4 + kMaxProps];
+        for (int a = 0; a < narrays; ++a)
+            rsrc[a] = recv_[a].p;
+        if (n) CSB_TRY(gatherMulti(order_.template as<uint32_t>(), n, narrays, rsrc, dst, eb));
+    }
+    else if (n)
+    {
+        GatherTwoArgs g{};
+        g.na = narrays;
+        for (int a = 0; a < narrays; ++a)
+            g.orig[a] = src[a], g.recv[a] = recv_[a].p, g.dst[a] = dst[a], g.words[a] = eb[a] / 4;
+        gatherTwoKernel<<<gridFor(n, 256, 8), 256, 0, s_>>>(map2_, n, g);
+        CSB_LAUNCHED();
+    }
+    return int(cudaStreamSynchronize(s_));
 }
 
 template<class K, class T>
@@ -1498,6 +1608,12 @@ void cstone_b200_local_world_destroy(void* world) { delete static_cast<csb::Loca
         int st = CSB_ENGINE(K, T, d)->exchangeHalos(na, arrays, eb);                                                   \
         if (st) return st;                                                                                             \
         return int(cudaStreamSynchronize(nullptr));                                                                    \
+    }                                                                                                                  \
+    int cstone_b200_domain_reapply_sync_##KS##_##TS(cstone_b200_domain* d, int na, const void* const* in,              \
+                                                    const int* eb, void* const* out)                                   \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return CSB_ENGINE(K, T, d)->reapplySync(na, in, eb, out);                                                      \
     }                                                                                                                  \
     int cstone_b200_domain_info_##KS##_##TS(const cstone_b200_domain* d, int64_t* info8)                               \
     {                                                                                                                  \

@@ -129,6 +129,20 @@ class Domain:
         eb = (C.c_int * k)(*[_row_bytes(a) for a in arrays])
         _check(_fn("exchange_halos", self.bits, self.fd)(self._h, k, arr, eb), "exchange_halos")
 
+    def reapply_sync(self, arrays):
+        """[ref: domain/domain.hpp:334-378 reapplySync] arrays in the layout BEFORE the last sync -> new tensors of the
+        new local size with the assigned range filled (halos: exchange_halos)"""
+        k = len(arrays)
+        if k == 0:
+            return []
+        n_new = self.n_particles_with_halos
+        out = [torch.zeros((n_new,) + tuple(a.shape[1:]), dtype=a.dtype, device=a.device) for a in arrays]
+        iarr = (C.c_void_p * k)(*[a.data_ptr() for a in arrays])
+        oarr = (C.c_void_p * k)(*[a.data_ptr() for a in out])
+        eb = (C.c_int * k)(*[_row_bytes(a) for a in arrays])
+        _check(_fn("reapply_sync", self.bits, self.fd)(self._h, k, iarr, eb, oarr), "reapply_sync")
+        return out
+
     # ---- accessors [ref: domain/domain.hpp:389-437]
     def _info(self):
         info = (C.c_int64 * 8)()

@@ -17,6 +17,7 @@
 #include <array>
 #include <cstdint>
 #include <tuple>
+#include <utility>
 #include <vector>
 
 #include "../cstone_b200_domain.h"
@@ -72,6 +73,7 @@ struct DomainApi;
         static constexpr auto syncBegin     = cstone_b200_domain_sync_begin_##KS##_##TS;                               \
         static constexpr auto syncFinish    = cstone_b200_domain_sync_finish_##KS##_##TS;                              \
         static constexpr auto exchangeHalos = cstone_b200_domain_exchange_halos_##KS##_##TS;                           \
+        static constexpr auto reapplySync   = cstone_b200_domain_reapply_sync_##KS##_##TS;                             \
         static constexpr auto info          = cstone_b200_domain_info_##KS##_##TS;                                     \
         static constexpr auto box           = cstone_b200_domain_box_##KS##_##TS;                                      \
         static constexpr auto stageMs       = cstone_b200_domain_stage_ms_##KS##_##TS;                                 \
@@ -206,6 +208,27 @@ public:
         detail::check(Api::exchangeHalos(d_, na, ptrs.data(), bytes.data()), "Domain::exchangeHalos");
     }
 
+    /*! [ref: domain/domain.hpp:334-378]  reapply the exchange and ordering of the last sync to further arrays, which
+     *  still have the layout the particle arrays had BEFORE that sync; on return they have nParticlesWithHalos()
+     *  elements with the assigned range valid.  Buffers and ordering are accepted for source compatibility (the
+     *  engine keeps the pattern itself); DEVICE vectors here, where the reference supports host vectors only. */
+    template<class... Vectors, class SendBuffer, class ReceiveBuffer, class OVec>
+    void reapplySync(std::tuple<Vectors&...> arrays, SendBuffer&, ReceiveBuffer&, OVec& /*ordering*/) const
+    {
+        static_assert(((sizeof(typename Vectors::value_type) % 4 == 0 && sizeof(typename Vectors::value_type) <= 16) && ...));
+        constexpr int na = sizeof...(Vectors);
+        std::array<const void*, na + 1> in{};
+        std::array<void*, na + 1> out{};
+        std::array<int, na + 1> bytes{};
+        std::tuple<std::remove_reference_t<Vectors>...> fresh;
+        int i = 0;
+        std::apply([&](auto&... a) { ((in[i] = a.data(), bytes[i] = int(sizeof(*a.data())), ++i), ...); }, arrays);
+        i = 0;
+        std::apply([&](auto&... f) { ((f.resize(info_[2]), out[i++] = f.data()), ...); }, fresh);
+        detail::check(Api::reapplySync(d_, na, in.data(), bytes.data(), out.data()), "Domain::reapplySync");
+        swapTuples(arrays, fresh, std::make_index_sequence<sizeof...(Vectors)>{});
+    }
+
     [[nodiscard]] LocalIndex startIndex() const { return LocalIndex(info_[0]); }
     [[nodiscard]] LocalIndex endIndex() const { return LocalIndex(info_[1]); }
     //! [ref: domain/domain.hpp:396] set the index of the last particle (used to increase the number of particles)
@@ -300,6 +323,12 @@ private:
         const std::size_t sizes[] = {arrays.size()..., value};
         for (std::size_t s : sizes)
             if (s != value) throw std::runtime_error("Domain sync: input array sizes are inconsistent\n");
+    }
+
+    template<class A, class B, std::size_t... I>
+    static void swapTuples(A& a, B& b, std::index_sequence<I...>)
+    {
+        (std::get<I>(a).swap(std::get<I>(b)), ...);
     }
 
     std::array<TreeNodeIndex, 2> cellRange() const

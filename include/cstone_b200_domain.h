@@ -76,6 +76,13 @@ void cstone_b200_local_world_destroy(void* world);
     /* [ref: domain/domain.hpp:381-386 exchangeHalos] arrays: HOST array of device pointers of length n_new */        \
     int cstone_b200_domain_exchange_halos_##KS##_##TS(cstone_b200_domain* d, int narrays, void* const* arrays,         \
                                                       const int* elem_bytes);                                          \
+    /* [ref: domain/domain.hpp:334-378 reapplySync] the particle exchange and re-ordering of the last sync applied to  \
+     * further arrays (device arrays here; the reference supports host arrays only).  in: HOST array of device        \
+     * pointers to arrays in the layout the caller's arrays had BEFORE that sync; out: HOST array of device pointers   \
+     * to arrays of the new size, whose assigned range [start, end) is written; element sizes 4, 8, 12 or 16 bytes.    \
+     * Collective over the ranks of the domain. */                                                                     \
+    int cstone_b200_domain_reapply_sync_##KS##_##TS(cstone_b200_domain* d, int narrays, const void* const* in,         \
+                                                    const int* elem_bytes, void* const* out);                          \
     /* [ref: domain/domain.hpp:389-437] accessors; info[8] = start, end, n_total, n_leaves(focus), n_nodes(focus),    \
      * n_leaves(global), num halo send particles, num halo recv particles */                                           \
     int cstone_b200_domain_info_##KS##_##TS(const cstone_b200_domain* d, int64_t* info8);                              \

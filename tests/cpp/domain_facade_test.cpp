@@ -95,7 +95,18 @@ static void run(int rank, int nRanks, const std::array<char, 128>& id, LocalInde
 
     for (int step = 0; step < 2; ++step)
     {
+        // a copy of one property in the layout BEFORE the sync: reapplySync must take it where sync takes pid
+        DeviceVector<unsigned> pidLate(pid);
         domain.sync(keys, x, y, z, h, std::tie(pid, psum), std::tie(s1, s2, s3));
+        domain.reapplySync(std::tie(pidLate), s1, s2, s3);
+        {
+            auto viaSync = toHost(pid), viaReapply = toHost(pidLate);
+            EXPECT(viaReapply.size() == viaSync.size());
+            bool same = viaReapply.size() == viaSync.size();
+            for (LocalIndex q = domain.startIndex(); same && q < domain.endIndex(); ++q)
+                same = viaSync[q] == viaReapply[q];
+            EXPECT(same);
+        }
         domain.exchangeHalos(std::tie(pid, psum), s1, s2);
 
         LocalIndex n = domain.nParticlesWithHalos(), a = domain.startIndex(), b = domain.endIndex();

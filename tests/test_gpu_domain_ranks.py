@@ -238,7 +238,11 @@ def test_wide_properties_accessors_and_growth():
 
     def one(r):
         sx, sy, sz, sh, g, w4, w3 = state[r]
+        late = [g.clone(), w4.clone()]  # layout before the sync, for reapplySync [ref: domain/domain.hpp:334-378]
         keys, sx, sy, sz, sh, (g, w4, w3) = doms[r].sync(sx, sy, sz, sh, [g, w4, w3])
+        lg, lw4 = doms[r].reapply_sync(late)
+        s_, e_ = doms[r].start_index, doms[r].end_index
+        assert torch.equal(lg[s_:e_], g[s_:e_]) and torch.equal(lw4[s_:e_], w4[s_:e_]), "reapplySync differs from sync"
         state[r] = [sx, sy, sz, sh, g, w4, w3]
         doms[r].exchange_halos([g, w4, w3])
         return keys
