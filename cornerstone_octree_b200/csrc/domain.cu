@@ -29,6 +29,7 @@
 
 #include "../../include/cstone_b200_domain.h"
 #include "comm.hpp"
+#include "let_tree.cuh"
 #include "halo_box.cuh"
 #include "scan.cuh"
 #include "domain_host.hpp"
@@ -278,6 +279,14 @@ struct Api
     {
         if constexpr (f64) return cstone_b200_halo_radii_f64(h, seg, n, scale, radii, s);
         else return cstone_b200_halo_radii_f32(h, seg, n, scale, radii, s);
+    }
+    static int findHalos(int kind, const K* prefixes, const int32_t* co, const int32_t* itl, const K* leaves, const float* radii,
+                         const CBox* box, int32_t first, int32_t last, int32_t* flags, void* s)
+    {
+        if constexpr (k64 && f64) return cstone_b200_find_halos_k64_f64(kind, prefixes, co, itl, leaves, radii, box, first, last, flags, s);
+        else if constexpr (k64 && !f64) return cstone_b200_find_halos_k64_f32(kind, prefixes, co, itl, leaves, radii, box, first, last, flags, s);
+        else if constexpr (!k64 && f64) return cstone_b200_find_halos_k32_f64(kind, prefixes, co, itl, leaves, radii, box, first, last, flags, s);
+        else return cstone_b200_find_halos_k32_f32(kind, prefixes, co, itl, leaves, radii, box, first, last, flags, s);
     }
     static int neighbors(const T* x, const T* y, const T* z, const T* h, uint32_t first, uint32_t last, const CBox* box,
                          const int32_t* co, const int32_t* itl, const uint32_t* layout, const T* centers, const T* sizes,
@@ -562,6 +571,20 @@ public:
         haloFactor_ = f;
         return 0;
     }
+    /*! how halos are found at nRanks > 1.  0 (default): surface boxes of every rank against the leaves of the assigned
+     *  particles (fast path, halo set a subset of the reference's).  1: the reference's way -- the multi-rank focus tree
+     *  (LET, let_tree.cuh) + findHalos on it + key-range requests between peers [ref: domain/domain.hpp:217-243]; then
+     *  halo flags, layout, startIndex / endIndex and the tree handed to findNeighbors are the reference's. */
+    int setHaloMode(int mode)
+    {
+        if ((mode != 0 && mode != 1) || !firstCall_) return CSTONE_E_INVALID_ARGUMENT;
+        haloMode_ = mode;
+        return 0;
+    }
+    //! LET mode: host copies of the focus-tree leaves, their counts, the halo flags, the layout, the peer assignment
+    const LetTree<K, T>* let() const { return let_.get(); }
+    const std::vector<int32_t>& letFlags() const { return hFlags_; }
+    const std::vector<uint32_t>& letLayout() const { return hLayout_; }
     //! [ref: domain/domain.hpp:404-406 startCell / endCell] leaves of the search tree that hold the assigned particles
     int cells(int32_t* out2)
     {
@@ -635,6 +658,7 @@ private:
     int convergeTree(LeafArrayDev<K, T>& tree, const K* keys, size_t n, bool& fresh, int maxSteadyIter = 64,
                      bool* leavesChanged = nullptr);
     int discoverHalos();
+    int discoverHalosLet();
     int hostCounts(const uint32_t* dev, int n, std::vector<uint32_t>& out)
     {
         out.resize(n);
@@ -679,6 +703,10 @@ private:
     cudaEvent_t fieldsReady_ = nullptr;
     int sfcKind_      = CSTONE_SFC_HILBERT;
     float haloFactor_ = 1.0f;
+    int haloMode_     = 0;
+    std::unique_ptr<LetTree<K, T>> let_;
+    std::vector<int32_t> hFlags_;
+    std::vector<uint32_t> hLayout_;
     cudaStream_t s_   = nullptr; // legacy default stream: ordered with the caller's default-stream work
 
     // particle state
@@ -1135,16 +1163,27 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
 
         mark(6);
         // 9. halos
-        CSB_TRY(discoverHalos());
+        CSB_TRY(haloMode_ == 1 ? discoverHalosLet() : discoverHalos());
         mark(8);
     }
 
     // 10. search tree over assigned + halo particles, linked, with node centres and layout
-    bool searchChanged = true;
-    CSB_TRY(convergeTree(search_, fkeys_.template as<K>(), size_t(nTotal_), searchFresh_, 64, &searchChanged));
-    mark(9);
-    CSB_TRY(linkTree(search_, lnS_, true, searchChanged));
-    mark(10);
+    if (nRanks_ > 1 && haloMode_ == 1)
+    {
+        // the LET is the search tree [ref: domain/domain.hpp:423-436 octreeProperties]; layout: present leaves only
+        mark(9);
+        CSB_TRY(linkTree(search_, lnS_, true, true));
+        CSB_CUDA(cudaMemcpyAsync(lnS_.layout.p, hLayout_.data(), 4 * hLayout_.size(), cudaMemcpyHostToDevice, s_));
+        mark(10);
+    }
+    else
+    {
+        bool searchChanged = true;
+        CSB_TRY(convergeTree(search_, fkeys_.template as<K>(), size_t(nTotal_), searchFresh_, 64, &searchChanged));
+        mark(9);
+        CSB_TRY(linkTree(search_, lnS_, true, searchChanged));
+        mark(10);
+    }
     CSB_CUDA(cudaStreamSynchronize(s_));
     firstCall_ = false;
     return int64_t(nTotal_);
@@ -1323,6 +1362,220 @@ int Engine<K, T>::discoverHalos()
     if (start_) CSB_TRY((Api<K, T>::keys(sfcKind_, fx, fy, fz, fk, size_t(start_), &box_, s_)));
     if (nTotal_ > end_)
         CSB_TRY((Api<K, T>::keys(sfcKind_, fx + end_, fy + end_, fz + end_, fk + end_, size_t(nTotal_ - end_), &box_, s_)));
+    return 0;
+}
+
+/*! halo discovery the reference's way [ref: domain/domain.hpp:217-243]: peers from the global tree, the multi-rank focus
+ *  tree brought up to date, findHalos on it, layout of the present leaves, key-range requests between peers. */
+template<class K, class T>
+int Engine<K, T>::discoverHalosLet()
+{
+    const int P    = nRanks_;
+    const size_t n = size_t(nAssigned_);
+    const K* skeys = skeys_.template as<K>();
+    const int na   = 4 + nprops_;
+    int eb[4 + kMaxProps];
+    for (int a = 0; a < na; ++a)
+        eb[a] = a < 4 ? int(sizeof(T)) : propBytes_[a - 4];
+    if (!let_) let_.reset(new LetTree<K, T>(rank_, P, bucketFocus_, sfcKind_));
+    LetTree<K, T>& let = *let_;
+
+    // a. peers [ref: traversal/peers.hpp:62-117], focus tree [ref: domain/domain.hpp:219-228]
+    HostOctree<K> gtree;
+    gtree.build(hGlobalLeaves_.data(), global_.numNodes);
+    const float invThetaEff = 1.0f / theta_ + 0.5f; // [ref: traversal/macs.hpp:45 invThetaMinMac]
+    const std::vector<int> peers = findPeersMacHost<K, T>(sfcKind_, rank_, boundaries_, gtree, box_, invThetaEff);
+    if (firstCall_)
+    {
+        // [ref: focus/octree_focus_mpi.hpp:528-547 converge]
+        CSB_TRY(small_.reserve(size_t(P + 1) * (sizeof(K) + 4) + size_t(P) * P * 4 + 4096));
+        int32_t* dConv = small_.template as<int32_t>();
+        for (int converged = 0, it = 0; converged != P; ++it)
+        {
+            if (it > 200) return CSTONE_E_LET;
+            CSB_TRY(let.updateMinMac(boundaries_, invThetaEff, s_));
+            CSB_TRY(let.updateTree(comm_.get(), peers, boundaries_, box_, &converged, s_));
+            CSB_TRY(let.updateCounts(comm_.get(), skeys, n, hGlobalLeaves_, hGlobalCounts_, s_));
+            CSB_CUDA(cudaMemcpyAsync(dConv, &converged, 4, cudaMemcpyHostToDevice, s_));
+            CSB_TRY(comm_->allReduce(dConv, 1, CommType::i32, CommOp::sum, s_));
+            CSB_CUDA(cudaMemcpyAsync(&converged, dConv, 4, cudaMemcpyDeviceToHost, s_));
+            CSB_CUDA(cudaStreamSynchronize(s_));
+        }
+    }
+    CSB_TRY(let.updateMinMac(boundaries_, invThetaEff, s_));
+    CSB_TRY(let.updateTree(comm_.get(), peers, boundaries_, box_, nullptr, s_));
+    CSB_TRY(let.updateCounts(comm_.get(), skeys, n, hGlobalLeaves_, hGlobalCounts_, s_));
+
+    const FocusTree<K>& ft           = let.t;
+    const int L                      = ft.numLeaves_;
+    const std::vector<K>& leaves     = let.leaves();
+    const std::vector<uint32_t>& cnt = let.leafCounts();
+    const auto& assign               = let.assignment();
+    const int firstNode = assign[rank_][0], lastNode = assign[rank_][1], numSearch = lastNode - firstNode;
+
+    // b. search radius of my leaves, collisions with the rest of the tree [ref: halos/halos.hpp:127-189 discover]
+    CSB_TRY(radii_.reserve(4 * size_t(L) + 256));
+    CSB_TRY(flags_.reserve(4 * size_t(L) + 256));
+    CSB_TRY(sendScan_.reserve(4 * (size_t(numSearch) + 2) + 256));
+    CSB_TRY(scanTemp_.reserve(cstone_b200_scan_temp_bytes(uint64_t(L) + 2) + 512));
+    CSB_CUDA(cudaMemsetAsync(radii_.p, 0, 4 * size_t(L), s_));
+    CSB_CUDA(cudaMemsetAsync(flags_.p, 0, 4 * size_t(L), s_));
+    if (numSearch > 0)
+    {
+        uint32_t* seg = sendScan_.template as<uint32_t>();
+        CSB_TRY(cstone_b200_exclusive_scan_u32(ft.leafCounts_.template as<uint32_t>() + firstNode, seg, size_t(numSearch) + 1, 0u,
+                                               scanTemp_.p, s_));
+        CSB_TRY((Api<K, T>::haloRadii(shAssigned_.template as<T>(), seg, size_t(numSearch), 2.0f * haloFactor_,
+                                      radii_.template as<float>() + firstNode, s_)));
+        CSB_TRY((Api<K, T>::findHalos(sfcKind_, ft.prefixes_.template as<K>(), ft.childOffsets_.template as<int32_t>(),
+                                      ft.i2l_.template as<int32_t>(), ft.leaves_.template as<K>(), radii_.template as<float>(), &box_,
+                                      firstNode, lastNode, flags_.template as<int32_t>(), s_)));
+    }
+    hFlags_.resize(size_t(L));
+    CSB_CUDA(cudaMemcpyAsync(hFlags_.data(), flags_.p, 4 * size_t(L), cudaMemcpyDeviceToHost, s_));
+    CSB_CUDA(cudaStreamSynchronize(s_));
+
+    // c. layout of the present leaves [ref: domain/layout.hpp:150-164 computeNodeLayout]
+    hLayout_.resize(size_t(L) + 1);
+    {
+        uint32_t run = 0;
+        for (int i = 0; i < L; ++i)
+        {
+            hLayout_[i] = run;
+            if ((firstNode <= i && i < lastNode) || hFlags_[i]) run += cnt[i];
+        }
+        hLayout_[L] = run;
+    }
+    start_ = hLayout_[firstNode], end_ = hLayout_[lastNode], nTotal_ = hLayout_[L];
+    pat_.start = start_;
+    if (nTotal_ >= (uint64_t(1) << 30)) return CSTONE_E_TOO_LARGE;
+
+    // d. per peer: the key ranges of its leaves that I flagged; it answers with particle ranges of ITS layout
+    //    [ref: domain/exchange_keys.hpp:62-118 exchangeRequestKeys, domain/layout.hpp:93-123 extractMarkedElements]
+    std::vector<std::vector<char>> requests(P), requested;
+    for (int peer : peers)
+    {
+        std::vector<K> req;
+        int i = assign[peer][0];
+        const int e = assign[peer][1];
+        while (i != e)
+        {
+            while (i < e && hFlags_[i] == 0)
+                ++i;
+            if (i != e)
+            {
+                req.push_back(leaves[i]);
+                while (i < e && hFlags_[i] == 1)
+                    ++i;
+                req.push_back(leaves[i]);
+            }
+        }
+        requests[peer].resize(req.size() * sizeof(K));
+        if (!req.empty()) std::memcpy(requests[peer].data(), req.data(), requests[peer].size());
+    }
+    CSB_TRY(let.exchangeBytes(comm_.get(), requests, requested, s_));
+    haloSendCount_.assign(P, 0), haloSendOffset_.assign(P + 1, 0);
+    std::vector<uint32_t> sendIdx;
+    bool consistent = uint64_t(end_ - start_) == uint64_t(n);
+    for (int q = 0; q < P; ++q)
+    {
+        haloSendOffset_[q] = uint32_t(sendIdx.size());
+        const size_t nk    = requested[q].size() / sizeof(K);
+        const K* rk        = reinterpret_cast<const K*>(requested[q].data());
+        for (size_t k = 0; k + 1 < nk; k += 2)
+        {
+            const uint32_t lo = hLayout_[findNodeAbove(leaves.data(), L + 1, rk[k])];
+            const uint32_t hi = hLayout_[findNodeAbove(leaves.data(), L + 1, rk[k + 1])];
+            // [ref: halos/halos.hpp:40-55 checkIndices] only assigned particles travel as halos
+            if (lo < start_ || hi > end_ || hi < lo)
+            {
+                consistent = false;
+                continue;
+            }
+            for (uint32_t j = lo; j < hi; ++j)
+                sendIdx.push_back(j - uint32_t(start_));
+        }
+        haloSendCount_[q] = uint32_t(sendIdx.size()) - haloSendOffset_[q];
+    }
+    haloSendOffset_[P] = uint32_t(sendIdx.size());
+    nHaloSend_         = sendIdx.size();
+    CSB_TRY(sendIdx_.reserve(4 * sendIdx.size() + 256));
+    if (!sendIdx.empty())
+        CSB_CUDA(cudaMemcpyAsync(sendIdx_.p, sendIdx.data(), 4 * sendIdx.size(), cudaMemcpyHostToDevice, s_));
+
+    // e. where the halos of each peer arrive [ref: domain/layout.hpp:166-183 computeHaloRecvList]
+    haloRecvCount_.assign(P, 0), haloRecvOffset_.assign(P, 0);
+    for (int peer : peers)
+    {
+        int firstNz = assign[peer][0], lastNz = assign[peer][1];
+        while (firstNz < assign[peer][1] && hFlags_[firstNz] != 1)
+            ++firstNz;
+        while (lastNz > firstNz && hFlags_[lastNz - 1] != 1)
+            --lastNz;
+        haloRecvOffset_[peer] = hLayout_[firstNz];
+        haloRecvCount_[peer]  = hLayout_[lastNz] - hLayout_[firstNz];
+    }
+    // [ref: halos/halos.hpp:58-100 checkHalos] every flagged leaf outside of my range must belong to a peer
+    for (int i = 0; i < L; ++i)
+    {
+        if (!hFlags_[i] || (firstNode <= i && i < lastNode)) continue;
+        bool found = false;
+        for (int peer : peers)
+            found = found || (assign[peer][0] <= i && i < assign[peer][1]);
+        if (!found) consistent = false;
+    }
+
+    /* f. every rank sees every send and expected receive count: a mismatch (counts of a peer's range that differ from
+     *    the owner's) ends the sync on ALL ranks with an error instead of a hanging exchange */
+    {
+        CSB_TRY(nSurf_.reserve(size_t(2 * P + 1) * 4 * size_t(P + 1) + 1024));
+        uint32_t* dMine = nSurf_.template as<uint32_t>();
+        uint32_t* dAll  = dMine + (2 * P + 1 + 63) / 64 * 64;
+        std::vector<uint32_t> mine(2 * P + 1), all(size_t(2 * P + 1) * P);
+        for (int q = 0; q < P; ++q)
+            mine[q] = haloSendCount_[q], mine[P + q] = haloRecvCount_[q];
+        mine[2 * P] = consistent ? 0u : 1u;
+        CSB_CUDA(cudaMemcpyAsync(dMine, mine.data(), 4 * mine.size(), cudaMemcpyHostToDevice, s_));
+        CSB_TRY(comm_->allGather(dMine, dAll, 4 * mine.size(), s_));
+        CSB_CUDA(cudaMemcpyAsync(all.data(), dAll, 4 * all.size(), cudaMemcpyDeviceToHost, s_));
+        CSB_CUDA(cudaStreamSynchronize(s_));
+        bool ok = true;
+        for (int a = 0; a < P; ++a)
+        {
+            ok = ok && all[size_t(a) * (2 * P + 1) + 2 * P] == 0;
+            for (int b = 0; b < P; ++b)
+                ok = ok && all[size_t(a) * (2 * P + 1) + b] == all[size_t(b) * (2 * P + 1) + P + a];
+        }
+        if (!ok) return CSTONE_E_LET;
+    }
+
+    // g. assigned particles to their final position, halos of x,y,z,h, keys of the halos
+    mark(7);
+    void* dst[4 + kMaxProps];
+    int which[4 + kMaxProps];
+    for (int a = 0; a < na; ++a)
+    {
+        CSB_TRY(fin_[a].reserve(size_t(eb[a]) * nTotal_ + 256));
+        which[a] = a;
+        dst[a]   = fin_[a].template as<char>() + size_t(start_) * eb[a];
+    }
+    CSB_TRY(gatherAssigned(n, na, which, dst, eb));
+    void* xyzh[4] = {fin_[0].p, fin_[1].p, fin_[2].p, fin_[3].p};
+    CSB_TRY(exchangeHalos(4, xyzh, eb));
+    CSB_TRY(fkeys_.reserve(sizeof(K) * nTotal_ + 256));
+    K* fk = fkeys_.template as<K>();
+    CSB_CUDA(cudaMemsetAsync(fk, 0, sizeof(K) * nTotal_, s_));
+    CSB_CUDA(cudaMemcpyAsync(fk + start_, skeys, sizeof(K) * n, cudaMemcpyDeviceToDevice, s_));
+    const T *fx = fin_[0].template as<T>(), *fy = fin_[1].template as<T>(), *fz = fin_[2].template as<T>();
+    if (start_) CSB_TRY((Api<K, T>::keys(sfcKind_, fx, fy, fz, fk, size_t(start_), &box_, s_)));
+    if (nTotal_ > end_)
+        CSB_TRY((Api<K, T>::keys(sfcKind_, fx + end_, fy + end_, fz + end_, fk + end_, size_t(nTotal_ - end_), &box_, s_)));
+
+    // h. the LET becomes the search tree (leaves + counts; linked in syncBegin)
+    CSB_TRY(search_.ensure(L, s_));
+    CSB_CUDA(cudaMemcpyAsync(search_.treeA.p, ft.leaves_.p, sizeof(K) * (size_t(L) + 1), cudaMemcpyDeviceToDevice, s_));
+    CSB_CUDA(cudaMemcpyAsync(search_.counts.p, ft.leafCounts_.p, 4 * size_t(L), cudaMemcpyDeviceToDevice, s_));
+    search_.numNodes = L;
     return 0;
 }
 
@@ -1578,6 +1831,33 @@ void cstone_b200_local_world_destroy(void* world) { delete static_cast<csb::Loca
     {                                                                                                                  \
         if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
         return CSB_ENGINE(K, T, d)->setHaloFactor(factor);                                                             \
+    }                                                                                                                  \
+    int cstone_b200_domain_set_halo_mode_##KS##_##TS(cstone_b200_domain* d, int mode)                                  \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return CSB_ENGINE(K, T, d)->setHaloMode(mode);                                                                 \
+    }                                                                                                                  \
+    int cstone_b200_domain_let_view_##KS##_##TS(const cstone_b200_domain* d, int32_t* numLeaves, const K** leaves,     \
+                                                const uint32_t** counts, const int32_t** flags,                        \
+                                                const uint32_t** layout, int32_t* assignment2P, int32_t* peers,        \
+                                                int32_t* numPeers)                                                     \
+    {                                                                                                                  \
+        if (!d || !numLeaves || !leaves || !counts || !flags || !layout || !assignment2P || !peers || !numPeers)       \
+            return CSTONE_E_INVALID_ARGUMENT;                                                                          \
+        auto* e = reinterpret_cast<const csb::Engine<K, T>*>(d);                                                      \
+        if (!e->let() || e->letLayout().empty()) return CSTONE_E_INVALID_ARGUMENT;                                     \
+        *numLeaves = e->let()->numLeaves();                                                                            \
+        *leaves    = e->let()->leaves().data();                                                                        \
+        *counts    = e->let()->leafCounts().data();                                                                    \
+        *flags     = e->letFlags().data();                                                                             \
+        *layout    = e->letLayout().data();                                                                            \
+        int q      = 0;                                                                                                \
+        for (const auto& a : e->let()->assignment())                                                                   \
+            assignment2P[2 * q] = a[0], assignment2P[2 * q + 1] = a[1], ++q;                                           \
+        *numPeers = int32_t(e->let()->peers().size());                                                                 \
+        for (int k = 0; k < *numPeers; ++k)                                                                            \
+            peers[k] = e->let()->peers()[k];                                                                           \
+        return 0;                                                                                                      \
     }                                                                                                                  \
     int cstone_b200_domain_cells_##KS##_##TS(cstone_b200_domain* d, int32_t* startEnd2)                                \
     {                                                                                                                  \

@@ -194,6 +194,28 @@ class Domain:
         _check(_fn("box", self.bits, self.fd)(self._h, C.byref(b)), "box")
         return b
 
+    def set_halo_mode(self, mode):
+        """0: fast halo discovery (default); 1: the reference's procedure on the multi-rank focus tree
+        [ref: domain/domain.hpp:217-243] -- halo flags, layout, start/end index and the search tree are the reference's"""
+        _check(_fn("set_halo_mode", self.bits, self.fd)(self._h, int(mode)), "set_halo_mode")
+
+    def let_view(self):
+        """halo mode 1: host copies of this rank's focus tree after a sync: leaves, leaf counts, halo flags, layout,
+        leaf index range of every rank (focus assignment) and the peer ranks"""
+        kt = C.c_uint64 if self.bits == 64 else C.c_uint32
+        n, npeers = C.c_int32(0), C.c_int32(0)
+        l, c, f, lay = C.POINTER(kt)(), C.POINTER(C.c_uint32)(), C.POINTER(C.c_int32)(), C.POINTER(C.c_uint32)()
+        asg = np.zeros(2 * self.num_ranks, dtype=np.int32)
+        peers = np.zeros(self.num_ranks, dtype=np.int32)
+        _check(_fn("let_view", self.bits, self.fd)(self._h, C.byref(n), C.byref(l), C.byref(c), C.byref(f), C.byref(lay),
+                                                   asg.ctypes.data_as(C.c_void_p), peers.ctypes.data_as(C.c_void_p),
+                                                   C.byref(npeers)), "let_view")
+        L = n.value
+        kd = np.uint64 if self.bits == 64 else np.uint32
+        return dict(leaves=np.ctypeslib.as_array(l, (L + 1,)).astype(kd), counts=np.ctypeslib.as_array(c, (L,)).copy(),
+                    flags=np.ctypeslib.as_array(f, (L,)).copy(), layout=np.ctypeslib.as_array(lay, (L + 1,)).copy(),
+                    assignment=asg.reshape(-1, 2), peers=peers[:npeers.value].copy())
+
     def global_tree(self):
         """replicated global leaf array, its counts and the rank boundaries (numpy, host)"""
         kt = C.c_uint64 if self.bits == 64 else C.c_uint32

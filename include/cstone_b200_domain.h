@@ -29,6 +29,7 @@ extern "C" {
 #endif
 
 #define CSTONE_E_NCCL (-6)
+#define CSTONE_E_LET (-8) /* reference halo mode: peers disagree on node counts / a halo leaf belongs to no peer [ref: halos/halos.hpp:58-100] */
 #define CSTONE_E_SIZE_MISMATCH (-7) /* array length differs from the previous sync [ref: domain/domain.hpp:130-133] */
 
 typedef struct cstone_b200_domain cstone_b200_domain;
@@ -63,6 +64,21 @@ void cstone_b200_local_world_destroy(void* world);
     int cstone_b200_domain_set_end_index_##KS##_##TS(cstone_b200_domain* d, uint64_t end);                             \
     /* [ref: domain/domain.hpp:412 setHaloFactor; halos/halos.hpp:162] halo radius = 2 * factor * max h per leaf */   \
     int cstone_b200_domain_set_halo_factor_##KS##_##TS(cstone_b200_domain* d, float factor);                           \
+    /* how halos are found on nranks > 1 (before the first sync).  0, the default: the fast path -- surface boxes of  \
+     * all ranks against the leaves of the assigned particles; the halo set is sufficient for 2h searches and a       \
+     * subset of the reference's.  1: the reference's own procedure [ref: domain/domain.hpp:217-243] -- peers by      \
+     * findPeersMac, the multi-rank FocusedOctree (focus/octree_focus_mpi.hpp:108-273), Halos::discover and           \
+     * computeLayout (halos/halos.hpp:127-223) -- halo flags, layout(), startIndex/endIndex, nParticlesWithHalos and   \
+     * the tree of octreeProperties() are then the reference's, bit for bit */                                         \
+    int cstone_b200_domain_set_halo_mode_##KS##_##TS(cstone_b200_domain* d, int mode);                                 \
+    /* halo mode 1, after a sync: HOST views of the focus tree of this rank, valid until the next sync: leaves        \
+     * K[L+1], leaf counts u32[L], halo flags i32[L], layout u32[L+1]; assignment2P receives the leaf index range      \
+     * [start, end) of every rank in this tree (0,0 for non-peers) [ref: focus/octree_focus_mpi.hpp:560             \
+     * assignment()], peers (capacity nranks) the peer ranks */                                                       \
+    int cstone_b200_domain_let_view_##KS##_##TS(const cstone_b200_domain* d, int32_t* num_leaves, const K** leaves,    \
+                                                const uint32_t** counts, const int32_t** flags,                        \
+                                                const uint32_t** layout, int32_t* assignment2P, int32_t* peers,        \
+                                                int32_t* num_peers);                                                   \
     /* [ref: domain/domain.hpp:404-406 startCell / endCell] first and one-past-last search-tree leaf of the assigned  \
      * SFC range; start_end2 is a HOST array; synchronises the stream */                                               \
     int cstone_b200_domain_cells_##KS##_##TS(cstone_b200_domain* d, int32_t* start_end2);                              \

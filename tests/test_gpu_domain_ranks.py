@@ -49,7 +49,7 @@ def make_cloud(name, n):
 class Ranks:
     """P CUDA engines over the in-process transport + the reference Domain on P thread-ranks, fed the same slabs"""
 
-    def __init__(self, P, bucket, bucket_focus, lim, pbc, x, y, z, h):
+    def __init__(self, P, bucket, bucket_focus, lim, pbc, x, y, z, h, halo_mode=0):
         import torch
         from cornerstone_octree_b200 import ops
         from cornerstone_octree_b200.domain import Domain, LocalWorld
@@ -59,6 +59,9 @@ class Ranks:
         self.doms = [Domain(r, P, bucket, bucket_focus, 0.5, ops.make_box(lim, bnd)) for r in range(P)]
         for d in self.doms:
             d.set_local_world(self.world)
+            if halo_mode:
+                d.set_halo_mode(halo_mode)
+        self.halo_mode = halo_mode
         self.ref = loader.RefDomain(P, bucket, bucket_focus, 0.5, list(lim), pbc=pbc, nprops=1)
         gid = np.arange(self.n, dtype=np.float64)
         self.state = []
@@ -155,6 +158,24 @@ class Ranks:
             full = nc_m <= ngmax
             assert np.array_equal(np.sort(gm[full], axis=1), np.sort(gr[full], axis=1)), "neighbour sets of rank %d" % r
             total += int(nc_m.sum())
+            if self.halo_mode == 1:
+                # the reference's halo procedure: focus tree, halo flags (through the layout), index ranges, every
+                # array with its halos and the raw neighbour lists are the reference's  [ref: domain/domain.hpp:217-243]
+                tr, lv = self.ref.trees(r), dom.let_view()
+                assert np.array_equal(lv["leaves"], tr["focus_leaves"]), "focus leaves of rank %d" % r
+                assert np.array_equal(lv["counts"], tr["focus_counts"]), "focus leaf counts of rank %d" % r
+                assert np.array_equal(lv["assignment"], tr["focus_assignment"]), "focus assignment of rank %d" % r
+                assert np.array_equal(lv["layout"], tr["layout"]), "layout of rank %d" % r
+                assert (s, e, dom.n_particles_with_halos) == (a, b, inf["size"]), "index ranges of rank %d" % r
+                assert dom.cells() == (inf["start_cell"], inf["end_cell"])
+                assert np.array_equal(k, rk), "keys with halos of rank %d" % r
+                for name, m, f in zip("xyzhg", mine, (rx, ry, rz, rh, rg)):
+                    assert np.array_equal(m, f), "%s with halos of rank %d" % (name, r)
+                ta = dom.tree_arrays()
+                assert np.array_equal(ta["leaves"].cpu().numpy().view(np.uint64), tr["focus_leaves"])
+                assert np.array_equal(ta["layout"].cpu().numpy().view(np.uint32), tr["layout"])
+                cols = np.arange(ngmax)[None, :] < np.minimum(nc_m, ngmax)[:, None]
+                assert np.array_equal(np.where(cols, nb_m, 0), np.where(cols, nb_r, 0)), "raw neighbour lists of rank %d" % r
         return total
 
     def halo_coordinates_match_ids(self, x, y, z):
@@ -185,6 +206,26 @@ def test_ranks_match_reference_domain(cloud, P, n, bucket, bucket_focus):
         rk.check()
         rk.halo_coordinates_match_ids(x, y, z)
         for amp in (0.002, 0.01):  # steady state: few particles change rank (merge path)
+            rk.displace(amp)
+            rk.sync()
+            rk.check()
+    finally:
+        rk.close()
+
+
+@pytest.mark.parametrize("cloud,P,n,bucket,bucket_focus", CASES, ids=["%s-P%d" % (c[0], c[1]) for c in CASES])
+def test_ranks_reference_halo_mode(cloud, P, n, bucket, bucket_focus):
+    """halo mode 1 (multi-rank focus tree + Halos::discover as in the reference): focus tree, layout, index ranges,
+    halos and raw neighbour lists bit-exact against the reference Domain, first sync and displaced steady-state syncs"""
+    if not loader.refdom_available():
+        pytest.skip("oracle/_ref/liboracle_refdom.so did not travel")
+    x, y, z, h, lim, pbc = make_cloud(cloud, n)
+    rk = Ranks(P, bucket, bucket_focus, lim, pbc, x, y, z, h, halo_mode=1)
+    try:
+        rk.sync()
+        rk.check()
+        rk.halo_coordinates_match_ids(x, y, z)
+        for amp in (0.002, 0.01, 0.03):
             rk.displace(amp)
             rk.sync()
             rk.check()
