@@ -271,6 +271,10 @@ def main():
     ap.add_argument("--ref-total", type=int, default=32_000_000,
                     help="upper bound of the particles (all thread-ranks together) of the reference arm")
     ap.add_argument("--cpu-n", type=int, default=8_000_000, help="particles of the bounded cpu_baseline leg (N = 1)")
+    ap.add_argument("--halo-mode", type=int, default=0, choices=[0, 1],
+                    help="N > 1: 0 = fast halo discovery (default), 1 = the reference's procedure on the multi-rank focus tree")
+    ap.add_argument("--halo-push", type=int, default=1, choices=[0, 1],
+                    help="N > 1: 1 = pack-and-push halo exchange over peer memory (default), 0 = gather + grouped send/recv")
     ap.add_argument("--no-check", action="store_true", help="skip the correctness checks inside the run")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
@@ -337,6 +341,10 @@ def main():
     box = ops.make_box(lim)
     sfc_kind = ops.HILBERT if args.curve == "hilbert" else ops.MORTON
     dom = Domain(rank, world, args.global_bucket, args.bucket, 0.5, box, key_bits=bits, sfc_kind=sfc_kind)
+    if world > 1 and args.halo_mode:
+        dom.set_halo_mode(args.halo_mode)
+    if world > 1:
+        dom.set_halo_push(bool(args.halo_push))
     dom.init_comm_from_torch()
     dev = [torch.from_numpy(a).cuda() for a in (x, y, z, h)]
     del x, y, z
@@ -680,6 +688,12 @@ def main():
                               global_leaves=int(info[5]), neighbours_mean=round(nc_mean, 2),
                               particles_per_leaf=round(n_assigned / max(int(info[3]), 1), 1),
                               first_sync_s=round(first_sync_s, 3),
+                              halo_exchange=("n/a (1 rank)" if world == 1 else
+                                             "pack-and-push over CUDA IPC peer memory" if args.halo_push else
+                                             "gather per array + grouped ncclSend/ncclRecv"),
+                              halo_discovery=("n/a (1 rank)" if world == 1 else
+                                              "reference procedure on the multi-rank focus tree (halo mode 1)" if args.halo_mode
+                                              else "fast path: surface boxes against assigned leaves (halo mode 0)"),
                               parallelism="1 rank" if world == 1 else
                               "%d ranks, SFC-range sharding, NCCL all-reduce of global leaf counts, grouped NCCL "
                               "send/recv for particle and halo exchange" % world),

@@ -194,6 +194,7 @@ _DOMAIN_PROTOS = {
     "set_halo_factor": (_i, [_vp, _f]),
     "cells": (_i, [_vp, _vp]),
     "set_halo_mode": (_i, [_vp, _i]),
+    "set_halo_push": (_i, [_vp, _i]),
     "let_view": (_i, [_vp] * 9),
     "sync_begin": (_i64, [_vp, _u64, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "sync_finish": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),

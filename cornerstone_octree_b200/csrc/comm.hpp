@@ -65,6 +65,18 @@ public:
     /*! one exchange step: all sends and receives of this rank.  Messages between the same pair of ranks are matched in
      *  the order they are listed.  Every rank calls it, also with empty lists. */
     virtual int exchange(const std::vector<CommMsg>& sends, const std::vector<CommMsg>& recvs, cudaStream_t s) = 0;
+
+    // ---- peer memory (pack-and-push halo exchange, domain.cu)
+    //! true: all ranks are host threads on one device and every step is host-synchronous (kernels must not wait for
+    //! a kernel of another rank, they share one stream)
+    virtual bool hostSynchronous() const = 0;
+    /*! collective: peers[r] = a device pointer through which THIS rank can write the buffer `mine` of rank r
+     *  (peers[rank()] = mine).  All ranks call it with buffers from cudaMalloc. */
+    virtual int shareBuffer(void* mine, std::vector<void*>& peers, cudaStream_t s) = 0;
+    //! undo shareBuffer (before the buffers are freed)
+    virtual void releaseShared(std::vector<void*>& peers) = 0;
+    //! all ranks have reached this point (host side); a no-op where kernels synchronise through flags instead
+    virtual int hostBarrier(cudaStream_t s) = 0;
 };
 
 // ------------------------------------------------------------------------------------------------ NCCL
@@ -101,6 +113,45 @@ public:
         ok = (ncclGroupEnd() == ncclSuccess) && ok;
         return ok ? 0 : CSTONE_E_NCCL;
     }
+
+    bool hostSynchronous() const override { return false; }
+    //! CUDA IPC: the ranks are processes on one node, the GPUs reach each other over NVLink / NVSwitch
+    int shareBuffer(void* mine, std::vector<void*>& peers, cudaStream_t s) override
+    {
+        cudaIpcMemHandle_t h;
+        if (cudaIpcGetMemHandle(&h, mine) != cudaSuccess) return int(cudaGetLastError());
+        void* stage = nullptr;
+        const size_t hb = sizeof(cudaIpcMemHandle_t);
+        if (cudaMalloc(&stage, hb * size_t(size_ + 1)) != cudaSuccess) return int(cudaGetLastError());
+        std::vector<cudaIpcMemHandle_t> all(size_);
+        cudaError_t e = cudaMemcpyAsync(stage, &h, hb, cudaMemcpyHostToDevice, s);
+        int st        = e == cudaSuccess ? allGather(stage, static_cast<char*>(stage) + hb, hb, s) : int(e);
+        if (st == 0) e = cudaMemcpyAsync(all.data(), static_cast<char*>(stage) + hb, hb * size_, cudaMemcpyDeviceToHost, s);
+        if (st == 0 && e == cudaSuccess) e = cudaStreamSynchronize(s);
+        cudaFree(stage);
+        if (st) return st;
+        if (e != cudaSuccess) return int(e);
+        peers.assign(size_, nullptr);
+        for (int r = 0; r < size_; ++r)
+        {
+            if (r == rank_) peers[r] = mine;
+            else if (cudaIpcOpenMemHandle(&peers[r], all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
+            {
+                int err = int(cudaGetLastError());
+                peers[r] = nullptr;
+                releaseShared(peers);
+                return err;
+            }
+        }
+        return 0;
+    }
+    void releaseShared(std::vector<void*>& peers) override
+    {
+        for (int r = 0; r < int(peers.size()); ++r)
+            if (r != rank_ && peers[r]) cudaIpcCloseMemHandle(peers[r]);
+        peers.clear();
+    }
+    int hostBarrier(cudaStream_t) override { return 0; }
 
 private:
     ncclComm_t comm_;
@@ -208,6 +259,27 @@ public:
         if (e == cudaSuccess) e = cudaStreamSynchronize(s);
         w_->barrier();
         return status ? status : int(e);
+    }
+
+    bool hostSynchronous() const override { return true; }
+    //! one process, one device: the peers' pointers are usable as they are
+    int shareBuffer(void* mine, std::vector<void*>& peers, cudaStream_t s) override
+    {
+        if (cudaStreamSynchronize(s) != cudaSuccess) return int(cudaGetLastError());
+        w_->ptrs[rank_] = mine;
+        w_->barrier();
+        peers.assign(w_->size, nullptr);
+        for (int r = 0; r < w_->size; ++r)
+            peers[r] = const_cast<void*>(w_->ptrs[r]);
+        w_->barrier();
+        return 0;
+    }
+    void releaseShared(std::vector<void*>& peers) override { peers.clear(); }
+    int hostBarrier(cudaStream_t s) override
+    {
+        cudaError_t e = cudaStreamSynchronize(s);
+        w_->barrier();
+        return int(e);
     }
 
 private:

@@ -525,6 +525,161 @@ __global__ void __launch_bounds__(256)
 }
 
 
+
+// ------------------------------------------------------------------------------------------------
+// pack-and-push halo exchange (n1): ONE kernel gathers the outgoing halo elements of all arrays and stores them
+// straight into the receive windows of the destination ranks over NVLink (peer pointers from CUDA IPC), then raises
+// a flag in every peer's window; ONE kernel on the receiving side waits for the flags and moves the window contents
+// into the halo ranges of the arrays.  Replaces gather-per-array + grouped send/recv
+// [ref: halos/exchange_halos_gpu.cuh:34-119 haloExchangeGpu: gatherRanges per array, MPI_Isend/Irecv, unpack].
+//
+// Window of rank q (device memory of q, mapped by every peer):
+//   [0, 4096)   header: flags[2][P] (uint64: last epoch whose data from rank r is complete, per slot), ticket, status
+//   slot 0/1    data of the exchanges with even / odd epoch; per array a region of align256(recvTotal[q] * elemBytes[a])
+//               bytes, inside it the elements of source rank r start at element sum(count[r' -> q], r' < r).
+// ------------------------------------------------------------------------------------------------
+constexpr int kMaxPushRanks  = 64;
+constexpr int kMaxPushArrays = 16;
+constexpr size_t kWinHeader  = 4096;
+
+struct PushArgs
+{
+    int na, P, me;
+    uint32_t nSend, start;
+    const void* src[kMaxPushArrays];
+    int words[kMaxPushArrays];
+    uint32_t sendOffset[kMaxPushRanks + 1];
+    uint32_t dstElemOff[kMaxPushRanks]; // where my elements start inside rank q's regions
+    uint32_t recvTotal[kMaxPushRanks];  // elements per region of rank q
+    char* peerData[kMaxPushRanks];      // data slot of this epoch in rank q's window
+    unsigned long long* peerFlag[kMaxPushRanks]; // flag (slot, me) in rank q's window
+    unsigned int* ticket;
+    unsigned long long epoch;
+};
+
+struct UnpackArgs
+{
+    int na, P, me, spin;
+    void* dst[kMaxPushArrays];
+    int words[kMaxPushArrays];
+    uint32_t recvCount[kMaxPushRanks], recvOffset[kMaxPushRanks], srcElemOff[kMaxPushRanks + 1];
+    const char* myData;
+    const unsigned long long* myFlags; // flags of this slot, one per source rank
+    unsigned long long epoch;
+    unsigned int* status;
+};
+
+__host__ __device__ inline size_t pushRegionOffset(const int* words, int a, uint32_t total)
+{
+    size_t off = 0;
+    for (int k = 0; k < a; ++k)
+        off += (size_t(total) * size_t(words[k]) * 4 + 255) / 256 * 256;
+    return off;
+}
+
+template<int W>
+__device__ inline void copyWords(const uint32_t* __restrict__ s, uint32_t* __restrict__ d)
+{
+    if (W == 1) *d = *s;
+    else if (W == 2) *reinterpret_cast<uint2*>(d) = *reinterpret_cast<const uint2*>(s);
+    else if (W == 4) *reinterpret_cast<uint4*>(d) = *reinterpret_cast<const uint4*>(s);
+    else
+    {
+        d[0] = s[0], d[1] = s[1], d[2] = s[2];
+    }
+}
+__device__ inline void copyElem(int words, const uint32_t* s, uint32_t* d)
+{
+    if (words == 1) copyWords<1>(s, d);
+    else if (words == 2) copyWords<2>(s, d);
+    else if (words == 4) copyWords<4>(s, d);
+    else copyWords<3>(s, d);
+}
+
+__global__ void __launch_bounds__(256) pushHalosKernel(const uint32_t* __restrict__ sendIdx, const __grid_constant__ PushArgs p)
+{
+    const int a     = blockIdx.y;
+    const int words = p.words[a];
+    __shared__ size_t regionOff[kMaxPushRanks];
+    for (int q = threadIdx.x; q < p.P; q += blockDim.x)
+        regionOff[q] = pushRegionOffset(p.words, a, p.recvTotal[q]);
+    __syncthreads();
+    const uint32_t* src = static_cast<const uint32_t*>(p.src[a]);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < p.nSend; i += gridDim.x * blockDim.x)
+    {
+        int lo = 0, hi = p.P; // destination: the q with sendOffset[q] <= i < sendOffset[q + 1]
+        while (hi - lo > 1)
+        {
+            const int mid = (lo + hi) / 2;
+            if (p.sendOffset[mid] <= i) lo = mid;
+            else hi = mid;
+        }
+        const int q         = lo;
+        const size_t elem   = size_t(p.dstElemOff[q]) + (i - p.sendOffset[q]);
+        uint32_t* d         = reinterpret_cast<uint32_t*>(p.peerData[q] + regionOff[q]) + elem * size_t(words);
+        const uint32_t* sEl = src + (size_t(sendIdx[i]) + p.start) * size_t(words);
+        copyElem(words, sEl, d);
+    }
+    // the last block of the grid tells every peer that my data of this epoch has arrived
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        const unsigned int blocks = gridDim.x * gridDim.y;
+        if (atomicAdd(p.ticket, 1u) == blocks - 1)
+        {
+            *p.ticket = 0;
+            __threadfence_system();
+            for (int q = 0; q < p.P; ++q)
+                if (q != p.me) *reinterpret_cast<volatile unsigned long long*>(p.peerFlag[q]) = p.epoch;
+            __threadfence_system();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) unpackHalosKernel(const __grid_constant__ UnpackArgs u)
+{
+    if (u.spin)
+    {
+        // every source rank has finished writing this epoch into my window (bounded wait: a lost flag must not hang the GPU)
+        if (threadIdx.x < u.P && int(threadIdx.x) != u.me)
+        {
+            const volatile unsigned long long* f = u.myFlags + threadIdx.x;
+            unsigned long long t0;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            while (*f < u.epoch)
+            {
+                unsigned long long t1;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 20000000000ull)
+                {
+                    atomicExch(u.status, 1u);
+                    break;
+                }
+            }
+        }
+        __threadfence_system();
+        __syncthreads();
+    }
+    const int a     = blockIdx.y;
+    const int words = u.words[a];
+    const uint32_t total = u.srcElemOff[u.P];
+    const uint32_t* region = reinterpret_cast<const uint32_t*>(u.myData + pushRegionOffset(u.words, a, total));
+    uint32_t* dst = static_cast<uint32_t*>(u.dst[a]);
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < total; j += gridDim.x * blockDim.x)
+    {
+        int lo = 0, hi = u.P;
+        while (hi - lo > 1)
+        {
+            const int mid = (lo + hi) / 2;
+            if (u.srcElemOff[mid] <= j) lo = mid;
+            else hi = mid;
+        }
+        const size_t di = size_t(u.recvOffset[lo]) + (j - u.srcElemOff[lo]);
+        copyElem(words, region + size_t(j) * size_t(words), dst + di * size_t(words));
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // the engine
 // ------------------------------------------------------------------------------------------------
@@ -549,6 +704,28 @@ public:
     {
         for (cudaEvent_t e : ev_)
             if (e) cudaEventDestroy(e);
+        if (comm_ && !winPeers_.empty()) comm_->releaseShared(winPeers_);
+        if (win_) cudaFree(win_);
+        for (void* w : winOld_)
+            cudaFree(w);
+    }
+    //! halo exchange transport: 1 = pack-and-push over peer memory (default), 0 = pack + grouped send/recv
+    int setHaloPush(int on)
+    {
+        if (on != 0 && on != 1) return CSTONE_E_INVALID_ARGUMENT;
+        haloPush_ = on;
+        return 0;
+    }
+    //! 1 if a receiving kernel gave up waiting for a peer's data (pack-and-push), 0 otherwise; synchronises the stream
+    int pushStatus(int32_t* out)
+    {
+        *out = 0;
+        if (!win_) return 0;
+        unsigned int st = 0;
+        CSB_CUDA(cudaMemcpyAsync(&st, static_cast<char*>(win_) + 3080, 4, cudaMemcpyDeviceToHost, s_));
+        CSB_CUDA(cudaStreamSynchronize(s_));
+        *out = int32_t(st);
+        return 0;
     }
     //! space-filling curve of the keys (the reference's Domain hard-wires Hilbert, sfc/sfc.hpp:54-55); before the first sync
     int setSfcKind(int kind)
@@ -659,6 +836,8 @@ private:
                      bool* leavesChanged = nullptr);
     int discoverHalos();
     int discoverHalosLet();
+    int exchangeHalosPush(int narrays, void* const* arrays, const int* elemBytes);
+    int ensureWindow(size_t slotBytes);
     int hostCounts(const uint32_t* dev, int n, std::vector<uint32_t>& out)
     {
         out.resize(n);
@@ -746,6 +925,13 @@ private:
     // halo exchange pattern
     DevBuf surf_, allSurf_, nSurf_, flags_, sendScan_, sendIdx_, haloPack_;
     std::vector<uint32_t> haloSendCount_, haloSendOffset_, haloRecvCount_, haloRecvOffset_;
+    std::vector<uint32_t> haloMatrix_; // [src * P + dst]: halo particles src sends to dst (the same on every rank)
+    // pack-and-push windows (see pushHalosKernel)
+    int haloPush_ = -1; // -1: decide at first use (on unless CSB_HALO_PUSH=0), 0 / 1
+    void* win_    = nullptr;
+    size_t winSlot_ = 0;
+    std::vector<void*> winPeers_, winOld_;
+    unsigned long long winEpoch_ = 0;
 };
 
 template<class K, class T>
@@ -1186,6 +1372,12 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
     }
     CSB_CUDA(cudaStreamSynchronize(s_));
     firstCall_ = false;
+    if (win_)
+    {
+        int32_t st = 0;
+        CSB_TRY(pushStatus(&st));
+        if (st) return CSTONE_E_PEER_TIMEOUT;
+    }
     return int64_t(nTotal_);
 }
 
@@ -1302,6 +1494,9 @@ int Engine<K, T>::discoverHalos()
     std::vector<uint32_t> matrix(size_t(P) * P);
     CSB_CUDA(cudaMemcpyAsync(matrix.data(), dAll, 4 * size_t(P) * P, cudaMemcpyDeviceToHost, s_));
     CSB_CUDA(cudaStreamSynchronize(s_));
+    haloMatrix_ = matrix;
+    for (int q = 0; q < P; ++q)
+        haloMatrix_[size_t(q) * P + q] = 0;
     haloRecvCount_.assign(P, 0), haloRecvOffset_.assign(P, 0);
     uint64_t left = 0, right = 0;
     for (int q = 0; q < P; ++q)
@@ -1547,6 +1742,10 @@ int Engine<K, T>::discoverHalosLet()
                 ok = ok && all[size_t(a) * (2 * P + 1) + b] == all[size_t(b) * (2 * P + 1) + P + a];
         }
         if (!ok) return CSTONE_E_LET;
+        haloMatrix_.assign(size_t(P) * P, 0);
+        for (int a = 0; a < P; ++a)
+            for (int b = 0; b < P; ++b)
+                haloMatrix_[size_t(a) * P + b] = all[size_t(a) * (2 * P + 1) + b];
     }
 
     // g. assigned particles to their final position, halos of x,y,z,h, keys of the halos
@@ -1594,6 +1793,13 @@ int Engine<K, T>::exchangeHalos(int narrays, void* const* arrays, const int* ele
         off[a] = total;
         total += (size_t(nHaloSend_) * elemBytes[a] + 255) / 256 * 256;
     }
+    if (haloPush_ < 0)
+    {
+        const char* env = std::getenv("CSB_HALO_PUSH");
+        haloPush_       = (env && env[0] == '0') ? 0 : 1;
+    }
+    if (haloPush_ == 1 && P <= kMaxPushRanks && narrays <= kMaxPushArrays && haloMatrix_.size() == size_t(P) * P)
+        return exchangeHalosPush(narrays, arrays, elemBytes);
     CSB_TRY(haloPack_.reserve(total + 256));
     // pack [ref: halos/gather_halos_gpu.cu:25-75 gatherRanges]
     if (nHaloSend_)
@@ -1634,6 +1840,93 @@ int Engine<K, T>::exchangeHalos(int narrays, void* const* arrays, const int* ele
         }
     }
     return comm_->exchange(sends, recvs, s_);
+}
+
+//! the window of this rank holds two slots of slotBytes; a collective when it has to grow (every rank sees the same need)
+template<class K, class T>
+int Engine<K, T>::ensureWindow(size_t slotBytes)
+{
+    if (win_ && slotBytes <= winSlot_) return 0;
+    const size_t slot = (size_t(double(slotBytes) * 1.5) + (size_t(1) << 20) + 255) / 256 * 256;
+    // the peers stop using the old window before its mappings go away (it is freed with the engine)
+    CSB_CUDA(cudaStreamSynchronize(s_));
+    if (win_)
+    {
+        CSB_TRY(small_.reserve(4096));
+        CSB_CUDA(cudaMemsetAsync(small_.p, 0, 4, s_));
+        CSB_TRY(comm_->allReduce(small_.p, 1, CommType::i32, CommOp::sum, s_));
+        CSB_CUDA(cudaStreamSynchronize(s_));
+        comm_->releaseShared(winPeers_);
+        winOld_.push_back(win_);
+        win_ = nullptr;
+    }
+    CSB_CUDA(cudaMalloc(&win_, kWinHeader + 2 * slot));
+    CSB_CUDA(cudaMemsetAsync(win_, 0, kWinHeader, s_));
+    winSlot_ = slot;
+    CSB_TRY(comm_->shareBuffer(win_, winPeers_, s_));
+    return 0;
+}
+
+/*! pack-and-push exchangeHalos: see pushHalosKernel.  Same arguments and result as the send/recv path. */
+template<class K, class T>
+int Engine<K, T>::exchangeHalosPush(int narrays, void* const* arrays, const int* elemBytes)
+{
+    const int P = nRanks_;
+    PushArgs p{};
+    UnpackArgs u{};
+    p.na = u.na = narrays, p.P = u.P = P, p.me = u.me = rank_;
+    for (int a = 0; a < narrays; ++a)
+    {
+        p.src[a] = arrays[a], u.dst[a] = arrays[a];
+        p.words[a] = u.words[a] = elemBytes[a] / 4;
+    }
+    // geometry of every rank's window for this call: the same numbers on all ranks
+    size_t need = 0;
+    for (int q = 0; q < P; ++q)
+    {
+        uint32_t total = 0;
+        for (int r = 0; r < P; ++r)
+        {
+            if (r == rank_) p.dstElemOff[q] = total;
+            if (q == rank_) u.srcElemOff[r] = total;
+            total += haloMatrix_[size_t(r) * P + q];
+        }
+        p.recvTotal[q] = total;
+        if (q == rank_) u.srcElemOff[P] = total;
+        need = std::max(need, pushRegionOffset(p.words, narrays, total));
+    }
+    CSB_TRY(ensureWindow(need));
+    const unsigned long long epoch = ++winEpoch_;
+    const int slot                 = int(epoch & 1);
+    for (int q = 0; q < P; ++q)
+    {
+        char* base        = static_cast<char*>(winPeers_[q]);
+        p.peerData[q]     = base + kWinHeader + size_t(slot) * winSlot_;
+        p.peerFlag[q]     = reinterpret_cast<unsigned long long*>(base) + size_t(slot) * kMaxPushRanks + rank_;
+        p.sendOffset[q]   = haloSendOffset_[q];
+        u.recvCount[q]    = haloRecvCount_[q];
+        u.recvOffset[q]   = haloRecvOffset_[q];
+    }
+    p.sendOffset[P] = haloSendOffset_[P];
+    p.nSend = uint32_t(nHaloSend_), p.start = uint32_t(start_), p.epoch = u.epoch = epoch;
+    char* mine = static_cast<char*>(win_);
+    p.ticket   = reinterpret_cast<unsigned int*>(mine + 3072);
+    u.status   = reinterpret_cast<unsigned int*>(mine + 3080);
+    u.myData   = mine + kWinHeader + size_t(slot) * winSlot_;
+    u.myFlags  = reinterpret_cast<const unsigned long long*>(mine) + size_t(slot) * kMaxPushRanks;
+    u.spin     = comm_->hostSynchronous() ? 0 : 1;
+    {
+        dim3 grid(std::max(1u, std::min(gridFor(size_t(nHaloSend_), 256, 2), 148u * 4u)), unsigned(narrays));
+        pushHalosKernel<<<grid, 256, 0, s_>>>(sendIdx_.template as<uint32_t>(), p);
+        CSB_LAUNCHED();
+    }
+    CSB_TRY(comm_->hostBarrier(s_)); // thread-ranks on one device: pushes complete before anybody unpacks
+    {
+        dim3 grid(std::max(1u, std::min(gridFor(size_t(u.srcElemOff[P]), 256, 2), 148u * 4u)), unsigned(narrays));
+        unpackHalosKernel<<<grid, 256, 0, s_>>>(u);
+        CSB_LAUNCHED();
+    }
+    return 0;
 }
 
 /*! [ref: domain/domain.hpp:334-378 reapplySync] the particle exchange and re-ordering of the LAST sync applied to further
@@ -1831,6 +2124,11 @@ void cstone_b200_local_world_destroy(void* world) { delete static_cast<csb::Loca
     {                                                                                                                  \
         if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
         return CSB_ENGINE(K, T, d)->setHaloFactor(factor);                                                             \
+    }                                                                                                                  \
+    int cstone_b200_domain_set_halo_push_##KS##_##TS(cstone_b200_domain* d, int on)                                    \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return CSB_ENGINE(K, T, d)->setHaloPush(on);                                                                   \
     }                                                                                                                  \
     int cstone_b200_domain_set_halo_mode_##KS##_##TS(cstone_b200_domain* d, int mode)                                  \
     {                                                                                                                  \

@@ -199,6 +199,10 @@ class Domain:
         [ref: domain/domain.hpp:217-243] -- halo flags, layout, start/end index and the search tree are the reference's"""
         _check(_fn("set_halo_mode", self.bits, self.fd)(self._h, int(mode)), "set_halo_mode")
 
+    def set_halo_push(self, on):
+        """transport of the halo exchange: True (default) = pack-and-push over peer memory, False = gather + send/recv"""
+        _check(_fn("set_halo_push", self.bits, self.fd)(self._h, 1 if on else 0), "set_halo_push")
+
     def let_view(self):
         """halo mode 1: host copies of this rank's focus tree after a sync: leaves, leaf counts, halo flags, layout,
         leaf index range of every rank (focus assignment) and the peer ranks"""

@@ -69,6 +69,7 @@ struct DomainApi;
         static constexpr auto setSfcKind    = cstone_b200_domain_set_sfc_kind_##KS##_##TS;                             \
         static constexpr auto setEndIndex   = cstone_b200_domain_set_end_index_##KS##_##TS;                            \
         static constexpr auto setHaloFactor = cstone_b200_domain_set_halo_factor_##KS##_##TS;                          \
+        static constexpr auto setHaloMode   = cstone_b200_domain_set_halo_mode_##KS##_##TS;                            \
         static constexpr auto cells         = cstone_b200_domain_cells_##KS##_##TS;                                    \
         static constexpr auto syncBegin     = cstone_b200_domain_sync_begin_##KS##_##TS;                               \
         static constexpr auto syncFinish    = cstone_b200_domain_sync_finish_##KS##_##TS;                              \
@@ -254,6 +255,11 @@ public:
     void setTreeConv(bool flag) { convergeTrees_ = flag; }
     //! [ref: domain/domain.hpp:412] halo search radius = 2 * factor * max h of a leaf
     void setHaloFactor(float factor) { detail::check(Api::setHaloFactor(d_, factor), "Domain::setHaloFactor"); }
+    /*! halos on more than one rank (call before the first sync).  false, the default: the fast path (halo set a subset
+     *  of the reference's, sufficient for 2h searches).  true: the reference's procedure on the multi-rank focus tree
+     *  [ref: domain/domain.hpp:217-243]; layout(), startIndex(), endIndex(), nParticlesWithHalos() and
+     *  octreeProperties() then equal the reference's bit for bit */
+    void setReferenceHalos(bool on) { detail::check(Api::setHaloMode(d_, on ? 1 : 0), "Domain::setReferenceHalos"); }
     //! [ref: domain/domain.hpp:413] over-allocation of the particle arrays when they have to grow
     void setGrowthAllocRate(float factor) { allocGrowthRate_ = factor; }
 

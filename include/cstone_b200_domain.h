@@ -30,6 +30,7 @@ extern "C" {
 
 #define CSTONE_E_NCCL (-6)
 #define CSTONE_E_LET (-8) /* reference halo mode: peers disagree on node counts / a halo leaf belongs to no peer [ref: halos/halos.hpp:58-100] */
+#define CSTONE_E_PEER_TIMEOUT (-9) /* pack-and-push halo exchange: a peer's data did not arrive within 20 s */
 #define CSTONE_E_SIZE_MISMATCH (-7) /* array length differs from the previous sync [ref: domain/domain.hpp:130-133] */
 
 typedef struct cstone_b200_domain cstone_b200_domain;
@@ -64,6 +65,12 @@ void cstone_b200_local_world_destroy(void* world);
     int cstone_b200_domain_set_end_index_##KS##_##TS(cstone_b200_domain* d, uint64_t end);                             \
     /* [ref: domain/domain.hpp:412 setHaloFactor; halos/halos.hpp:162] halo radius = 2 * factor * max h per leaf */   \
     int cstone_b200_domain_set_halo_factor_##KS##_##TS(cstone_b200_domain* d, float factor);                           \
+    /* transport of the halo exchange on nranks > 1.  1, the default: pack-and-push -- one kernel gathers the outgoing  \
+     * elements of all arrays and stores them into the receivers' windows over NVLink (CUDA IPC peer memory), one      \
+     * kernel per receiver waits for the senders' flags and fills the halo ranges; 0: one gather per array + a grouped \
+     * ncclSend/ncclRecv.  What it replaces: halos/exchange_halos_gpu.cuh:34-119 haloExchangeGpu.  The environment    \
+     * variable CSB_HALO_PUSH=0 selects 0 for engines that were not told otherwise */                                   \
+    int cstone_b200_domain_set_halo_push_##KS##_##TS(cstone_b200_domain* d, int on);                                   \
     /* how halos are found on nranks > 1 (before the first sync).  0, the default: the fast path -- surface boxes of  \
      * all ranks against the leaves of the assigned particles; the halo set is sufficient for 2h searches and a       \
      * subset of the reference's.  1: the reference's own procedure [ref: domain/domain.hpp:217-243] -- peers by      \

@@ -1,6 +1,6 @@
 """GPU probe: P engine instances as P host threads on ONE GPU (in-process transport), steady-state syncs with drift —
 the multi-rank kernels (merge re-sort, two-source gather, surface boxes, reverse collision, send lists, halo pack) under
-one process, e.g. for ncu.  usage: local_ranks_probe.py [P] [n_per_rank] [steps]"""
+one process, e.g. for ncu.  usage: local_ranks_probe.py [P] [n_per_rank] [steps] [halo_mode]"""
 import math, os, sys
 import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -10,10 +10,13 @@ from cornerstone_octree_b200.domain import Domain, LocalWorld
 P = int(sys.argv[1]) if len(sys.argv) > 1 else 2
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 8_000_000
 steps = int(sys.argv[3]) if len(sys.argv) > 3 else 4
+halo_mode = int(sys.argv[4]) if len(sys.argv) > 4 else 0
 world = LocalWorld(P)
 doms = [Domain(r, P, 65536, 64, 0.5, ops.make_box((0.0, 1.0))) for r in range(P)]
 for d in doms:
     d.set_local_world(world)
+    if halo_mode:
+        d.set_halo_mode(halo_mode)
 state = []
 for r in range(P):
     x, y, z, h, _ = bench.make_particles(n, "uniform", 42 + r)
