@@ -118,8 +118,11 @@ public:
     //! CUDA IPC: the ranks are processes on one node, the GPUs reach each other over NVLink / NVSwitch
     int shareBuffer(void* mine, std::vector<void*>& peers, cudaStream_t s) override
     {
+        // every rank goes through the all-gather, also one that could not export its buffer (the peers would hang)
         cudaIpcMemHandle_t h;
-        if (cudaIpcGetMemHandle(&h, mine) != cudaSuccess) return int(cudaGetLastError());
+        std::memset(&h, 0, sizeof(h));
+        int status = 0;
+        if (cudaIpcGetMemHandle(&h, mine) != cudaSuccess) status = int(cudaGetLastError());
         void* stage = nullptr;
         const size_t hb = sizeof(cudaIpcMemHandle_t);
         if (cudaMalloc(&stage, hb * size_t(size_ + 1)) != cudaSuccess) return int(cudaGetLastError());
@@ -131,6 +134,7 @@ public:
         cudaFree(stage);
         if (st) return st;
         if (e != cudaSuccess) return int(e);
+        if (status) return status;
         peers.assign(size_, nullptr);
         for (int r = 0; r < size_; ++r)
         {

@@ -1863,7 +1863,20 @@ int Engine<K, T>::ensureWindow(size_t slotBytes)
     CSB_CUDA(cudaMalloc(&win_, kWinHeader + 2 * slot));
     CSB_CUDA(cudaMemsetAsync(win_, 0, kWinHeader, s_));
     winSlot_ = slot;
-    CSB_TRY(comm_->shareBuffer(win_, winPeers_, s_));
+    // peer memory may be unavailable (no P2P between two GPUs): all ranks agree, and fall back to send/recv together
+    int32_t failed = comm_->shareBuffer(win_, winPeers_, s_) != 0 ? 1 : 0;
+    CSB_TRY(small_.reserve(4096));
+    CSB_CUDA(cudaMemcpyAsync(small_.p, &failed, 4, cudaMemcpyHostToDevice, s_));
+    CSB_TRY(comm_->allReduce(small_.p, 1, CommType::i32, CommOp::max, s_));
+    CSB_CUDA(cudaMemcpyAsync(&failed, small_.p, 4, cudaMemcpyDeviceToHost, s_));
+    CSB_CUDA(cudaStreamSynchronize(s_));
+    if (failed)
+    {
+        if (!winPeers_.empty()) comm_->releaseShared(winPeers_);
+        winOld_.push_back(win_);
+        win_ = nullptr, winSlot_ = 0, haloPush_ = 0;
+        return CSTONE_E_PEER_TIMEOUT; // caller switches to the send/recv path
+    }
     return 0;
 }
 
@@ -1895,7 +1908,11 @@ int Engine<K, T>::exchangeHalosPush(int narrays, void* const* arrays, const int*
         if (q == rank_) u.srcElemOff[P] = total;
         need = std::max(need, pushRegionOffset(p.words, narrays, total));
     }
-    CSB_TRY(ensureWindow(need));
+    {
+        const int st = ensureWindow(need);
+        if (st == CSTONE_E_PEER_TIMEOUT && haloPush_ == 0) return exchangeHalos(narrays, arrays, elemBytes);
+        if (st) return st;
+    }
     const unsigned long long epoch = ++winEpoch_;
     const int slot                 = int(epoch & 1);
     for (int q = 0; q < P; ++q)
