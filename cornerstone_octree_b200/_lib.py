@@ -197,6 +197,8 @@ _DOMAIN_PROTOS = {
     "set_halo_push": (_i, [_vp, _i]),
     "let_view": (_i, [_vp] * 9),
     "sync_begin": (_i64, [_vp, _u64, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "sync_grav_begin": (_i64, [_vp, _u64, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "let_centers": (_i, [_vp, _vp, _vp, _vp]),
     "sync_finish": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "exchange_halos": (_i, [_vp, _i, _vp, _vp]),
     "reapply_sync": (_i, [_vp, _i, _vp, _vp, _vp]),

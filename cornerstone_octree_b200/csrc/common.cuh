@@ -9,6 +9,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <atomic>
+#include <cstdio>
+#include <cstdlib>
 
 #include "../../include/cstone_b200.h"
 
@@ -24,11 +26,26 @@ extern std::atomic<uint64_t> g_launchCount;
 
 inline void countLaunch(int n = 1) { g_launchCount.fetch_add(uint64_t(n), std::memory_order_relaxed); }
 
+//! CSB_TRACE_ERRORS=1 in the environment: the first failing step of a library call is named on stderr
+inline int traceStatus(int status, const char* file, int line)
+{
+    static const bool on = std::getenv("CSB_TRACE_ERRORS") != nullptr;
+    if (on && status != 0) std::fprintf(stderr, "[cstone_b200] status %d at %s:%d\n", status, file, line);
+    return status;
+}
+
 #define CSB_CUDA(expr)                                                                                                 \
     do                                                                                                                 \
     {                                                                                                                  \
         cudaError_t e_ = (expr);                                                                                       \
-        if (e_ != cudaSuccess) return int(e_);                                                                         \
+        if (e_ != cudaSuccess) return csb::traceStatus(int(e_), __FILE__, __LINE__);                                   \
+    } while (0)
+
+#define CSB_TRY(expr)                                                                                                  \
+    do                                                                                                                 \
+    {                                                                                                                  \
+        int tryStatus_ = (expr);                                                                                       \
+        if (tryStatus_ != 0) return csb::traceStatus(tryStatus_, __FILE__, __LINE__);                                  \
     } while (0)
 
 //! to be placed after every kernel launch

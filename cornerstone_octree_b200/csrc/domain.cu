@@ -44,12 +44,6 @@ namespace csb
         if (r_ != ncclSuccess) return CSTONE_E_NCCL;                                                                   \
     } while (0)
 
-#define CSB_TRY(expr)                                                                                                  \
-    do                                                                                                                 \
-    {                                                                                                                  \
-        int tryStatus_ = (expr);                                                                                       \
-        if (tryStatus_ != 0) return tryStatus_;                                                                        \
-    } while (0)
 
 //! grow-only device buffer (capacity grows by 5 %, as the reference's reallocate policy, util/reallocate.hpp:37-66)
 struct DevBuf
@@ -538,6 +532,14 @@ __global__ void __launch_bounds__(256)
 //   slot 0/1    data of the exchanges with even / odd epoch; per array a region of align256(recvTotal[q] * elemBytes[a])
 //               bytes, inside it the elements of source rank r start at element sum(count[r' -> q], r' < r).
 // ------------------------------------------------------------------------------------------------
+//! [ref: focus/octree_focus_mpi.hpp:600-610 addMacs] leaves whose node failed the MAC become halos too
+__global__ void __launch_bounds__(256)
+    addMacsKernel(const char* __restrict__ macs, const int32_t* __restrict__ leafToInternal, int numLeaves, int32_t* __restrict__ flags)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < numLeaves && macs[leafToInternal[i]] && !flags[i]) flags[i] = 1;
+}
+
 constexpr int kMaxPushRanks  = 64;
 constexpr int kMaxPushArrays = 16;
 constexpr size_t kWinHeader  = 4096;
@@ -704,10 +706,16 @@ public:
     {
         for (cudaEvent_t e : ev_)
             if (e) cudaEventDestroy(e);
+        /* windows that were exported to other processes are NOT freed here: a peer may still have them mapped, and
+         * freeing exported memory before every importer closed it is undefined; they go with the process (an engine
+         * lives as long as its process in every client we know).  The peers' mappings in THIS process are closed. */
         if (comm_ && !winPeers_.empty()) comm_->releaseShared(winPeers_);
-        if (win_) cudaFree(win_);
-        for (void* w : winOld_)
-            cudaFree(w);
+        if (comm_ && comm_->hostSynchronous())
+        {
+            if (win_) cudaFree(win_);
+            for (void* w : winOld_)
+                cudaFree(w);
+        }
     }
     //! halo exchange transport: 1 = pack-and-push over peer memory (default), 0 = pack + grouped send/recv
     int setHaloPush(int on)
@@ -792,6 +800,24 @@ public:
 
     int64_t syncBegin(uint64_t nIn, const T* x, const T* y, const T* z, const T* h, int nprops, const void* const* props,
                       const int* propBytes);
+    /*! [ref: domain/domain.hpp:245-325 syncGrav] sync with the focus tree refined by the vector MAC around the
+     *  expansion (mass) centres; props[0] must be the masses (element type T).  Needs halo mode 1 and nRanks > 1. */
+    int64_t syncGravBegin(uint64_t nIn, const T* x, const T* y, const T* z, const T* h, int nprops, const void* const* props,
+                          const int* propBytes)
+    {
+        if (nRanks_ < 2 || haloMode_ != 1 || nprops < 1 || propBytes[0] != int(sizeof(T))) return CSTONE_E_INVALID_ARGUMENT;
+        grav_           = true;
+        const int64_t r = syncBegin(nIn, x, y, z, h, nprops, props, propBytes);
+        grav_           = false;
+        return r;
+    }
+    //! syncGrav: expansion centres (x, y, z, MAC radius^2) per node of the focus tree and its MAC marks (device)
+    void letCenters(const void** centers4, const char** macs, int32_t* numNodes) const
+    {
+        *centers4 = let_ ? let_->t.centers_.p : nullptr;
+        *macs     = let_ ? let_->t.macs_.template as<char>() : nullptr;
+        *numNodes = let_ ? let_->t.numNodes_ : 0;
+    }
     int syncFinish(K* keys, T* x, T* y, T* z, T* h, void* const* props);
     int exchangeHalos(int narrays, void* const* arrays, const int* elemBytes);
     int reapplySync(int narrays, const void* const* in, const int* elemBytes, void* const* out);
@@ -883,6 +909,10 @@ private:
     int sfcKind_      = CSTONE_SFC_HILBERT;
     float haloFactor_ = 1.0f;
     int haloMode_     = 0;
+    bool grav_        = false; // this sync is a syncGrav: property 0 is the mass
+    bool gravReady_   = false; // the expansion centres belong to the current tree (the last sync was a syncGrav)
+    float centerDriftTol_ = 1.05f; // [ref: domain/domain.hpp:665]
+    DevBuf sgx_, sgy_, sgz_, sgm_; // x, y, z, m of the assigned particles in SFC order (syncGrav: expansion centres)
     std::unique_ptr<LetTree<K, T>> let_;
     std::vector<int32_t> hFlags_;
     std::vector<uint32_t> hLayout_;
@@ -1347,6 +1377,19 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
             CSB_TRY(gatherAssigned(n, 1, which, d1, eb));
         }
 
+        if (grav_ && n)
+        {
+            // [ref: domain/domain.hpp:262-264] x, y, z, m of the assigned particles in SFC order for the expansion centres
+            DevBuf* gb[4]      = {&sgx_, &sgy_, &sgz_, &sgm_};
+            const int which[4] = {0, 1, 2, 4};
+            void* d4[4];
+            for (int k = 0; k < 4; ++k)
+            {
+                CSB_TRY(gb[k]->reserve(sizeof(T) * n + 256));
+                d4[k] = gb[k]->p;
+            }
+            CSB_TRY(gatherAssigned(n, 4, which, d4, eb));
+        }
         mark(6);
         // 9. halos
         CSB_TRY(haloMode_ == 1 ? discoverHalosLet() : discoverHalos());
@@ -1578,28 +1621,76 @@ int Engine<K, T>::discoverHalosLet()
     // a. peers [ref: traversal/peers.hpp:62-117], focus tree [ref: domain/domain.hpp:219-228]
     HostOctree<K> gtree;
     gtree.build(hGlobalLeaves_.data(), global_.numNodes);
-    const float invThetaEff = 1.0f / theta_ + 0.5f; // [ref: traversal/macs.hpp:45 invThetaMinMac]
+    const bool grav = grav_;
+    // [ref: traversal/macs.hpp:45-48 invThetaMinMac / invThetaVecMac]
+    const float invThetaEff = grav ? 1.0f / theta_ + std::sqrt(3.0f) : 1.0f / theta_ + 0.5f;
     const std::vector<int> peers = findPeersMacHost<K, T>(sfcKind_, rank_, boundaries_, gtree, box_, invThetaEff);
-    if (firstCall_)
+    CSB_TRY(small_.reserve(size_t(P + 1) * (sizeof(K) + 4) + size_t(P) * P * 4 + 4096));
+    auto allSum = [&](int& v) -> int
     {
-        // [ref: focus/octree_focus_mpi.hpp:528-547 converge]
-        CSB_TRY(small_.reserve(size_t(P + 1) * (sizeof(K) + 4) + size_t(P) * P * 4 + 4096));
-        int32_t* dConv = small_.template as<int32_t>();
+        int32_t* dv = small_.template as<int32_t>();
+        CSB_CUDA(cudaMemcpyAsync(dv, &v, 4, cudaMemcpyHostToDevice, s_));
+        CSB_TRY(comm_->allReduce(dv, 1, CommType::i32, CommOp::sum, s_));
+        CSB_CUDA(cudaMemcpyAsync(&v, dv, 4, cudaMemcpyDeviceToHost, s_));
+        CSB_CUDA(cudaStreamSynchronize(s_));
+        return 0;
+    };
+    auto treeAndCounts = [&](int* converged) -> int
+    {
+        CSB_TRY(let.updateTree(comm_.get(), peers, boundaries_, box_, converged, s_));
+        return let.updateCounts(comm_.get(), skeys, n, hGlobalLeaves_, hGlobalCounts_, s_);
+    };
+    auto centers = [&]() -> int
+    {
+        return let.updateCenters(comm_.get(), skeys, n, sgx_.template as<T>(), sgy_.template as<T>(), sgz_.template as<T>(),
+                                 sgm_.template as<T>(), hGlobalLeaves_, s_);
+    };
+    /* The reference converges the tree on the first call only; its syncGrav after plain syncs would read expansion
+     * centres of an older tree (undefined there).  Here a syncGrav that does not follow a syncGrav converges again. */
+    if (firstCall_ || (grav && !gravReady_))
+    {
+        // [ref: focus/octree_focus_mpi.hpp:528-547 converge] with the min-distance MAC
+        const float invThetaConv = grav ? 1.0f : invThetaEff;
         for (int converged = 0, it = 0; converged != P; ++it)
         {
             if (it > 200) return CSTONE_E_LET;
-            CSB_TRY(let.updateMinMac(boundaries_, invThetaEff, s_));
-            CSB_TRY(let.updateTree(comm_.get(), peers, boundaries_, box_, &converged, s_));
-            CSB_TRY(let.updateCounts(comm_.get(), skeys, n, hGlobalLeaves_, hGlobalCounts_, s_));
-            CSB_CUDA(cudaMemcpyAsync(dConv, &converged, 4, cudaMemcpyHostToDevice, s_));
-            CSB_TRY(comm_->allReduce(dConv, 1, CommType::i32, CommOp::sum, s_));
-            CSB_CUDA(cudaMemcpyAsync(&converged, dConv, 4, cudaMemcpyDeviceToHost, s_));
-            CSB_CUDA(cudaStreamSynchronize(s_));
+            CSB_TRY(let.updateMinMac(boundaries_, invThetaConv, s_));
+            CSB_TRY(treeAndCounts(&converged));
+            CSB_TRY(allSum(converged));
+        }
+        if (grav)
+        {
+            // [ref: domain/domain.hpp:272-286] then with the vector MAC around the expansion centres, twice at least
+            CSB_TRY(let.updateMinMac(boundaries_, 1.0f, s_));
+            for (int converged = 0, reps = 0; converged != P || reps < 2; ++reps)
+            {
+                if (reps > 200) return CSTONE_E_LET;
+                CSB_TRY(treeAndCounts(&converged));
+                CSB_TRY(centers());
+                CSB_TRY(let.updateMacs(boundaries_, float(1.0 / theta_), s_));
+                CSB_TRY(allSum(converged));
+            }
         }
     }
-    CSB_TRY(let.updateMinMac(boundaries_, invThetaEff, s_));
-    CSB_TRY(let.updateTree(comm_.get(), peers, boundaries_, box_, nullptr, s_));
-    CSB_TRY(let.updateCounts(comm_.get(), skeys, n, hGlobalLeaves_, hGlobalCounts_, s_));
+    int haloFail = 0;
+    bool consistent = true;
+    std::vector<uint32_t> sendIdx;
+    do
+    {
+    haloFail = 0;
+    if (grav)
+    {
+        // [ref: domain/domain.hpp:289-296]
+        CSB_TRY(let.updateMacs(boundaries_, centerDriftTol_ / theta_, s_));
+        CSB_TRY(treeAndCounts(nullptr));
+        CSB_TRY(centers());
+        CSB_TRY(let.updateMacs(boundaries_, float(1.0 / theta_), s_));
+    }
+    else
+    {
+        CSB_TRY(let.updateMinMac(boundaries_, invThetaEff, s_));
+        CSB_TRY(treeAndCounts(nullptr));
+    }
 
     const FocusTree<K>& ft           = let.t;
     const int L                      = ft.numLeaves_;
@@ -1626,6 +1717,12 @@ int Engine<K, T>::discoverHalosLet()
                                       ft.i2l_.template as<int32_t>(), ft.leaves_.template as<K>(), radii_.template as<float>(), &box_,
                                       firstNode, lastNode, flags_.template as<int32_t>(), s_)));
     }
+    if (grav)
+    {
+        addMacsKernel<<<gridFor(size_t(L), 256), 256, 0, s_>>>(ft.macs_.template as<char>(), ft.l2i_.template as<int32_t>() + ft.numInternal_,
+                                                              L, flags_.template as<int32_t>());
+        CSB_LAUNCHED();
+    }
     hFlags_.resize(size_t(L));
     CSB_CUDA(cudaMemcpyAsync(hFlags_.data(), flags_.p, 4 * size_t(L), cudaMemcpyDeviceToHost, s_));
     CSB_CUDA(cudaStreamSynchronize(s_));
@@ -1643,7 +1740,7 @@ int Engine<K, T>::discoverHalosLet()
     }
     start_ = hLayout_[firstNode], end_ = hLayout_[lastNode], nTotal_ = hLayout_[L];
     pat_.start = start_;
-    if (nTotal_ >= (uint64_t(1) << 30)) return CSTONE_E_TOO_LARGE;
+    const bool tooLarge = nTotal_ >= (uint64_t(1) << 30); // reported with the other flags in step f, on all ranks
 
     // d. per peer: the key ranges of its leaves that I flagged; it answers with particle ranges of ITS layout
     //    [ref: domain/exchange_keys.hpp:62-118 exchangeRequestKeys, domain/layout.hpp:93-123 extractMarkedElements]
@@ -1670,8 +1767,8 @@ int Engine<K, T>::discoverHalosLet()
     }
     CSB_TRY(let.exchangeBytes(comm_.get(), requests, requested, s_));
     haloSendCount_.assign(P, 0), haloSendOffset_.assign(P + 1, 0);
-    std::vector<uint32_t> sendIdx;
-    bool consistent = uint64_t(end_ - start_) == uint64_t(n);
+    sendIdx.clear();
+    consistent = uint64_t(end_ - start_) == uint64_t(n) && !tooLarge;
     for (int q = 0; q < P; ++q)
     {
         haloSendOffset_[q] = uint32_t(sendIdx.size());
@@ -1717,8 +1814,17 @@ int Engine<K, T>::discoverHalosLet()
         bool found = false;
         for (int peer : peers)
             found = found || (assign[peer][0] <= i && i < assign[peer][1]);
-        if (!found) consistent = false;
+        if (!found) haloFail = 1;
     }
+    if (grav)
+    {
+        // [ref: domain/domain.hpp:309-317] a halo leaf outside of every peer: the tree lags the moving centres
+        CSB_TRY(allSum(haloFail));
+        if (haloFail) centerDriftTol_ += 0.05f;
+        if (centerDriftTol_ > 10.f) return CSTONE_E_LET;
+    }
+    else if (haloFail) consistent = false;
+    } while (grav && haloFail);
 
     /* f. every rank sees every send and expected receive count: a mismatch (counts of a peer's range that differ from
      *    the owner's) ends the sync on ALL ranks with an error instead of a hanging exchange */
@@ -1729,7 +1835,7 @@ int Engine<K, T>::discoverHalosLet()
         std::vector<uint32_t> mine(2 * P + 1), all(size_t(2 * P + 1) * P);
         for (int q = 0; q < P; ++q)
             mine[q] = haloSendCount_[q], mine[P + q] = haloRecvCount_[q];
-        mine[2 * P] = consistent ? 0u : 1u;
+        mine[2 * P] = (consistent && !let.takeError()) ? 0u : 1u;
         CSB_CUDA(cudaMemcpyAsync(dMine, mine.data(), 4 * mine.size(), cudaMemcpyHostToDevice, s_));
         CSB_TRY(comm_->allGather(dMine, dAll, 4 * mine.size(), s_));
         CSB_CUDA(cudaMemcpyAsync(all.data(), dAll, 4 * all.size(), cudaMemcpyDeviceToHost, s_));
@@ -1770,7 +1876,10 @@ int Engine<K, T>::discoverHalosLet()
     if (nTotal_ > end_)
         CSB_TRY((Api<K, T>::keys(sfcKind_, fx + end_, fy + end_, fz + end_, fk + end_, size_t(nTotal_ - end_), &box_, s_)));
 
+    gravReady_ = grav;
     // h. the LET becomes the search tree (leaves + counts; linked in syncBegin)
+    const FocusTree<K>& ft = let.t;
+    const int L            = ft.numLeaves_;
     CSB_TRY(search_.ensure(L, s_));
     CSB_CUDA(cudaMemcpyAsync(search_.treeA.p, ft.leaves_.p, sizeof(K) * (size_t(L) + 1), cudaMemcpyDeviceToDevice, s_));
     CSB_CUDA(cudaMemcpyAsync(search_.counts.p, ft.leafCounts_.p, 4 * size_t(L), cudaMemcpyDeviceToDevice, s_));
@@ -2190,6 +2299,21 @@ void cstone_b200_local_world_destroy(void* world) { delete static_cast<csb::Loca
     {                                                                                                                  \
         if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
         return CSB_ENGINE(K, T, d)->syncBegin(n, x, y, z, h, nprops, props, pb);                                       \
+    }                                                                                                                  \
+    int64_t cstone_b200_domain_sync_grav_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n, const T* x, const T* y, const T* z,\
+                                                      const T* h, int nprops, const void* const* props, const int* pb) \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return CSB_ENGINE(K, T, d)->syncGravBegin(n, x, y, z, h, nprops, props, pb);                                       \
+    }                                                                                                                  \
+    int cstone_b200_domain_let_centers_##KS##_##TS(const cstone_b200_domain* d, const T** centers4, const char** macs, \
+                                                   int32_t* numNodes)                                                  \
+    {                                                                                                                  \
+        if (!d || !centers4 || !macs || !numNodes) return CSTONE_E_INVALID_ARGUMENT;                                   \
+        const void* c = nullptr;                                                                                       \
+        reinterpret_cast<const csb::Engine<K, T>*>(d)->letCenters(&c, macs, numNodes);                                 \
+        *centers4 = static_cast<const T*>(c);                                                                          \
+        return 0;                                                                                                      \
     }                                                                                                                  \
     int cstone_b200_domain_sync_finish_##KS##_##TS(cstone_b200_domain* d, K* keys, T* x, T* y, T* z, T* h,             \
                                                    void* const* props)                                                 \

@@ -11,14 +11,6 @@
 namespace csb
 {
 
-#ifndef CSB_TRY
-#define CSB_TRY(expr)                                                                                                  \
-    do                                                                                                                 \
-    {                                                                                                                  \
-        int tryStatus_ = (expr);                                                                                       \
-        if (tryStatus_ != 0) return tryStatus_;                                                                        \
-    } while (0)
-#endif
 
 //! grow-only device array (5 % head room, as the reference's reallocate policy, util/reallocate.hpp:37-66)
 struct FBuf

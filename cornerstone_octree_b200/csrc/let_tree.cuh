@@ -278,6 +278,37 @@ inline std::vector<K> hostApplyOps(const K* tree, int first, int last, const std
     return out;
 }
 
+/*! mass centre of the particles whose keys lie in [ranges[2i], ranges[2i+1]), summed in particle order as the
+ *  reference's massCenter does [ref: focus/source_center.hpp:68-80]; one thread per range (a handful of ranges) */
+template<class K, class T>
+__global__ void rangeMassCenterKernel(const K* __restrict__ keys, uint32_t numKeys, const T* __restrict__ x,
+                                      const T* __restrict__ y, const T* __restrict__ z, const T* __restrict__ m,
+                                      const K* __restrict__ ranges, int numRanges, T* __restrict__ out4)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= numRanges) return;
+    auto lowerBound = [&](K v)
+    {
+        uint32_t lo = 0, hi = numKeys;
+        while (lo < hi)
+        {
+            const uint32_t mid = (lo + hi) / 2;
+            if (keys[mid] < v) lo = mid + 1;
+            else hi = mid;
+        }
+        return lo;
+    };
+    const uint32_t a = lowerBound(ranges[2 * i]), b = lowerBound(ranges[2 * i + 1]);
+    T c[4] = {0, 0, 0, 0};
+    for (uint32_t j = a; j < b; ++j)
+    {
+        const T w = fabs(m[j]);
+        c[0] += w * x[j], c[1] += w * y[j], c[2] += w * z[j], c[3] += w;
+    }
+    const T invM = (c[3] != T(0)) ? T(1) / c[3] : T(1);
+    out4[4 * i] = c[0] * invM, out4[4 * i + 1] = c[1] * invM, out4[4 * i + 2] = c[2] * invM, out4[4 * i + 3] = c[3];
+}
+
 // ------------------------------------------------------------------------------------------------
 // the tree
 // ------------------------------------------------------------------------------------------------
@@ -316,6 +347,15 @@ public:
     const std::vector<std::array<int, 2>>& assignment() const { return assign_; }
     const std::vector<int>& peers() const { return peers_; }
     int numLeaves() const { return int(leaves_.size()) - 1; }
+    /*! true if a step of this rank found the trees of the ranks inconsistent since the last call.  Such a step does not
+     *  return early: its peers would wait forever in the next exchange.  The engine reduces the flags of all ranks at
+     *  the end of the sync and fails on all of them together. */
+    bool takeError()
+    {
+        const bool e = error_;
+        error_       = false;
+        return e;
+    }
 
     //! [ref: octree_focus_mpi.hpp:457-525 updateMinMac + updateMacs]  (box: the one of the last updateTree)
     int updateMinMac(const std::vector<K>& bnd, float invThetaEff, cudaStream_t s)
@@ -355,6 +395,7 @@ public:
         translateAssignment(bnd);
 
         box_       = box;
+        globBnd_   = bnd;
         prevStart_ = focusStart, prevEnd_ = focusEnd;
         if (converged) *converged = conv ? 1 : 0;
         return 0;
@@ -369,29 +410,16 @@ public:
 
         // leaves outside of my range and of every peer's range: sums over the global leaves they span
         // [ref: domain/layout.hpp:57-90 invertRanges + enumerateRanges, focus/rebalance.hpp:278-299 rangeCount]
-        std::vector<uint32_t> idx, val;
+        std::vector<uint32_t> idx = nonPeerLeaves(), val(0);
+        val.reserve(idx.size());
+        for (uint32_t i : idx)
         {
-            int current = 0;
-            auto fill = [&](int a, int b)
-            {
-                for (int i = a; i < b; ++i)
-                {
-                    const int gs = findNodeBelow(gLeaves.data(), int(gLeaves.size()), leaves_[i]);
-                    const int ge = findNodeAbove(gLeaves.data(), int(gLeaves.size()), leaves_[i + 1]);
-                    uint64_t sum = 0;
-                    for (int g = gs; g < ge; ++g)
-                        sum += gCounts[g];
-                    idx.push_back(uint32_t(i));
-                    val.push_back(uint32_t(std::min<uint64_t>(0xFFFFFFFFull, sum)));
-                }
-            };
-            for (const auto& r : assign_)
-            {
-                if (r[0] == r[1]) continue;
-                if (current < r[0]) fill(current, r[0]);
-                current = r[1];
-            }
-            if (current < L) fill(current, L);
+            const int gs = findNodeBelow(gLeaves.data(), int(gLeaves.size()), leaves_[i]);
+            const int ge = findNodeAbove(gLeaves.data(), int(gLeaves.size()), leaves_[i + 1]);
+            uint64_t sum = 0;
+            for (int g = gs; g < ge; ++g)
+                sum += gCounts[g];
+            val.push_back(uint32_t(std::min<uint64_t>(0xFFFFFFFFull, sum)));
         }
         if (!idx.empty())
         {
@@ -413,6 +441,199 @@ public:
         leafCounts_.resize(L);
         CSB_CUDA(cudaMemcpyAsync(leafCounts_.data(), t.leafCounts_.p, 4 * size_t(L), cudaMemcpyDeviceToHost, s));
         CSB_CUDA(cudaStreamSynchronize(s));
+        return 0;
+    }
+
+    //! leaves that lie neither in my range nor in a peer's: their data comes from the replicated global tree
+    //! [ref: domain/layout.hpp:57-90 invertRanges + enumerateRanges]
+    std::vector<uint32_t> nonPeerLeaves() const
+    {
+        std::vector<uint32_t> idx;
+        const int L = int(leaves_.size()) - 1;
+        int current = 0;
+        for (const auto& r : assign_)
+        {
+            if (r[0] == r[1]) continue;
+            for (int i = current; i < r[0]; ++i)
+                idx.push_back(uint32_t(i));
+            current = r[1];
+        }
+        for (int i = current; i < L; ++i)
+            idx.push_back(uint32_t(i));
+        return idx;
+    }
+
+    //! index of the node [start, end) in a linked tree given by its prefixes and level ranges, -1 if absent
+    //! [ref: tree/octree.hpp locateNode]
+    static int locateNode(K start, K end, const K* prefixes, const int* levelRange)
+    {
+        const unsigned level = treeLevel<K>(end - start);
+        const K prefix       = encodePlaceholderBit<K>(start, 3 * int(level));
+        const K* first       = prefixes + levelRange[level];
+        const K* last        = prefixes + levelRange[level + 1];
+        const K* it          = std::lower_bound(first, last, prefix);
+        return (it == last || *it != prefix) ? -1 : int(it - prefixes);
+    }
+
+    /*! expansion (mass) centres of every node [ref: octree_focus_mpi.hpp:368-449 updateCenters]: leaves of my range from
+     *  the particles (x, y, z, m: the assigned particles in SFC order), upsweep; cells above the local domains through
+     *  the replicated global tree (every rank contributes the centres of its global leaves, upsweep there, the leaves
+     *  of non-peer ranks read theirs back: populateGlobal / gatherGlobalLeaves / extractGlobal :288-366); leaves in a
+     *  peer's range from the owner; upsweep.  gLeaves: host copy of the global leaf keys. */
+    int updateCenters(Comm* comm, const K* keysDev, size_t numKeys, const T* x, const T* y, const T* z, const T* m,
+                      const std::vector<K>& gLeaves, cudaStream_t s)
+    {
+        constexpr int vb   = 4 * int(sizeof(T)); // bytes of one centre
+        const int L        = t.numLeaves_, M = t.numNodes_;
+        const int firstIdx = assign_[rank_][0], lastIdx = assign_[rank_][1];
+        const int levels   = int(KeyTraits<K>::maxLevel) + 1;
+        /* particle ranges of my leaves, every other leaf empty.  (The reference leaves layout[i] = 0 behind my range, i.e.
+         * start above end there; the kernel wants a monotone layout, so those entries hold the total: the same empty
+         * ranges.) */
+        CSB_TRY(layoutOwn_.reserve(4 * (size_t(L) + 2)));
+        CSB_TRY(t.temp_.reserve(size_t(cstone_b200_scan_temp_bytes(uint64_t(L) + 2)) + 4096));
+        CSB_CUDA(cudaMemsetAsync(layoutOwn_.p, 0, 4 * (size_t(L) + 1), s));
+        if (lastIdx > firstIdx)
+        {
+            CSB_TRY(cstone_b200_exclusive_scan_u32(t.leafCounts_.template as<uint32_t>() + firstIdx,
+                                                   layoutOwn_.as<uint32_t>() + firstIdx, size_t(lastIdx - firstIdx) + 1, 0u,
+                                                   t.temp_.p, s));
+            uint32_t total = 0;
+            for (int i = firstIdx; i < lastIdx; ++i)
+                total += leafCounts_[i];
+            if (L > lastIdx) CSB_TRY(cstone_b200_fill(layoutOwn_.as<uint32_t>() + lastIdx + 1, size_t(L - lastIdx), &total, 4, s));
+        }
+        CSB_TRY(t.centers_.reserve(size_t(M) * vb));
+        CSB_TRY(leafCenters(x, y, z, m, t.l2i_.template as<int32_t>() + t.numInternal_, L, layoutOwn_.as<uint32_t>(),
+                            t.centers_.template as<T>(), s));
+        CSB_TRY(upsweepCenters(levels, t.levelRange_, t.childOffsets_.template as<int32_t>(), t.centers_.template as<T>(), s));
+
+        // ---- the global tree, linked on the device
+        const int Lg = int(gLeaves.size()) - 1;
+        CSB_TRY(g_.setLeavesHost(gLeaves.data(), Lg, s));
+        const int Mg = g_.numNodes_;
+        gPrefixes_.resize(size_t(Mg));
+        CSB_CUDA(cudaMemcpyAsync(gPrefixes_.data(), g_.prefixes_.p, size_t(Mg) * sizeof(K), cudaMemcpyDeviceToHost, s));
+        CSB_CUDA(cudaStreamSynchronize(s));
+        CSB_TRY(gLeafCenters_.reserve(size_t(Lg) * vb + 256));
+        CSB_TRY(g_.centers_.reserve(size_t(Mg) * vb + 256));
+        CSB_CUDA(cudaMemsetAsync(gLeafCenters_.p, 0, size_t(Lg) * vb, s));
+        // my global leaves take the centres of the nodes of my tree that cover them (populateGlobal)
+        const int nk       = int(gLeaves.size());
+        const int firstGlb = findNodeAbove(gLeaves.data(), nk, prevStart_), lastGlb = findNodeAbove(gLeaves.data(), nk, prevEnd_);
+        /* A global leaf of my range that is no node of my tree (the focus tree follows the particles one rebalance step
+         * per sync and can be coarser than the global tree for a step; the reference then reads an unrelated node) takes
+         * its centre from the particles directly. */
+        std::vector<uint32_t> gmap, missing;
+        std::vector<K> missingRanges;
+        for (int i = firstGlb; i < lastGlb; ++i)
+        {
+            const int node = locateNode(gLeaves[i], gLeaves[i + 1], prefixes_.data(), t.levelRange_);
+            if (node < 0)
+            {
+                missing.push_back(uint32_t(i));
+                missingRanges.push_back(gLeaves[i]), missingRanges.push_back(gLeaves[i + 1]);
+            }
+            gmap.push_back(uint32_t(std::max(node, 0)));
+        }
+        CSB_TRY(stage_.reserve(8 * std::max(gmap.size(), size_t(L)) + 1024));
+        if (!gmap.empty())
+        {
+            CSB_CUDA(cudaMemcpyAsync(stage_.p, gmap.data(), 4 * gmap.size(), cudaMemcpyHostToDevice, s));
+            CSB_TRY(cstone_b200_gather(stage_.as<uint32_t>(), gmap.size(), t.centers_.p,
+                                       gLeafCenters_.as<char>() + size_t(firstGlb) * vb, vb, s));
+        }
+        if (!missing.empty())
+        {
+            const size_t nm = missing.size();
+            CSB_TRY(xchg_.reserve(nm * (2 * sizeof(K) + vb + 4) + 1024));
+            K* dRanges     = xchg_.as<K>();
+            T* dOut        = reinterpret_cast<T*>(xchg_.as<char>() + (nm * 2 * sizeof(K) + 255) / 256 * 256);
+            uint32_t* dIdx = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(dOut) + (nm * vb + 255) / 256 * 256);
+            CSB_TRY(xchg_.reserve(size_t(reinterpret_cast<char*>(dIdx) - xchg_.as<char>()) + 4 * nm + 256));
+            dRanges = xchg_.as<K>();
+            dOut    = reinterpret_cast<T*>(xchg_.as<char>() + (nm * 2 * sizeof(K) + 255) / 256 * 256);
+            dIdx    = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(dOut) + (nm * vb + 255) / 256 * 256);
+            CSB_CUDA(cudaMemcpyAsync(dRanges, missingRanges.data(), nm * 2 * sizeof(K), cudaMemcpyHostToDevice, s));
+            CSB_CUDA(cudaMemcpyAsync(dIdx, missing.data(), 4 * nm, cudaMemcpyHostToDevice, s));
+            rangeMassCenterKernel<K, T><<<unsigned((nm + 63) / 64), 64, 0, s>>>(keysDev, uint32_t(numKeys), x, y, z, m, dRanges,
+                                                                               int(nm), dOut);
+            CSB_LAUNCHED();
+            CSB_TRY(cstone_b200_scatter(dIdx, nm, dOut, gLeafCenters_.p, vb, s));
+            CSB_CUDA(cudaStreamSynchronize(s));
+        }
+        // every rank's part goes to everybody (gatherGlobalLeaves: in-place all-gather with ragged counts)
+        {
+            std::vector<int> displ(size_t(P_) + 1);
+            for (int r = 0; r < P_; ++r)
+                displ[r] = findNodeAbove(gLeaves.data(), Lg, globBnd_[r]);
+            displ[P_] = Lg;
+            std::vector<CommMsg> sends, recvs;
+            for (int r = 0; r < P_; ++r)
+            {
+                if (r == rank_) continue;
+                const size_t mineBytes = size_t(displ[rank_ + 1] - displ[rank_]) * vb;
+                const size_t hisBytes  = size_t(displ[r + 1] - displ[r]) * vb;
+                if (mineBytes) sends.push_back({r, gLeafCenters_.as<char>() + size_t(displ[rank_]) * vb, mineBytes});
+                if (hisBytes) recvs.push_back({r, gLeafCenters_.as<char>() + size_t(displ[r]) * vb, hisBytes});
+            }
+            CSB_TRY(comm->exchange(sends, recvs, s));
+        }
+        CSB_TRY(cstone_b200_scatter(g_.l2i_.template as<uint32_t>() + g_.numInternal_, size_t(Lg), gLeafCenters_.p, g_.centers_.p, vb, s));
+        CSB_TRY(upsweepCenters(levels, g_.levelRange_, g_.childOffsets_.template as<int32_t>(), g_.centers_.template as<T>(), s));
+        // leaves of non-peer ranks read the centre of the global node with their key range (extractGlobal)
+        {
+            std::vector<uint32_t> idx = nonPeerLeaves(), nodeIdx, gIdx;
+            l2iHost_.resize(size_t(L));
+            CSB_CUDA(cudaMemcpyAsync(l2iHost_.data(), t.l2i_.template as<int32_t>() + t.numInternal_, 4 * size_t(L),
+                                     cudaMemcpyDeviceToHost, s));
+            CSB_CUDA(cudaStreamSynchronize(s));
+            for (uint32_t i : idx)
+            {
+                const int gi = locateNode(leaves_[i], leaves_[i + 1], gPrefixes_.data(), g_.levelRange_);
+                if (gi < 0)
+                {
+                    // finer than the global tree outside of every peer: no source for this cell.  The other ranks are
+                    // not left alone in the exchanges that follow; the error surfaces on all ranks at the end of the sync
+                    fail(__LINE__);
+                    continue;
+                }
+                nodeIdx.push_back(uint32_t(l2iHost_[i]));
+                gIdx.push_back(uint32_t(gi));
+            }
+            if (!idx.empty())
+            {
+                const size_t n = idx.size();
+                CSB_TRY(stage_.reserve(8 * n + 1024));
+                CSB_TRY(xchg_.reserve(n * vb + 512));
+                uint32_t* dG = stage_.as<uint32_t>();
+                uint32_t* dN = dG + (n + 63) / 64 * 64;
+                CSB_CUDA(cudaMemcpyAsync(dG, gIdx.data(), 4 * n, cudaMemcpyHostToDevice, s));
+                CSB_CUDA(cudaMemcpyAsync(dN, nodeIdx.data(), 4 * n, cudaMemcpyHostToDevice, s));
+                CSB_TRY(cstone_b200_gather(dG, n, g_.centers_.p, xchg_.p, vb, s));
+                CSB_TRY(cstone_b200_scatter(dN, n, xchg_.p, t.centers_.p, vb, s));
+                CSB_CUDA(cudaStreamSynchronize(s));
+            }
+        }
+        CSB_TRY(peerExchange(comm, t.centers_.p, vb, s));
+        CSB_TRY(upsweepCenters(levels, t.levelRange_, t.childOffsets_.template as<int32_t>(), t.centers_.template as<T>(), s));
+        return 0;
+    }
+
+    //! MAC radius around the expansion centres, marks w.r.t. my leaves [ref: octree_focus_mpi.hpp:481-525
+    //! setMacRadius + updateMacs]
+    int updateMacs(const std::vector<K>& bnd, float invTheta, cudaStream_t s)
+    {
+        using A = FocusApi<K>;
+        CSB_TRY(t.temp_.reserve(size_t(cstone_b200_reduce_temp_bytes()) + 4096));
+        CSB_TRY(setMac(kind_, t.prefixes_.template as<K>(), t.numNodes_, t.centers_.template as<T>(), invTheta, &box_, s));
+        CSB_TRY(t.macs_.reserve(size_t(t.numNodes_)));
+        CSB_CUDA(cudaMemsetAsync(t.macs_.p, 0, size_t(t.numNodes_), s));
+        const int nk     = int(leaves_.size()) - 1;
+        const int fStart = findNodeAbove(leaves_.data(), nk, bnd[rank_]), fEnd = findNodeAbove(leaves_.data(), nk, bnd[rank_ + 1]);
+        if (fEnd > fStart)
+            CSB_TRY(A::mark(kind_, t.prefixes_.template as<K>(), t.childOffsets_.template as<int>(), t.centers_.template as<T>(),
+                            &box_, t.leaves_.template as<K>() + fStart, fEnd - fStart, 0, t.macs_.template as<char>(), s));
         return 0;
     }
 
@@ -516,6 +737,46 @@ public:
     }
 
 private:
+    void fail(int line)
+    {
+        error_ = true;
+        traceStatus(CSTONE_E_LET, __FILE__, line);
+    }
+    bool error_ = false;
+    static int leafCenters(const float* x, const float* y, const float* z, const float* m, const int32_t* l2i, int L,
+                           const uint32_t* layout, float* c, void* s)
+    {
+        return cstone_b200_compute_leaf_source_center_f32_f32_f32(x, y, z, m, l2i, L, layout, c, s);
+    }
+    static int leafCenters(const double* x, const double* y, const double* z, const double* m, const int32_t* l2i, int L,
+                           const uint32_t* layout, double* c, void* s)
+    {
+        return cstone_b200_compute_leaf_source_center_f64_f64_f64(x, y, z, m, l2i, L, layout, c, s);
+    }
+    static int upsweepCenters(int levels, const int* lr, const int32_t* co, float* c, void* s)
+    {
+        return cstone_b200_upsweep_centers_f32(levels, lr, co, c, s);
+    }
+    static int upsweepCenters(int levels, const int* lr, const int32_t* co, double* c, void* s)
+    {
+        return cstone_b200_upsweep_centers_f64(levels, lr, co, c, s);
+    }
+    static int setMac(int kind, const uint32_t* p, int n, float* c, float it, const cstone_box_f32* b, void* s)
+    {
+        return cstone_b200_set_mac_k32_f32(kind, p, n, c, it, b, s);
+    }
+    static int setMac(int kind, const uint32_t* p, int n, double* c, float it, const cstone_box_f64* b, void* s)
+    {
+        return cstone_b200_set_mac_k32_f64(kind, p, n, c, it, b, s);
+    }
+    static int setMac(int kind, const uint64_t* p, int n, float* c, float it, const cstone_box_f32* b, void* s)
+    {
+        return cstone_b200_set_mac_k64_f32(kind, p, n, c, it, b, s);
+    }
+    static int setMac(int kind, const uint64_t* p, int n, double* c, float it, const cstone_box_f64* b, void* s)
+    {
+        return cstone_b200_set_mac_k64_f64(kind, p, n, c, it, b, s);
+    }
     static std::vector<char> asBytes(const std::vector<K>& v)
     {
         std::vector<char> b(v.size() * sizeof(K));
@@ -662,7 +923,11 @@ private:
                 const K* first       = prefixes_.data() + t.levelRange_[level];
                 const K* last        = prefixes_.data() + t.levelRange_[level + 1];
                 const K* it          = std::lower_bound(first, last, prefix);
-                if (it == last || *it != prefix) return CSTONE_E_LET;
+                if (it == last || *it != prefix)
+                {
+                    fail(__LINE__);
+                    continue;
+                }
                 tlIdx_[size_t(tlOffset_[peer]) + i] = uint32_t(it - prefixes_.data());
             }
         }
@@ -686,6 +951,11 @@ private:
     std::vector<uint32_t> tlIdx_;
     std::vector<std::array<int, 2>> assign_;
     FBuf stage_, xchg_, sizes_, tlIdxDev_;
+    // gravity side: the global tree linked on the device, centres of its leaves / nodes, helpers
+    FocusTree<K> g_{CSTONE_SFC_HILBERT, 1u, 1.0f};
+    std::vector<K> gPrefixes_, globBnd_;
+    std::vector<int32_t> l2iHost_;
+    FBuf layoutOwn_, gLeafCenters_;
 };
 
 } // namespace csb

@@ -184,6 +184,8 @@ const char* cstone_b200_status_string(int status)
         case CSTONE_E_CAPACITY: return "cstone_b200: output capacity too small";
         case -6: return "cstone_b200: NCCL error";
         case -7: return "cstone_b200: array size differs from the previous sync";
+        case -8: return "cstone_b200: focus tree / halo bookkeeping of the ranks is inconsistent (reference halo mode)";
+        case -9: return "cstone_b200: a peer's halo data did not arrive (pack-and-push exchange)";
         default: break;
     }
     if (status > 0) return cudaGetErrorString(cudaError_t(status));

@@ -89,7 +89,23 @@ class Domain:
         _check(_fn("set_local_world", self.bits, self.fd)(self._h, world.handle), "set_local_world")
 
     # ---- sync
-    def sync(self, x, y, z, h, props=(), fields_ready=None):
+    def sync_grav(self, x, y, z, h, m, props=()):
+        """[ref: domain/domain.hpp:245-325 syncGrav] like sync, with the focus tree refined by the vector MAC around the
+        expansion centres; m (masses, same dtype as x) travels like a property and is returned after h:
+        (keys, x, y, z, h, m, props).  Needs set_halo_mode(1) and more than one rank."""
+        out = self.sync(x, y, z, h, (m,) + tuple(props), _entry="sync_grav_begin")
+        return out[0], out[1], out[2], out[3], out[4], out[5][0], out[5][1:]
+
+    def let_centers(self):
+        """after sync_grav: expansion centres [numNodes, 4] = x, y, z, MAC radius squared, and the MAC marks [numNodes]
+        of the focus tree (torch tensors that alias engine memory, valid until the next sync)"""
+        fd = C.c_double if self.fd == torch.float64 else C.c_float
+        c, m, n = C.POINTER(fd)(), C.c_char_p(), C.c_int32(0)
+        cp, mp = C.c_void_p(0), C.c_void_p(0)
+        _check(_fn("let_centers", self.bits, self.fd)(self._h, C.byref(cp), C.byref(mp), C.byref(n)), "let_centers")
+        return _alias(cp.value, 4 * n.value, self.fd).view(n.value, 4), _alias(mp.value, n.value, torch.int8)
+
+    def sync(self, x, y, z, h, props=(), fields_ready=None, _entry="sync_begin"):
         """[ref: domain/domain.hpp:196-243] returns (keys, x, y, z, h, props) as NEW tensors of the new local size:
         assigned particles in [start_index, end_index), halos elsewhere, everything in SFC order.
         fields_ready: optional torch.cuda.Event after which h and props are valid (e.g. the end of their upload on
@@ -107,10 +123,9 @@ class Domain:
         if fields_ready is not None:
             _check(_fn("set_fields_ready_event", self.bits, self.fd)(self._h, C.c_void_p(fields_ready.cuda_event)),
                    "set_fields_ready_event")
-        n_new = _fn("sync_begin", self.bits, self.fd)(self._h, n_in, ops._p(x), ops._p(y), ops._p(z), ops._p(h), k, parr,
-                                                     pbytes)
+        n_new = _fn(_entry, self.bits, self.fd)(self._h, n_in, ops._p(x), ops._p(y), ops._p(z), ops._p(h), k, parr, pbytes)
         if n_new < 0:
-            raise CstoneError(int(n_new), "cstone_b200_domain_sync_begin")
+            raise CstoneError(int(n_new), "cstone_b200_domain_" + _entry)
         dev = x.device
         keys = torch.empty(n_new, dtype=ops.KEY_TORCH[self.bits], device=dev)
         out = [torch.empty(n_new, dtype=x.dtype, device=dev) for _ in range(4)]

@@ -72,6 +72,7 @@ struct DomainApi;
         static constexpr auto setHaloMode   = cstone_b200_domain_set_halo_mode_##KS##_##TS;                            \
         static constexpr auto cells         = cstone_b200_domain_cells_##KS##_##TS;                                    \
         static constexpr auto syncBegin     = cstone_b200_domain_sync_begin_##KS##_##TS;                               \
+        static constexpr auto syncGravBegin = cstone_b200_domain_sync_grav_begin_##KS##_##TS;                          \
         static constexpr auto syncFinish    = cstone_b200_domain_sync_finish_##KS##_##TS;                              \
         static constexpr auto exchangeHalos = cstone_b200_domain_exchange_halos_##KS##_##TS;                           \
         static constexpr auto reapplySync   = cstone_b200_domain_reapply_sync_##KS##_##TS;                             \
@@ -158,6 +159,31 @@ public:
               std::tuple<Vectors1&...> particleProperties,
               std::tuple<Vectors2&...> /*scratchBuffers*/)
     {
+        syncImpl(false, particleKeys, x, y, z, h, particleProperties);
+    }
+
+    /*! [ref: domain/domain.hpp:245-325]  sync for N-body clients: the focus tree is refined with the vector MAC around
+     *  the expansion centres of its cells, leaves that fail it become halos.  m travels like x, y, z, h (valid in the
+     *  assigned range on return).  Needs setReferenceHalos(true) and more than one rank. */
+    template<class KeyVec, class VectorX, class VectorH, class VectorM, class... Vectors1, class... Vectors2>
+    void syncGrav(KeyVec& particleKeys,
+                  VectorX& x,
+                  VectorX& y,
+                  VectorX& z,
+                  VectorH& h,
+                  VectorM& m,
+                  std::tuple<Vectors1&...> particleProperties,
+                  std::tuple<Vectors2&...> /*scratchBuffers*/)
+    {
+        static_assert(std::is_same_v<typename VectorM::value_type, T>, "masses must hold T");
+        syncImpl(true, particleKeys, x, y, z, h, std::tuple_cat(std::tie(m), particleProperties));
+    }
+
+private:
+    template<class KeyVec, class VectorX, class VectorH, class... Vectors1>
+    void syncImpl(bool grav, KeyVec& particleKeys, VectorX& x, VectorX& y, VectorX& z, VectorH& h,
+                  std::tuple<Vectors1&...> particleProperties)
+    {
         static_assert(sizeof(typename KeyVec::value_type) == sizeof(K), "key vector does not match KeyType");
         static_assert(std::is_same_v<typename VectorX::value_type, T>, "coordinate vectors must hold T");
         static_assert(std::is_same_v<typename VectorH::value_type, T>, "h must hold T");
@@ -175,7 +201,8 @@ public:
         std::apply([&](auto&... p) { ((in[i] = p.data(), bytes[i] = int(sizeof(*p.data())), ++i), ...); },
                    particleProperties);
 
-        long long nNew = Api::syncBegin(d_, n, x.data(), y.data(), z.data(), h.data(), np, in.data(), bytes.data());
+        long long nNew = grav ? Api::syncGravBegin(d_, n, x.data(), y.data(), z.data(), h.data(), np, in.data(), bytes.data())
+                              : Api::syncBegin(d_, n, x.data(), y.data(), z.data(), h.data(), np, in.data(), bytes.data());
         if (nNew == CSTONE_E_SIZE_MISMATCH) throw std::runtime_error("Domain sync: input array sizes are inconsistent\n");
         detail::check(nNew < 0 ? nNew : 0, "Domain::sync");
 
@@ -196,6 +223,7 @@ public:
         refresh();
     }
 
+public:
     //! [ref: domain/domain.hpp:381-386]  send/receive buffers accepted for source compatibility
     template<class... Vectors, class SendBuffer, class ReceiveBuffer>
     void exchangeHalos(std::tuple<Vectors&...> arrays, SendBuffer&, ReceiveBuffer&) const

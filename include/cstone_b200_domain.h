@@ -94,6 +94,19 @@ void cstone_b200_local_world_destroy(void* world);
     int64_t cstone_b200_domain_sync_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n_in, const T* x, const T* y,    \
                                                       const T* z, const T* h, int nprops, const void* const* props,    \
                                                       const int* prop_bytes);                                          \
+    /* [ref: domain/domain.hpp:245-325 syncGrav] sync for N-body clients: the focus tree is refined by the vector MAC   \
+     * around the expansion (mass) centres of its nodes, which are made consistent over the ranks (own leaves from the  \
+     * particles, cells above the local domains through the replicated global tree, peers' cells from their owners)    \
+     * [ref: focus/octree_focus_mpi.hpp:368-525 updateCenters / updateMacs]; leaves that fail the MAC become halos.   \
+     * props[0] MUST be the masses (element type T); halo mode 1 and nranks > 1 are required, otherwise               \
+     * CSTONE_E_INVALID_ARGUMENT.  Finish with sync_finish as after sync_begin */                                      \
+    int64_t cstone_b200_domain_sync_grav_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n_in, const T* x, const T* y,    \
+                                                      const T* z, const T* h, int nprops, const void* const* props,    \
+                                                      const int* prop_bytes);                                          \
+    /* after sync_grav_begin: DEVICE views of the expansion centres (x, y, z, MAC radius^2) T[4 M] and the MAC marks   \
+     * char[M] of the focus tree, M = *num_nodes nodes in the order of tree_view's prefixes */                         \
+    int cstone_b200_domain_let_centers_##KS##_##TS(const cstone_b200_domain* d, const T** centers4, const char** macs, \
+                                                   int32_t* num_nodes);                                                \
     int cstone_b200_domain_sync_finish_##KS##_##TS(cstone_b200_domain* d, K* keys, T* x, T* y, T* z, T* h,             \
                                                    void* const* props);                                                \
     /* [ref: domain/domain.hpp:381-386 exchangeHalos] arrays: HOST array of device pointers of length n_new */        \

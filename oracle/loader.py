@@ -456,6 +456,28 @@ class RefDomain:
         st = self._f("sync")(self.h)
         assert st == 0, "reference Domain::sync failed"
 
+    def set_mass(self, rank, m):
+        m = np.ascontiguousarray(m, dtype=self.fd)
+        self._f("set_mass")(self.h, rank, C.c_uint64(m.size), _ptr(m))
+
+    def sync_grav(self):
+        """Domain::syncGrav on every rank (masses from set_mass)"""
+        st = self._f("sync_grav")(self.h)
+        assert st == 0, "reference Domain::syncGrav failed"
+
+    def masses(self, rank):
+        out = np.zeros(self.info(rank)["n"], dtype=self.fd)
+        self._f("get_array")(self.h, rank, 7, _ptr(out))
+        return out
+
+    def centers(self, rank):
+        """expansion centres of the focus tree after sync_grav: [numNodes, 4] = x, y, z, MAC radius squared"""
+        n = np.zeros(1, dtype=np.int64)
+        self._f("get_tree")(self.h, rank, 6, _ptr(n))
+        out = np.zeros((int(n[0]), 4), dtype=self.fd)
+        self._f("get_tree")(self.h, rank, 5, _ptr(out))
+        return out
+
     def info(self, rank):
         out = np.zeros(8, dtype=np.int64)
         box = np.zeros(6, dtype=self.fd)

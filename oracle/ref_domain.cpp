@@ -36,6 +36,7 @@ struct RankState
     std::vector<K> keys;
     std::vector<T> x, y, z, h;
     std::vector<T> p0, p1, p2, p3; // up to four conserved properties (0, 1, 2 or 4 are wired)
+    std::vector<T> m; // masses (syncGrav)
     std::vector<T> s1, s2, s3;
     double syncSeconds = 0, nbSeconds = 0;
     std::vector<unsigned> nb, nc; // neighbour lists / counts kept between bench steps
@@ -63,6 +64,20 @@ void syncRank(int rank, void* arg)
     else r.domain->sync(r.keys, r.x, r.y, r.z, r.h, std::tie(r.p0, r.p1), std::tie(r.s1, r.s2, r.s3));
     MPI_Barrier(MPI_COMM_WORLD);
     r.syncSeconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+//! Domain::syncGrav [ref: domain/domain.hpp:245-325] with the masses set by set_mass; one conserved property at most
+template<class K, class T>
+void syncGravRank(int rank, void* arg)
+{
+    auto* w = static_cast<World<K, T>*>(arg);
+    auto& r = w->ranks[rank];
+    omp_set_num_threads(w->ompPerRank);
+    r.keys.resize(r.x.size());
+    MPI_Barrier(MPI_COMM_WORLD);
+    if (w->nprops == 0) r.domain->syncGrav(r.keys, r.x, r.y, r.z, r.h, r.m, std::tuple{}, std::tie(r.s1, r.s2, r.s3));
+    else r.domain->syncGrav(r.keys, r.x, r.y, r.z, r.h, r.m, std::tie(r.p0), std::tie(r.s1, r.s2, r.s3));
+    MPI_Barrier(MPI_COMM_WORLD);
 }
 
 template<class K, class T>
@@ -232,6 +247,7 @@ int getArray(void* h, int rank, int which, void* out)
         case 4: cp(r.h); break;
         case 5: cp(r.p0); break;
         case 6: cp(r.p1); break;
+        case 7: cp(r.m); break;
         default: return 1;
     }
     return 0;
@@ -270,6 +286,17 @@ int getTree(void* h, int rank, int which, void* out)
             std::memcpy(out, l.data(), l.size() * sizeof(LocalIndex));
             break;
         }
+        case 5: // expansion centres of the focus tree after syncGrav: (x, y, z, mac radius^2) per node
+        {
+            auto c = d.focusTree().expansionCentersAcc();
+            std::memcpy(out, c.data(), c.size() * sizeof(c[0]));
+            break;
+        }
+        case 6: // number of nodes of the focus tree (int64)
+        {
+            *static_cast<int64_t*>(out) = int64_t(d.focusTree().octreeViewAcc().numNodes);
+            break;
+        }
         case 4:
         {
             auto a = d.focusTree().assignment();
@@ -296,6 +323,16 @@ int getTree(void* h, int rank, int which, void* out)
                                       const T* p0, const T* p1)                                                        \
     {                                                                                                                  \
         return setRank<K, T>(h, rank, n, x, y, z, hh, p0, p1);                                                         \
+    }                                                                                                                  \
+    int cstone_refdom_set_mass_##KS##_##TS(void* h, int rank, uint64_t n, const T* m)                                  \
+    {                                                                                                                  \
+        static_cast<World<K, T>*>(h)->ranks[rank].m.assign(m, m + n);                                                  \
+        return 0;                                                                                                      \
+    }                                                                                                                  \
+    int cstone_refdom_sync_grav_##KS##_##TS(void* h)                                                                   \
+    {                                                                                                                  \
+        auto* w = static_cast<World<K, T>*>(h);                                                                        \
+        return mpi_shim_run(w->P, syncGravRank<K, T>, w);                                                              \
     }                                                                                                                  \
     int cstone_refdom_sync_##KS##_##TS(void* h)                                                                        \
     {                                                                                                                  \

@@ -66,11 +66,13 @@ static T minImage(T d, T l, bool pbc)
 }
 
 template<class KeyType, class T>
-static void run(int rank, int nRanks, const std::array<char, 128>& id, LocalIndex numGlobal, bool pbc)
+static void run(int rank, int nRanks, const std::array<char, 128>& id, LocalIndex numGlobal, bool pbc, bool refHalos = false)
 {
     Box<T> box = pbc ? Box<T>(-1, 1, BoundaryType::periodic) : Box<T>(-1, 1);
     Domain<KeyType, T, GpuTag> domain(rank, nRanks, 64, 8, 1.0f, box);
     if (nRanks > 1) domain.initNcclComm(id);
+    if (refHalos) domain.setReferenceHalos(true); // the reference's halo procedure on the multi-rank focus tree
+    std::fprintf(stderr, "rank %d: run(pbc %d, reference halos %d) starts\n", rank, int(pbc), int(refHalos));
 
     numGlobal = (numGlobal / nRanks) * nRanks;
     std::vector<T> xg(numGlobal), yg(numGlobal), zg(numGlobal), hg(numGlobal);
@@ -97,7 +99,9 @@ static void run(int rank, int nRanks, const std::array<char, 128>& id, LocalInde
     {
         // a copy of one property in the layout BEFORE the sync: reapplySync must take it where sync takes pid
         DeviceVector<unsigned> pidLate(pid);
+        std::fprintf(stderr, "rank %d: sync %d\n", rank, step);
         domain.sync(keys, x, y, z, h, std::tie(pid, psum), std::tie(s1, s2, s3));
+        std::fprintf(stderr, "rank %d: sync %d done\n", rank, step);
         domain.reapplySync(std::tie(pidLate), s1, s2, s3);
         {
             auto viaSync = toHost(pid), viaReapply = toHost(pidLate);
@@ -201,6 +205,28 @@ static void run(int rank, int nRanks, const std::array<char, 128>& id, LocalInde
         x = cx, y = cy, psum = csum;
     }
 
+    if (refHalos && nRanks > 1)
+    {
+        // [ref: domain/domain.hpp:245-325 syncGrav] masses travel with the particles, keys stay sorted, sizes agree
+        DeviceVector<T> m(std::vector<T>(x.size(), T(1) / T(numGlobal)));
+        for (int step = 0; step < 2; ++step)
+        {
+            std::fprintf(stderr, "rank %d: syncGrav %d\n", rank, step);
+            domain.syncGrav(keys, x, y, z, h, m, std::tie(pid, psum), std::tie(s1, s2, s3));
+            LocalIndex n = domain.nParticlesWithHalos(), a = domain.startIndex(), b = domain.endIndex();
+            EXPECT(keys.size() == n && x.size() == n && m.size() == n && pid.size() == n);
+            auto k  = toHost(keys);
+            auto cm = toHost(m);
+            EXPECT(std::is_sorted(k.begin(), k.end()));
+            bool massOk = true;
+            for (LocalIndex q = a; q < b; ++q)
+                massOk = massOk && cm[q] == T(1) / T(numGlobal);
+            EXPECT(massOk);
+            auto view = domain.octreeProperties();
+            EXPECT(view.numLeafNodes > 0);
+        }
+    }
+
     // array sizes must not change between calls [ref: domain/domain.hpp:130-133]
     if (nRanks == 1)
     {
@@ -228,6 +254,29 @@ static void run(int rank, int nRanks, const std::array<char, 128>& id, LocalInde
     }
 }
 
+//! rank 0 draws a NCCL id and leaves it in a file, the others wait for it
+static std::array<char, 128> shareId(int rank, int nRanks, const std::string& idFile)
+{
+    std::array<char, 128> id{};
+    if (nRanks < 2) return id;
+    if (rank == 0)
+    {
+        id = Domain<uint64_t, double, GpuTag>::ncclUniqueId();
+        std::ofstream(idFile + ".tmp", std::ios::binary).write(id.data(), 128);
+        std::rename((idFile + ".tmp").c_str(), idFile.c_str());
+    }
+    else
+    {
+        for (int t = 0; t < 600; ++t)
+        {
+            std::ifstream f(idFile, std::ios::binary);
+            if (f && f.read(id.data(), 128)) break;
+            std::this_thread::sleep_for(std::chrono::milliseconds(100));
+        }
+    }
+    return id;
+}
+
 int main(int argc, char** argv)
 {
     if (argc < 4)
@@ -243,26 +292,14 @@ int main(int argc, char** argv)
     if (const char* dev = std::getenv("CSB_TEST_DEVICE")) { detail::check(cstone_b200_set_device(std::atoi(dev)), "set_device"); }
     else if (nRanks > 1) { detail::check(cstone_b200_set_device(rank), "set_device"); }
 
-    std::array<char, 128> id{};
+    std::array<char, 128> id = shareId(rank, nRanks, idFile);
+    run<uint64_t, double>(rank, nRanks, id, n, false);
     if (nRanks > 1)
     {
-        if (rank == 0)
-        {
-            id = Domain<uint64_t, double, GpuTag>::ncclUniqueId();
-            std::ofstream(idFile + ".tmp", std::ios::binary).write(id.data(), 128);
-            std::rename((idFile + ".tmp").c_str(), idFile.c_str());
-        }
-        else
-        {
-            for (int t = 0; t < 600; ++t)
-            {
-                std::ifstream f(idFile, std::ios::binary);
-                if (f && f.read(id.data(), 128)) break;
-                std::this_thread::sleep_for(std::chrono::milliseconds(100));
-            }
-        }
+        // the same checks with the reference's halo procedure, then syncGrav on that domain (a second communicator)
+        std::array<char, 128> id2 = shareId(rank, nRanks, idFile + ".let");
+        run<uint64_t, double>(rank, nRanks, id2, n, false, true);
     }
-    run<uint64_t, double>(rank, nRanks, id, n, false);
     if (nRanks == 1)
     {
         run<uint64_t, double>(rank, nRanks, id, n, true);

@@ -233,6 +233,84 @@ def test_ranks_reference_halo_mode(cloud, P, n, bucket, bucket_focus):
         rk.close()
 
 
+@pytest.mark.parametrize("cloud,P,n,bucket,bucket_focus", [("gaussian", 2, 20000, 64, 8), ("gaussian", 4, 20000, 50, 10),
+                                                          ("two-clusters", 3, 24000, 64, 8), ("gaussian", 8, 40000, 128, 16)],
+                         ids=["gaussian-P2", "gaussian-P4", "two-clusters-P3", "gaussian-P8"])
+def test_ranks_sync_grav_matches_reference(cloud, P, n, bucket, bucket_focus):
+    """Domain::syncGrav [ref: domain/domain.hpp:245-325] on thread-ranks against the reference's: focus tree refined by
+    the vector MAC (leaves, counts, assignment), expansion centres and MAC radii of every node, layout, index ranges,
+    every array with its halos, the masses of the assigned particles; first sync and displaced syncs"""
+    if not loader.refdom_available():
+        pytest.skip("oracle/_ref/liboracle_refdom.so did not travel")
+    import torch
+    from cornerstone_octree_b200 import ops
+    from cornerstone_octree_b200.domain import Domain, LocalWorld
+    x, y, z, h, lim, pbc = make_cloud(cloud, n)
+    rng = np.random.default_rng(5)
+    m = 0.5 + rng.random(n)
+    world = LocalWorld(P)
+    doms = [Domain(r, P, bucket, bucket_focus, 0.5, ops.make_box(lim)) for r in range(P)]
+    ref = loader.RefDomain(P, bucket, bucket_focus, 0.5, list(lim), pbc=pbc, nprops=0)
+    state = []
+    for r, d in enumerate(doms):
+        d.set_local_world(world)
+        d.set_halo_mode(1)
+        s = slice(r * n // P, (r + 1) * n // P)
+        ref.set(r, x[s], y[s], z[s], h[s])
+        ref.set_mass(r, m[s])
+        state.append([_dev(a[s]) for a in (x, y, z, h, m)])
+    try:
+        for it in range(3):
+            if it:
+                # the same displacement on both sides, addressed through the mass (unique per particle)
+                d = 0.01 * it * np.random.default_rng(40 + it).standard_normal((3, n))
+                order = np.argsort(m)
+                for r in range(P):
+                    s_, e_ = doms[r].start_index, doms[r].end_index
+                    mine = state[r][4][s_:e_].cpu().numpy()
+                    gid = order[np.searchsorted(m[order], mine)]
+                    inf = ref.info(r)
+                    arr = ref.arrays(r)
+                    rm = ref.masses(r)
+                    gr = order[np.searchsorted(m[order], rm[inf["start"]:inf["end"]])]
+                    new = [a.copy() for a in arr[1:5]]
+                    for k in range(3):
+                        cur = state[r][k][s_:e_].cpu().numpy()
+                        state[r][k][s_:e_] = _dev(np.clip(cur + d[k][gid], lim[0], lim[1]))
+                        new[k][inf["start"]:inf["end"]] = np.clip(new[k][inf["start"]:inf["end"]] + d[k][gr], lim[0], lim[1])
+                    ref.set(r, new[0], new[1], new[2], new[3])
+                    ref.set_mass(r, rm)
+
+            def one(r):
+                sx, sy, sz, sh, sm = state[r]
+                keys, sx, sy, sz, sh, sm, _ = doms[r].sync_grav(sx, sy, sz, sh, sm)
+                state[r] = [sx, sy, sz, sh, sm]
+                return keys
+            keys = world.run(one)
+            ref.sync_grav()
+            for r in range(P):
+                dom, inf, tr = doms[r], ref.info(r), ref.trees(r)
+                lv = dom.let_view()
+                assert np.array_equal(lv["leaves"], tr["focus_leaves"]), "sync %d: focus leaves of rank %d" % (it, r)
+                assert np.array_equal(lv["counts"], tr["focus_counts"]), "sync %d: leaf counts of rank %d" % (it, r)
+                assert np.array_equal(lv["assignment"], tr["focus_assignment"])
+                assert np.array_equal(lv["layout"], tr["layout"]), "sync %d: layout of rank %d" % (it, r)
+                assert (dom.start_index, dom.end_index, dom.n_particles_with_halos) == (inf["start"], inf["end"], inf["size"])
+                cen, macs = dom.let_centers()
+                assert np.array_equal(cen.cpu().numpy(), ref.centers(r)), "sync %d: expansion centres of rank %d" % (it, r)
+                rk, rx, ry, rz, rh = ref.arrays(r)
+                assert np.array_equal(keys[r].cpu().numpy().view(np.uint64), rk)
+                for name, mine, f in zip("xyzh", state[r][:4], (rx, ry, rz, rh)):
+                    assert np.array_equal(mine.cpu().numpy(), f), "sync %d: %s with halos of rank %d" % (it, name, r)
+                s_, e_ = dom.start_index, dom.end_index
+                assert np.array_equal(state[r][4][s_:e_].cpu().numpy(), ref.masses(r)[s_:e_])
+    finally:
+        for d in doms:
+            d.close()
+        world.close()
+        ref.close()
+
+
 def test_ranks_with_fewer_particles_than_the_bucket():
     """every rank holds fewer particles than bucketSizeFocus: the only focus leaf is the root and straddles every rank
     boundary (such leaves used to publish no halo box, neighbour lists came out truncated)"""
