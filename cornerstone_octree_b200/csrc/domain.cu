@@ -805,7 +805,7 @@ public:
     int64_t syncGravBegin(uint64_t nIn, const T* x, const T* y, const T* z, const T* h, int nprops, const void* const* props,
                           const int* propBytes)
     {
-        if (nRanks_ < 2 || haloMode_ != 1 || nprops < 1 || propBytes[0] != int(sizeof(T))) return CSTONE_E_INVALID_ARGUMENT;
+        if (haloMode_ != 1 || nprops < 1 || propBytes[0] != int(sizeof(T))) return CSTONE_E_INVALID_ARGUMENT;
         grav_           = true;
         const int64_t r = syncBegin(nIn, x, y, z, h, nprops, props, propBytes);
         grav_           = false;
@@ -909,6 +909,9 @@ private:
     int sfcKind_      = CSTONE_SFC_HILBERT;
     float haloFactor_ = 1.0f;
     int haloMode_     = 0;
+    //! the multi-rank code path (assignment, exchange, focus tree, halos) runs, possibly over a world of one rank
+    bool multi() const { return nRanks_ > 1 || haloMode_ == 1; }
+    std::unique_ptr<LocalWorld> selfWorld_;
     bool grav_        = false; // this sync is a syncGrav: property 0 is the mass
     bool gravReady_   = false; // the expansion centres belong to the current tree (the last sync was a syncGrav)
     float centerDriftTol_ = 1.05f; // [ref: domain/domain.hpp:665]
@@ -1127,6 +1130,12 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
 {
     if (nprops < 0 || nprops > kMaxProps || (nIn && (!x || !y || !z || !h))) return CSTONE_E_INVALID_ARGUMENT;
     if (nRanks_ > 1 && !comm_) return CSTONE_E_INVALID_ARGUMENT; // set_comm or set_local_world first
+    if (nRanks_ == 1 && haloMode_ == 1 && !comm_)
+    {
+        // one rank in the reference halo mode runs the multi-rank code path (focus tree and all) over a world of one
+        selfWorld_.reset(new LocalWorld(1));
+        comm_.reset(new LocalComm(selfWorld_.get(), 0));
+    }
     if (nIn >= (uint64_t(1) << 30)) return CSTONE_E_TOO_LARGE;
     uint64_t inStart = 0, inEnd = nIn;
     if (!firstCall_)
@@ -1187,7 +1196,7 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
     mark(4);
 
     void* dst[4 + kMaxProps];
-    if (nRanks_ == 1)
+    if (!multi())
     {
         // every particle stays: one gather into the final arrays, no halos
         nAssigned_ = np, start_ = 0, end_ = np, nTotal_ = np, nHaloSend_ = 0;
@@ -1397,7 +1406,7 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
     }
 
     // 10. search tree over assigned + halo particles, linked, with node centres and layout
-    if (nRanks_ > 1 && haloMode_ == 1)
+    if (haloMode_ == 1)
     {
         // the LET is the search tree [ref: domain/domain.hpp:423-436 octreeProperties]; layout: present leaves only
         mark(9);
@@ -2075,7 +2084,7 @@ int Engine<K, T>::reapplySync(int narrays, const void* const* in, const int* eb,
         src[a] = static_cast<const char*>(in[a]) + size_t(pat_.inStart) * eb[a];
         dst[a] = static_cast<char*>(out[a]) + size_t(pat_.start) * eb[a];
     }
-    if (nRanks_ == 1)
+    if (!multi())
     {
         if (np) CSB_TRY(gatherMulti(order_.template as<uint32_t>(), np, narrays, src, dst, eb));
         return int(cudaStreamSynchronize(s_));

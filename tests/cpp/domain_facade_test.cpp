@@ -205,7 +205,7 @@ static void run(int rank, int nRanks, const std::array<char, 128>& id, LocalInde
         x = cx, y = cy, psum = csum;
     }
 
-    if (refHalos && nRanks > 1)
+    if (refHalos)
     {
         // [ref: domain/domain.hpp:245-325 syncGrav] masses travel with the particles, keys stay sorted, sizes agree
         DeviceVector<T> m(std::vector<T>(x.size(), T(1) / T(numGlobal)));
@@ -302,6 +302,7 @@ int main(int argc, char** argv)
     }
     if (nRanks == 1)
     {
+        run<uint64_t, double>(rank, nRanks, id, n, false, true); // focus tree of the reference halo mode + syncGrav, one rank
         run<uint64_t, double>(rank, nRanks, id, n, true);
         run<uint32_t, float>(rank, nRanks, id, n / 2, false);
     }

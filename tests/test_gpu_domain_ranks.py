@@ -213,7 +213,10 @@ def test_ranks_match_reference_domain(cloud, P, n, bucket, bucket_focus):
         rk.close()
 
 
-@pytest.mark.parametrize("cloud,P,n,bucket,bucket_focus", CASES, ids=["%s-P%d" % (c[0], c[1]) for c in CASES])
+LET_CASES = CASES + [("gaussian", 1, 12000, 64, 8)]  # one rank: the focus tree alone (no peers, no halos)
+
+
+@pytest.mark.parametrize("cloud,P,n,bucket,bucket_focus", LET_CASES, ids=["%s-P%d" % (c[0], c[1]) for c in LET_CASES])
 def test_ranks_reference_halo_mode(cloud, P, n, bucket, bucket_focus):
     """halo mode 1 (multi-rank focus tree + Halos::discover as in the reference): focus tree, layout, index ranges,
     halos and raw neighbour lists bit-exact against the reference Domain, first sync and displaced steady-state syncs"""
@@ -234,8 +237,9 @@ def test_ranks_reference_halo_mode(cloud, P, n, bucket, bucket_focus):
 
 
 @pytest.mark.parametrize("cloud,P,n,bucket,bucket_focus", [("gaussian", 2, 20000, 64, 8), ("gaussian", 4, 20000, 50, 10),
-                                                          ("two-clusters", 3, 24000, 64, 8), ("gaussian", 8, 40000, 128, 16)],
-                         ids=["gaussian-P2", "gaussian-P4", "two-clusters-P3", "gaussian-P8"])
+                                                          ("two-clusters", 3, 24000, 64, 8), ("gaussian", 8, 40000, 128, 16),
+                                                          ("gaussian", 1, 12000, 64, 8)],
+                         ids=["gaussian-P2", "gaussian-P4", "two-clusters-P3", "gaussian-P8", "gaussian-P1"])
 def test_ranks_sync_grav_matches_reference(cloud, P, n, bucket, bucket_focus):
     """Domain::syncGrav [ref: domain/domain.hpp:245-325] on thread-ranks against the reference's: focus tree refined by
     the vector MAC (leaves, counts, assignment), expansion centres and MAC radii of every node, layout, index ranges,
