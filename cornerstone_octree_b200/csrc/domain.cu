@@ -2408,6 +2408,28 @@ int cstone_b200_host_assignment_k32(int nranks, const uint32_t* leaves, const ui
     std::copy(c.begin(), c.end(), rankCounts);
     return 0;
 }
+#define CSB_HOST_PEERS(KS, K, TS, T)                                                                                   \
+    int cstone_b200_host_find_peers_##KS##_##TS(int sfcKind, int myRank, int nranks, const K* boundaries,              \
+                                                const K* leaves, int32_t numLeaves, const cstone_box_##TS* box,        \
+                                                float invThetaEff, int32_t* isPeer)                                    \
+    {                                                                                                                  \
+        if (!boundaries || !leaves || !box || !isPeer || numLeaves < 1 || nranks < 1 || myRank < 0 || myRank >= nranks) \
+            return CSTONE_E_INVALID_ARGUMENT;                                                                          \
+        csb::HostOctree<K> tree;                                                                                       \
+        tree.build(leaves, numLeaves);                                                                                 \
+        std::vector<K> bnd(boundaries, boundaries + nranks + 1);                                                       \
+        std::vector<int> peers = csb::findPeersMacHost<K, T>(sfcKind, myRank, bnd, tree, *box, invThetaEff);           \
+        for (int r = 0; r < nranks; ++r)                                                                               \
+            isPeer[r] = 0;                                                                                             \
+        for (int p : peers)                                                                                            \
+            isPeer[p] = 1;                                                                                             \
+        return 0;                                                                                                      \
+    }
+CSB_HOST_PEERS(k32, uint32_t, f32, float)
+CSB_HOST_PEERS(k32, uint32_t, f64, double)
+CSB_HOST_PEERS(k64, uint64_t, f32, float)
+CSB_HOST_PEERS(k64, uint64_t, f64, double)
+
 int cstone_b200_host_uniform_bins(const uint32_t* counts, int32_t numLeaves, int32_t numBins, int32_t* bins,
                                   uint32_t* binCounts)
 {

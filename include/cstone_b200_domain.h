@@ -153,6 +153,17 @@ int cstone_b200_host_assignment_k64(int nranks, const uint64_t* leaves, const ui
                                     const uint64_t* old_boundaries, uint64_t* boundaries, uint32_t* rank_counts);
 int cstone_b200_host_assignment_k32(int nranks, const uint32_t* leaves, const uint32_t* counts, int32_t num_leaves,
                                     const uint32_t* old_boundaries, uint32_t* boundaries, uint32_t* rank_counts);
+/* [ref: traversal/peers.hpp:62-117 findPeersMac] HOST function: ranks owning a global leaf that fails the mutual
+ * minimum-distance / vector MAC (inv_theta_eff) against a global leaf of my_rank, by a dual traversal of the global
+ * tree given as its leaf keys (num_leaves + 1 keys); boundaries: nranks + 1 keys; is_peer: nranks flags */
+#define CSTONE_B200_HOST_PEERS_DECL(KS, K, TS)                                                                         \
+    int cstone_b200_host_find_peers_##KS##_##TS(int sfc_kind, int my_rank, int nranks, const K* boundaries,            \
+                                                const K* leaves, int32_t num_leaves, const cstone_box_##TS* box,       \
+                                                float inv_theta_eff, int32_t* is_peer);
+CSTONE_B200_HOST_PEERS_DECL(k32, uint32_t, f32)
+CSTONE_B200_HOST_PEERS_DECL(k32, uint32_t, f64)
+CSTONE_B200_HOST_PEERS_DECL(k64, uint64_t, f32)
+CSTONE_B200_HOST_PEERS_DECL(k64, uint64_t, f64)
 /* [ref: domain/domaindecomp.hpp:48-71 uniformBins] bins[num_bins+1] (leaf indices), bin_counts[num_bins] */
 int cstone_b200_host_uniform_bins(const uint32_t* counts, int32_t num_leaves, int32_t num_bins, int32_t* bins,
                                   uint32_t* bin_counts);

@@ -310,6 +310,24 @@ int getTree(void* h, int rank, int which, void* out)
     return 0;
 }
 
+//! the reference's findPeersMac [ref: traversal/peers.hpp:62-117] on a global leaf array and rank boundaries
+template<class K, class T>
+int findPeers(int myRank, int numRanks, const K* boundaries, const K* leaves, int numLeaves, const T* lim, const int* pbc,
+              float invThetaEff, int* isPeer)
+{
+    Octree<K> tree;
+    tree.update(leaves, numLeaves);
+    SfcAssignment<K> assignment(numRanks);
+    for (int r = 0; r <= numRanks; ++r)
+        assignment.set(r, boundaries[r], 0);
+    std::vector<int> peers = findPeersMac(myRank, assignment, tree, toBox<T>(lim, pbc), invThetaEff);
+    for (int r = 0; r < numRanks; ++r)
+        isPeer[r] = 0;
+    for (int p : peers)
+        isPeer[p] = 1;
+    return 0;
+}
+
 } // namespace
 
 #define REFDOM_DEF(KS, K, TS, T)                                                                                       \
@@ -323,6 +341,12 @@ int getTree(void* h, int rank, int which, void* out)
                                       const T* p0, const T* p1)                                                        \
     {                                                                                                                  \
         return setRank<K, T>(h, rank, n, x, y, z, hh, p0, p1);                                                         \
+    }                                                                                                                  \
+    int cstone_refdom_find_peers_##KS##_##TS(int myRank, int numRanks, const K* boundaries, const K* leaves,           \
+                                             int numLeaves, const T* lim, const int* pbc, float invThetaEff,           \
+                                             int* isPeer)                                                              \
+    {                                                                                                                  \
+        return findPeers<K, T>(myRank, numRanks, boundaries, leaves, numLeaves, lim, pbc, invThetaEff, isPeer);        \
     }                                                                                                                  \
     int cstone_refdom_set_mass_##KS##_##TS(void* h, int rank, uint64_t n, const T* m)                                  \
     {                                                                                                                  \

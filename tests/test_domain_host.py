@@ -164,3 +164,48 @@ def test_limit_box_shrinking_golden():
     fit = np.array([-1, 2, -2, 3, -4, 6], dtype=np.float64)
     lib.cstone_b200_host_limit_box_shrinking_f64(_p(fit), _p(prev), _p(out))
     assert out.tolist() == fit.tolist()
+
+
+@pytest.mark.parametrize("kd,fd", [(np.uint64, np.float64), (np.uint32, np.float64), (np.uint64, np.float32)])
+def test_find_peers_vs_reference(port, kd, fd):
+    """findPeersMac [ref: traversal/peers.hpp:62-117]: the host dual traversal of the library (csrc/let_tree.cuh) against
+    the reference's, on global trees of clustered clouds: many rank counts, open and periodic boxes, min-MAC and
+    vector-MAC opening parameters"""
+    import ctypes as C
+    import gen
+    from oracle import loader
+    if not loader.refdom_available():
+        pytest.skip("oracle/_ref/liboracle_refdom.so not built")
+    from cornerstone_octree_b200 import _lib, ops
+    rlib = C.CDLL(loader._REFDOM_PATH)
+    sfx = "_%s_%s" % ("k64" if kd == np.uint64 else "k32", "f64" if fd == np.float64 else "f32")
+    mine = getattr(_lib.lib, "cstone_b200_host_find_peers" + sfx)
+    refp = getattr(rlib, "cstone_refdom_find_peers" + sfx)
+    mine.restype = refp.restype = C.c_int
+    ptr = lambda a: a.ctypes.data_as(C.c_void_p)
+    checked = with_non_peers = 0
+    for trial, (nranks, bucket, theta) in enumerate([(2, 64, 0.5), (8, 32, 1.0), (13, 8, 0.4), (64, 4, 0.5)]):
+        keys = np.sort(gen.gaussian_keys(12000 + 1000 * trial, kd, seed=40 + trial))
+        leaves, counts = port.compute_octree(keys, bucket)
+        bnd, _ = assignment(nranks, leaves, counts)
+        bnd = np.ascontiguousarray(bnd, dtype=kd)
+        for pbc in ((0, 0, 0), (1, 0, 1)):
+            lim = np.array([-1.0, 1.0, -1.0, 1.0, -1.0, 1.0], dtype=fd)
+            import torch
+            box = ops.make_box((-1.0, 1.0), tuple(1 if p else 0 for p in pbc), dtype=torch.float64 if fd == np.float64 else torch.float32)
+            pb = np.array(pbc, dtype=np.int32)
+            for inv_theta in (np.float32(1.0 / theta + 0.5), np.float32(1.0 / theta + np.sqrt(np.float32(3.0))), np.float32(1.0)):
+                for rank in sorted({0, nranks // 2, nranks - 1}):
+                    a = np.zeros(nranks, dtype=np.int32)
+                    b = np.zeros(nranks, dtype=np.int32)
+                    st = mine(1, rank, nranks, ptr(bnd), ptr(leaves), C.c_int32(leaves.size - 1), C.byref(box),
+                              C.c_float(float(inv_theta)), ptr(a))
+                    assert st == 0
+                    st = refp(rank, nranks, ptr(bnd), ptr(leaves), leaves.size - 1, ptr(lim), ptr(pb), C.c_float(float(inv_theta)),
+                              ptr(b))
+                    assert st == 0
+                    assert np.array_equal(a, b), "peers of rank %d of %d (pbc %s, 1/theta %g)" % (rank, nranks, pbc, inv_theta)
+                    assert a[rank] == 0
+                    checked += 1
+                    with_non_peers += int(a.sum() < nranks - 1)
+    assert checked >= 60 and with_non_peers > 10
