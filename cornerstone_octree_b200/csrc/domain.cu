@@ -21,7 +21,9 @@
  */
 #include <nccl.h>
 
+#include <chrono>
 #include <cstdio>
+#include <string>
 #include <memory>
 #include <cstdlib>
 #include <cstring>
@@ -532,6 +534,23 @@ __global__ void __launch_bounds__(256)
 //   slot 0/1    data of the exchanges with even / odd epoch; per array a region of align256(recvTotal[q] * elemBytes[a])
 //               bytes, inside it the elements of source rank r start at element sum(count[r' -> q], r' < r).
 // ------------------------------------------------------------------------------------------------
+//! out[rangeOffset[r] + k] = rangeStart[r] + k for k < rangeOffset[r + 1] - rangeOffset[r]: index ranges written out
+__global__ void __launch_bounds__(256) expandRangesKernel(const uint32_t* __restrict__ rangeStart, const uint32_t* __restrict__ rangeOffset,
+                                                          int numRanges, uint32_t total, uint32_t* __restrict__ out)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
+    {
+        int lo = 0, hi = numRanges; // the range with rangeOffset[r] <= i < rangeOffset[r + 1]
+        while (hi - lo > 1)
+        {
+            const int mid = (lo + hi) / 2;
+            if (rangeOffset[mid] <= i) lo = mid;
+            else hi = mid;
+        }
+        out[i] = rangeStart[lo] + (i - rangeOffset[lo]);
+    }
+}
+
 //! [ref: focus/octree_focus_mpi.hpp:600-610 addMacs] leaves whose node failed the MAC become halos too
 __global__ void __launch_bounds__(256)
     addMacsKernel(const char* __restrict__ macs, const int32_t* __restrict__ leafToInternal, int numLeaves, int32_t* __restrict__ flags)
@@ -768,8 +787,8 @@ public:
     }
     //! LET mode: host copies of the focus-tree leaves, their counts, the halo flags, the layout, the peer assignment
     const LetTree<K, T>* let() const { return let_.get(); }
-    const std::vector<int32_t>& letFlags() const { return hFlags_; }
-    const std::vector<uint32_t>& letLayout() const { return hLayout_; }
+    const PinnedVec<int32_t>& letFlags() const { return hFlags_; }
+    const PinnedVec<uint32_t>& letLayout() const { return hLayout_; }
     //! [ref: domain/domain.hpp:404-406 startCell / endCell] leaves of the search tree that hold the assigned particles
     int cells(int32_t* out2)
     {
@@ -917,8 +936,9 @@ private:
     float centerDriftTol_ = 1.05f; // [ref: domain/domain.hpp:665]
     DevBuf sgx_, sgy_, sgz_, sgm_; // x, y, z, m of the assigned particles in SFC order (syncGrav: expansion centres)
     std::unique_ptr<LetTree<K, T>> let_;
-    std::vector<int32_t> hFlags_;
-    std::vector<uint32_t> hLayout_;
+    PinnedVec<int32_t> hFlags_;   // host copies in page-locked memory
+    PinnedVec<uint32_t> hLayout_;
+    DevBuf letLayoutDev_;
     cudaStream_t s_   = nullptr; // legacy default stream: ordered with the caller's default-stream work
 
     // particle state
@@ -1411,7 +1431,7 @@ int64_t Engine<K, T>::syncBegin(uint64_t nIn, const T* x, const T* y, const T* z
         // the LET is the search tree [ref: domain/domain.hpp:423-436 octreeProperties]; layout: present leaves only
         mark(9);
         CSB_TRY(linkTree(search_, lnS_, true, true));
-        CSB_CUDA(cudaMemcpyAsync(lnS_.layout.p, hLayout_.data(), 4 * hLayout_.size(), cudaMemcpyHostToDevice, s_));
+        CSB_CUDA(cudaMemcpyAsync(lnS_.layout.p, letLayoutDev_.p, 4 * hLayout_.size(), cudaMemcpyDeviceToDevice, s_));
         mark(10);
     }
     else
@@ -1627,6 +1647,20 @@ int Engine<K, T>::discoverHalosLet()
     if (!let_) let_.reset(new LetTree<K, T>(rank_, P, bucketFocus_, sfcKind_));
     LetTree<K, T>& let = *let_;
 
+    // optional section timing (CSB_HALO_TIMING=1): wall time between laps, stream drained at each lap, rank 0 prints
+    static const bool lapOn = std::getenv("CSB_HALO_TIMING") != nullptr;
+    std::string lapLog;
+    auto lapT = std::chrono::steady_clock::now();
+    auto lap = [&](const char* name)
+    {
+        if (!lapOn) return;
+        cudaStreamSynchronize(s_);
+        auto now = std::chrono::steady_clock::now();
+        char buf[64];
+        std::snprintf(buf, sizeof(buf), " %s %.2f", name, std::chrono::duration<double, std::milli>(now - lapT).count());
+        lapLog += buf;
+        lapT = now;
+    };
     // a. peers [ref: traversal/peers.hpp:62-117], focus tree [ref: domain/domain.hpp:219-228]
     HostOctree<K> gtree;
     gtree.build(hGlobalLeaves_.data(), global_.numNodes);
@@ -1634,6 +1668,7 @@ int Engine<K, T>::discoverHalosLet()
     // [ref: traversal/macs.hpp:45-48 invThetaMinMac / invThetaVecMac]
     const float invThetaEff = grav ? 1.0f / theta_ + std::sqrt(3.0f) : 1.0f / theta_ + 0.5f;
     const std::vector<int> peers = findPeersMacHost<K, T>(sfcKind_, rank_, boundaries_, gtree, box_, invThetaEff);
+    lap("peers");
     CSB_TRY(small_.reserve(size_t(P + 1) * (sizeof(K) + 4) + size_t(P) * P * 4 + 4096));
     auto allSum = [&](int& v) -> int
     {
@@ -1683,7 +1718,6 @@ int Engine<K, T>::discoverHalosLet()
     }
     int haloFail = 0;
     bool consistent = true;
-    std::vector<uint32_t> sendIdx;
     do
     {
     haloFail = 0;
@@ -1698,13 +1732,17 @@ int Engine<K, T>::discoverHalosLet()
     else
     {
         CSB_TRY(let.updateMinMac(boundaries_, invThetaEff, s_));
-        CSB_TRY(treeAndCounts(nullptr));
+        lap("minMac");
+        CSB_TRY(let.updateTree(comm_.get(), peers, boundaries_, box_, nullptr, s_));
+        lap("updateTree");
+        CSB_TRY(let.updateCounts(comm_.get(), skeys, n, hGlobalLeaves_, hGlobalCounts_, s_));
+        lap("updateCounts");
     }
 
     const FocusTree<K>& ft           = let.t;
     const int L                      = ft.numLeaves_;
-    const std::vector<K>& leaves     = let.leaves();
-    const std::vector<uint32_t>& cnt = let.leafCounts();
+    const PinnedVec<K>& leaves     = let.leaves();
+    const PinnedVec<uint32_t>& cnt = let.leafCounts();
     const auto& assign               = let.assignment();
     const int firstNode = assign[rank_][0], lastNode = assign[rank_][1], numSearch = lastNode - firstNode;
 
@@ -1736,17 +1774,14 @@ int Engine<K, T>::discoverHalosLet()
     CSB_CUDA(cudaMemcpyAsync(hFlags_.data(), flags_.p, 4 * size_t(L), cudaMemcpyDeviceToHost, s_));
     CSB_CUDA(cudaStreamSynchronize(s_));
 
+    lap("findHalos");
     // c. layout of the present leaves [ref: domain/layout.hpp:150-164 computeNodeLayout]
     hLayout_.resize(size_t(L) + 1);
-    {
-        uint32_t run = 0;
-        for (int i = 0; i < L; ++i)
-        {
-            hLayout_[i] = run;
-            if ((firstNode <= i && i < lastNode) || hFlags_[i]) run += cnt[i];
-        }
-        hLayout_[L] = run;
-    }
+    CSB_TRY(letLayoutDev_.reserve(4 * (size_t(L) + 1) + 256));
+    CSB_TRY(cstone_b200_compute_node_layout(ft.leafCounts_.template as<uint32_t>(), flags_.template as<int32_t>(), firstNode, lastNode, L,
+                                            letLayoutDev_.template as<uint32_t>(), scanTemp_.p, s_));
+    CSB_CUDA(cudaMemcpyAsync(hLayout_.data(), letLayoutDev_.p, 4 * (size_t(L) + 1), cudaMemcpyDeviceToHost, s_));
+    CSB_CUDA(cudaStreamSynchronize(s_));
     start_ = hLayout_[firstNode], end_ = hLayout_[lastNode], nTotal_ = hLayout_[L];
     pat_.start = start_;
     const bool tooLarge = nTotal_ >= (uint64_t(1) << 30); // reported with the other flags in step f, on all ranks
@@ -1776,33 +1811,51 @@ int Engine<K, T>::discoverHalosLet()
     }
     CSB_TRY(let.exchangeBytes(comm_.get(), requests, requested, s_));
     haloSendCount_.assign(P, 0), haloSendOffset_.assign(P + 1, 0);
-    sendIdx.clear();
+    std::vector<uint32_t> rangeStart, rangeOffset;
+    uint32_t numSend = 0;
     consistent = uint64_t(end_ - start_) == uint64_t(n) && !tooLarge;
     for (int q = 0; q < P; ++q)
     {
-        haloSendOffset_[q] = uint32_t(sendIdx.size());
+        haloSendOffset_[q] = numSend;
         const size_t nk    = requested[q].size() / sizeof(K);
         const K* rk        = reinterpret_cast<const K*>(requested[q].data());
+        int pos            = 0;
         for (size_t k = 0; k + 1 < nk; k += 2)
         {
-            const uint32_t lo = hLayout_[findNodeAbove(leaves.data(), L + 1, rk[k])];
-            const uint32_t hi = hLayout_[findNodeAbove(leaves.data(), L + 1, rk[k + 1])];
+            // (the requested key ranges of one peer ascend)
+            pos               = findNodeAboveFrom(leaves.data(), L + 1, pos, rk[k]);
+            const uint32_t lo = hLayout_[pos];
+            pos               = findNodeAboveFrom(leaves.data(), L + 1, pos, rk[k + 1]);
+            const uint32_t hi = hLayout_[pos];
             // [ref: halos/halos.hpp:40-55 checkIndices] only assigned particles travel as halos
             if (lo < start_ || hi > end_ || hi < lo)
             {
                 consistent = false;
                 continue;
             }
-            for (uint32_t j = lo; j < hi; ++j)
-                sendIdx.push_back(j - uint32_t(start_));
+            if (hi == lo) continue;
+            rangeStart.push_back(lo - uint32_t(start_));
+            rangeOffset.push_back(numSend);
+            numSend += hi - lo;
         }
-        haloSendCount_[q] = uint32_t(sendIdx.size()) - haloSendOffset_[q];
+        haloSendCount_[q] = numSend - haloSendOffset_[q];
     }
-    haloSendOffset_[P] = uint32_t(sendIdx.size());
-    nHaloSend_         = sendIdx.size();
-    CSB_TRY(sendIdx_.reserve(4 * sendIdx.size() + 256));
-    if (!sendIdx.empty())
-        CSB_CUDA(cudaMemcpyAsync(sendIdx_.p, sendIdx.data(), 4 * sendIdx.size(), cudaMemcpyHostToDevice, s_));
+    rangeOffset.push_back(numSend);
+    haloSendOffset_[P] = numSend;
+    nHaloSend_         = numSend;
+    CSB_TRY(sendIdx_.reserve(4 * size_t(numSend) + 256));
+    if (numSend)
+    {
+        // the index list of the ranges is written on the device
+        const size_t nr = rangeStart.size();
+        CSB_TRY(sendScan_.reserve(4 * (2 * nr + 2) + 512));
+        uint32_t* dStart  = sendScan_.template as<uint32_t>();
+        uint32_t* dOffset = dStart + nr;
+        CSB_CUDA(cudaMemcpyAsync(dStart, rangeStart.data(), 4 * nr, cudaMemcpyHostToDevice, s_));
+        CSB_CUDA(cudaMemcpyAsync(dOffset, rangeOffset.data(), 4 * (nr + 1), cudaMemcpyHostToDevice, s_));
+        expandRangesKernel<<<gridFor(size_t(numSend), 256), 256, 0, s_>>>(dStart, dOffset, int(nr), numSend, sendIdx_.template as<uint32_t>());
+        CSB_LAUNCHED();
+    }
 
     // e. where the halos of each peer arrive [ref: domain/layout.hpp:166-183 computeHaloRecvList]
     haloRecvCount_.assign(P, 0), haloRecvOffset_.assign(P, 0);
@@ -1817,14 +1870,8 @@ int Engine<K, T>::discoverHalosLet()
         haloRecvCount_[peer]  = hLayout_[lastNz] - hLayout_[firstNz];
     }
     // [ref: halos/halos.hpp:58-100 checkHalos] every flagged leaf outside of my range must belong to a peer
-    for (int i = 0; i < L; ++i)
-    {
-        if (!hFlags_[i] || (firstNode <= i && i < lastNode)) continue;
-        bool found = false;
-        for (int peer : peers)
-            found = found || (assign[peer][0] <= i && i < assign[peer][1]);
-        if (!found) haloFail = 1;
-    }
+    for (uint32_t i : let.nonPeerLeaves()) // (the leaves outside of my range and of every peer's range)
+        if (hFlags_[i]) haloFail = 1;
     if (grav)
     {
         // [ref: domain/domain.hpp:309-317] a halo leaf outside of every peer: the tree lags the moving centres
@@ -1835,6 +1882,7 @@ int Engine<K, T>::discoverHalosLet()
     else if (haloFail) consistent = false;
     } while (grav && haloFail);
 
+    lap("layout+requests");
     /* f. every rank sees every send and expected receive count: a mismatch (counts of a peer's range that differ from
      *    the owner's) ends the sync on ALL ranks with an error instead of a hanging exchange */
     {
@@ -1863,6 +1911,7 @@ int Engine<K, T>::discoverHalosLet()
                 haloMatrix_[size_t(a) * P + b] = all[size_t(a) * (2 * P + 1) + b];
     }
 
+    lap("agree");
     // g. assigned particles to their final position, halos of x,y,z,h, keys of the halos
     mark(7);
     void* dst[4 + kMaxProps];
@@ -1885,6 +1934,8 @@ int Engine<K, T>::discoverHalosLet()
     if (nTotal_ > end_)
         CSB_TRY((Api<K, T>::keys(sfcKind_, fx + end_, fy + end_, fz + end_, fk + end_, size_t(nTotal_ - end_), &box_, s_)));
 
+    lap("gather+halos");
+    if (lapOn && rank_ == 0) std::fprintf(stderr, "[csb rank 0] reference halo mode ms:%s\n", lapLog.c_str());
     gravReady_ = grav;
     // h. the LET becomes the search tree (leaves + counts; linked in syncBegin)
     const FocusTree<K>& ft = let.t;

@@ -4,6 +4,9 @@
  * description of the update steps and the reference lines they follow.
  */
 #pragma once
+#include <cstdlib>
+#include <cstring>
+#include <initializer_list>
 #include <vector>
 
 #include "common.cuh"
@@ -44,6 +47,65 @@ struct FBuf
     FBuf()                       = default;
     FBuf(const FBuf&)            = delete;
     FBuf& operator=(const FBuf&) = delete;
+};
+
+/*! host array in page-locked memory (grow-only, 30 % head room): the host copies of leaf keys, counts, halo flags and
+ *  layout that the multi-rank focus tree reads and writes every sync cross PCIe at full speed and asynchronously.
+ *  Falls back to pageable memory if the pinned allocation fails.  Only what the callers need of std::vector. */
+template<class U>
+class PinnedVec
+{
+public:
+    PinnedVec() = default;
+    PinnedVec(std::initializer_list<U> init) { assign(init.begin(), init.end()); }
+    PinnedVec(const PinnedVec&)            = delete;
+    PinnedVec& operator=(const PinnedVec&) = delete;
+    ~PinnedVec() { release(p_, pinned_); }
+
+    void resize(size_t n)
+    {
+        if (n > cap_)
+        {
+            const size_t cap = size_t(double(n) * 1.3) + 1024;
+            U* q             = nullptr;
+            bool pinned      = cudaMallocHost(reinterpret_cast<void**>(&q), cap * sizeof(U)) == cudaSuccess;
+            if (!pinned)
+            {
+                cudaGetLastError();
+                q = static_cast<U*>(std::malloc(cap * sizeof(U)));
+            }
+            if (n_) std::memcpy(q, p_, n_ * sizeof(U));
+            release(p_, pinned_);
+            p_ = q, cap_ = cap, pinned_ = pinned;
+        }
+        n_ = n;
+    }
+    void assign(const U* first, const U* last)
+    {
+        n_ = 0;
+        resize(size_t(last - first));
+        if (n_) std::memcpy(p_, first, n_ * sizeof(U));
+    }
+    U* data() { return p_; }
+    const U* data() const { return p_; }
+    size_t size() const { return n_; }
+    bool empty() const { return n_ == 0; }
+    U& operator[](size_t i) { return p_[i]; }
+    const U& operator[](size_t i) const { return p_[i]; }
+    const U& back() const { return p_[n_ - 1]; }
+    const U* begin() const { return p_; }
+    const U* end() const { return p_ + n_; }
+
+private:
+    static void release(U* p, bool pinned)
+    {
+        if (!p) return;
+        if (pinned) cudaFreeHost(p);
+        else std::free(p);
+    }
+    U* p_        = nullptr;
+    size_t n_    = 0, cap_ = 0;
+    bool pinned_ = false;
 };
 
 template<class K>
@@ -93,6 +155,14 @@ inline int lowerBoundKey(const uint32_t* first, size_t n, uint32_t v, uint64_t* 
 inline int lowerBoundKey(const uint64_t* first, size_t n, uint64_t v, uint64_t* out, void* temp, void* s)
 {
     return cstone_b200_lower_bound_u64(first, n, v, out, temp, s);
+}
+
+//! ops[idx[i]] = 0
+template<class I>
+__global__ void zeroAtKernel(const I* __restrict__ idx, int n, int* __restrict__ ops)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) ops[idx[i]] = 0;
 }
 
 template<class K>
@@ -163,6 +233,30 @@ public:
     int scatterCounts(cudaStream_t s);
     //! step 8c: internal node counts = sums of their children
     int upsweepCounts(cudaStream_t s);
+    /*! remove the leaves with the given indices (device array, n > 0): their key ranges join the leaf before them;
+     *  rebalance with ops 0 / 1 and relink  [ref: focus/exchange_focus.hpp:188-217 syncTreeletsGpu] */
+    int dropLeaves(const uint32_t* idxDev, int n, cudaStream_t s)
+    {
+        using A     = FocusApi<K>;
+        const int L = numLeaves_;
+        CSB_TRY(leafOps_.reserve((size_t(L) + 1) * 4));
+        CSB_TRY(nodeOps_.reserve((size_t(numNodes_) + 1) * 4));
+        CSB_TRY(temp_.reserve(size_t(cstone_b200_scan_temp_bytes(uint64_t(L) + 1)) + 4096));
+        const int one = 1;
+        CSB_TRY(cstone_b200_fill(leafOps_.p, size_t(L), &one, 4, s));
+        CSB_CUDA(cudaMemsetAsync(leafOps_.as<int>() + L, 0, 4, s));
+        zeroAtKernel<uint32_t><<<unsigned((n + 255) / 256), 256, 0, s>>>(idxDev, n, leafOps_.as<int>());
+        CSB_LAUNCHED();
+        CSB_TRY(cstone_b200_exclusive_scan_u32(leafOps_.as<uint32_t>(), nodeOps_.as<uint32_t>(), size_t(L) + 1, 0u, temp_.p, s));
+        int newL = 0;
+        CSB_CUDA(cudaMemcpyAsync(&newL, nodeOps_.as<int>() + L, 4, cudaMemcpyDeviceToHost, s));
+        CSB_CUDA(cudaStreamSynchronize(s));
+        CSB_TRY(newLeaves_.reserve((size_t(newL) + 1) * sizeof(K)));
+        CSB_TRY(A::rebal(leaves_.as<K>(), L, newL, nodeOps_.as<int>(), newLeaves_.as<K>(), s));
+        leaves_.swap(newLeaves_);
+        numLeaves_ = newL;
+        return link(s);
+    }
     //! replace the leaves by a HOST array and relink (counts / macs keep their buffers, contents are stale)
     int setLeavesHost(const K* leavesHost, int numLeaves, cudaStream_t s)
     {

@@ -27,7 +27,10 @@
 #include <algorithm>
 #include <array>
 #include <cmath>
+#include <chrono>
+#include <cstdio>
 #include <cstring>
+#include <string>
 #include <vector>
 
 #include "comm.hpp"
@@ -42,6 +45,21 @@ template<class K>
 inline int findNodeBelow(const K* leaves, int numLeafKeys, K key)
 {
     return int(std::upper_bound(leaves, leaves + numLeafKeys, key) - leaves) - 1;
+}
+
+//! findNodeAbove for a run of ascending keys: the search starts at the previous hit and gallops forward, so that a
+//! treelet of m keys is matched against n leaves in O(m log(n / m)) steps that stay in cache
+template<class K>
+inline int findNodeAboveFrom(const K* leaves, int numLeafKeys, int from, K key)
+{
+    int lo = std::min(from, numLeafKeys), step = 1;
+    while (lo + step < numLeafKeys && leaves[lo + step] < key)
+    {
+        lo += step;
+        step *= 2;
+    }
+    const int hi = std::min(lo + step + 1, numLeafKeys);
+    return int(std::lower_bound(leaves + lo, leaves + hi, key) - leaves);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -278,6 +296,28 @@ inline std::vector<K> hostApplyOps(const K* tree, int first, int last, const std
     return out;
 }
 
+/*! out[i] = index, in a linked tree given by its prefixes and level ranges, of the node that covers exactly the key
+ *  range [pairs[2i], pairs[2i+1]); -1 if the tree has no such node  [ref: tree/octree.hpp locateNode] */
+template<class K>
+__global__ void locateNodesKernel(const K* __restrict__ prefixes, const int* __restrict__ levelRange,
+                                  const K* __restrict__ pairs, int n, int32_t* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const K start        = pairs[2 * i];
+    const unsigned level = treeLevel<K>(K(pairs[2 * i + 1] - start));
+    const K prefix       = encodePlaceholderBit<K>(start, 3 * int(level));
+    int lo = levelRange[level], hi = levelRange[level + 1];
+    const int last = hi;
+    while (lo < hi)
+    {
+        const int mid = (lo + hi) / 2;
+        if (prefixes[mid] < prefix) lo = mid + 1;
+        else hi = mid;
+    }
+    out[i] = (lo < last && prefixes[lo] == prefix) ? lo : -1;
+}
+
 /*! mass centre of the particles whose keys lie in [ranges[2i], ranges[2i+1]), summed in particle order as the
  *  reference's massCenter does [ref: focus/source_center.hpp:68-80]; one thread per range (a handful of ranges) */
 template<class K, class T>
@@ -336,14 +376,16 @@ public:
             box_.lengths[d] = 1, box_.inv_lengths[d] = 1;
             box_.boundaries[d] = CSTONE_BOUNDARY_OPEN;
         }
-        leaves_ = {K(0), nodeRange<K>(0)};
-        leafCounts_ = {bucket + 1};
+        const K root[2]         = {K(0), nodeRange<K>(0)};
+        const uint32_t rootCount = bucket + 1;
+        leaves_.assign(root, root + 2);
+        leafCounts_.assign(&rootCount, &rootCount + 1);
     }
 
     FocusTree<K> t; // leaves, linked tree, counts, macs: device
 
-    const std::vector<K>& leaves() const { return leaves_; }
-    const std::vector<uint32_t>& leafCounts() const { return leafCounts_; }
+    const PinnedVec<K>& leaves() const { return leaves_; }
+    const PinnedVec<uint32_t>& leafCounts() const { return leafCounts_; }
     const std::vector<std::array<int, 2>>& assignment() const { return assign_; }
     const std::vector<int>& peers() const { return peers_; }
     int numLeaves() const { return int(leaves_.size()) - 1; }
@@ -382,17 +424,37 @@ public:
         }
         enforced.erase(std::unique(enforced.begin(), enforced.end()), enforced.end());
 
+        static const bool lapOn = std::getenv("CSB_HALO_TIMING") != nullptr;
+        auto lapT = std::chrono::steady_clock::now();
+        std::string lapLog;
+        auto lap = [&](const char* name)
+        {
+            if (!lapOn) return;
+            cudaStreamSynchronize(s);
+            auto now = std::chrono::steady_clock::now();
+            char buf[64];
+            std::snprintf(buf, sizeof(buf), " %s %.2f", name, std::chrono::duration<double, std::milli>(now - lapT).count());
+            lapLog += buf;
+            lapT = now;
+        };
+        lap("focusTransfer");
         bool conv = false;
         CSB_TRY(t.rebalanceStep(focusStart, focusEnd, enforced.data(), int(enforced.size()), &conv, s));
+        lap("rebalance");
         const float invThetaRefine = float(std::sqrt(3) / 2 + 1e-6);
         for (int c = 0; !c;)
             CSB_TRY(t.template macRefine<T>(&box, prevStart_, prevEnd_, focusStart, focusEnd, invThetaRefine, &c, s));
 
+        lap("macRefine");
         CSB_TRY(downloadLeaves(s));
         translateAssignment(bnd);
+        lap("leaves");
         CSB_TRY(syncTreelets(comm, s));
+        lap("treelets");
         CSB_TRY(indexTreelets(s));
         translateAssignment(bnd);
+        lap("index");
+        if (lapOn && rank_ == 0) std::fprintf(stderr, "[csb rank 0]   updateTree ms:%s\n", lapLog.c_str());
 
         box_       = box;
         globBnd_   = bnd;
@@ -525,10 +587,14 @@ public:
          * per sync and can be coarser than the global tree for a step; the reference then reads an unrelated node) takes
          * its centre from the particles directly. */
         std::vector<uint32_t> gmap, missing;
-        std::vector<K> missingRanges;
+        std::vector<K> missingRanges, myGlobal;
+        for (int i = firstGlb; i < lastGlb; ++i)
+            myGlobal.push_back(gLeaves[i]), myGlobal.push_back(gLeaves[i + 1]);
+        std::vector<int32_t> located;
+        CSB_TRY(locateNodes(t, myGlobal, located, s));
         for (int i = firstGlb; i < lastGlb; ++i)
         {
-            const int node = locateNode(gLeaves[i], gLeaves[i + 1], prefixes_.data(), t.levelRange_);
+            const int node = located[size_t(i - firstGlb)];
             if (node < 0)
             {
                 missing.push_back(uint32_t(i));
@@ -869,10 +935,13 @@ private:
             std::vector<K> tl = asKeys(from[peer]);
             std::vector<K> rej, kept;
             const int numNodes = int(tl.size()) - 1;
+            kept.reserve(tl.size());
+            int pos = 0;
             for (int i = 0; i < numNodes; ++i)
             {
                 const K k = tl[i];
-                if (k != leaves_[findNodeAbove(leaves_.data(), nk - 1, k)]) rej.push_back(k);
+                pos       = findNodeAboveFrom(leaves_.data(), nk - 1, pos, k); // (treelet keys ascend)
+                if (k != leaves_[pos]) rej.push_back(k);
                 else kept.push_back(k);
             }
             if (!tl.empty()) kept.push_back(tl.back());
@@ -880,23 +949,19 @@ private:
             rejected[peer]  = asBytes(rej);
         }
         CSB_TRY(exchangeBytes(comm, rejected, rejectedHere, s));
-        std::vector<char> keep(size_t(nk), 1);
-        bool any = false;
+        // the rejected keys leave my tree: on the device, then the host copy of the leaves is refreshed
+        std::vector<uint32_t> drop;
         for (int peer : peers_)
             for (K k : asKeys(rejectedHere[peer]))
-            {
-                keep[findNodeAbove(leaves_.data(), nk, k)] = 0;
-                any = true;
-            }
-        if (any)
+                drop.push_back(uint32_t(findNodeAbove(leaves_.data(), nk, k)));
+        if (!drop.empty())
         {
-            std::vector<K> nl;
-            nl.reserve(size_t(nk));
-            for (int i = 0; i + 1 < nk; ++i)
-                if (keep[i]) nl.push_back(leaves_[i]);
-            nl.push_back(leaves_.back());
-            leaves_.swap(nl);
-            CSB_TRY(uploadLeaves(s));
+            std::sort(drop.begin(), drop.end());
+            drop.erase(std::unique(drop.begin(), drop.end()), drop.end());
+            CSB_TRY(stage_.reserve(4 * drop.size() + 256));
+            CSB_CUDA(cudaMemcpyAsync(stage_.p, drop.data(), 4 * drop.size(), cudaMemcpyHostToDevice, s));
+            CSB_TRY(t.dropLeaves(stage_.as<uint32_t>(), int(drop.size()), s));
+            CSB_TRY(downloadLeaves(s));
         }
         return 0;
     }
@@ -905,35 +970,52 @@ private:
     //! [ref: focus/exchange_focus.hpp:237-262 indexTreelets, tree/octree.hpp locateNode]
     int indexTreelets(cudaStream_t s)
     {
-        const int M = t.numNodes_;
-        prefixes_.resize(size_t(M));
-        CSB_CUDA(cudaMemcpyAsync(prefixes_.data(), t.prefixes_.p, size_t(M) * sizeof(K), cudaMemcpyDeviceToHost, s));
-        CSB_CUDA(cudaStreamSynchronize(s));
         std::fill(tlOffset_.begin(), tlOffset_.end(), 0);
         for (int r = 0; r < P_; ++r)
             tlOffset_[r + 1] = tlOffset_[r] + (treelets_[r].empty() ? 0 : int(treelets_[r].size()) - 1);
-        tlIdx_.assign(size_t(tlOffset_[P_]), 0);
+        std::vector<K> pairs(2 * size_t(tlOffset_[P_]));
         for (int peer : peers_)
         {
             const std::vector<K>& tl = treelets_[peer];
             for (int i = 0; i + 1 < int(tl.size()); ++i)
             {
-                const unsigned level = treeLevel<K>(tl[i + 1] - tl[i]);
-                const K prefix       = encodePlaceholderBit<K>(tl[i], 3 * int(level));
-                const K* first       = prefixes_.data() + t.levelRange_[level];
-                const K* last        = prefixes_.data() + t.levelRange_[level + 1];
-                const K* it          = std::lower_bound(first, last, prefix);
-                if (it == last || *it != prefix)
-                {
-                    fail(__LINE__);
-                    continue;
-                }
-                tlIdx_[size_t(tlOffset_[peer]) + i] = uint32_t(it - prefixes_.data());
+                pairs[2 * (size_t(tlOffset_[peer]) + i)]     = tl[i];
+                pairs[2 * (size_t(tlOffset_[peer]) + i) + 1] = tl[i + 1];
             }
         }
+        // (ranks that are no peers any more keep a count of zero nodes: treelets_ was cleared in syncTreelets)
+        CSB_TRY(locateNodes(t, pairs, tlIdx_, s));
+        bool missing = false;
+        for (int32_t& v : tlIdx_)
+            if (v < 0)
+            {
+                fail(__LINE__);
+                v = 0, missing = true;
+            }
         CSB_TRY(tlIdxDev_.reserve(4 * tlIdx_.size() + 256));
         if (!tlIdx_.empty())
-            CSB_CUDA(cudaMemcpyAsync(tlIdxDev_.p, tlIdx_.data(), 4 * tlIdx_.size(), cudaMemcpyHostToDevice, s));
+        {
+            if (missing) CSB_CUDA(cudaMemcpyAsync(tlIdxDev_.p, tlIdx_.data(), 4 * tlIdx_.size(), cudaMemcpyHostToDevice, s));
+            else CSB_CUDA(cudaMemcpyAsync(tlIdxDev_.p, locOut_.p, 4 * tlIdx_.size(), cudaMemcpyDeviceToDevice, s));
+        }
+        CSB_CUDA(cudaStreamSynchronize(s));
+        return 0;
+    }
+
+    //! out[i] = node of `tree` covering [pairs[2i], pairs[2i+1]) or -1, located on the device (the prefixes stay in HBM);
+    //! the result is left in locOut_ as well
+    int locateNodes(const FocusTree<K>& tree, const std::vector<K>& pairs, std::vector<int32_t>& out, cudaStream_t s)
+    {
+        const size_t n = pairs.size() / 2;
+        out.assign(n, 0);
+        if (n == 0) return 0;
+        CSB_TRY(locIn_.reserve(2 * n * sizeof(K) + 256));
+        CSB_TRY(locOut_.reserve(4 * n + 256));
+        CSB_CUDA(cudaMemcpyAsync(locIn_.p, pairs.data(), 2 * n * sizeof(K), cudaMemcpyHostToDevice, s));
+        locateNodesKernel<K><<<unsigned((n + 255) / 256), 256, 0, s>>>(tree.prefixes_.template as<K>(), tree.levelRangeDev_.template as<int>(),
+                                                                      locIn_.template as<K>(), int(n), locOut_.template as<int32_t>());
+        CSB_LAUNCHED();
+        CSB_CUDA(cudaMemcpyAsync(out.data(), locOut_.p, 4 * n, cudaMemcpyDeviceToHost, s));
         CSB_CUDA(cudaStreamSynchronize(s));
         return 0;
     }
@@ -943,12 +1025,13 @@ private:
     int kind_;
     CBox box_;
     K prevStart_ = 0, prevEnd_ = 0;
-    std::vector<K> leaves_, prefixes_;
-    std::vector<uint32_t> leafCounts_;
+    PinnedVec<K> leaves_;               // host copy of the leaf keys
+    PinnedVec<uint32_t> leafCounts_;    // host copy of the leaf counts
+    FBuf locIn_, locOut_;               // key ranges to locate in a linked tree / their node indices
     std::vector<int> peers_;
     std::vector<std::vector<K>> treelets_;
     std::vector<int> tlOffset_;
-    std::vector<uint32_t> tlIdx_;
+    std::vector<int32_t> tlIdx_;
     std::vector<std::array<int, 2>> assign_;
     FBuf stage_, xchg_, sizes_, tlIdxDev_;
     // gravity side: the global tree linked on the device, centres of its leaves / nodes, helpers
