@@ -315,6 +315,68 @@ def test_ranks_sync_grav_matches_reference(cloud, P, n, bucket, bucket_focus):
         ref.close()
 
 
+@pytest.mark.parametrize("kd,fd", [(np.uint32, np.float64), (np.uint64, np.float32)], ids=["u32-f64", "u64-f32"])
+def test_reference_halo_mode_other_types(kd, fd):
+    """halo mode 1 and syncGrav with 32-bit keys / single-precision coordinates against the reference Domain of the same
+    types: focus tree, counts, layout, index ranges, arrays with halos, expansion centres"""
+    if not loader.refdom_available():
+        pytest.skip("oracle/_ref/liboracle_refdom.so did not travel")
+    import torch
+    from cornerstone_octree_b200 import ops
+    from cornerstone_octree_b200.domain import Domain, LocalWorld
+    P, n, bucket, bucket_focus = 3, 18000, 64, 8
+    x, y, z, h, lim, pbc = make_cloud("gaussian", n)
+    x, y, z, h = (a.astype(fd) for a in (x, y, z, h))
+    m = (0.5 + np.random.default_rng(5).random(n)).astype(fd)
+    td = torch.float64 if fd == np.float64 else torch.float32
+    bits = 8 * np.dtype(kd).itemsize
+    for grav in (False, True):
+        world = LocalWorld(P)
+        doms = [Domain(r, P, bucket, bucket_focus, 0.5, ops.make_box(lim, dtype=td), key_bits=bits, dtype=td) for r in range(P)]
+        ref = loader.RefDomain(P, bucket, bucket_focus, 0.5, list(lim), pbc=pbc, kdtype=kd, fdtype=fd, nprops=0)
+        state = []
+        for r, d in enumerate(doms):
+            d.set_local_world(world)
+            d.set_halo_mode(1)
+            s = slice(r * n // P, (r + 1) * n // P)
+            ref.set(r, x[s], y[s], z[s], h[s])
+            ref.set_mass(r, m[s])
+            state.append([_dev(a[s]) for a in (x, y, z, h, m)])
+        try:
+            for it in range(2):
+                def one(r):
+                    sx, sy, sz, sh, sm = state[r]
+                    if grav:
+                        keys, sx, sy, sz, sh, sm, _ = doms[r].sync_grav(sx, sy, sz, sh, sm)
+                    else:
+                        keys, sx, sy, sz, sh, (sm,) = doms[r].sync(sx, sy, sz, sh, [sm])
+                    state[r] = [sx, sy, sz, sh, sm]
+                    return keys
+                keys = world.run(one)
+                ref.sync_grav() if grav else ref.sync()
+                for r in range(P):
+                    dom, inf, tr, lv = doms[r], ref.info(r), ref.trees(r), doms[r].let_view()
+                    assert np.array_equal(lv["leaves"], tr["focus_leaves"]), "focus leaves of rank %d" % r
+                    assert np.array_equal(lv["counts"], tr["focus_counts"]), "leaf counts of rank %d" % r
+                    assert np.array_equal(lv["layout"], tr["layout"]), "layout of rank %d" % r
+                    assert np.array_equal(lv["assignment"], tr["focus_assignment"])
+                    assert (dom.start_index, dom.end_index, dom.n_particles_with_halos) == (inf["start"], inf["end"], inf["size"])
+                    rk, rx, ry, rz, rh = ref.arrays(r)
+                    assert np.array_equal(keys[r].cpu().numpy().view(kd), rk), "keys with halos of rank %d" % r
+                    for name, mine, f in zip("xyzh", state[r][:4], (rx, ry, rz, rh)):
+                        assert np.array_equal(mine.cpu().numpy(), f), "%s with halos of rank %d" % (name, r)
+                    if grav:
+                        assert np.array_equal(dom.let_centers()[0].cpu().numpy(), ref.centers(r)), "centres of rank %d" % r
+                    else:
+                        # the plain reference sync does not carry the masses: keep its arrays in step with ours
+                        ref.set_mass(r, np.zeros(inf["n"], dtype=fd))
+        finally:
+            for d in doms:
+                d.close()
+            world.close()
+            ref.close()
+
+
 def test_ranks_with_fewer_particles_than_the_bucket():
     """every rank holds fewer particles than bucketSizeFocus: the only focus leaf is the root and straddles every rank
     boundary (such leaves used to publish no halo box, neighbour lists came out truncated)"""
