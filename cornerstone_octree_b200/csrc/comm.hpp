@@ -18,6 +18,7 @@
 
 #include <condition_variable>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -276,6 +277,13 @@ public:
         for (int r = 0; r < w_->size; ++r)
             peers[r] = const_cast<void*>(w_->ptrs[r]);
         w_->barrier();
+        // test hook: the last rank behaves as if the peers' memory could not be mapped (the engine must then fall back
+        // to send/recv on ALL ranks)
+        if (std::getenv("CSB_TEST_FAIL_SHARE") && rank_ == w_->size - 1)
+        {
+            peers.clear();
+            return int(cudaErrorPeerAccessUnsupported);
+        }
         return 0;
     }
     void releaseShared(std::vector<void*>& peers) override { peers.clear(); }

@@ -377,6 +377,24 @@ def test_reference_halo_mode_other_types(kd, fd):
             ref.close()
 
 
+def test_halo_push_falls_back_when_peer_memory_cannot_be_mapped(monkeypatch):
+    """one rank cannot map its peers' windows (test hook in the in-process transport): all ranks switch to the
+    send/recv halo exchange together and the results stay those of the reference"""
+    if not loader.refdom_available():
+        pytest.skip("oracle/_ref/liboracle_refdom.so did not travel")
+    monkeypatch.setenv("CSB_TEST_FAIL_SHARE", "1")
+    x, y, z, h, lim, pbc = make_cloud("gaussian", 20000)
+    rk = Ranks(3, 64, 8, lim, pbc, x, y, z, h)
+    try:
+        rk.sync()
+        rk.check()
+        rk.displace(0.01)
+        rk.sync()
+        rk.check()
+    finally:
+        rk.close()
+
+
 def test_ranks_with_fewer_particles_than_the_bucket():
     """every rank holds fewer particles than bucketSizeFocus: the only focus leaf is the root and straddles every rank
     boundary (such leaves used to publish no halo box, neighbour lists came out truncated)"""
