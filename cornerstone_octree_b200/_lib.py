@@ -199,6 +199,10 @@ _DOMAIN_PROTOS = {
     "sync_begin": (_i64, [_vp, _u64, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "sync_grav_begin": (_i64, [_vp, _u64, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "let_centers": (_i, [_vp, _vp, _vp, _vp]),
+    "focus_peer_exchange": (_i, [_vp, _vp, _i]),
+    "focus_global_gather": (_i, [_vp, _vp, _i, _vp]),
+    "focus_global_extract": (_i, [_vp, _vp, _i, _vp]),
+    "global_octree": (_i, [_vp, _vp, _vp, _vp, _vp]),
     "sync_finish": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "exchange_halos": (_i, [_vp, _i, _vp, _vp]),
     "reapply_sync": (_i, [_vp, _i, _vp, _vp, _vp]),

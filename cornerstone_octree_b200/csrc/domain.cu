@@ -830,6 +830,44 @@ public:
         grav_           = false;
         return r;
     }
+    // ---- globalFocusExchange for client quantities [ref: focus/octree_focus_mpi.hpp:276-300 peerExchange, :762-784]
+    static bool elemOk(int eb) { return eb == 4 || eb == 8 || eb == 12 || eb == 16 || eb == 24 || eb == 32; }
+    //! nodeQ: one element per node of the focus tree (device).  Cells in a peer's range take the owner's values.
+    int focusPeerExchange(void* nodeQ, int eb)
+    {
+        if (haloMode_ != 1 || !let_ || !nodeQ || !elemOk(eb)) return CSTONE_E_INVALID_ARGUMENT;
+        CSB_TRY(let_->peerExchange(comm_.get(), nodeQ, eb, s_));
+        return int(cudaStreamSynchronize(s_));
+    }
+    //! gLeafQ: one element per GLOBAL leaf (device): my leaves from nodeQ, everybody else's from their owners
+    int focusGlobalGather(const void* nodeQ, int eb, void* gLeafQ)
+    {
+        if (haloMode_ != 1 || !let_ || !nodeQ || !gLeafQ || !elemOk(eb)) return CSTONE_E_INVALID_ARGUMENT;
+        CSB_TRY(let_->linkGlobal(hGlobalLeaves_, s_));
+        CSB_TRY(let_->populateGlobal(nodeQ, eb, hGlobalLeaves_, gLeafQ, nullptr, s_));
+        CSB_TRY(let_->gatherGlobalLeaves(comm_.get(), gLeafQ, eb, hGlobalLeaves_, s_));
+        CSB_CUDA(cudaStreamSynchronize(s_));
+        return let_->takeError() ? CSTONE_E_LET : 0;
+    }
+    //! gNodeQ: one element per node of the global octree (globalOctree()); cells of my tree that belong to no peer read theirs
+    int focusGlobalExtract(const void* gNodeQ, int eb, void* nodeQ)
+    {
+        if (haloMode_ != 1 || !let_ || !nodeQ || !gNodeQ || !elemOk(eb)) return CSTONE_E_INVALID_ARGUMENT;
+        CSB_TRY(let_->extractGlobal(gNodeQ, eb, nodeQ, s_));
+        CSB_CUDA(cudaStreamSynchronize(s_));
+        return let_->takeError() ? CSTONE_E_LET : 0;
+    }
+    //! the replicated global tree, linked on the device (valid after focusGlobalGather or syncGrav, until the next sync)
+    int globalOctree(int32_t* numLeaves, int32_t* numNodes, const void** p6, int32_t* levelRangeHost) const
+    {
+        if (!let_ || let_->globalTree().numLeaves_ == 0) return CSTONE_E_INVALID_ARGUMENT;
+        const FocusTree<K>& g = let_->globalTree();
+        *numLeaves = g.numLeaves_, *numNodes = g.numNodes_;
+        p6[0] = g.prefixes_.p, p6[1] = g.childOffsets_.p, p6[2] = g.parents_.p, p6[3] = g.levelRangeDev_.p, p6[4] = g.i2l_.p, p6[5] = g.l2i_.p;
+        for (unsigned l = 0; l < KeyTraits<K>::maxLevel + 2; ++l)
+            levelRangeHost[l] = g.levelRange_[l];
+        return 0;
+    }
     //! syncGrav: expansion centres (x, y, z, MAC radius^2) per node of the focus tree and its MAC marks (device)
     void letCenters(const void** centers4, const char** macs, int32_t* numNodes) const
     {
@@ -1892,7 +1930,12 @@ int Engine<K, T>::discoverHalosLet()
         std::vector<uint32_t> mine(2 * P + 1), all(size_t(2 * P + 1) * P);
         for (int q = 0; q < P; ++q)
             mine[q] = haloSendCount_[q], mine[P + q] = haloRecvCount_[q];
-        mine[2 * P] = (consistent && !let.takeError()) ? 0u : 1u;
+        const bool letError = let.takeError();
+        mine[2 * P]         = (consistent && !letError) ? 0u : 1u;
+        if (mine[2 * P] && std::getenv("CSB_TRACE_ERRORS"))
+            std::fprintf(stderr, "[cstone_b200] rank %d: inconsistent halo bookkeeping: assigned %llu, layout range %llu, halo leaf "
+                                 "outside of all peers %d, total %llu, tree step failed %d\n", rank_, (unsigned long long)n,
+                         (unsigned long long)(end_ - start_), haloFail, (unsigned long long)nTotal_, int(letError));
         CSB_CUDA(cudaMemcpyAsync(dMine, mine.data(), 4 * mine.size(), cudaMemcpyHostToDevice, s_));
         CSB_TRY(comm_->allGather(dMine, dAll, 4 * mine.size(), s_));
         CSB_CUDA(cudaMemcpyAsync(all.data(), dAll, 4 * all.size(), cudaMemcpyDeviceToHost, s_));
@@ -1902,7 +1945,13 @@ int Engine<K, T>::discoverHalosLet()
         {
             ok = ok && all[size_t(a) * (2 * P + 1) + 2 * P] == 0;
             for (int b = 0; b < P; ++b)
-                ok = ok && all[size_t(a) * (2 * P + 1) + b] == all[size_t(b) * (2 * P + 1) + P + a];
+            {
+                const bool same = all[size_t(a) * (2 * P + 1) + b] == all[size_t(b) * (2 * P + 1) + P + a];
+                if (!same && rank_ == 0 && std::getenv("CSB_TRACE_ERRORS"))
+                    std::fprintf(stderr, "[cstone_b200] halo counts disagree: rank %d sends %u to rank %d, which expects %u\n", a,
+                                 all[size_t(a) * (2 * P + 1) + b], b, all[size_t(b) * (2 * P + 1) + P + a]);
+                ok = ok && same;
+            }
         }
         if (!ok) return CSTONE_E_LET;
         haloMatrix_.assign(size_t(P) * P, 0);
@@ -2365,6 +2414,29 @@ void cstone_b200_local_world_destroy(void* world) { delete static_cast<csb::Loca
     {                                                                                                                  \
         if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
         return CSB_ENGINE(K, T, d)->syncGravBegin(n, x, y, z, h, nprops, props, pb);                                       \
+    }                                                                                                                  \
+    int cstone_b200_domain_focus_peer_exchange_##KS##_##TS(cstone_b200_domain* d, void* nodeQ, int eb)                 \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return CSB_ENGINE(K, T, d)->focusPeerExchange(nodeQ, eb);                                                      \
+    }                                                                                                                  \
+    int cstone_b200_domain_focus_global_gather_##KS##_##TS(cstone_b200_domain* d, const void* nodeQ, int eb,           \
+                                                           void* gLeafQ)                                               \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return CSB_ENGINE(K, T, d)->focusGlobalGather(nodeQ, eb, gLeafQ);                                              \
+    }                                                                                                                  \
+    int cstone_b200_domain_focus_global_extract_##KS##_##TS(cstone_b200_domain* d, const void* gNodeQ, int eb,         \
+                                                            void* nodeQ)                                               \
+    {                                                                                                                  \
+        if (!d) return CSTONE_E_INVALID_ARGUMENT;                                                                      \
+        return CSB_ENGINE(K, T, d)->focusGlobalExtract(gNodeQ, eb, nodeQ);                                             \
+    }                                                                                                                  \
+    int cstone_b200_domain_global_octree_##KS##_##TS(const cstone_b200_domain* d, int32_t* numLeaves,                  \
+                                                     int32_t* numNodes, const void** ptrs6, int32_t* levelRangeHost)   \
+    {                                                                                                                  \
+        if (!d || !numLeaves || !numNodes || !ptrs6 || !levelRangeHost) return CSTONE_E_INVALID_ARGUMENT;              \
+        return reinterpret_cast<const csb::Engine<K, T>*>(d)->globalOctree(numLeaves, numNodes, ptrs6, levelRangeHost);\
     }                                                                                                                  \
     int cstone_b200_domain_let_centers_##KS##_##TS(const cstone_b200_domain* d, const T** centers4, const char** macs, \
                                                    int32_t* numNodes)                                                  \

@@ -570,56 +570,27 @@ public:
                             t.centers_.template as<T>(), s));
         CSB_TRY(upsweepCenters(levels, t.levelRange_, t.childOffsets_.template as<int32_t>(), t.centers_.template as<T>(), s));
 
-        // ---- the global tree, linked on the device
-        const int Lg = int(gLeaves.size()) - 1;
-        CSB_TRY(g_.setLeavesHost(gLeaves.data(), Lg, s));
-        const int Mg = g_.numNodes_;
-        gPrefixes_.resize(size_t(Mg));
-        CSB_CUDA(cudaMemcpyAsync(gPrefixes_.data(), g_.prefixes_.p, size_t(Mg) * sizeof(K), cudaMemcpyDeviceToHost, s));
-        CSB_CUDA(cudaStreamSynchronize(s));
+        // ---- cells above the local domains: through the replicated global tree
+        CSB_TRY(linkGlobal(gLeaves, s));
+        const int Lg = g_.numLeaves_, Mg = g_.numNodes_;
         CSB_TRY(gLeafCenters_.reserve(size_t(Lg) * vb + 256));
         CSB_TRY(g_.centers_.reserve(size_t(Mg) * vb + 256));
-        CSB_CUDA(cudaMemsetAsync(gLeafCenters_.p, 0, size_t(Lg) * vb, s));
-        // my global leaves take the centres of the nodes of my tree that cover them (populateGlobal)
-        const int nk       = int(gLeaves.size());
-        const int firstGlb = findNodeAbove(gLeaves.data(), nk, prevStart_), lastGlb = findNodeAbove(gLeaves.data(), nk, prevEnd_);
         /* A global leaf of my range that is no node of my tree (the focus tree follows the particles one rebalance step
          * per sync and can be coarser than the global tree for a step; the reference then reads an unrelated node) takes
          * its centre from the particles directly. */
-        std::vector<uint32_t> gmap, missing;
-        std::vector<K> missingRanges, myGlobal;
-        for (int i = firstGlb; i < lastGlb; ++i)
-            myGlobal.push_back(gLeaves[i]), myGlobal.push_back(gLeaves[i + 1]);
-        std::vector<int32_t> located;
-        CSB_TRY(locateNodes(t, myGlobal, located, s));
-        for (int i = firstGlb; i < lastGlb; ++i)
-        {
-            const int node = located[size_t(i - firstGlb)];
-            if (node < 0)
-            {
-                missing.push_back(uint32_t(i));
-                missingRanges.push_back(gLeaves[i]), missingRanges.push_back(gLeaves[i + 1]);
-            }
-            gmap.push_back(uint32_t(std::max(node, 0)));
-        }
-        CSB_TRY(stage_.reserve(8 * std::max(gmap.size(), size_t(L)) + 1024));
-        if (!gmap.empty())
-        {
-            CSB_CUDA(cudaMemcpyAsync(stage_.p, gmap.data(), 4 * gmap.size(), cudaMemcpyHostToDevice, s));
-            CSB_TRY(cstone_b200_gather(stage_.as<uint32_t>(), gmap.size(), t.centers_.p,
-                                       gLeafCenters_.as<char>() + size_t(firstGlb) * vb, vb, s));
-        }
+        std::vector<uint32_t> missing;
+        CSB_TRY(populateGlobal(t.centers_.p, vb, gLeaves, gLeafCenters_.p, &missing, s));
         if (!missing.empty())
         {
             const size_t nm = missing.size();
-            CSB_TRY(xchg_.reserve(nm * (2 * sizeof(K) + vb + 4) + 1024));
+            std::vector<K> missingRanges;
+            for (uint32_t i : missing)
+                missingRanges.push_back(gLeaves[i]), missingRanges.push_back(gLeaves[i + 1]);
+            const size_t oOut = (nm * 2 * sizeof(K) + 255) / 256 * 256, oIdx = oOut + (nm * vb + 255) / 256 * 256;
+            CSB_TRY(xchg_.reserve(oIdx + 4 * nm + 256));
             K* dRanges     = xchg_.as<K>();
-            T* dOut        = reinterpret_cast<T*>(xchg_.as<char>() + (nm * 2 * sizeof(K) + 255) / 256 * 256);
-            uint32_t* dIdx = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(dOut) + (nm * vb + 255) / 256 * 256);
-            CSB_TRY(xchg_.reserve(size_t(reinterpret_cast<char*>(dIdx) - xchg_.as<char>()) + 4 * nm + 256));
-            dRanges = xchg_.as<K>();
-            dOut    = reinterpret_cast<T*>(xchg_.as<char>() + (nm * 2 * sizeof(K) + 255) / 256 * 256);
-            dIdx    = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(dOut) + (nm * vb + 255) / 256 * 256);
+            T* dOut        = reinterpret_cast<T*>(xchg_.as<char>() + oOut);
+            uint32_t* dIdx = reinterpret_cast<uint32_t*>(xchg_.as<char>() + oIdx);
             CSB_CUDA(cudaMemcpyAsync(dRanges, missingRanges.data(), nm * 2 * sizeof(K), cudaMemcpyHostToDevice, s));
             CSB_CUDA(cudaMemcpyAsync(dIdx, missing.data(), 4 * nm, cudaMemcpyHostToDevice, s));
             rangeMassCenterKernel<K, T><<<unsigned((nm + 63) / 64), 64, 0, s>>>(keysDev, uint32_t(numKeys), x, y, z, m, dRanges,
@@ -628,61 +599,121 @@ public:
             CSB_TRY(cstone_b200_scatter(dIdx, nm, dOut, gLeafCenters_.p, vb, s));
             CSB_CUDA(cudaStreamSynchronize(s));
         }
-        // every rank's part goes to everybody (gatherGlobalLeaves: in-place all-gather with ragged counts)
-        {
-            std::vector<int> displ(size_t(P_) + 1);
-            for (int r = 0; r < P_; ++r)
-                displ[r] = findNodeAbove(gLeaves.data(), Lg, globBnd_[r]);
-            displ[P_] = Lg;
-            std::vector<CommMsg> sends, recvs;
-            for (int r = 0; r < P_; ++r)
-            {
-                if (r == rank_) continue;
-                const size_t mineBytes = size_t(displ[rank_ + 1] - displ[rank_]) * vb;
-                const size_t hisBytes  = size_t(displ[r + 1] - displ[r]) * vb;
-                if (mineBytes) sends.push_back({r, gLeafCenters_.as<char>() + size_t(displ[rank_]) * vb, mineBytes});
-                if (hisBytes) recvs.push_back({r, gLeafCenters_.as<char>() + size_t(displ[r]) * vb, hisBytes});
-            }
-            CSB_TRY(comm->exchange(sends, recvs, s));
-        }
+        CSB_TRY(gatherGlobalLeaves(comm, gLeafCenters_.p, vb, gLeaves, s));
         CSB_TRY(cstone_b200_scatter(g_.l2i_.template as<uint32_t>() + g_.numInternal_, size_t(Lg), gLeafCenters_.p, g_.centers_.p, vb, s));
         CSB_TRY(upsweepCenters(levels, g_.levelRange_, g_.childOffsets_.template as<int32_t>(), g_.centers_.template as<T>(), s));
-        // leaves of non-peer ranks read the centre of the global node with their key range (extractGlobal)
-        {
-            std::vector<uint32_t> idx = nonPeerLeaves(), nodeIdx, gIdx;
-            l2iHost_.resize(size_t(L));
-            CSB_CUDA(cudaMemcpyAsync(l2iHost_.data(), t.l2i_.template as<int32_t>() + t.numInternal_, 4 * size_t(L),
-                                     cudaMemcpyDeviceToHost, s));
-            CSB_CUDA(cudaStreamSynchronize(s));
-            for (uint32_t i : idx)
-            {
-                const int gi = locateNode(leaves_[i], leaves_[i + 1], gPrefixes_.data(), g_.levelRange_);
-                if (gi < 0)
-                {
-                    // finer than the global tree outside of every peer: no source for this cell.  The other ranks are
-                    // not left alone in the exchanges that follow; the error surfaces on all ranks at the end of the sync
-                    fail(__LINE__);
-                    continue;
-                }
-                nodeIdx.push_back(uint32_t(l2iHost_[i]));
-                gIdx.push_back(uint32_t(gi));
-            }
-            if (!idx.empty())
-            {
-                const size_t n = idx.size();
-                CSB_TRY(stage_.reserve(8 * n + 1024));
-                CSB_TRY(xchg_.reserve(n * vb + 512));
-                uint32_t* dG = stage_.as<uint32_t>();
-                uint32_t* dN = dG + (n + 63) / 64 * 64;
-                CSB_CUDA(cudaMemcpyAsync(dG, gIdx.data(), 4 * n, cudaMemcpyHostToDevice, s));
-                CSB_CUDA(cudaMemcpyAsync(dN, nodeIdx.data(), 4 * n, cudaMemcpyHostToDevice, s));
-                CSB_TRY(cstone_b200_gather(dG, n, g_.centers_.p, xchg_.p, vb, s));
-                CSB_TRY(cstone_b200_scatter(dN, n, xchg_.p, t.centers_.p, vb, s));
-                CSB_CUDA(cudaStreamSynchronize(s));
-            }
-        }
+        CSB_TRY(extractGlobal(g_.centers_.p, vb, t.centers_.p, s));
         CSB_TRY(peerExchange(comm, t.centers_.p, vb, s));
         CSB_TRY(upsweepCenters(levels, t.levelRange_, t.childOffsets_.template as<int32_t>(), t.centers_.template as<T>(), s));
+        return 0;
+    }
+
+    // ---- the three steps of globalFocusExchange [ref: octree_focus_mpi.hpp:762-784] for node quantities of any element
+    //      size (4 - 32 bytes); between gatherGlobalLeaves and extractGlobal the caller scatters the global leaf
+    //      quantities to the nodes of the global tree (globalTree()) and runs ITS upsweep there
+
+    //! the replicated global tree, linked on the device
+    int linkGlobal(const std::vector<K>& gLeaves, cudaStream_t s)
+    {
+        CSB_TRY(g_.setLeavesHost(gLeaves.data(), int(gLeaves.size()) - 1, s));
+        gPrefixes_.resize(size_t(g_.numNodes_));
+        CSB_CUDA(cudaMemcpyAsync(gPrefixes_.data(), g_.prefixes_.p, size_t(g_.numNodes_) * sizeof(K), cudaMemcpyDeviceToHost, s));
+        CSB_CUDA(cudaStreamSynchronize(s));
+        return 0;
+    }
+    const FocusTree<K>& globalTree() const { return g_; }
+
+    /*! [ref: octree_focus_mpi.hpp:288-316 populateGlobal] gLeafQ (device, one element per global leaf) is zeroed, then
+     *  the global leaves of my range take the quantities of the nodes of my tree that cover them.  Global leaves without
+     *  such a node are listed in *missing if given, otherwise they count as an inconsistency. */
+    int populateGlobal(const void* nodeQ, int elemBytes, const std::vector<K>& gLeaves, void* gLeafQ,
+                       std::vector<uint32_t>* missing, cudaStream_t s)
+    {
+        const int nk = int(gLeaves.size()), Lg = nk - 1;
+        CSB_CUDA(cudaMemsetAsync(gLeafQ, 0, size_t(Lg) * elemBytes, s));
+        const int firstGlb = findNodeAbove(gLeaves.data(), nk, prevStart_), lastGlb = findNodeAbove(gLeaves.data(), nk, prevEnd_);
+        std::vector<K> myGlobal;
+        for (int i = firstGlb; i < lastGlb; ++i)
+            myGlobal.push_back(gLeaves[i]), myGlobal.push_back(gLeaves[i + 1]);
+        std::vector<int32_t> located;
+        CSB_TRY(locateNodes(t, myGlobal, located, s));
+        std::vector<uint32_t> gmap;
+        for (int i = firstGlb; i < lastGlb; ++i)
+        {
+            const int node = located[size_t(i - firstGlb)];
+            if (node < 0)
+            {
+                if (missing) missing->push_back(uint32_t(i));
+                else fail(__LINE__);
+            }
+            gmap.push_back(uint32_t(std::max(node, 0)));
+        }
+        if (!gmap.empty())
+        {
+            CSB_TRY(stage_.reserve(4 * gmap.size() + 1024));
+            CSB_CUDA(cudaMemcpyAsync(stage_.p, gmap.data(), 4 * gmap.size(), cudaMemcpyHostToDevice, s));
+            CSB_TRY(cstone_b200_gather(stage_.as<uint32_t>(), gmap.size(), nodeQ, static_cast<char*>(gLeafQ) + size_t(firstGlb) * elemBytes,
+                                       elemBytes, s));
+            CSB_CUDA(cudaStreamSynchronize(s)); // gmap is a host temporary
+        }
+        return 0;
+    }
+
+    //! [ref: octree_focus_mpi.hpp:350-366 gatherGlobalLeaves] every rank's part of gLeafQ goes to every rank (the
+    //! in-place all-gather with ragged counts of the reference, as one exchange step)
+    int gatherGlobalLeaves(Comm* comm, void* gLeafQ, int elemBytes, const std::vector<K>& gLeaves, cudaStream_t s)
+    {
+        const int Lg = int(gLeaves.size()) - 1;
+        std::vector<int> displ(size_t(P_) + 1);
+        for (int r = 0; r < P_; ++r)
+            displ[r] = findNodeAbove(gLeaves.data(), Lg, globBnd_[r]);
+        displ[P_] = Lg;
+        std::vector<CommMsg> sends, recvs;
+        char* q = static_cast<char*>(gLeafQ);
+        for (int r = 0; r < P_; ++r)
+        {
+            if (r == rank_) continue;
+            const size_t mineBytes = size_t(displ[rank_ + 1] - displ[rank_]) * elemBytes;
+            const size_t hisBytes  = size_t(displ[r + 1] - displ[r]) * elemBytes;
+            if (mineBytes) sends.push_back({r, q + size_t(displ[rank_]) * elemBytes, mineBytes});
+            if (hisBytes) recvs.push_back({r, q + size_t(displ[r]) * elemBytes, hisBytes});
+        }
+        return comm->exchange(sends, recvs, s);
+    }
+
+    //! [ref: octree_focus_mpi.hpp:325-347 extractGlobal] the leaves of my tree outside of my range and of every peer's
+    //! range take the quantity of the global node with their key range; gNodeQ: one element per node of globalTree()
+    int extractGlobal(const void* gNodeQ, int elemBytes, void* nodeQ, cudaStream_t s)
+    {
+        std::vector<uint32_t> leafIdx, gIdx;
+        for (uint32_t i : nonPeerLeaves())
+        {
+            const int gi = locateNode(leaves_[i], leaves_[i + 1], gPrefixes_.data(), g_.levelRange_);
+            if (gi < 0)
+            {
+                // finer than the global tree outside of every peer: no source for this cell.  The other ranks are not
+                // left alone in the exchanges that follow; the error surfaces on all ranks at the end of the sync
+                fail(__LINE__);
+                continue;
+            }
+            leafIdx.push_back(i);
+            gIdx.push_back(uint32_t(gi));
+        }
+        const size_t n = leafIdx.size();
+        if (n == 0) return 0;
+        const size_t stride = (n + 63) / 64 * 64;
+        CSB_TRY(stage_.reserve(12 * stride + 1024));
+        CSB_TRY(xchg_.reserve(n * elemBytes + 512));
+        uint32_t* dG = stage_.as<uint32_t>();
+        uint32_t* dL = dG + stride;
+        uint32_t* dN = dL + stride;
+        CSB_CUDA(cudaMemcpyAsync(dG, gIdx.data(), 4 * n, cudaMemcpyHostToDevice, s));
+        CSB_CUDA(cudaMemcpyAsync(dL, leafIdx.data(), 4 * n, cudaMemcpyHostToDevice, s));
+        // node index of those leaves, then quantity: global node -> buffer -> node of my tree
+        CSB_TRY(cstone_b200_gather(dL, n, t.l2i_.template as<uint32_t>() + t.numInternal_, dN, 4, s));
+        CSB_TRY(cstone_b200_gather(dG, n, gNodeQ, xchg_.p, elemBytes, s));
+        CSB_TRY(cstone_b200_scatter(dN, n, xchg_.p, nodeQ, elemBytes, s));
+        CSB_CUDA(cudaStreamSynchronize(s));
         return 0;
     }
 
@@ -1037,7 +1068,6 @@ private:
     // gravity side: the global tree linked on the device, centres of its leaves / nodes, helpers
     FocusTree<K> g_{CSTONE_SFC_HILBERT, 1u, 1.0f};
     std::vector<K> gPrefixes_, globBnd_;
-    std::vector<int32_t> l2iHost_;
     FBuf layoutOwn_, gLeafCenters_;
 };
 

@@ -105,6 +105,40 @@ class Domain:
         _check(_fn("let_centers", self.bits, self.fd)(self._h, C.byref(cp), C.byref(mp), C.byref(n)), "let_centers")
         return _alias(cp.value, 4 * n.value, self.fd).view(n.value, 4), _alias(mp.value, n.value, torch.int8)
 
+    # ---- globalFocusExchange for client node quantities [ref: focus/octree_focus_mpi.hpp:276-366, :762-784]
+    def focus_peer_exchange(self, node_q):
+        """cells of the focus tree in a peer's SFC range take the owner's values (node_q: one row per tree node)"""
+        _check(_fn("focus_peer_exchange", self.bits, self.fd)(self._h, ops._p(node_q), _row_bytes(node_q)), "focus_peer_exchange")
+
+    def focus_global_gather(self, node_q):
+        """one row per leaf of the replicated global tree: this rank's leaves from node_q, the others from their owners"""
+        n_global = self._info()[5]
+        out = torch.zeros((n_global,) + tuple(node_q.shape[1:]), dtype=node_q.dtype, device=node_q.device)
+        _check(_fn("focus_global_gather", self.bits, self.fd)(self._h, ops._p(node_q), _row_bytes(node_q), ops._p(out)),
+               "focus_global_gather")
+        return out
+
+    def focus_global_extract(self, global_node_q, node_q):
+        """cells of the focus tree that belong to no peer read their rows from global_node_q (one row per global tree node)"""
+        _check(_fn("focus_global_extract", self.bits, self.fd)(self._h, ops._p(global_node_q), _row_bytes(node_q), ops._p(node_q)),
+               "focus_global_extract")
+
+    def global_octree(self):
+        """the replicated global tree linked on the device (after focus_global_gather or sync_grav): dict of tensors +
+        the level ranges as a host list"""
+        nl, nn = C.c_int32(0), C.c_int32(0)
+        ptrs = (C.c_void_p * 6)()
+        ml = ops.max_level(self.bits)
+        lr = (C.c_int32 * (ml + 2))()
+        _check(_fn("global_octree", self.bits, self.fd)(self._h, C.byref(nl), C.byref(nn), ptrs, lr), "global_octree")
+        L, M = nl.value, nn.value
+        kt, i32 = ops.KEY_TORCH[self.bits], torch.int32
+        shapes = [("prefixes", kt, M), ("child_offsets", i32, M + 1), ("parents", i32, max(1, (M - 1) // 8)),
+                  ("level_range", i32, ml + 2), ("internal_to_leaf", i32, M), ("leaf_to_internal", i32, M)]
+        out = {name: _alias(p, n, dt) for (name, dt, n), p in zip(shapes, ptrs)}
+        out.update(num_leaves=L, num_nodes=M, level_range_host=[int(v) for v in lr])
+        return out
+
     def sync(self, x, y, z, h, props=(), fields_ready=None, _entry="sync_begin"):
         """[ref: domain/domain.hpp:196-243] returns (keys, x, y, z, h, props) as NEW tensors of the new local size:
         assigned particles in [start_index, end_index), halos elsewhere, everything in SFC order.

@@ -103,6 +103,27 @@ void cstone_b200_local_world_destroy(void* world);
     int64_t cstone_b200_domain_sync_grav_begin_##KS##_##TS(cstone_b200_domain* d, uint64_t n_in, const T* x, const T* y,    \
                                                       const T* z, const T* h, int nprops, const void* const* props,    \
                                                       const int* prop_bytes);                                          \
+    /* globalFocusExchange for node quantities of a client (multipoles, any per-cell data of 4 - 32 bytes), halo mode 1,   \
+     * after a sync [ref: focus/octree_focus_mpi.hpp:276-300 peerExchange, :288-366 populateGlobal / gatherGlobalLeaves /  \
+     * extractGlobal, :762-784 globalFocusExchange].  node_q: DEVICE array, one element per node of the focus tree      \
+     * (order of tree_view's prefixes), valid for the cells inside this rank's SFC range.                               \
+     *   focus_peer_exchange   cells in a peer's range take the owner's values                                          \
+     *   focus_global_gather   global_leaf_q (DEVICE, one element per leaf of the global tree): this rank's leaves from  \
+     *                         node_q, all others from their owners                                                     \
+     *   global_octree         the global tree linked on the device, for the CLIENT's upsweep over the gathered leaves:  \
+     *                         ptrs6 = prefixes K[M], child_offsets i32[M+1], parents, level_range (device),            \
+     *                         internal_to_leaf, leaf_to_internal i32[M]; level_range_host i32[maxLevel+2]               \
+     *   focus_global_extract  cells of the focus tree that belong to no peer read global_node_q (DEVICE, one element    \
+     *                         per node of the global octree)                                                            \
+     * All ranks call them together (the first two communicate).  CSTONE_E_LET if a cell has no counterpart. */          \
+    int cstone_b200_domain_focus_peer_exchange_##KS##_##TS(cstone_b200_domain* d, void* node_q, int elem_bytes);       \
+    int cstone_b200_domain_focus_global_gather_##KS##_##TS(cstone_b200_domain* d, const void* node_q, int elem_bytes,  \
+                                                           void* global_leaf_q);                                       \
+    int cstone_b200_domain_focus_global_extract_##KS##_##TS(cstone_b200_domain* d, const void* global_node_q,          \
+                                                            int elem_bytes, void* node_q);                             \
+    int cstone_b200_domain_global_octree_##KS##_##TS(const cstone_b200_domain* d, int32_t* num_leaves,                 \
+                                                     int32_t* num_nodes, const void** ptrs6,                           \
+                                                     int32_t* level_range_host);                                       \
     /* after sync_grav_begin: DEVICE views of the expansion centres (x, y, z, MAC radius^2) T[4 M] and the MAC marks   \
      * char[M] of the focus tree, M = *num_nodes nodes in the order of tree_view's prefixes */                         \
     int cstone_b200_domain_let_centers_##KS##_##TS(const cstone_b200_domain* d, const T** centers4, const char** macs, \

@@ -213,7 +213,8 @@ def test_ranks_match_reference_domain(cloud, P, n, bucket, bucket_focus):
         rk.close()
 
 
-LET_CASES = CASES + [("gaussian", 1, 12000, 64, 8)]  # one rank: the focus tree alone (no peers, no halos)
+# one rank: the focus tree alone (no peers, no halos); two clumps on 8 ranks: cells of far-away, non-peer ranks
+LET_CASES = CASES + [("gaussian", 1, 12000, 64, 8), ("two-clusters", 8, 48000, 128, 16)]
 
 
 @pytest.mark.parametrize("cloud,P,n,bucket,bucket_focus", LET_CASES, ids=["%s-P%d" % (c[0], c[1]) for c in LET_CASES])
@@ -238,8 +239,8 @@ def test_ranks_reference_halo_mode(cloud, P, n, bucket, bucket_focus):
 
 @pytest.mark.parametrize("cloud,P,n,bucket,bucket_focus", [("gaussian", 2, 20000, 64, 8), ("gaussian", 4, 20000, 50, 10),
                                                           ("two-clusters", 3, 24000, 64, 8), ("gaussian", 8, 40000, 128, 16),
-                                                          ("gaussian", 1, 12000, 64, 8)],
-                         ids=["gaussian-P2", "gaussian-P4", "two-clusters-P3", "gaussian-P8", "gaussian-P1"])
+                                                          ("gaussian", 1, 12000, 64, 8), ("two-clusters", 8, 48000, 128, 16)],
+                         ids=["gaussian-P2", "gaussian-P4", "two-clusters-P3", "gaussian-P8", "gaussian-P1", "two-clusters-P8"])
 def test_ranks_sync_grav_matches_reference(cloud, P, n, bucket, bucket_focus):
     """Domain::syncGrav [ref: domain/domain.hpp:245-325] on thread-ranks against the reference's: focus tree refined by
     the vector MAC (leaves, counts, assignment), expansion centres and MAC radii of every node, layout, index ranges,
@@ -393,6 +394,63 @@ def test_halo_push_falls_back_when_peer_memory_cannot_be_mapped(monkeypatch):
         rk.check()
     finally:
         rk.close()
+
+
+@pytest.mark.parametrize("P", [2, 8])
+def test_global_focus_exchange_reproduces_the_node_counts(P):
+    """peerExchange + globalFocusExchange for a client quantity, as the reference tests them
+    [ref: test/integration_mpi/exchange_general.cpp:55-150]: particle counts of this rank's own cells, upsweep, peer
+    exchange, global gather / upsweep on the global tree / extract, upsweep -- must give the count of EVERY cell of the
+    focus tree (peers' cells and far-away cells included), which is what updateCounts computed its own way"""
+    import torch
+    from cornerstone_octree_b200 import ops
+    from cornerstone_octree_b200.domain import Domain, LocalWorld
+    # two distant clumps: ranks of one clump see the cells of the other from afar (non-peer cells, extractGlobal)
+    n = 48000
+    x, y, z, h, lim, pbc = make_cloud("gaussian" if P == 2 else "two-clusters", n)
+    world = LocalWorld(P)
+    theta = 0.5
+    doms = [Domain(r, P, 128, 16, theta, ops.make_box(lim)) for r in range(P)]
+    state = []
+    for r, d in enumerate(doms):
+        d.set_local_world(world)
+        d.set_halo_mode(1)
+        s = slice(r * n // P, (r + 1) * n // P)
+        state.append([_dev(a[s]) for a in (x, y, z, h)])
+    try:
+        def one(r):
+            dom = doms[r]
+            dom.sync(*state[r])
+            ta, lv = dom.tree_arrays(), dom.let_view()
+            L, M = lv["leaves"].size - 1, ta["prefixes"].numel()
+            l2i = ta["leaf_to_internal"][M - L:].long()
+            lr = ta["level_range"].cpu().numpy()
+            c0, c1 = dom.cells()
+            leaf_counts = torch.from_numpy(lv["counts"].astype(np.int32)).cuda()
+            q = torch.zeros(M, dtype=torch.int32, device="cuda")
+            q[l2i[c0:c1]] = leaf_counts[c0:c1]
+            ops.upsweep_sum(lr, ta["child_offsets"], q)
+            dom.focus_peer_exchange(q)
+            g_leaf = dom.focus_global_gather(q)
+            go = dom.global_octree()
+            Lg, Mg = go["num_leaves"], go["num_nodes"]
+            g_node = torch.zeros(Mg, dtype=torch.int32, device="cuda")
+            g_node[go["leaf_to_internal"][Mg - Lg:].long()] = g_leaf
+            ops.upsweep_sum(np.array(go["level_range_host"], dtype=np.int32), go["child_offsets"], g_node)
+            assert int(g_node[0]) == n, "the root of the global tree holds every particle"
+            dom.focus_global_extract(g_node, q)
+            ops.upsweep_sum(lr, ta["child_offsets"], q)
+            torch.cuda.synchronize()
+            assert int(q[0]) == n, "the root of the focus tree of rank %d holds every particle" % r
+            assert np.array_equal(q[l2i].cpu().numpy().astype(np.uint32), lv["counts"]), "cell counts of rank %d" % r
+            return len(lv["peers"])
+        peers = world.run(one)
+        print("peers per rank:", peers)
+        assert P == 2 or min(peers) < P - 1, "the 8-rank case is meant to have far-away (non-peer) cells"
+    finally:
+        for d in doms:
+            d.close()
+        world.close()
 
 
 def test_ranks_with_fewer_particles_than_the_bucket():
