@@ -2531,6 +2531,22 @@ int cstone_b200_host_assignment_k32(int nranks, const uint32_t* leaves, const ui
     std::copy(c.begin(), c.end(), rankCounts);
     return 0;
 }
+#define CSB_HOST_TREELET(KS, K)                                                                                        \
+    int cstone_b200_host_update_treelet_##KS(const K* leaves, const uint32_t* counts, int32_t first, int32_t last,     \
+                                             uint32_t bucket, K* out, int32_t capacity)                                \
+    {                                                                                                                  \
+        if (!leaves || !counts || !out || first < 0 || last < first) return CSTONE_E_INVALID_ARGUMENT;                 \
+        std::vector<int> ops(size_t(last - first));                                                                    \
+        for (int i = first; i < last; ++i)                                                                             \
+            ops[i - first] = csb::hostNodeOp<K>(leaves, i, counts, bucket);                                            \
+        std::vector<K> tl = csb::hostApplyOps<K>(leaves, first, last, ops);                                            \
+        if (int64_t(tl.size()) > int64_t(capacity)) return CSTONE_E_CAPACITY;                                          \
+        std::memcpy(out, tl.data(), tl.size() * sizeof(K));                                                            \
+        return int(tl.size());                                                                                         \
+    }
+CSB_HOST_TREELET(k32, uint32_t)
+CSB_HOST_TREELET(k64, uint64_t)
+
 #define CSB_HOST_PEERS(KS, K, TS, T)                                                                                   \
     int cstone_b200_host_find_peers_##KS##_##TS(int sfcKind, int myRank, int nranks, const K* boundaries,              \
                                                 const K* leaves, int32_t numLeaves, const cstone_box_##TS* box,        \

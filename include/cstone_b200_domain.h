@@ -174,6 +174,14 @@ int cstone_b200_host_assignment_k64(int nranks, const uint64_t* leaves, const ui
                                     const uint64_t* old_boundaries, uint64_t* boundaries, uint32_t* rank_counts);
 int cstone_b200_host_assignment_k32(int nranks, const uint32_t* leaves, const uint32_t* counts, int32_t num_leaves,
                                     const uint32_t* old_boundaries, uint32_t* boundaries, uint32_t* rank_counts);
+/* [ref: tree/csarray.hpp:477-488 updateTreelet, as called by focus/exchange_focus.hpp:380-405 focusTransfer] HOST
+ * function: leaves [first, last) of a full cornerstone leaf array rebalanced once with their counts (sibling groups may
+ * reach outside of the range, as in the reference); out receives the new keys incl. the upper boundary leaves[last].
+ * Returns the number of keys written (> 0), CSTONE_E_CAPACITY if out is too small */
+int cstone_b200_host_update_treelet_k32(const uint32_t* leaves, const uint32_t* counts, int32_t first, int32_t last,
+                                        uint32_t bucket, uint32_t* out, int32_t capacity);
+int cstone_b200_host_update_treelet_k64(const uint64_t* leaves, const uint32_t* counts, int32_t first, int32_t last,
+                                        uint32_t bucket, uint64_t* out, int32_t capacity);
 /* [ref: traversal/peers.hpp:62-117 findPeersMac] HOST function: ranks owning a global leaf that fails the mutual
  * minimum-distance / vector MAC (inv_theta_eff) against a global leaf of my_rank, by a dual traversal of the global
  * tree given as its leaf keys (num_leaves + 1 keys); boundaries: nranks + 1 keys; is_peer: nranks flags */

@@ -348,6 +348,16 @@ int findPeers(int myRank, int numRanks, const K* boundaries, const K* leaves, in
     {                                                                                                                  \
         return findPeers<K, T>(myRank, numRanks, boundaries, leaves, numLeaves, lim, pbc, invThetaEff, isPeer);        \
     }                                                                                                                  \
+    /* updateTreelet [ref: tree/csarray.hpp:477-488] on leaves [first, last) of a full leaf array, as focusTransfer calls \
+     * it [ref: focus/exchange_focus.hpp:380-405]; out has room for 4096 * (last - first) + 1 keys; returns the count */ \
+    int cstone_refdom_update_treelet_##KS##_##TS(const K* leaves, const unsigned* counts, int first, int last,         \
+                                                 unsigned bucket, K* out)                                              \
+    {                                                                                                                  \
+        auto tl = updateTreelet(gsl::span<const K>(leaves + first, size_t(last - first) + 1),                          \
+                                gsl::span<const unsigned>(counts + first, size_t(last - first)), bucket);              \
+        std::memcpy(out, tl.data(), tl.size() * sizeof(K));                                                            \
+        return int(tl.size());                                                                                         \
+    }                                                                                                                  \
     int cstone_refdom_set_mass_##KS##_##TS(void* h, int rank, uint64_t n, const T* m)                                  \
     {                                                                                                                  \
         static_cast<World<K, T>*>(h)->ranks[rank].m.assign(m, m + n);                                                  \

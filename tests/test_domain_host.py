@@ -209,3 +209,45 @@ def test_find_peers_vs_reference(port, kd, fd):
                     checked += 1
                     with_non_peers += int(a.sum() < nranks - 1)
     assert checked >= 60 and with_non_peers > 10
+
+
+@pytest.mark.parametrize("kd", [np.uint64, np.uint32])
+def test_update_treelet_vs_reference(port, kd):
+    """the rebalance of a leaf range that is handed to a neighbour rank (focusTransfer -> updateTreelet
+    [ref: focus/exchange_focus.hpp:380-405, tree/csarray.hpp:477-488]): merges whose sibling group reaches outside of the
+    range, multi-level splits and plain copies, against the reference's function on the same full leaf array"""
+    import ctypes as C
+    import gen
+    from oracle import loader
+    if not loader.refdom_available():
+        pytest.skip("oracle/_ref/liboracle_refdom.so not built")
+    from cornerstone_octree_b200 import _lib
+    rlib = C.CDLL(loader._REFDOM_PATH)
+    ks = "k64" if kd == np.uint64 else "k32"
+    mine = getattr(_lib.lib, "cstone_b200_host_update_treelet_" + ks)
+    refp = getattr(rlib, "cstone_refdom_update_treelet_%s_f64" % ks)
+    mine.restype = refp.restype = C.c_int
+    ptr = lambda a: a.ctypes.data_as(C.c_void_p)
+    rng = np.random.default_rng(3)
+    cases = changed = 0
+    for trial in range(6):
+        keys = np.sort(gen.gaussian_keys(20000 + 3000 * trial, kd, seed=60 + trial))
+        leaves, counts = port.compute_octree(keys, 8 + 4 * trial)
+        # counts of a LATER particle set on the same leaves: merges and (multi-level) splits become due
+        keys2 = np.sort(gen.gaussian_keys(keys.size * (1 + trial % 3), kd, seed=160 + trial) // kd(1 + trial % 2))
+        counts2 = port.compute_node_counts(leaves, keys2)
+        L = leaves.size - 1
+        for _ in range(12):
+            first = int(rng.integers(0, L - 1))
+            last = int(min(L, first + rng.integers(1, max(2, L // 3))))
+            for bucket in (4, 8 + 4 * trial, 64):
+                cap = 4096 * (last - first) + 1
+                a = np.zeros(cap, dtype=kd)
+                b = np.zeros(cap, dtype=kd)
+                na = mine(ptr(leaves), ptr(counts2), first, last, C.c_uint32(bucket), ptr(a), cap)
+                nb = refp(ptr(leaves), ptr(counts2), first, last, C.c_uint(bucket), ptr(b))
+                assert na == nb and na > 0, "treelet size, leaves [%d, %d) bucket %d" % (first, last, bucket)
+                assert np.array_equal(a[:na], b[:nb])
+                cases += 1
+                changed += int(na != last - first + 1)
+    assert cases >= 200 and changed > 50
