@@ -221,7 +221,8 @@ lib.cstone_b200_local_world_destroy.argtypes = [_vp]
 DOMAIN_EXPORTED = ["nccl_unique_id", "nccl_comm_init", "nccl_comm_destroy", "local_world_create", "local_world_destroy",
                    "host_assignment_k32",
                    "host_assignment_k64", "host_limit_box_shrinking_f32", "host_limit_box_shrinking_f64",
-                   "host_uniform_bins", "host_limit_boundary_shifts_k32", "host_limit_boundary_shifts_k64"]
+                   "host_uniform_bins", "host_limit_boundary_shifts_k32", "host_limit_boundary_shifts_k64",
+                   "host_update_treelet_k32", "host_update_treelet_k64"]
 for ks in ("k32", "k64"):
     for ts in ("f32", "f64"):
         for _name, (_res, _args) in _DOMAIN_PROTOS.items():
